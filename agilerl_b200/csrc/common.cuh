@@ -1,0 +1,56 @@
+// common.cuh — shared helpers for libb200xp (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "b200xp.h"
+
+#ifndef __CUDA_ARCH__
+#define XP_HOST_ONLY 1
+#endif
+
+namespace xp {
+
+// thread-local error text behind xp_last_error()
+void set_error(const char *fmt, ...);
+
+// grid sizing: the B200 has 148 SMs; queried once per device.
+int sm_count();
+
+inline xp_status_t check_launch(const char *what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return XP_ERR_CUDA;
+  }
+  return XP_OK;
+}
+
+#define XP_REQUIRE(cond, code, ...) \
+  do {                              \
+    if (!(cond)) {                  \
+      xp::set_error(__VA_ARGS__);   \
+      return (code);                \
+    }                               \
+  } while (0)
+
+// ---- device helpers -------------------------------------------------------------------
+// L2-coherent loads (bypass the non-coherent L1) for data other CTAs write in this launch.
+__device__ __forceinline__ double ld_cg_f64(const double *p) { return __ldcg(p); }
+
+// streaming 128-bit accesses: read-once / write-once data should not pollute L1.
+__device__ __forceinline__ int4 ld_stream_v4(const int4 *p) {
+  int4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream_v4(int4 *p, const int4 &v) {
+  asm volatile("st.global.L1::no_allocate.v4.s32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+}  // namespace xp

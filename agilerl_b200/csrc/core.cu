@@ -1,0 +1,51 @@
+// core.cu — library plumbing: version, thread-local error text, device facts.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace xp {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+}  // namespace xp
+
+extern "C" {
+
+int xp_version(void) { return 1; }
+
+const char *xp_last_error(void) { return xp::g_err; }
+
+xp_status_t xp_device_info(int device, int *sm_count, int *cc_major, int *cc_minor) {
+  XP_REQUIRE(sm_count && cc_major && cc_minor, XP_ERR_INVALID, "xp_device_info: null output");
+  cudaError_t e = cudaDeviceGetAttribute(sm_count, cudaDevAttrMultiProcessorCount, device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(cc_major, cudaDevAttrComputeCapabilityMajor, device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(cc_minor, cudaDevAttrComputeCapabilityMinor, device);
+  if (e != cudaSuccess) {
+    xp::set_error("xp_device_info: %s", cudaGetErrorString(e));
+    return XP_ERR_CUDA;
+  }
+  return XP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,409 @@
+// segtree.cu — SumSegmentTree / MinSegmentTree and the PER ops built on them.
+// Reference: agilerl/components/segment_tree.py:5-182, replay_buffer.py:261-428.
+//
+// Layout: heap order, node 1 = root, leaves cap..2cap-1, node i at base[i*stride].  The PER
+// buffer interleaves (sum,min) per node (stride 2) so that the two children of a node in both
+// trees are one aligned 32-byte sector.
+//
+// Batched set (B sequential `tree[idx] = val` of the reference, segment_tree.py:81-95):
+//   K1 ticket : atomicMax(aux[cap+idx], i+1)              -> last writer per leaf
+//   K2 mark   : winner writes its leaf, then walks up doing atomicAdd(aux[parent], 1); it stops
+//               at the first parent that was already marked.  aux[p] = number of dirty children.
+//   K3 rebuild: winner walks up again; at each parent atomicSub(aux[p], 1); only the LAST
+//               arriving dirty child (old == 1) recomputes p = op(left, right) from final
+//               children and continues.  aux returns to all-zero.
+// Every touched internal node is recomputed exactly once, after both children are final, so the
+// result is bit-identical to the reference's sequential root walks (same operands, same op).
+#include "common.cuh"
+#include "pow.cuh"
+
+namespace {
+
+struct Tree {
+  double *sum;
+  double *mn;
+  long long stride;
+  long long cap;
+  int *aux;
+};
+
+__device__ __forceinline__ double py_min(double a, double b) { return (b < a) ? b : a; }
+
+// ---- init ---------------------------------------------------------------------------------
+__global__ void tree_init_kernel(Tree t) {
+  const long long n = 2 * t.cap;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    if (t.sum) t.sum[i * t.stride] = 0.0;
+    if (t.mn) t.mn[i * t.stride] = __longlong_as_double(0x7ff0000000000000ll);
+    if (t.aux) t.aux[i] = 0;
+  }
+}
+
+// ---- batched set ------------------------------------------------------------------------------
+// Source of (idx, value) for item i of a batch.
+enum { kSrcVal = 0, kSrcPrio = 1, kSrcRange = 2 };
+struct SetSrc {
+  int kind;
+  const long long *idx;   // kSrcVal / kSrcPrio
+  const double *val;      // kSrcVal
+  const float *prio;      // kSrcPrio: leaf = max(f64(prio), 1e-5) ** alpha
+  double alpha;
+  unsigned long long *max_priority_bits;  // device xp_per_state.max_priority (positive double)
+  long long range_start, range_mod;       // kSrcRange: idx = (start + i) % mod, value = max_priority ** alpha
+  long long limit;                        // valid idx in [0, limit)
+  int *err;
+};
+
+__device__ __forceinline__ long long src_idx(const SetSrc &s, long long i) {
+  if (s.kind == kSrcRange) {
+    long long x = s.range_start + i;
+    return x >= s.range_mod ? x - s.range_mod : x;
+  }
+  return s.idx[i];
+}
+
+__global__ void set_ticket_kernel(Tree t, SetSrc s, long long B) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  double p = 0.0;
+  if (i < B) {
+    const long long idx = s.idx[i];
+    if (idx < 0 || idx >= s.limit) {
+      if (s.err) *s.err = 1;
+    } else {
+      atomicMax(&t.aux[t.cap + idx], (int)(i + 1));
+      if (s.kind == kSrcPrio) {
+        // new_priority = max(priority.item(), 1e-5)  (replay_buffer.py:425); Python max keeps
+        // the first argument unless the second is greater.
+        double q = (double)s.prio[i];
+        p = (1e-5 > q) ? 1e-5 : q;
+      }
+    }
+  }
+  if (s.kind == kSrcPrio) {
+    // max_priority = max(max_priority, p) over every item, overwritten duplicates included (:329)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) p = fmax(p, __shfl_xor_sync(0xffffffffu, p, o));
+    if ((threadIdx.x & 31) == 0 && p > 0.0)
+      atomicMax(s.max_priority_bits, (unsigned long long)__double_as_longlong(p));
+  }
+}
+
+template <bool UNIQUE>
+__global__ void set_mark_kernel(Tree t, SetSrc s, long long B) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  const long long idx = src_idx(s, i);
+  if (idx < 0 || idx >= s.limit) return;
+  long long n = t.cap + idx;
+  if (!UNIQUE && t.aux[n] != (int)(i + 1)) return;  // a later item overwrites this leaf
+  double v;
+  if (s.kind == kSrcVal) {
+    v = s.val[i];
+  } else if (s.kind == kSrcPrio) {
+    double q = (double)s.prio[i];
+    q = (1e-5 > q) ? 1e-5 : q;
+    v = xp::xp_pow(q, s.alpha);
+  } else {
+    v = xp::xp_pow(__longlong_as_double((long long)*s.max_priority_bits), s.alpha);
+  }
+  if (t.sum) __stcg(&t.sum[n * t.stride], v);
+  if (t.mn) __stcg(&t.mn[n * t.stride], v);
+  while (n > 1) {
+    const long long p = n >> 1;
+    if (atomicAdd(&t.aux[p], 1) != 0) break;  // p (and its ancestors) already marked
+    n = p;
+  }
+}
+
+template <bool UNIQUE>
+__global__ void set_rebuild_kernel(Tree t, SetSrc s, long long B) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  const long long idx = src_idx(s, i);
+  if (idx < 0 || idx >= s.limit) return;
+  long long n = t.cap + idx;
+  if (!UNIQUE) {
+    if (t.aux[n] != (int)(i + 1)) return;
+    t.aux[n] = 0;  // ticket consumed; aux is all-zero again when the kernel ends
+  }
+  while (n > 1) {
+    const long long p = n >> 1;
+    __threadfence();  // publish tree[n] before announcing arrival
+    if (atomicSub(&t.aux[p], 1) != 1) break;  // the other dirty child will finish p
+    __threadfence();
+    const long long l = 2 * p * t.stride, r = (2 * p + 1) * t.stride;
+    if (t.sum) __stcg(&t.sum[p * t.stride], __dadd_rn(__ldcg(&t.sum[l]), __ldcg(&t.sum[r])));
+    if (t.mn) __stcg(&t.mn[p * t.stride], py_min(__ldcg(&t.mn[l]), __ldcg(&t.mn[r])));
+    n = p;
+  }
+}
+
+xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, bool unique, cudaStream_t st) {
+  if (B == 0) return XP_OK;
+  XP_REQUIRE(B < (1ll << 31) - 1, XP_ERR_INVALID, "tree set: batch too large");
+  const int threads = 256;
+  const unsigned grid = (unsigned)((B + threads - 1) / threads);
+  if (!unique) {
+    set_ticket_kernel<<<grid, threads, 0, st>>>(t, s, B);
+    set_mark_kernel<false><<<grid, threads, 0, st>>>(t, s, B);
+    set_rebuild_kernel<false><<<grid, threads, 0, st>>>(t, s, B);
+  } else {
+    set_mark_kernel<true><<<grid, threads, 0, st>>>(t, s, B);
+    set_rebuild_kernel<true><<<grid, threads, 0, st>>>(t, s, B);
+  }
+  return xp::check_launch("tree set");
+}
+
+// ---- queries ----------------------------------------------------------------------------------
+// SegmentTree._operate_helper (segment_tree.py:28-62), same recursion => same association.
+template <bool IS_SUM>
+__device__ double operate_helper(const double *base, long long stride, long long start,
+                                 long long end, long long node, long long ns, long long ne) {
+  if (start == ns && end == ne) return base[node * stride];
+  const long long mid = (ns + ne) / 2;
+  if (end <= mid) return operate_helper<IS_SUM>(base, stride, start, end, 2 * node, ns, mid);
+  if (mid + 1 <= start)
+    return operate_helper<IS_SUM>(base, stride, start, end, 2 * node + 1, mid + 1, ne);
+  const double a = operate_helper<IS_SUM>(base, stride, start, mid, 2 * node, ns, mid);
+  const double b = operate_helper<IS_SUM>(base, stride, mid + 1, end, 2 * node + 1, mid + 1, ne);
+  return IS_SUM ? __dadd_rn(a, b) : py_min(a, b);
+}
+
+__global__ void tree_query_kernel(Tree t, long long start, long long end, double *out) {
+  if (t.sum) out[0] = operate_helper<true>(t.sum, t.stride, start, end, 1, 0, t.cap - 1);
+  if (t.mn) out[1] = operate_helper<false>(t.mn, t.stride, start, end, 1, 0, t.cap - 1);
+}
+
+// SumSegmentTree.retrieve (segment_tree.py:147-156): strict '>' and unfused subtraction.
+__device__ __forceinline__ long long descend(const double *sum, long long stride, long long cap,
+                                             double ub) {
+  long long idx = 1;
+  while (idx < cap) {
+    const long long left = 2 * idx;
+    const double lv = __ldg(&sum[left * stride]);
+    if (lv > ub) {
+      idx = left;
+    } else {
+      ub = __dsub_rn(ub, lv);
+      idx = left + 1;
+    }
+  }
+  return idx - cap;
+}
+
+__global__ void tree_retrieve_kernel(Tree t, const double *ub, long long B, long long *out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B) out[i] = descend(t.sum, t.stride, t.cap, ub[i]);
+}
+
+// IS weight of one leaf (replay_buffer.py:398-407).
+__device__ __forceinline__ double is_max_weight(const Tree &t, double total, double size,
+                                                double neg_beta) {
+  const double p_min = __ddiv_rn(__ldg(&t.mn[t.stride]), total);
+  return xp::xp_pow(__dmul_rn(p_min, size), neg_beta);
+}
+__device__ __forceinline__ float is_weight(const Tree &t, long long leaf, double total,
+                                           double size, double neg_beta, double max_w) {
+  const double p = __ddiv_rn(__ldg(&t.sum[(t.cap + leaf) * t.stride]), total);
+  const double w = xp::xp_pow(__dmul_rn(p, size), neg_beta);
+  return __double2float_rn(__ddiv_rn(w, max_w));
+}
+
+// _sample_proportional (+ _calculate_weights) for P agents x B strata, one thread per sample.
+__global__ void __launch_bounds__(256) per_sample_kernel(Tree t, const float *u, long long B,
+                                                         long long total_samples, double size,
+                                                         double neg_beta, long long *idx_out,
+                                                         float *w_out) {
+  __shared__ double s_max_w;
+  const double total = __ldg(&t.sum[t.stride]);  // sum_tree.sum() == tree[1]
+  if (w_out && threadIdx.x == 0) s_max_w = is_max_weight(t, total, size, neg_beta);
+  if (w_out) __syncthreads();
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= total_samples) return;
+  const long long i = j % B;
+  const double seg = __ddiv_rn(total, (double)B);
+  const double a = __dmul_rn(seg, (double)i);
+  const double b = __dmul_rn(seg, (double)(i + 1));
+  // torch.rand(1).item() widens fp32 -> fp64 exactly; u*(b-a)+a in three rounded ops (:377)
+  const double ub = __dadd_rn(__dmul_rn((double)u[j], __dsub_rn(b, a)), a);
+  const long long leaf = descend(t.sum, t.stride, t.cap, ub);
+  idx_out[j] = leaf;
+  if (w_out) w_out[j] = is_weight(t, leaf, total, size, neg_beta, s_max_w);
+}
+
+__global__ void __launch_bounds__(256) per_weights_kernel(Tree t, const long long *idx,
+                                                          long long B, double size,
+                                                          double neg_beta, float *w_out) {
+  __shared__ double s_max_w;
+  const double total = __ldg(&t.sum[t.stride]);
+  if (threadIdx.x == 0) s_max_w = is_max_weight(t, total, size, neg_beta);
+  __syncthreads();
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= B) return;
+  long long leaf = idx[j];
+  if (leaf < 0) leaf += t.cap;  // Python negative indexing is not reachable here; keep in range
+  w_out[j] = is_weight(t, leaf, total, size, neg_beta, s_max_w);
+}
+
+__global__ void pow_batch_kernel(const double *x, double y, double *out, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    out[i] = xp::xp_pow(x[i], y);
+}
+
+xp_status_t to_tree(const xp_tree *in, Tree &t, const char *what, bool need_aux) {
+  XP_REQUIRE(in != nullptr, XP_ERR_INVALID, "%s: null tree", what);
+  XP_REQUIRE(in->cap > 0 && (in->cap & (in->cap - 1)) == 0, XP_ERR_INDEX,
+             "capacity must be positive and a power of 2.");
+  XP_REQUIRE(in->sum || in->min, XP_ERR_INVALID, "%s: both tree pointers null", what);
+  XP_REQUIRE(in->stride >= 1, XP_ERR_INVALID, "%s: stride < 1", what);
+  XP_REQUIRE(!need_aux || in->aux, XP_ERR_INVALID, "%s: aux scratch required", what);
+  t.sum = in->sum;
+  t.mn = in->min;
+  t.stride = in->stride;
+  t.cap = in->cap;
+  t.aux = in->aux;
+  return XP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+xp_status_t xp_tree_init(const xp_tree *tree, void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_tree_init", false);
+  if (st != XP_OK) return st;
+  long long n = 2 * t.cap;
+  unsigned grid = (unsigned)((n + 255) / 256 > 148 * 16 ? 148 * 16 : (n + 255) / 256);
+  tree_init_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(t);
+  return xp::check_launch("xp_tree_init");
+}
+
+xp_status_t xp_tree_set_batch(const xp_tree *tree, const int64_t *idx_dev, const double *val_dev,
+                              int64_t B, int *err_flag_dev, void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_tree_set_batch", true);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(B >= 0, XP_ERR_INVALID, "xp_tree_set_batch: B < 0");
+  XP_REQUIRE(B == 0 || (idx_dev && val_dev), XP_ERR_INVALID, "xp_tree_set_batch: null input");
+  SetSrc s{};
+  s.kind = kSrcVal;
+  s.idx = (const long long *)idx_dev;
+  s.val = val_dev;
+  s.limit = t.cap;
+  s.err = err_flag_dev;
+  return run_set(t, s, B, false, (cudaStream_t)stream);
+}
+
+xp_status_t xp_tree_query(const xp_tree *tree, int64_t start, int64_t end, double *out_dev,
+                          void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_tree_query", false);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(out_dev, XP_ERR_INVALID, "xp_tree_query: null output");
+  // SegmentTree.operate (segment_tree.py:75-79)
+  if (end <= 0) end += t.cap;
+  end -= 1;
+  XP_REQUIRE(start >= 0 && end < t.cap && start <= end, XP_ERR_INDEX,
+             "xp_tree_query: bad range [%lld, %lld]", (long long)start, (long long)end);
+  tree_query_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(t, start, end, out_dev);
+  return xp::check_launch("xp_tree_query");
+}
+
+xp_status_t xp_tree_retrieve(const xp_tree *tree, const double *ub_dev, int64_t B,
+                             int64_t *idx_out_dev, void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_tree_retrieve", false);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(t.sum, XP_ERR_INVALID, "xp_tree_retrieve: needs a sum tree");
+  if (B == 0) return XP_OK;
+  XP_REQUIRE(B > 0 && ub_dev && idx_out_dev, XP_ERR_INVALID, "xp_tree_retrieve: bad args");
+  tree_retrieve_kernel<<<(unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      t, ub_dev, B, (long long *)idx_out_dev);
+  return xp::check_launch("xp_tree_retrieve");
+}
+
+xp_status_t xp_per_add(const xp_tree *tree, xp_per_state *state_dev, int64_t tree_ptr, int64_t n,
+                       int64_t max_size, double alpha, void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_per_add", true);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(state_dev, XP_ERR_INVALID, "xp_per_add: null state");
+  XP_REQUIRE(max_size > 0 && max_size <= t.cap, XP_ERR_INVALID, "xp_per_add: bad max_size");
+  XP_REQUIRE(tree_ptr >= 0 && tree_ptr < max_size, XP_ERR_INDEX, "xp_per_add: tree_ptr out of range");
+  XP_REQUIRE(n >= 0, XP_ERR_INVALID, "xp_per_add: n < 0");
+  SetSrc s{};
+  s.kind = kSrcRange;
+  s.alpha = alpha;
+  s.max_priority_bits = (unsigned long long *)&state_dev->max_priority;
+  s.range_mod = max_size;
+  s.limit = max_size;
+  // n >= max_size touches every leaf of [0,max_size) with one value: same set, no duplicates.
+  s.range_start = (n >= max_size) ? 0 : tree_ptr;
+  const long long count = (n >= max_size) ? max_size : n;
+  return run_set(t, s, count, true, (cudaStream_t)stream);
+}
+
+xp_status_t xp_per_sample(const xp_tree *tree, const float *u_dev, int64_t B, int64_t P,
+                          int64_t size, double beta, int64_t *idx_out_dev, float *w_out_dev,
+                          void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_per_sample", false);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(t.sum, XP_ERR_INVALID, "xp_per_sample: needs a sum tree");
+  XP_REQUIRE(!w_out_dev || t.mn, XP_ERR_INVALID, "xp_per_sample: weights need a min tree");
+  XP_REQUIRE(B >= 0 && P >= 0, XP_ERR_INVALID, "xp_per_sample: negative extent");
+  const long long total = B * P;
+  if (total == 0) return XP_OK;
+  XP_REQUIRE(u_dev && idx_out_dev, XP_ERR_INVALID, "xp_per_sample: null pointer");
+  per_sample_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      t, u_dev, B, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
+  return xp::check_launch("xp_per_sample");
+}
+
+xp_status_t xp_per_weights(const xp_tree *tree, const int64_t *idx_dev, int64_t B, int64_t size,
+                           double beta, float *w_out_dev, void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_per_weights", false);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(t.sum && t.mn, XP_ERR_INVALID, "xp_per_weights: needs both trees");
+  if (B == 0) return XP_OK;
+  XP_REQUIRE(B > 0 && idx_dev && w_out_dev, XP_ERR_INVALID, "xp_per_weights: bad args");
+  per_weights_kernel<<<(unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      t, (const long long *)idx_dev, B, (double)size, -beta, w_out_dev);
+  return xp::check_launch("xp_per_weights");
+}
+
+xp_status_t xp_per_update(const xp_tree *tree, xp_per_state *state_dev, const int64_t *idx_dev,
+                          const float *prio_dev, int64_t B, int64_t max_size, double alpha,
+                          int *err_flag_dev, void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_per_update", true);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(state_dev, XP_ERR_INVALID, "xp_per_update: null state");
+  XP_REQUIRE(max_size > 0 && max_size <= t.cap, XP_ERR_INVALID, "xp_per_update: bad max_size");
+  XP_REQUIRE(B >= 0, XP_ERR_INVALID, "xp_per_update: B < 0");
+  XP_REQUIRE(B == 0 || (idx_dev && prio_dev), XP_ERR_INVALID, "xp_per_update: null input");
+  SetSrc s{};
+  s.kind = kSrcPrio;
+  s.idx = (const long long *)idx_dev;
+  s.prio = prio_dev;
+  s.alpha = alpha;
+  s.max_priority_bits = (unsigned long long *)&state_dev->max_priority;
+  s.limit = max_size;
+  s.err = err_flag_dev;
+  return run_set(t, s, B, false, (cudaStream_t)stream);
+}
+
+xp_status_t xp_pow_batch(const double *x_dev, double y, double *out_dev, int64_t n, void *stream) {
+  if (n == 0) return XP_OK;
+  XP_REQUIRE(n > 0 && x_dev && out_dev, XP_ERR_INVALID, "xp_pow_batch: bad args");
+  long long blocks = (n + 255) / 256;
+  unsigned grid = (unsigned)(blocks > 148 * 8 ? 148 * 8 : blocks);
+  pow_batch_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x_dev, y, out_dev, n);
+  return xp::check_launch("xp_pow_batch");
+}
+
+}  // extern "C"

@@ -1,0 +1,193 @@
+/*
+ * b200xp.h — C-ABI of libb200xp.so, the B200-native (sm_100a) experience-path engine.
+ *
+ * This is the drop-in boundary for the hot path of AgileRL's agilerl/components/
+ * (replay_buffer.py, segment_tree.py, rollout_buffer.py).  Every entry point names the
+ * reference interface it replaces (file:line relative to the AgileRL source tree).
+ *
+ * Conventions
+ *   - All `dev` pointers are DEVICE pointers owned by the caller (the PyTorch caching
+ *     allocator in the Python host).  The library owns no device memory and never allocates.
+ *   - Every device op is ASYNCHRONOUS on the `stream` argument (a cudaStream_t passed as
+ *     void*; NULL = legacy default stream).  No entry point synchronises.
+ *   - Return value: XP_OK (0) or a negative xp_status_t; the message is in xp_last_error()
+ *     (thread-local).  The Python host maps XP_ERR_INDEX -> AssertionError (index range,
+ *     replay_buffer.py:319; power-of-two capacity, segment_tree.py:20-23) and
+ *     XP_ERR_INVALID -> ValueError.
+ *   - One host thread per buffer (the reference is single-threaded per buffer); different
+ *     buffers may use different streams.
+ *   - Integer / index / tree results are bit-exact against the reference; floating point
+ *     follows the reference's rounding sequence (no FMA contraction) — see DESIGN.md.
+ */
+#ifndef B200XP_H_
+#define B200XP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int xp_status_t;
+#define XP_OK 0
+#define XP_ERR_INVALID (-1) /* bad argument (shape, null pointer, size)            */
+#define XP_ERR_INDEX (-2)   /* index out of range / capacity not a power of two     */
+#define XP_ERR_CUDA (-3)    /* CUDA runtime error; text in xp_last_error()          */
+#define XP_ERR_STATE (-4)   /* call made in the wrong state                         */
+
+#define XP_MAX_KEYS 24   /* keys (columns) per ring/gather launch                 */
+#define XP_MAX_NSTEP 32  /* n of the n-step fold                                   */
+
+/* ---- library ---------------------------------------------------------------------- */
+int xp_version(void);               /* ABI version, bumped on any signature change  */
+const char *xp_last_error(void);    /* thread-local, never NULL                     */
+/* Device facts used for grid sizing (SM count, compute capability). */
+xp_status_t xp_device_info(int device, int *sm_count, int *cc_major, int *cc_minor);
+
+/* ---- keys: one column of a transition table ---------------------------------------- */
+/* A replay storage is struct-of-arrays: one [max_size, row_bytes] device array per key
+ * (replay_buffer.py:60-70).  `src`/`dst` meaning depends on the op.                     */
+typedef struct xp_key {
+  const void *src;   /* device pointer                                                 */
+  void *dst;         /* device pointer                                                 */
+  int64_t row_bytes; /* bytes per row of this key                                      */
+} xp_key;
+
+/* ---- ring insert / indexed gather (ReplayBuffer.add / storage[idx]) ------------------ */
+/* replaces ReplayBuffer.add's circular slice-assign (replay_buffer.py:99-107):
+ * for r in [0,n_rows): dst[(cursor + r) % max_size] = src[r], for every key, one launch. */
+xp_status_t xp_ring_insert(const xp_key *keys, int n_keys, int64_t n_rows, int64_t cursor,
+                           int64_t max_size, void *stream);
+/* replaces TensorDict index-gather `storage[indices]` + `.clone()`
+ * (replay_buffer.py:126,204,345-346): dst[b] = src[idx[b]] for every key, one launch.
+ * idx_dev: int64[B]. Rows with idx outside [0,n_src_rows) set *err_flag_dev (if not NULL)
+ * to 1 and are written as zeros.                                                        */
+xp_status_t xp_gather(const xp_key *keys, int n_keys, const int64_t *idx_dev, int64_t B,
+                      int64_t n_src_rows, int *err_flag_dev, void *stream);
+
+/* ---- uniform sampling without replacement (ReplayBuffer.sample) ---------------------- */
+/* replaces `torch.randperm(size)[:batch]` (replay_buffer.py:125, rollout_buffer.py:570):
+ * given the raw 32-bit mt19937 draws x_0..x_{B-1} torch would consume, produce the first
+ * B entries of the forward Fisher-Yates permutation of range(n), exactly, in O(B log B).
+ * P independent agents per launch: raw_dev is u32[P*B], idx_out_dev int64[P*B].
+ * Requires 1 <= B <= n, B <= 4096.                                                      */
+xp_status_t xp_randperm_prefix(const uint32_t *raw_dev, int64_t B, int64_t P, int64_t n,
+                               int64_t *idx_out_dev, void *stream);
+/* Counter-based raw draws on the device (throughput mode; Philox4x32-10). out u32[n].   */
+xp_status_t xp_philox_u32(uint64_t seed, uint64_t offset, uint32_t *out_dev, int64_t n,
+                          void *stream);
+
+/* ---- segment trees (SumSegmentTree / MinSegmentTree, segment_tree.py:5-182) ---------- */
+/* A tree of capacity `cap` (power of two) is 2*cap fp64 nodes in heap order: node 1 is the
+ * root, leaves are cap..2cap-1 (segment_tree.py:25,89-95).  Node i of a tree lives at
+ * base[i*stride] (stride in doubles) so that a (sum,min) pair can be interleaved
+ * (stride 2, min = sum+1) or stored separately (stride 1).  Either tree pointer may be
+ * NULL to operate on one tree only.                                                     */
+typedef struct xp_tree {
+  double *sum;     /* device; node i at sum[i*stride]; init 0.0   (segment_tree.py:122) */
+  double *min;     /* device; node i at min[i*stride]; init +inf  (segment_tree.py:170) */
+  int64_t stride;  /* in doubles                                                        */
+  int64_t cap;     /* power of two                                                      */
+  int32_t *aux;    /* device int32[2*cap], zero between calls: leaf slots [cap,2cap) hold
+                      the last-writer ticket, internal slots [1,cap) the pending count   */
+} xp_tree;
+
+/* fill all nodes with the initial values (SegmentTree.__init__, segment_tree.py:25).    */
+xp_status_t xp_tree_init(const xp_tree *t, void *stream);
+/* replaces a batch of `tree[idx] = val` (SegmentTree.__setitem__, segment_tree.py:81-95)
+ * applied SEQUENTIALLY: duplicates resolve last-writer-wins, every ancestor ends up as
+ * op(left,right) of its final children — bit-identical to the sequential loop.
+ * idx_dev int64[B] in [0,cap); val_dev fp64[B].  Out-of-range sets *err_flag_dev.        */
+xp_status_t xp_tree_set_batch(const xp_tree *t, const int64_t *idx_dev, const double *val_dev,
+                              int64_t B, int *err_flag_dev, void *stream);
+/* replaces SegmentTree.operate(start,end) (segment_tree.py:28-79) with the reference's
+ * recursive association order; result written to out_dev[0] (sum) and out_dev[1] (min).   */
+xp_status_t xp_tree_query(const xp_tree *t, int64_t start, int64_t end, double *out_dev,
+                          void *stream);
+/* replaces SumSegmentTree.retrieve (segment_tree.py:136-156) for a batch of upper bounds. */
+xp_status_t xp_tree_retrieve(const xp_tree *t, const double *ub_dev, int64_t B,
+                             int64_t *idx_out_dev, void *stream);
+
+/* ---- prioritized replay (PrioritizedReplayBuffer, replay_buffer.py:261-428) ---------- */
+/* device-resident scalar state of one PER buffer */
+typedef struct xp_per_state {
+  double max_priority; /* replay_buffer.py:284,329 */
+} xp_per_state;
+
+/* replaces the per-row loop of PrioritizedReplayBuffer.add (replay_buffer.py:306-309):
+ * leaves (tree_ptr + r) % max_size, r in [0,n) := max_priority ** alpha in both trees.   */
+xp_status_t xp_per_add(const xp_tree *t, xp_per_state *state_dev, int64_t tree_ptr, int64_t n,
+                       int64_t max_size, double alpha, void *stream);
+/* replaces _sample_proportional (replay_buffer.py:357-381) and _calculate_weights
+ * (:383-409) for P agents x B samples in one launch.  u_dev fp32[P*B] are the torch.rand
+ * draws; sample j uses stratum i = j % B.  idx_out_dev int64[P*B]; w_out_dev fp32[P*B] or
+ * NULL (indices only).  `size` is the replay size (len(buffer)).                         */
+xp_status_t xp_per_sample(const xp_tree *t, const float *u_dev, int64_t B, int64_t P,
+                          int64_t size, double beta, int64_t *idx_out_dev, float *w_out_dev,
+                          void *stream);
+/* _calculate_weights alone (replay_buffer.py:383-409) for given indices int64[B].        */
+xp_status_t xp_per_weights(const xp_tree *t, const int64_t *idx_dev, int64_t B, int64_t size,
+                           double beta, float *w_out_dev, void *stream);
+/* replaces update_priorities (replay_buffer.py:411-428): sequential semantics
+ * p = max(float(prio), 1e-5); leaf = p ** alpha; max_priority = max(max_priority, p).
+ * idx_dev int64[B] must lie in [0,max_size) (else *err_flag_dev = 1, row skipped);
+ * prio_dev fp32[B].                                                                     */
+xp_status_t xp_per_update(const xp_tree *t, xp_per_state *state_dev, const int64_t *idx_dev,
+                          const float *prio_dev, int64_t B, int64_t max_size, double alpha,
+                          int *err_flag_dev, void *stream);
+/* priority ** alpha as CPython computes it (glibc pow), batch, fp64 in/out
+ * (replay_buffer.py:322,401,406).                                                       */
+xp_status_t xp_pow_batch(const double *x_dev, double y, double *out_dev, int64_t n,
+                         void *stream);
+
+/* ---- n-step fold (MultiStepReplayBuffer._get_n_step_info, replay_buffer.py:206-258) --- */
+/* The last n env-steps live in a device stage ring of n slots x N envs per key; `slot0`
+ * is the slot of the OLDEST step.  For every env e writes one row at ring position
+ * (cursor + e) % max_size of the replay storage:
+ *   keys[k].src = stage base [n_step, N, row_bytes], keys[k].dst = storage base;
+ *   role[k]: XP_ROLE_FIRST  -> copied from the oldest step
+ *            XP_ROLE_LAST   -> copied from step m (next_obs, done)
+ *            XP_ROLE_REWARD -> fp32 fold R = r_0; R += r_i * gpow[i], i = 1..m (no FMA)
+ *   m = first i >= 1 whose done flag is set for ANY env, else n_step-1 (:252).
+ * done_key indexes keys[]; done_elem_bytes is 1 (bool/uint8) or 4 (fp32).               */
+#define XP_ROLE_FIRST 0
+#define XP_ROLE_LAST 1
+#define XP_ROLE_REWARD 2
+xp_status_t xp_nstep_fold_insert(const xp_key *keys, const int *roles, int n_keys, int done_key,
+                                 int done_elem_bytes, int n_step, int slot0, const float *gpow,
+                                 int64_t N, int64_t cursor, int64_t max_size, void *stream);
+
+/* ---- rollout returns (RolloutBuffer.compute_returns_and_advantages) ------------------- */
+/* replaces the GAE branch (rollout_buffer.py:448-467) for P agents in one launch.
+ * rewards/values fp32 [P][T][N] (agent_stride elements between agents, row stride N),
+ * dones u8 same layout; last_value/last_done fp64 [P][N]; adv/ret fp32 out, same layout
+ * as rewards.  Carry in fp64; gamma*v[t+1] rounded in fp32 for t < T-1 (:455-456), fp64 at
+ * t = T-1 (:452-453); ret = fp32(adv) + v in fp32 (:467).                                */
+xp_status_t xp_gae(const float *rewards, const float *values, const uint8_t *dones,
+                   const double *last_value, const double *last_done, float *adv, float *ret,
+                   int64_t T, int64_t N, int64_t P, int64_t agent_stride, double gamma,
+                   double gae_lambda, void *stream);
+/* replaces the Monte-Carlo branch (rollout_buffer.py:468-477). */
+xp_status_t xp_mc_returns(const float *rewards, const float *values, const uint8_t *dones,
+                          const double *last_value, const double *last_done, float *adv,
+                          float *ret, int64_t T, int64_t N, int64_t P, int64_t agent_stride,
+                          double gamma, void *stream);
+
+/* ---- host-side RNG mirror (no GPU needed) -------------------------------------------- */
+/* torch's CPU generator is mt19937; these reproduce the raw 32-bit stream so that the
+ * engine consumes "identical uniform draws" (replay_buffer.py:125,377).
+ * state: 624 words + index, as torch.get_rng_state() stores them.                        */
+typedef struct xp_mt19937 {
+  uint32_t mt[624];
+  int32_t idx; /* number of words already consumed from mt[] (0..624) */
+} xp_mt19937;
+void xp_mt19937_seed(xp_mt19937 *g, uint32_t seed);
+void xp_mt19937_draw(xp_mt19937 *g, uint32_t *out, int64_t n);
+void xp_mt19937_skip(xp_mt19937 *g, int64_t n);
+/* host restatement of the O(B) randperm prefix for small cases / index validation.      */
+xp_status_t xp_host_randperm_prefix(const uint32_t *raw, int64_t B, int64_t n, int64_t *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200XP_H_ */

@@ -1,0 +1,139 @@
+"""TEST INFRASTRUCTURE — generates tests/golden/*.npz by running the UNMODIFIED reference.
+
+Run in the build container (needs /root/reference):  ``python oracle/make_golden.py``
+The fixtures are committed; the GPU box (no reference tree) only reads them.
+Every fixture stores the inputs and the reference's outputs for one seeded scenario.
+"""
+
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+
+from oracle import ref_loader  # noqa: E402
+
+OUT = os.path.join(os.path.dirname(HERE), "tests", "golden")
+
+
+def save(name, **arrays):
+    os.makedirs(OUT, exist_ok=True)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **arrays)
+    print("wrote", name, {k: np.asarray(v).shape for k, v in arrays.items()})
+
+
+def gen_gae():
+    for seed, (T, N) in [(0, (16, 8)), (1, (128, 64)), (2, (37, 33))]:
+        g = torch.Generator().manual_seed(seed)
+        r = torch.randn(T, N, generator=g).numpy()
+        v = torch.randn(T, N, generator=g).numpy()
+        d = (torch.rand(T, N, generator=g) < 0.05).numpy()
+        lv = torch.randn(N, generator=g).numpy()
+        ld = (torch.rand(N, generator=g) < 0.1).numpy()
+        adv, ret = ref_loader.reference_gae(r, v, d, lv, ld, 0.99, 0.95, use_gae=True)
+        adv_mc, ret_mc = ref_loader.reference_gae(r, v, d, lv, ld, 0.99, 0.95, use_gae=False)
+        save(f"gae_s{seed}", rewards=r, values=v, dones=d, last_value=lv, last_done=ld,
+             gamma=0.99, gae_lambda=0.95, adv=adv, ret=ret, adv_mc=adv_mc, ret_mc=ret_mc)
+
+
+def gen_per():
+    ref = ref_loader.load_reference()
+    TD = ref.TensorDict
+    for seed, max_size, B in [(0, 100, 16), (1, 256, 64), (2, 1000, 128)]:
+        torch.manual_seed(seed)
+        g = torch.Generator().manual_seed(1000 + seed)
+        buf = ref.PrioritizedReplayBuffer(max_size=max_size, alpha=0.6)
+        rec = {}
+        # fill beyond capacity in uneven batches so tree_ptr wraps at max_size
+        n_added = 0
+        step = 0
+        sizes = []
+        while n_added < max_size + max_size // 3:
+            n = int(torch.randint(1, 17, (1,), generator=g))
+            sizes.append(n)
+            td = TD({"obs": torch.randn(n, 4, generator=g), "reward": torch.randn(n, generator=g)},
+                    batch_size=[n])
+            buf.add(td)
+            n_added += n
+            step += 1
+            if step == 3:  # early update so max_priority grows before later adds
+                idx = torch.randint(0, buf.size, (8,), generator=g)
+                pr = (torch.randn(8, generator=g).abs() * 3 + 1e-6).numpy()
+                buf.update_priorities(idx, pr)
+                rec["early_idx"], rec["early_prio"], rec["early_at"] = idx.numpy(), pr, n_added
+        rec["add_sizes"] = np.array(sizes)
+        rec["tree_ptr"] = buf.tree_ptr
+        rec["size"] = buf.size
+        # updates with forced duplicates and a tiny priority (1e-5 clamp)
+        idx = torch.randint(0, max_size, (B,), generator=g)
+        idx[B // 2:] = idx[: B - B // 2]
+        pr = (torch.randn(B, generator=g).abs() + 1e-6).numpy().astype(np.float32)
+        pr[0] = 1e-9
+        buf.update_priorities(idx, pr)
+        rec["upd_idx"], rec["upd_prio"] = idx.numpy(), pr
+        rec["sum_tree_after_update"] = np.array(buf.sum_tree.tree)
+        rec["min_tree_after_update"] = np.array(buf.min_tree.tree)
+        rec["max_priority"] = buf.max_priority
+        # sampling with known uniforms: torch.rand(1) per stratum from the global generator
+        torch.manual_seed(77 + seed)
+        u = torch.rand(B)
+        torch.manual_seed(77 + seed)
+        indices = buf._sample_proportional(B)
+        weights = buf._calculate_weights(indices, 0.4)
+        rec["u"], rec["sample_idx"], rec["weights"], rec["beta"] = u.numpy(), indices.numpy(), weights.numpy(), 0.4
+        save(f"per_s{seed}", max_size=max_size, alpha=0.6, **rec)
+
+
+def gen_ring_nstep():
+    ref = ref_loader.load_reference()
+    TD = ref.TensorDict
+    for seed, (max_size, N, n_step) in [(0, (10, 4, 3)), (1, (50, 16, 3)), (2, (23, 5, 5))]:
+        g = torch.Generator().manual_seed(seed)
+        steps = 3 * max_size // N + 7
+        obs = torch.randint(0, 256, (steps, N, 6), generator=g, dtype=torch.uint8)
+        nobs = torch.randint(0, 256, (steps, N, 6), generator=g, dtype=torch.uint8)
+        act = torch.randint(0, 4, (steps, N), generator=g).float()
+        rew = torch.randn(steps, N, generator=g)
+        done = (torch.rand(steps, N, generator=g) < 0.08).float()
+        ring = ref.ReplayBuffer(max_size=max_size)
+        nbuf = ref.MultiStepReplayBuffer(max_size=max_size, n_step=n_step, gamma=0.99)
+        returned_none = []
+        for s in range(steps):
+            td = TD({"obs": obs[s], "action": act[s], "reward": rew[s], "next_obs": nobs[s],
+                     "done": done[s]}, batch_size=[N])
+            ring.add(td.clone())
+            out = nbuf.add(td.clone())
+            returned_none.append(out is None)
+        save(f"ring_nstep_s{seed}", max_size=max_size, N=N, n_step=n_step, gamma=0.99,
+             obs=obs.numpy(), next_obs=nobs.numpy(), action=act.numpy(), reward=rew.numpy(),
+             done=done.numpy(), returned_none=np.array(returned_none),
+             ring_cursor=ring._cursor, ring_size=ring.size,
+             **{f"ring_{k}": v.numpy() for k, v in ring.storage.items()},
+             nstep_cursor=nbuf._cursor, nstep_size=nbuf.size,
+             **{f"nstep_{k}": v.numpy() for k, v in nbuf.storage.items()})
+
+
+def gen_rng():
+    rec = {}
+    cases = [(0, 100000, 64), (7, 1000000, 1024), (3, 50, 50), (5, 1000, 999), (11, 4097, 2048),
+             (2, 10_000_000, 1024), (13, 1, 1), (17, 2, 2)]
+    for k, (seed, n, B) in enumerate(cases):
+        torch.manual_seed(seed)
+        rec[f"perm_{k}"] = torch.randperm(n)[:B].numpy()
+    rec["cases"] = np.array(cases)
+    for seed in (0, 1, 123456789):
+        torch.manual_seed(seed)
+        rec[f"rand_{seed}"] = torch.rand(700).numpy()  # crosses the 624-word twist boundary
+    save("torch_rng", **rec)
+
+
+if __name__ == "__main__":
+    gen_gae()
+    gen_per()
+    gen_ring_nstep()
+    gen_rng()

@@ -1,0 +1,211 @@
+"""TEST INFRASTRUCTURE — loads the UNMODIFIED reference (AgileRL) hot-path modules by file path.
+
+Only usable where /root/reference exists (this build container); it is used by
+``oracle/make_golden.py`` to generate the committed fixtures under ``tests/golden/`` and by
+``tests/test_oracle_vs_reference.py`` (skipped when the reference tree is absent, e.g. on the GPU
+box).  Nothing in the product package imports this file.
+
+``import agilerl`` itself fails here (tensordict / gymnasium / accelerate are not installed), so:
+  * agilerl/components/segment_tree.py is stdlib-only        -> loaded as is;
+  * agilerl/components/replay_buffer.py needs `tensordict`   -> a minimal shim is registered;
+  * RolloutBuffer.compute_returns_and_advantages             -> AST-extracted and exec'd.
+No reference source is copied into this repository.
+"""
+
+from __future__ import annotations
+
+import ast
+import importlib.util
+import os
+import sys
+import textwrap
+import types
+
+import numpy as np
+import torch
+
+REF_ROOT = os.environ.get("AGILERL_REFERENCE", "/root/reference")
+REF_PKG = os.path.join(REF_ROOT, "agilerl")
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REF_PKG, "components", "replay_buffer.py"))
+
+
+# --------------------------------------------------------------------------------------------
+# Minimal TensorDict stand-in: just the operations replay_buffer.py performs on its storage.
+# --------------------------------------------------------------------------------------------
+class ShimTensorDict:
+    def __init__(self, source=None, batch_size=None, device=None):
+        self._d = {}
+        source = source or {}
+        for k, v in source.items():
+            if isinstance(v, dict):
+                v = ShimTensorDict(v, batch_size=batch_size)
+            elif not isinstance(v, (torch.Tensor, ShimTensorDict)):
+                v = torch.as_tensor(v)
+            self._d[k] = v
+        if batch_size is None:
+            batch_size = []
+        if isinstance(batch_size, int):
+            batch_size = [batch_size]
+        self.batch_size = torch.Size(batch_size)
+
+    # -- mapping ---------------------------------------------------------------------------
+    @property
+    def shape(self):
+        return self.batch_size
+
+    def keys(self):
+        return self._d.keys()
+
+    def items(self):
+        return list(self._d.items())
+
+    def values(self):
+        return self._d.values()
+
+    def __contains__(self, k):
+        return k in self._d
+
+    def get(self, k, default=None):
+        return self._d.get(k, default)
+
+    def _map(self, fn, batch_size=None):
+        out = ShimTensorDict({}, batch_size=self.batch_size if batch_size is None else batch_size)
+        for k, v in self._d.items():
+            out._d[k] = v._map(fn, batch_size) if isinstance(v, ShimTensorDict) else fn(v)
+        return out
+
+    def __getitem__(self, idx):
+        if isinstance(idx, str):
+            return self._d[idx]
+        probe = torch.empty(self.batch_size + (1,), device="meta")[idx]
+        new_bs = probe.shape[:-1]
+        return self._map(lambda t: t[idx], new_bs)
+
+    def __setitem__(self, idx, value):
+        if isinstance(idx, str):
+            self._d[idx] = value
+            return
+        for k, v in self._d.items():
+            src = value[k] if not isinstance(value, torch.Tensor) else value
+            if isinstance(v, ShimTensorDict):
+                v[idx] = src
+            else:
+                v[idx] = src
+
+    def to(self, *a, **kw):
+        return self._map(lambda t: t.to(*a, **kw))
+
+    def clone(self):
+        return self._map(lambda t: t.clone())
+
+    def expand(self, shape):
+        shape = tuple(shape)
+        nb = len(self.batch_size)
+        return self._map(lambda t: t.expand(*shape, *t.shape[nb:]), torch.Size(shape))
+
+    def unsqueeze(self, dim):
+        bs = list(self.batch_size)
+        bs.insert(dim, 1)
+        return self._map(lambda t: t.unsqueeze(dim), torch.Size(bs))
+
+    @classmethod
+    def __torch_function__(cls, func, types_, args=(), kwargs=None):
+        kwargs = kwargs or {}
+        if func is torch.zeros_like:
+            return args[0]._map(lambda t: torch.zeros_like(t))
+        return NotImplemented
+
+
+def _load(name: str, path: str):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+_cache: dict = {}
+
+
+def load_reference():
+    """Returns a namespace with the reference's SumSegmentTree, MinSegmentTree, ReplayBuffer,
+    MultiStepReplayBuffer, PrioritizedReplayBuffer (unmodified code) and TensorDict (the shim)."""
+    if "ns" in _cache:
+        return _cache["ns"]
+    if not available():
+        raise RuntimeError(f"reference tree not found under {REF_ROOT}")
+    saved = {k: sys.modules.get(k) for k in
+             ("agilerl", "agilerl.components", "agilerl.typing", "tensordict",
+              "agilerl.components.segment_tree", "agilerl.components.replay_buffer")}
+    try:
+        for n in ("agilerl", "agilerl.components"):
+            pkg = types.ModuleType(n)
+            pkg.__path__ = []
+            sys.modules[n] = pkg
+        seg = _load("agilerl.components.segment_tree",
+                    os.path.join(REF_PKG, "components", "segment_tree.py"))
+        td = types.ModuleType("tensordict")
+        td.TensorDict = td.TensorDictBase = ShimTensorDict
+        td.is_tensor_collection = lambda x: isinstance(x, ShimTensorDict)
+        sys.modules["tensordict"] = td
+        ty = types.ModuleType("agilerl.typing")
+        ty.ArrayOrTensor = object
+        sys.modules["agilerl.typing"] = ty
+        rb = _load("agilerl.components.replay_buffer",
+                   os.path.join(REF_PKG, "components", "replay_buffer.py"))
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+    ns = types.SimpleNamespace(
+        SumSegmentTree=seg.SumSegmentTree, MinSegmentTree=seg.MinSegmentTree,
+        ReplayBuffer=rb.ReplayBuffer, MultiStepReplayBuffer=rb.MultiStepReplayBuffer,
+        PrioritizedReplayBuffer=rb.PrioritizedReplayBuffer, TensorDict=ShimTensorDict,
+    )
+    _cache["ns"] = ns
+    return ns
+
+
+def load_reference_gae():
+    """AST-extract RolloutBuffer.compute_returns_and_advantages (rollout_buffer.py:413-481) and
+    return ``f(self_like, last_value, last_done)``; ``self_like`` needs num_envs, capacity, full,
+    pos, gamma, gae_lambda, use_gae and ``buffer`` = dict of CPU torch tensors."""
+    if "gae" in _cache:
+        return _cache["gae"]
+    path = os.path.join(REF_PKG, "components", "rollout_buffer.py")
+    src = open(path).read()
+    tree = ast.parse(src)
+    fn_src = None
+    for node in tree.body:
+        if isinstance(node, ast.ClassDef) and node.name == "RolloutBuffer":
+            for item in node.body:
+                if isinstance(item, ast.FunctionDef) and item.name == "compute_returns_and_advantages":
+                    fn_src = ast.get_source_segment(src, item)
+    assert fn_src is not None
+    g = {"np": np, "torch": torch, "ArrayOrTensor": object}
+    exec(textwrap.dedent(fn_src), g)
+    _cache["gae"] = g["compute_returns_and_advantages"]
+    return _cache["gae"]
+
+
+def reference_gae(rewards, values, dones, last_value, last_done, gamma, gae_lambda, use_gae=True):
+    """Run the reference GAE/MC on numpy inputs [T,N]; returns (advantages, returns) fp32."""
+    f = load_reference_gae()
+    T, N = rewards.shape
+    self_like = types.SimpleNamespace(
+        num_envs=N, capacity=T, full=True, pos=0, gamma=gamma, gae_lambda=gae_lambda,
+        use_gae=use_gae,
+        buffer={
+            "rewards": torch.from_numpy(np.ascontiguousarray(rewards)),
+            "values": torch.from_numpy(np.ascontiguousarray(values)),
+            "dones": torch.from_numpy(np.ascontiguousarray(dones)),
+            "advantages": torch.zeros(T, N), "returns": torch.zeros(T, N),
+        },
+    )
+    f(self_like, last_value, last_done)
+    return self_like.buffer["advantages"].numpy().copy(), self_like.buffer["returns"].numpy().copy()

@@ -1,0 +1,287 @@
+"""TEST INFRASTRUCTURE — CPU restatement (numpy / pure Python) of the AgileRL experience path.
+
+This is the parity ORACLE, not product code: only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import it.  Each function cites the reference
+file:line (relative to the AgileRL tree) it follows.  It deliberately keeps the reference's
+data structures (Python lists of floats for the trees, per-sample Python loops, numpy time loop
+for GAE) so that timing it is representative of the reference's own CPU path.
+
+Parity pin: tests/test_oracle_golden.py checks every function against the fixtures in
+tests/golden/ that oracle/make_golden.py produced by running the unmodified reference code
+(oracle/ref_loader.py) in the build container, and against the reference's own known-answer
+tests (tests/test_components/test_segment_tree.py, test_replay_buffer.py).
+"""
+
+from __future__ import annotations
+
+import math
+import operator
+
+import numpy as np
+
+# ---------------------------------------------------------------------------------------------
+# segment trees — agilerl/components/segment_tree.py:5-182
+# ---------------------------------------------------------------------------------------------
+
+
+class SegTree:
+    """Heap-layout tree over a Python list of floats (segment_tree.py:19-26)."""
+
+    def __init__(self, capacity: int, kind: str):
+        assert capacity > 0 and capacity & (capacity - 1) == 0, (
+            "capacity must be positive and a power of 2."
+        )
+        self.capacity = capacity
+        self.kind = kind
+        if kind == "sum":
+            self.operation, init = operator.add, 0.0
+        else:
+            self.operation, init = min, float("inf")
+        self.tree = [init for _ in range(2 * capacity)]
+
+    def _helper(self, start, end, node, ns, ne):  # segment_tree.py:28-62
+        if start == ns and end == ne:
+            return self.tree[node]
+        mid = (ns + ne) // 2
+        if end <= mid:
+            return self._helper(start, end, 2 * node, ns, mid)
+        if mid + 1 <= start:
+            return self._helper(start, end, 2 * node + 1, mid + 1, ne)
+        return self.operation(
+            self._helper(start, mid, 2 * node, ns, mid),
+            self._helper(mid + 1, end, 2 * node + 1, mid + 1, ne),
+        )
+
+    def operate(self, start=0, end=0):  # segment_tree.py:64-79
+        if end <= 0:
+            end += self.capacity
+        end -= 1
+        return self._helper(start, end, 1, 0, self.capacity - 1)
+
+    def __setitem__(self, idx, val):  # segment_tree.py:81-95
+        idx += self.capacity
+        self.tree[idx] = val
+        idx //= 2
+        while idx >= 1:
+            self.tree[idx] = self.operation(self.tree[2 * idx], self.tree[2 * idx + 1])
+            idx //= 2
+
+    def __getitem__(self, idx):  # segment_tree.py:97-108
+        assert 0 <= idx < self.capacity
+        return self.tree[self.capacity + idx]
+
+    def retrieve(self, upperbound):  # segment_tree.py:136-156
+        assert 0 <= upperbound <= self.operate() + 1e-5, f"upperbound: {upperbound}"
+        idx = 1
+        while idx < self.capacity:
+            left = 2 * idx
+            if self.tree[left] > upperbound:
+                idx = left
+            else:
+                upperbound -= self.tree[left]
+                idx = left + 1
+        return idx - self.capacity
+
+    def rebuild_from_leaves(self):
+        """Bulk construction (not in the reference): every internal node = op(children).
+        Yields exactly the tree the sequential root walks produce."""
+        t = self.tree
+        for i in range(self.capacity - 1, 0, -1):
+            t[i] = self.operation(t[2 * i], t[2 * i + 1])
+
+
+class PerOracle:
+    """PrioritizedReplayBuffer's tree logic without storage (replay_buffer.py:261-428)."""
+
+    def __init__(self, max_size: int, alpha: float = 0.6):
+        self.max_size = max_size
+        self.alpha = alpha
+        self.max_priority = 1.0  # :284
+        self.tree_ptr = 0
+        self.size = 0
+        cap = 1
+        while cap < max_size:  # :288-290
+            cap *= 2
+        self.sum_tree = SegTree(cap, "sum")
+        self.min_tree = SegTree(cap, "min")
+
+    def _update_priority(self, idx: int, priority: float):  # :311-329
+        assert 0 <= idx < self.max_size
+        pa = priority**self.alpha
+        self.sum_tree[idx] = pa
+        self.min_tree[idx] = pa
+        self.max_priority = max(self.max_priority, priority)
+
+    def add(self, n: int):  # :296-309
+        self.size = min(self.size + n, self.max_size)
+        for _ in range(n):
+            self._update_priority(self.tree_ptr, self.max_priority)
+            self.tree_ptr = (self.tree_ptr + 1) % self.max_size
+
+    def sample_proportional(self, batch_size: int, u) -> np.ndarray:  # :357-381
+        """``u[i]`` is the value ``torch.rand(1).item()`` returns for stratum i (fp32 widened)."""
+        indices = np.zeros(batch_size, dtype=np.int64)
+        total = self.sum_tree.operate()
+        segment = total / batch_size
+        for i in range(batch_size):
+            a = segment * i
+            b = segment * (i + 1)
+            upperbound = float(u[i]) * (b - a) + a
+            indices[i] = self.sum_tree.retrieve(upperbound)
+        return indices
+
+    def calculate_weights(self, indices, beta: float) -> np.ndarray:  # :383-409
+        w = np.zeros(len(indices), dtype=np.float32)
+        p_min = self.min_tree.operate() / self.sum_tree.operate()
+        max_weight = (p_min * self.size) ** -beta
+        for i, idx in enumerate(indices):
+            p_sample = self.sum_tree[int(idx)] / self.sum_tree.operate()
+            weight = (p_sample * self.size) ** -beta
+            w[i] = weight / max_weight
+        return w
+
+    def update_priorities(self, indices, priorities):  # :411-428
+        for idx, p in zip(indices, priorities):
+            self._update_priority(int(idx), max(float(p), 1e-5))
+
+
+# ---------------------------------------------------------------------------------------------
+# ring buffer — replay_buffer.py:72-131
+# ---------------------------------------------------------------------------------------------
+
+
+def ring_insert(storage: dict, data: dict, cursor: int, max_size: int) -> int:
+    """ReplayBuffer.add's circular write (:99-110). ``storage[k]`` is [max_size, ...] numpy."""
+    n = next(iter(data.values())).shape[0]
+    end = cursor + n
+    for k, v in data.items():
+        if end > max_size:
+            first = max_size - cursor
+            storage[k][cursor:] = v[:first]
+            storage[k][: n - first] = v[first:]
+        else:
+            storage[k][cursor:end] = v
+    return end % max_size
+
+
+def gather(storage: dict, idx) -> dict:
+    """``storage[indices]`` (:126,:204,:345)."""
+    return {k: v[np.asarray(idx)] for k, v in storage.items()}
+
+
+def randperm_prefix(raw, batch: int, n: int) -> np.ndarray:
+    """First ``batch`` entries of torch.randperm(n) given the raw mt19937 draws it consumes
+    (replay_buffer.py:125; ATen randperm_cpu: ``z = random() % (n - i); swap(p[i], p[i+z])``)."""
+    disp: dict[int, int] = {}
+    out = np.empty(batch, dtype=np.int64)
+    for i in range(batch):
+        if i >= n - 1:  # the loop stops at n-2; the last element stays in place
+            out[i] = disp.get(i, i)
+            continue
+        j = i + int(raw[i]) % (n - i)
+        vi = disp.get(i, i)
+        vj = disp.get(j, j)
+        out[i] = vj
+        disp[j] = vi
+        disp[i] = vj
+    return out
+
+
+def mt19937_raw(seed: int, count: int) -> np.ndarray:
+    """Raw 32-bit outputs of mt19937 seeded like torch.manual_seed(seed)."""
+    rs = np.random.RandomState(seed & 0xFFFFFFFF)
+    return np.frombuffer(rs.bytes(4 * count), dtype="<u4").copy()
+
+
+def torch_rand_from_raw(raw) -> np.ndarray:
+    """torch.rand fp32 values from raw draws: (x & (2^24-1)) * 2^-24."""
+    return ((np.asarray(raw, dtype=np.uint32) & np.uint32(0xFFFFFF)).astype(np.float32)
+            * np.float32(2.0**-24))
+
+
+# ---------------------------------------------------------------------------------------------
+# n-step fold — replay_buffer.py:206-258
+# ---------------------------------------------------------------------------------------------
+
+
+def nstep_fold(steps: list[dict], gamma: float, reward_key="reward", done_key="done",
+               ns_key="next_obs") -> dict:
+    """``steps`` = the deque contents, oldest first; values are numpy arrays [N, ...]."""
+    first = {k: v.copy() for k, v in steps[0].items()}
+    R = first[reward_key].copy()
+    for i, tr in enumerate(steps[1:]):
+        # fp32 tensor * Python float: the scalar is taken in fp32, product then sum (:244)
+        R += tr[reward_key] * np.float32(gamma ** (i + 1))
+        first[ns_key] = tr[ns_key].copy()
+        first[done_key] = tr[done_key].copy()
+        if tr[done_key].astype(bool).any():  # :252
+            break
+    first[reward_key] = R
+    return first
+
+
+# ---------------------------------------------------------------------------------------------
+# rollout returns — rollout_buffer.py:413-481
+# ---------------------------------------------------------------------------------------------
+
+
+def gae(rewards, values, dones, last_value, last_done, gamma: float, gae_lambda: float):
+    """GAE branch (:448-467). rewards/values fp32 [T,N], dones bool [T,N]."""
+    T, N = rewards.shape
+    last_value = np.asarray(last_value).reshape(N)
+    last_done = np.asarray(last_done).reshape(N)
+    adv = np.zeros((T, N), dtype=np.float32)
+    last_gae_lambda = np.zeros(N, dtype=np.float32)
+    for t in reversed(range(T)):
+        if t == T - 1:
+            next_non_terminal = 1.0 - last_done.astype(float)
+            next_values = last_value.astype(float)
+        else:
+            next_non_terminal = 1.0 - dones[t + 1].astype(float)
+            next_values = values[t + 1]
+        delta = rewards[t] + gamma * next_values * next_non_terminal - values[t]
+        adv[t] = last_gae_lambda = (
+            delta + gamma * gae_lambda * next_non_terminal * last_gae_lambda
+        )
+    ret = adv + values
+    return adv, ret
+
+
+def mc_returns(rewards, values, dones, last_value, last_done, gamma: float):
+    """Monte-Carlo branch (:468-477)."""
+    T, N = rewards.shape
+    last_value = np.asarray(last_value).reshape(N)
+    last_done = np.asarray(last_done).reshape(N)
+    ret = np.zeros((T, N), dtype=np.float32)
+    last_returns = last_value.astype(float) * (1.0 - last_done.astype(float))
+    for t in reversed(range(T)):
+        ret[t] = last_returns = rewards[t] + gamma * last_returns * (1.0 - dones[t].astype(float))
+    adv = ret - values
+    return adv, ret
+
+
+def gae_scalar(rewards, values, dones, last_value, last_done, gamma: float, gae_lambda: float):
+    """Explicit per-element restatement of the rounding sequence; used to pin
+    the semantics the CUDA kernel implements against the vectorised numpy form above."""
+    T, N = rewards.shape
+    adv = np.zeros((T, N), dtype=np.float32)
+    g32 = np.float32(gamma)
+    gl = gamma * gae_lambda
+    for e in range(N):
+        carry = 0.0
+        for t in reversed(range(T)):
+            if t == T - 1:
+                nnt = 1.0 - float(last_done[e])
+                g_nv = gamma * float(last_value[e])
+            else:
+                nnt = 1.0 - float(bool(dones[t + 1, e]))
+                g_nv = float(np.float32(g32 * values[t + 1, e]))
+            delta = (float(rewards[t, e]) + g_nv * nnt) - float(values[t, e])
+            carry = delta + (gl * nnt) * carry
+            adv[t, e] = np.float32(carry)
+    return adv, adv + values
+
+
+def pow_cpython(x: float, y: float) -> float:
+    """float ** float in CPython = libm pow (replay_buffer.py:322,401,406)."""
+    return math.pow(x, y)

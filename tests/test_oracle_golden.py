@@ -1,0 +1,205 @@
+"""Pins the oracle (oracle/xp_oracle.py) to the reference: golden vectors generated from the
+unmodified reference code (oracle/make_golden.py) and the reference's own known-answer tests
+(tests/test_components/test_segment_tree.py, test_replay_buffer.py in the AgileRL tree)."""
+
+import numpy as np
+import pytest
+
+from conftest import load_golden
+from oracle import xp_oracle as xo
+
+
+# ---- GAE / MC ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_gae_matches_reference_bitwise(seed):
+    g = load_golden(f"gae_s{seed}")
+    adv, ret = xo.gae(g["rewards"], g["values"], g["dones"], g["last_value"], g["last_done"],
+                      float(g["gamma"]), float(g["gae_lambda"]))
+    assert np.array_equal(adv, g["adv"]) and np.array_equal(ret, g["ret"])
+    adv, ret = xo.mc_returns(g["rewards"], g["values"], g["dones"], g["last_value"],
+                             g["last_done"], float(g["gamma"]))
+    assert np.array_equal(adv, g["adv_mc"]) and np.array_equal(ret, g["ret_mc"])
+
+
+@pytest.mark.parametrize("seed", [0, 2])
+def test_gae_scalar_restatement_is_the_same_rounding_sequence(seed):
+    g = load_golden(f"gae_s{seed}")
+    adv, ret = xo.gae_scalar(g["rewards"], g["values"], g["dones"], g["last_value"].astype(float),
+                             g["last_done"].astype(float), float(g["gamma"]), float(g["gae_lambda"]))
+    assert np.array_equal(adv, g["adv"]) and np.array_equal(ret, g["ret"])
+
+
+# ---- segment tree KATs (reference tests/test_components/test_segment_tree.py:39-129) -----------
+def test_tree_set_and_sum_kat():
+    t = xo.SegTree(4, "sum")
+    t[2] = 1.0
+    t[3] = 3.0
+    assert np.isclose(t.operate(), 4.0)
+    assert np.isclose(t.operate(0, 2), 0.0)
+    assert np.isclose(t.operate(0, 3), 1.0)
+    assert np.isclose(t.operate(2, 3), 1.0)
+    assert np.isclose(t.operate(2, -1), 1.0)
+    assert np.isclose(t.operate(2, 4), 4.0)
+
+
+def test_tree_set_overlap_kat():
+    t = xo.SegTree(4, "sum")
+    t[2] = 1.0
+    t[2] = 3.0
+    assert np.isclose(t.operate(), 3.0)
+    assert np.isclose(t.operate(2, 3), 3.0)
+    assert np.isclose(t.operate(2, -1), 3.0)
+    assert np.isclose(t.operate(2, 4), 3.0)
+    assert np.isclose(t.operate(1, 2), 0.0)
+
+
+def test_prefixsum_idx_kat():
+    t = xo.SegTree(4, "sum")
+    t[2] = 1.0
+    t[3] = 3.0
+    assert t.retrieve(0.0) == 2
+    assert t.retrieve(0.5) == 2
+    assert t.retrieve(0.99) == 2
+    assert t.retrieve(1.01) == 3
+    assert t.retrieve(3.00) == 3
+    assert t.retrieve(4.00) == 3
+
+
+def test_prefixsum_idx2_kat():
+    t = xo.SegTree(4, "sum")
+    t[0] = 0.5
+    t[1] = 1.0
+    t[2] = 1.0
+    t[3] = 3.0
+    assert t.retrieve(0.00) == 0
+    assert t.retrieve(0.55) == 1
+    assert t.retrieve(0.99) == 1
+    assert t.retrieve(1.51) == 2
+    assert t.retrieve(3.00) == 3
+    assert t.retrieve(5.50) == 3
+
+
+def test_max_interval_tree_kat():
+    t = xo.SegTree(4, "min")
+    t[0] = 1.0
+    t[2] = 0.5
+    t[3] = 3.0
+    assert np.isclose(t.operate(), 0.5)
+    assert np.isclose(t.operate(0, 2), 1.0)
+    assert np.isclose(t.operate(0, 3), 0.5)
+    assert np.isclose(t.operate(0, -1), 0.5)
+    assert np.isclose(t.operate(2, 4), 0.5)
+    assert np.isclose(t.operate(3, 4), 3.0)
+    t[2] = 0.7
+    assert np.isclose(t.operate(), 0.7)
+    assert np.isclose(t.operate(0, 2), 1.0)
+    assert np.isclose(t.operate(0, 3), 0.7)
+    t[2] = 4.0
+    assert np.isclose(t.operate(), 1.0)
+    assert np.isclose(t.operate(0, 2), 1.0)
+    assert np.isclose(t.operate(2, 3), 4.0)
+    assert np.isclose(t.operate(2, -1), 4.0)
+    assert np.isclose(t.operate(3, 4), 3.0)
+
+
+def test_non_pow2_capacity_asserts():
+    with pytest.raises(AssertionError):
+        xo.SegTree(6, "sum")
+
+
+# ---- PER scenario ------------------------------------------------------------------------------
+def replay_per_scenario(per, g):
+    """Drives any PER-like object (oracle or engine adapter) through the golden scenario."""
+    n_added = 0
+    for step, n in enumerate(g["add_sizes"], start=1):
+        per.add(int(n))
+        n_added += int(n)
+        if step == 3:
+            assert n_added == int(g["early_at"])
+            per.update_priorities(g["early_idx"], g["early_prio"])
+    per.update_priorities(g["upd_idx"], g["upd_prio"])
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_per_oracle_matches_reference(seed):
+    g = load_golden(f"per_s{seed}")
+    per = xo.PerOracle(int(g["max_size"]), float(g["alpha"]))
+    replay_per_scenario(per, g)
+    assert per.tree_ptr == int(g["tree_ptr"]) and per.size == int(g["size"])
+    assert np.array_equal(np.array(per.sum_tree.tree), g["sum_tree_after_update"])
+    assert np.array_equal(np.array(per.min_tree.tree), g["min_tree_after_update"])
+    assert per.max_priority == float(g["max_priority"])
+    idx = per.sample_proportional(len(g["u"]), g["u"])
+    assert np.array_equal(idx, g["sample_idx"])
+    w = per.calculate_weights(idx, float(g["beta"]))
+    assert np.array_equal(w, g["weights"])
+
+
+def test_bulk_rebuild_equals_sequential_sets():
+    rng = np.random.default_rng(0)
+    a, b = xo.SegTree(64, "sum"), xo.SegTree(64, "sum")
+    vals = rng.random(64)
+    for i in rng.permutation(64):
+        a[int(i)] = float(vals[i])
+    for i in range(64):
+        b.tree[64 + i] = float(vals[i])
+    b.rebuild_from_leaves()
+    assert a.tree == b.tree
+
+
+# ---- ring + n-step ------------------------------------------------------------------------------
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_ring_and_nstep_oracle_match_reference(seed):
+    g = load_golden(f"ring_nstep_s{seed}")
+    max_size, N, n_step = int(g["max_size"]), int(g["N"]), int(g["n_step"])
+    keys = ["obs", "action", "reward", "next_obs", "done"]
+
+    def step_dict(s):
+        d = {k: g[k][s] for k in keys}
+        return {k: (v.reshape(N, 1) if v.ndim == 1 else v) for k, v in d.items()}
+
+    ring = {k: np.zeros_like(g[f"ring_{k}"]) for k in keys}
+    nst = {k: np.zeros_like(g[f"nstep_{k}"]) for k in keys}
+    cur = ncur = 0
+    window = []
+    for s in range(g["obs"].shape[0]):
+        d = step_dict(s)
+        cur = xo.ring_insert(ring, d, cur, max_size)
+        window.append(d)
+        window = window[-n_step:]
+        assert (len(window) < n_step) == bool(g["returned_none"][s])
+        if len(window) == n_step:
+            ncur = xo.ring_insert(nst, xo.nstep_fold(window, float(g["gamma"])), ncur, max_size)
+    assert cur == int(g["ring_cursor"]) and ncur == int(g["nstep_cursor"])
+    for k in keys:
+        assert np.array_equal(ring[k], g[f"ring_{k}"]), k
+        assert np.array_equal(nst[k], g[f"nstep_{k}"]), k
+
+
+def test_nstep_reward_kat():
+    # reference tests/test_components/test_replay_buffer.py:532-569: 1 + 0.9*2 + 0.81*3
+    steps = [{"reward": np.array([[r]], np.float32), "done": np.zeros((1, 1), np.float32),
+              "next_obs": np.full((1, 2), r, np.float32)} for r in (1.0, 2.0, 3.0)]
+    out = xo.nstep_fold(steps, 0.9)
+    assert np.isclose(out["reward"][0, 0], 1.0 + 0.9 * 2.0 + 0.81 * 3.0)
+    assert np.array_equal(out["next_obs"], steps[2]["next_obs"])
+    # early termination (:571-628): done at the second transition stops the fold there
+    steps[1]["done"][:] = 1.0
+    out = xo.nstep_fold(steps, 0.9)
+    assert np.isclose(out["reward"][0, 0], 1.0 + 0.9 * 2.0)
+    assert np.array_equal(out["next_obs"], steps[1]["next_obs"]) and out["done"][0, 0] == 1.0
+
+
+# ---- host RNG streams ---------------------------------------------------------------------------
+def test_mt19937_stream_is_torch_rand():
+    g = load_golden("torch_rng")
+    for seed in (0, 1, 123456789):
+        raw = xo.mt19937_raw(seed, 700)
+        assert np.array_equal(xo.torch_rand_from_raw(raw), g[f"rand_{seed}"])
+
+
+def test_randperm_prefix_is_torch_randperm():
+    g = load_golden("torch_rng")
+    for k, (seed, n, B) in enumerate(g["cases"]):
+        raw = xo.mt19937_raw(int(seed), int(B))
+        assert np.array_equal(xo.randperm_prefix(raw, int(B), int(n)), g[f"perm_{k}"]), (seed, n, B)
