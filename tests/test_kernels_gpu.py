@@ -1,0 +1,392 @@
+"""Kernel-level parity (through the C-ABI) against the oracle and the committed golden vectors.
+
+Bars: integer / index / tree work bit-exact; GAE and n-step bit-exact (stricter than the 1e-6
+relative the north star asks); IS weights bit-exact in fp32 (device pow is the glibc algorithm)."""
+
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import xp_oracle as xo
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def xp(cuda_device):
+    from agilerl_b200 import xp as _xp
+
+    return _xp
+
+
+def dev(a, device, dtype=None):
+    t = torch.as_tensor(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.to(device).contiguous()
+
+
+# ---- GAE ----------------------------------------------------------------------------------------
+def run_gae(xp, device, r, v, d, lv, ld, gamma, lam, use_gae=True):
+    """r, v, d: [P,T,N] numpy; lv, ld: [P,N]."""
+    P, T, N = r.shape
+    R, V, D = dev(r, device), dev(v, device), dev(d, device, torch.bool)
+    LV, LD = dev(lv, device, torch.float64), dev(ld, device, torch.float64)
+    A, G = torch.full_like(R, float("nan")), torch.full_like(R, float("nan"))
+    xp.gae(R, V, D, LV, LD, A, G, T, N, P, T * N, gamma, lam, use_gae)
+    torch.cuda.synchronize()
+    return A.cpu().numpy(), G.cpu().numpy()
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_gae_golden_bitwise(xp, cuda_device, seed):
+    g = load_golden(f"gae_s{seed}")
+    args = (g["rewards"][None], g["values"][None], g["dones"][None], g["last_value"][None],
+            g["last_done"][None], float(g["gamma"]), float(g["gae_lambda"]))
+    adv, ret = run_gae(xp, cuda_device, *args)
+    assert np.array_equal(adv[0], g["adv"]) and np.array_equal(ret[0], g["ret"])
+    adv, ret = run_gae(xp, cuda_device, *args, use_gae=False)
+    assert np.array_equal(adv[0], g["adv_mc"]) and np.array_equal(ret[0], g["ret_mc"])
+
+
+@pytest.mark.parametrize("shape", [(3, 50, 96), (2, 1, 32), (1, 7, 1), (4, 130, 64), (2, 33, 40)])
+@pytest.mark.parametrize("use_gae", [True, False])
+def test_gae_population_vs_oracle(xp, cuda_device, shape, use_gae):
+    P, T, N = shape
+    rng = np.random.default_rng(P * 1000 + T)
+    r = rng.standard_normal((P, T, N)).astype(np.float32)
+    v = rng.standard_normal((P, T, N)).astype(np.float32)
+    d = rng.random((P, T, N)) < 0.05
+    lv = rng.standard_normal((P, N)).astype(np.float32)
+    ld = rng.random((P, N)) < 0.1
+    adv, ret = run_gae(xp, cuda_device, r, v, d, lv, ld, 0.99, 0.95, use_gae)
+    for p in range(P):
+        if use_gae:
+            a, g = xo.gae(r[p], v[p], d[p], lv[p], ld[p], 0.99, 0.95)
+        else:
+            a, g = xo.mc_returns(r[p], v[p], d[p], lv[p], ld[p], 0.99)
+        assert np.array_equal(adv[p], a) and np.array_equal(ret[p], g)
+
+
+def test_gae_empty_is_noop(xp, cuda_device):
+    z = torch.empty(0, device=cuda_device)
+    zd = torch.empty(0, device=cuda_device, dtype=torch.float64)
+    xp.gae(z, z, z.bool(), zd, zd, z, z, 0, 4, 1, 0, 0.99, 0.95)
+
+
+def test_gae_full_size_properties(xp, cuda_device):
+    """C3 size (1024 envs x 128 steps x 16 agents): linearity-free properties that hold exactly:
+    with gamma = 0 the advantage is r - v; with done everywhere episodes do not leak."""
+    P, T, N = 16, 128, 1024
+    g = torch.Generator(device="cpu").manual_seed(0)
+    r = torch.randn(P, T, N, generator=g).numpy()
+    v = torch.randn(P, T, N, generator=g).numpy()
+    d = np.ones((P, T, N), dtype=bool)
+    lv = torch.randn(P, N, generator=g).numpy()
+    ld = np.ones((P, N), dtype=bool)
+    adv, ret = run_gae(xp, cuda_device, r, v, d, lv, ld, 0.99, 0.95)
+    assert np.array_equal(adv, (r.astype(np.float64) - v.astype(np.float64)).astype(np.float32))
+    # and one agent against the oracle at the full size
+    d = np.random.default_rng(1).random((P, T, N)) < 0.02
+    ld = np.zeros((P, N), dtype=bool)
+    adv, ret = run_gae(xp, cuda_device, r, v, d, lv, ld, 0.99, 0.95)
+    a, g2 = xo.gae(r[5], v[5], d[5], lv[5], ld[5], 0.99, 0.95)
+    assert np.array_equal(adv[5], a) and np.array_equal(ret[5], g2)
+
+
+# ---- trees --------------------------------------------------------------------------------------
+class DevTree:
+    """(sum,min) interleaved device tree driven through the C-ABI."""
+
+    def __init__(self, xp, device, cap, interleaved=True):
+        self.xp, self.device, self.cap = xp, device, cap
+        if interleaved:
+            self.nodes = torch.empty(2 * cap, 2, dtype=torch.float64, device=device)
+            self.sum, self.min, self.stride = self.nodes[:, 0], self.nodes[:, 1], 2
+        else:
+            self.sum = torch.empty(2 * cap, dtype=torch.float64, device=device)
+            self.min = torch.empty(2 * cap, dtype=torch.float64, device=device)
+            self.stride = 1
+        self.aux = torch.ones(2 * cap, dtype=torch.int32, device=device)  # init must zero it
+        self.t = xp.make_tree(self.sum, self.min, self.stride, cap, self.aux)
+        xp.tree_init(self.t, torch.cuda.current_stream(device).cuda_stream)
+        self.err = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def set(self, idx, val):
+        self.xp.tree_set_batch(self.t, dev(idx, self.device, torch.int64),
+                               dev(val, self.device, torch.float64), self.err)
+
+    def query(self, start=0, end=0):
+        out = torch.zeros(2, dtype=torch.float64, device=self.device)
+        self.xp.tree_query(self.t, start, end, out)
+        return out.cpu().numpy()
+
+    def arrays(self):
+        torch.cuda.synchronize()
+        return self.sum.cpu().numpy().copy(), self.min.cpu().numpy().copy()
+
+
+def test_tree_kats(xp, cuda_device):
+    # reference tests/test_components/test_segment_tree.py:39-129
+    t = DevTree(xp, cuda_device, 4)
+    t.set([2, 3], [1.0, 3.0])
+    assert t.query()[0] == 4.0 and t.query(0, 2)[0] == 0.0 and t.query(0, 3)[0] == 1.0
+    assert t.query(2, 3)[0] == 1.0 and t.query(2, -1)[0] == 1.0 and t.query(2, 4)[0] == 4.0
+    r = xp.tree_retrieve(t.t, dev([0.0, 0.5, 0.99, 1.01, 3.0, 4.0], cuda_device, torch.float64))
+    assert r.cpu().tolist() == [2, 2, 2, 3, 3, 3]
+    t.set([2, 2], [1.0, 3.0])  # overwrite inside one batch: last writer wins
+    assert t.query()[0] == 6.0 and t.query(2, 3)[0] == 3.0 and t.query(1, 2)[0] == 0.0
+    m = DevTree(xp, cuda_device, 4)
+    m.set([0, 2, 3], [1.0, 0.5, 3.0])
+    assert m.query()[1] == 0.5 and m.query(0, 2)[1] == 1.0 and m.query(3, 4)[1] == 3.0
+    m.set([2], [4.0])
+    assert m.query()[1] == 1.0 and m.query(2, 3)[1] == 4.0 and m.query(2, -1)[1] == 4.0
+
+
+def test_tree_non_pow2_capacity_is_assertion(xp, cuda_device):
+    bad = xp.make_tree(torch.zeros(12, dtype=torch.float64, device=cuda_device), None, 1, 6, None)
+    with pytest.raises(AssertionError):
+        xp.tree_init(bad, 0)
+
+
+@pytest.mark.parametrize("cap,B,interleaved", [(1, 3, True), (2, 5, False), (64, 40, True),
+                                               (4096, 256, True), (4096, 5000, False), (1 << 16, 20000, True)])
+def test_tree_set_batch_equals_sequential_reference(xp, cuda_device, cap, B, interleaved):
+    rng = np.random.default_rng(cap + B)
+    t = DevTree(xp, cuda_device, cap, interleaved)
+    s, m = xo.SegTree(cap, "sum"), xo.SegTree(cap, "min")
+    for rnd in range(3):
+        idx = rng.integers(0, cap, B)
+        if B > 4:
+            idx[B // 2:] = idx[: B - B // 2]  # forced duplicates
+        val = rng.random(B) * 10.0 + 1e-3
+        t.set(idx, val)
+        for i, x in zip(idx, val):
+            s[int(i)] = float(x)
+            m[int(i)] = float(x)
+        ds, dm = t.arrays()
+        assert np.array_equal(ds, np.array(s.tree)) and np.array_equal(dm, np.array(m.tree))
+        assert int(t.aux.abs().sum()) == 0  # scratch returned to zero
+    # descents: bit-exact indices for random upper bounds, incl. both ends
+    total = s.operate()
+    ub = np.concatenate([rng.random(512) * total, [0.0, total]])
+    got = xp.tree_retrieve(t.t, dev(ub, cuda_device, torch.float64)).cpu().numpy()
+    assert np.array_equal(got, np.array([s.retrieve(float(x)) for x in ub]))
+    # range queries in the reference's association order
+    for _ in range(10):
+        a, b = sorted(rng.integers(0, cap + 1, 2))
+        if a == b:
+            continue
+        q = t.query(int(a), int(b))
+        assert q[0] == s.operate(int(a), int(b)) and q[1] == m.operate(int(a), int(b))
+
+
+def test_tree_set_out_of_range_flags(xp, cuda_device):
+    t = DevTree(xp, cuda_device, 8)
+    t.set([1, 8, -1], [1.0, 2.0, 3.0])
+    torch.cuda.synchronize()
+    assert int(t.err.item()) == 1
+    assert t.query()[0] == 1.0
+
+
+# ---- PER ----------------------------------------------------------------------------------------
+class DevPer:
+    def __init__(self, xp, device, max_size, alpha):
+        cap = 1
+        while cap < max_size:
+            cap *= 2
+        self.tree = DevTree(xp, device, cap)
+        self.xp, self.device, self.max_size, self.alpha = xp, device, max_size, alpha
+        self.state = torch.ones(1, dtype=torch.float64, device=device)  # max_priority = 1.0
+        self.tree_ptr = 0
+        self.size = 0
+
+    def add(self, n):
+        self.xp.per_add(self.tree.t, self.state, self.tree_ptr, n, self.max_size, self.alpha)
+        self.tree_ptr = (self.tree_ptr + n) % self.max_size
+        self.size = min(self.size + n, self.max_size)
+
+    def update_priorities(self, idx, prio):
+        self.xp.per_update(self.tree.t, self.state, dev(idx, self.device, torch.int64),
+                           dev(prio, self.device, torch.float32), self.max_size, self.alpha,
+                           self.tree.err)
+
+    def sample(self, u, beta, P=1):
+        B = len(u) // P
+        idx = torch.empty(len(u), dtype=torch.int64, device=self.device)
+        w = torch.empty(len(u), dtype=torch.float32, device=self.device)
+        self.xp.per_sample(self.tree.t, dev(u, self.device, torch.float32), B, P, self.size, beta, idx, w)
+        return idx.cpu().numpy(), w.cpu().numpy()
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_per_scenario_golden_bitwise(xp, cuda_device, seed):
+    from test_oracle_golden import replay_per_scenario
+
+    g = load_golden(f"per_s{seed}")
+    per = DevPer(xp, cuda_device, int(g["max_size"]), float(g["alpha"]))
+    replay_per_scenario(per, g)
+    assert per.tree_ptr == int(g["tree_ptr"]) and per.size == int(g["size"])
+    s, m = per.tree.arrays()
+    assert np.array_equal(s, g["sum_tree_after_update"])
+    assert np.array_equal(m, g["min_tree_after_update"])
+    assert float(per.state.item()) == float(g["max_priority"])
+    idx, w = per.sample(g["u"], float(g["beta"]))
+    assert np.array_equal(idx, g["sample_idx"])
+    assert np.array_equal(w, g["weights"])
+    w2 = torch.empty(len(idx), dtype=torch.float32, device=cuda_device)
+    xp.per_weights(per.tree.t, dev(idx, cuda_device), per.size, float(g["beta"]), w2)
+    assert np.array_equal(w2.cpu().numpy(), g["weights"])
+    assert int(per.tree.err.item()) == 0
+
+
+def test_per_population_batch_vs_oracle(xp, cuda_device):
+    """P agents x B strata in one launch == P sequential reference calls; cap 2^16."""
+    max_size, alpha, B, P = 50000, 0.6, 512, 4
+    rng = np.random.default_rng(3)
+    per = DevPer(xp, cuda_device, max_size, alpha)
+    ora = xo.PerOracle(max_size, alpha)
+    per.add(max_size)
+    # oracle: direct leaf fill + bottom-up pass (sequential adds at 50k leaves take too long)
+    ora.size, ora.tree_ptr = max_size, 0
+    for i in range(max_size):
+        ora.sum_tree.tree[ora.sum_tree.capacity + i] = 1.0
+        ora.min_tree.tree[ora.min_tree.capacity + i] = 1.0
+    ora.sum_tree.rebuild_from_leaves()
+    ora.min_tree.rebuild_from_leaves()
+    for _ in range(2):
+        idx = rng.integers(0, max_size, 4000)
+        pr = (np.abs(rng.standard_normal(4000)) + 1e-6).astype(np.float32)
+        per.update_priorities(idx, pr)
+        ora.update_priorities(idx, pr)
+    s, m = per.tree.arrays()
+    assert np.array_equal(s, np.array(ora.sum_tree.tree)) and np.array_equal(m, np.array(ora.min_tree.tree))
+    assert float(per.state.item()) == ora.max_priority
+    u = rng.random(P * B).astype(np.float32)
+    idx, w = per.sample(u, 0.4, P)
+    for p in range(P):
+        oi = ora.sample_proportional(B, u[p * B:(p + 1) * B])
+        assert np.array_equal(idx[p * B:(p + 1) * B], oi)
+        assert np.array_equal(w[p * B:(p + 1) * B], ora.calculate_weights(oi, 0.4))
+
+
+def test_pow_is_cpython_pow(xp, cuda_device):
+    rng = np.random.default_rng(0)
+    x = np.concatenate([np.maximum(np.abs(rng.standard_normal(200000)), 1e-5),
+                        rng.random(100000) * 1e-3, np.exp(rng.uniform(-30, 30, 100000)),
+                        [1.0, 1e-5, 0.5, 2.0, 1e-300, 1e300]])
+    for y in (0.6, -0.4, 0.5, 1.0, 0.0, -1.0, 0.25):
+        got = xp.pow_batch(dev(x, cuda_device, torch.float64), y).cpu().numpy()
+        want = np.array([math.pow(float(a), y) for a in x])
+        assert np.array_equal(got, want), y
+
+
+# ---- ring / gather / n-step -----------------------------------------------------------------------
+KEYS = ["obs", "action", "reward", "next_obs", "done"]
+
+
+def step_tensors(g, s, N, device):
+    out = {}
+    for k in KEYS:
+        v = g[k][s]
+        out[k] = dev(v.reshape(N, 1) if v.ndim == 1 else v, device)
+    return out
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_ring_and_nstep_golden(xp, cuda_device, seed):
+    g = load_golden(f"ring_nstep_s{seed}")
+    max_size, N, n_step, gamma = int(g["max_size"]), int(g["N"]), int(g["n_step"]), float(g["gamma"])
+    ring = {k: torch.zeros_like(dev(g[f"ring_{k}"], cuda_device)) for k in KEYS}
+    nst = {k: torch.zeros_like(dev(g[f"nstep_{k}"], cuda_device)) for k in KEYS}
+    stage = {k: torch.zeros(n_step * N, *ring[k].shape[1:], dtype=ring[k].dtype, device=cuda_device) for k in KEYS}
+    roles = [0, 0, 2, 1, 1]  # obs, action FIRST; reward fold; next_obs, done LAST
+    gpow = [float(np.float32(gamma**i)) for i in range(n_step)]
+    cur = ncur = count = 0
+    for s in range(g["obs"].shape[0]):
+        d = step_tensors(g, s, N, cuda_device)
+        xp.ring_insert([(d[k], ring[k]) for k in KEYS], N, cur, max_size)
+        cur = (cur + N) % max_size
+        slot = count % n_step
+        xp.ring_insert([(d[k], stage[k]) for k in KEYS], N, slot * N, n_step * N)
+        count += 1
+        if count >= n_step:
+            xp.nstep_fold_insert([(stage[k], nst[k]) for k in KEYS], roles, 4, 4, n_step,
+                                 count % n_step, gpow, N, ncur, max_size)
+            ncur = (ncur + N) % max_size
+    torch.cuda.synchronize()
+    assert cur == int(g["ring_cursor"]) and ncur == int(g["nstep_cursor"])
+    for k in KEYS:
+        assert np.array_equal(ring[k].cpu().numpy(), g[f"ring_{k}"]), k
+        assert np.array_equal(nst[k].cpu().numpy(), g[f"nstep_{k}"]), k
+
+
+@pytest.mark.parametrize("row_shape,dtype", [((84, 84, 4), torch.uint8), ((376,), torch.float32),
+                                            ((1,), torch.float32), ((3,), torch.uint8),
+                                            ((5,), torch.int16), ((7,), torch.float64), ((1031,), torch.uint8)])
+def test_gather_and_insert_all_row_widths(xp, cuda_device, row_shape, dtype):
+    rows, B = 300, 77
+    g = torch.Generator(device="cpu").manual_seed(0)
+    src = torch.randint(0, 200, (rows, *row_shape), generator=g).to(dtype).to(cuda_device)
+    idx = torch.randint(0, rows, (B,), generator=g).to(cuda_device)
+    out = torch.empty(B, *row_shape, dtype=dtype, device=cuda_device)
+    err = torch.zeros(1, dtype=torch.int32, device=cuda_device)
+    xp.gather([(src, out)], idx, rows, err)
+    assert torch.equal(out, src[idx]) and int(err.item()) == 0
+    # wrap-around insert: cursor near the end
+    store = torch.zeros(rows, *row_shape, dtype=dtype, device=cuda_device)
+    xp.ring_insert([(out, store)], B, rows - 10, rows)
+    want = torch.zeros_like(store)
+    want[rows - 10:] = out[:10]
+    want[: B - 10] = out[10:]
+    assert torch.equal(store, want)
+    # unaligned views (odd byte offsets) still move correctly
+    if dtype == torch.uint8 and len(row_shape) == 1:
+        flat = torch.randint(0, 255, (rows * row_shape[0] + 1,), generator=g).to(dtype).to(cuda_device)
+        usrc = flat[1:].view(rows, *row_shape)
+        xp.gather([(usrc, out)], idx, rows, err)
+        assert torch.equal(out, usrc[idx])
+
+
+def test_gather_out_of_range_flags_and_zeroes(xp, cuda_device):
+    src = torch.arange(40, dtype=torch.float32, device=cuda_device).view(10, 4)
+    idx = torch.tensor([0, 10, 3, -1], device=cuda_device)
+    out = torch.full((4, 4), 7.0, device=cuda_device)
+    err = torch.zeros(1, dtype=torch.int32, device=cuda_device)
+    xp.gather([(src, out)], idx, 10, err)
+    assert int(err.item()) == 1
+    assert torch.equal(out[0], src[0]) and torch.equal(out[2], src[3])
+    assert float(out[1].abs().sum()) == 0.0 and float(out[3].abs().sum()) == 0.0
+
+
+# ---- uniform sampling ---------------------------------------------------------------------------
+def test_randperm_prefix_golden(xp, cuda_device):
+    g = load_golden("torch_rng")
+    for k, (seed, n, B) in enumerate(g["cases"]):
+        raw = xo.mt19937_raw(int(seed), int(B)).view(np.int32)
+        got = xp.randperm_prefix(dev(raw, cuda_device), int(B), 1, int(n)).cpu().numpy()
+        assert np.array_equal(got, g[f"perm_{k}"]), (seed, n, B)
+
+
+def test_randperm_prefix_population_and_dense(xp, cuda_device):
+    rng = np.random.default_rng(0)
+    for n, B, P in [(4096, 4096, 3), (5000, 4096, 2), (10_000_000, 1024, 32), (16384, 16384, 1)]:
+        raw = rng.integers(0, 2**32, P * B, dtype=np.uint64).astype(np.uint32)
+        got = xp.randperm_prefix(dev(raw.view(np.int32), cuda_device), B, P, n).cpu().numpy()
+        for p in (0, P - 1):
+            want = xo.randperm_prefix(raw[p * B:(p + 1) * B], B, n)
+            assert np.array_equal(got[p * B:(p + 1) * B], want)
+            assert len(np.unique(got[p * B:(p + 1) * B])) == B  # without replacement
+
+
+def test_philox_is_deterministic_and_counter_based(xp, cuda_device):
+    a = xp.philox_u32(123, 0, 4096, cuda_device)
+    b = xp.philox_u32(123, 0, 4096, cuda_device)
+    c = xp.philox_u32(123, 256, 3072, cuda_device)  # 256 counters * 4 words = offset 1024
+    assert torch.equal(a, b) and torch.equal(a[1024:], c)
+    # Philox4x32-10 known answer (Random123 kat_vectors: ctr=0, key=0)
+    z = xp.philox_u32(0, 0, 4, cuda_device).cpu().numpy().view(np.uint32)
+    assert z.tolist() == [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]

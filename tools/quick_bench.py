@@ -1,0 +1,114 @@
+"""Developer micro-benchmarks (CUDA events, cold L2 via buffer rotation). Not the judged bench."""
+
+import sys
+import os
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from agilerl_b200 import xp  # noqa: E402
+
+dev = torch.device("cuda", 0)
+
+
+def timeit(fn, iters=50, warm=5):
+    for _ in range(warm):
+        fn(0)
+    torch.cuda.synchronize()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+    for i, (a, b) in enumerate(evs):
+        a.record()
+        fn(i)
+        b.record()
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) * 1e3 for a, b in evs)
+    return ts[len(ts) // 2], ts[0]
+
+
+def bench_gae(P=16, T=128, N=1024, sets=8):
+    bufs = []
+    for s in range(sets):
+        r = torch.randn(P, T, N, device=dev)
+        v = torch.randn(P, T, N, device=dev)
+        d = torch.rand(P, T, N, device=dev) < 0.02
+        lv = torch.randn(P, N, device=dev, dtype=torch.float64)
+        ld = torch.zeros(P, N, device=dev, dtype=torch.float64)
+        bufs.append((r, v, d, lv, ld, torch.empty_like(r), torch.empty_like(r)))
+
+    def fn(i):
+        r, v, d, lv, ld, a, g = bufs[i % sets]
+        xp.gae(r, v, d, lv, ld, a, g, T, N, P, T * N, 0.99, 0.95)
+
+    med, best = timeit(fn)
+    bytes_ = P * T * N * 17
+    print(f"GAE P={P} T={T} N={N}: median {med:.1f} us best {best:.1f} us -> {bytes_ / med / 1e3:.0f} GB/s "
+          f"({P * T * N / med / 1e3:.1f} G steps/s)")
+
+
+def bench_per(cap_log2=24, B=4096, P=64):
+    cap = 1 << cap_log2
+    nodes = torch.empty(2 * cap, 2, dtype=torch.float64, device=dev)
+    aux = torch.zeros(2 * cap, dtype=torch.int32, device=dev)
+    t = xp.make_tree(nodes[:, 0], nodes[:, 1], 2, cap, aux)
+    xp.tree_init(t, torch.cuda.current_stream().cuda_stream)
+    state = torch.ones(1, dtype=torch.float64, device=dev)
+    xp.per_add(t, state, 0, cap, cap, 0.6)
+    idx0 = torch.randint(0, cap, (1 << 22,), device=dev)
+    pr0 = torch.randn(1 << 22, device=dev).abs() + 1e-3
+    xp.per_update(t, state, idx0, pr0, cap, 0.6)
+    torch.cuda.synchronize()
+    u = [torch.rand(P * B, device=dev) for _ in range(4)]
+    pr = [torch.randn(P * B, device=dev).abs() + 1e-6 for _ in range(4)]
+    idx = torch.empty(P * B, dtype=torch.int64, device=dev)
+    w = torch.empty(P * B, dtype=torch.float32, device=dev)
+
+    def sample(i):
+        xp.per_sample(t, u[i % 4], B, P, cap, 0.4, idx, w)
+
+    def update(i):
+        xp.per_update(t, state, idx, pr[i % 4], cap, 0.6)
+
+    def both(i):
+        sample(i)
+        update(i)
+
+    for name, fn in (("sample", sample), ("update", update), ("sample+update", both)):
+        med, best = timeit(fn, iters=30)
+        print(f"PER cap=2^{cap_log2} B={B} P={P} {name}: median {med:.1f} us best {best:.1f} us -> "
+              f"{P * B / med:.1f} M samples/s")
+    L = cap_log2
+    alg = 8 * L + 12 + 12 + 12 + 2 * (8 + L * 24)
+    med, _ = timeit(both, iters=30)
+    print(f"  algorithmic {alg} B/sample -> {P * B * alg / med / 1e3:.0f} GB/s")
+
+
+def bench_gather(rows=200_000, row_shape=(84, 84, 4), dtype=torch.uint8, B=256, P=8):
+    if dtype == torch.uint8:
+        src = torch.randint(0, 255, (rows, *row_shape), device=dev, dtype=torch.uint8)
+    else:
+        src = torch.randn(rows, *row_shape, device=dev).to(dtype)
+    outs = [torch.empty(P * B, *src.shape[1:], dtype=src.dtype, device=dev) for _ in range(2)]
+    idxs = [torch.randint(0, rows, (P * B,), device=dev) for _ in range(8)]
+
+    def fn(i):
+        xp.gather([(src, outs[i % 2])], idxs[i % 8], rows)
+
+    med, best = timeit(fn)
+    rb = xp.row_bytes(src)
+    print(f"gather rows={rows} row_bytes={rb} B={P * B}: median {med:.1f} us best {best:.1f} us -> "
+          f"{2 * rb * P * B / med / 1e3:.0f} GB/s")
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["gae", "per", "gather"]
+    print(torch.cuda.get_device_name(0))
+    if "gae" in which:
+        bench_gae()
+        bench_gae(P=256)
+    if "per" in which:
+        bench_per(20, 256, 8)
+        bench_per(24, 4096, 64)
+    if "gather" in which:
+        bench_gather()
+        bench_gather(rows=2_000_000, row_shape=(376,), dtype=torch.float32, B=1024, P=32)
