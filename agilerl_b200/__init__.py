@@ -1,0 +1,28 @@
+"""agilerl_b200 — B200-native (sm_100a) experience-path engine with AgileRL's components API.
+
+``from agilerl_b200.components import ReplayBuffer, MultiStepReplayBuffer,
+PrioritizedReplayBuffer, RolloutBuffer, Sampler`` mirrors ``agilerl.components``;
+``agilerl_b200.install()`` swaps the classes into an importable ``agilerl`` package.
+The compute path is libb200xp.so (include/b200xp.h); there is no CPU fallback.
+"""
+
+__version__ = "0.1.0"
+
+
+def install() -> None:
+    """Monkey-patch ``agilerl.components`` so existing AgileRL code uses the B200 engine."""
+    import importlib
+
+    from . import components as c
+
+    mods = {
+        "agilerl.components": ("ReplayBuffer", "MultiStepReplayBuffer", "PrioritizedReplayBuffer"),
+        "agilerl.components.replay_buffer": ("ReplayBuffer", "MultiStepReplayBuffer", "PrioritizedReplayBuffer"),
+        "agilerl.components.segment_tree": ("SumSegmentTree", "MinSegmentTree"),
+        "agilerl.components.rollout_buffer": ("RolloutBuffer",),
+        "agilerl.components.sampler": ("Sampler",),
+    }
+    for name, symbols in mods.items():
+        mod = importlib.import_module(name)
+        for s in symbols:
+            setattr(mod, s, getattr(c, s))

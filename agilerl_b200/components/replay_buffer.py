@@ -1,0 +1,462 @@
+"""Device-resident replay buffers with the API of agilerl/components/replay_buffer.py.
+
+``ReplayBuffer`` / ``MultiStepReplayBuffer`` / ``PrioritizedReplayBuffer`` keep the reference's
+names, inheritance, constructor signatures, attributes and returned keys/shapes, so ``Sampler``'s
+``isinstance`` dispatch (sampler.py:71-72) and the training loops (train_off_policy.py:341-412)
+work unchanged.  Storage is struct-of-arrays in HBM; add / sample / n-step fold / priority
+update are CUDA kernels behind the C-ABI (include/b200xp.h).  There is no CPU path.
+
+Random draws ("identical uniform draws"): with ``rng="torch"`` (default) the buffers consume
+torch's global CPU mt19937 stream exactly where the reference does — ``torch.rand`` per stratum
+for PER (:377) and the raw draws of ``torch.randperm`` for uniform sampling (:125) — so a seeded
+run yields the reference's indices bit-for-bit.  ``rng="device"`` draws with Philox on the GPU.
+"""
+
+from __future__ import annotations
+
+from collections import deque
+from typing import Any
+
+import numpy as np
+import torch
+
+from .. import _native as nv
+from .. import xp
+from .rng import TorchCpuStream
+from .tensor_batch import TensorBatch, as_batch
+
+DataType = Any
+
+
+def _flatten(batch: TensorBatch, prefix=()) -> list[tuple[tuple, torch.Tensor]]:
+    out = []
+    for k, v in batch.items():
+        if isinstance(v, TensorBatch):
+            out.extend(_flatten(v, prefix + (k,)))
+        else:
+            out.append((prefix + (k,), v))
+    return out
+
+
+def _unflatten(leaves: dict[tuple, torch.Tensor], batch_size) -> TensorBatch:
+    root = TensorBatch({}, batch_size=batch_size)
+    for path, t in leaves.items():
+        node = root
+        for k in path[:-1]:
+            if k not in node:
+                node._d[k] = TensorBatch({}, batch_size=batch_size)
+            node = node._d[k]
+        node._d[path[-1]] = t
+    return root
+
+
+class ReplayBuffer:
+    """A circular replay buffer (reference: replay_buffer.py:12-138), stored on the GPU.
+
+    :param max_size: Maximum number of transitions to store
+    :param device: Device sampled batches are returned on (as in the reference).  Storage
+        lives on this device when it is a CUDA device, else on the current CUDA device.
+    :param dtype: kept for signature compatibility (the reference ignores it too)
+    :param rng: "torch" (reference's CPU mt19937 stream) or "device" (Philox on the GPU)
+    :param exact_rng_advance: also skip the ``size-1-batch`` draws torch.randperm would have
+        consumed, so that *subsequent* calls stay aligned with the reference (O(size) host work).
+    """
+
+    def __init__(self, max_size: int, device: str | torch.device = "cpu",
+                 dtype: torch.dtype = torch.float32, *, rng: str = "torch",
+                 exact_rng_advance: bool = False, seed: int = 0) -> None:
+        self.max_size = max_size
+        self.device = device
+        self.dtype = dtype
+        self.counter = 0
+        self.initialized = False
+
+        self._cursor = 0
+        self._size = 0
+        self._storage: TensorBatch | None = None
+        self._leaves: dict[tuple, torch.Tensor] = {}
+        self._sdev: torch.device | None = None
+        assert rng in ("torch", "device")
+        self.rng = rng
+        self.exact_rng_advance = exact_rng_advance
+        self._philox_seed = seed
+        self._philox_offset = 0
+        self._err: torch.Tensor | None = None
+
+    # -- properties (reference :39-58) ----------------------------------------------------------
+    @property
+    def storage(self) -> TensorBatch | None:
+        return self._storage
+
+    @property
+    def size(self) -> int:
+        return self._size
+
+    @size.setter
+    def size(self, value: int) -> None:
+        self._size = value
+
+    @property
+    def is_full(self) -> bool:
+        return len(self) == self.max_size
+
+    def __len__(self) -> int:
+        return self._size
+
+    @property
+    def storage_device(self) -> torch.device:
+        if self._sdev is None:
+            self._sdev = nv.require_cuda(self.device)
+        return self._sdev
+
+    def _out(self, batch: TensorBatch) -> TensorBatch:
+        """Move a sampled batch to ``self.device`` (no-op when that is the storage device)."""
+        dev = torch.device(self.device)
+        if dev.type == "cuda" and (dev.index is None or dev == self.storage_device):
+            return batch
+        return batch.to(dev)
+
+    # -- add (reference :60-112) ---------------------------------------------------------------
+    def _init(self, data: TensorBatch) -> None:
+        self._leaves = {}
+        for path, t in _flatten(data):
+            self._leaves[path] = torch.zeros((self.max_size, *t.shape[1:]), dtype=t.dtype,
+                                             device=self.storage_device)
+        self._storage = _unflatten(self._leaves, [self.max_size])
+        self._err = torch.zeros(1, dtype=torch.int32, device=self.storage_device)
+        self.initialized = True
+
+    def _prepare(self, data) -> tuple[TensorBatch, int]:
+        """``.to(device)`` and the 1-D -> (n,1) reshape of :79-94 (which mutates ``data``)."""
+        data = as_batch(data)
+        data = data.to(self.storage_device)
+        n = data.shape[0]
+        for key, item in list(data.items()):
+            if isinstance(item, TensorBatch):
+                for k, v in list(item.items()):
+                    if v.ndim == 1:
+                        item[k] = v.reshape(n, 1)
+            elif item.ndim == 1:
+                item = item.reshape(n, 1)
+            data[key] = item
+        return data, n
+
+    def _pairs(self, data: TensorBatch, dst: dict[tuple, torch.Tensor]):
+        pairs = []
+        for path, t in _flatten(data):
+            if path not in dst:
+                raise KeyError(f"key {'.'.join(path)} not in buffer storage")
+            d = dst[path]
+            if t.dtype != d.dtype:
+                t = t.to(d.dtype)
+            pairs.append((t.contiguous(), d))
+        return pairs
+
+    def add(self, data: DataType) -> None:
+        data, n = self._prepare(data)
+        if self._storage is None:
+            self._init(data)
+        with torch.cuda.device(self.storage_device):
+            xp.ring_insert(self._pairs(data, self._leaves), n, self._cursor, self.max_size)
+        self._advance(n)
+
+    def _advance(self, n: int) -> None:
+        self._cursor = (self._cursor + n) % self.max_size
+        self._size = min(self._size + n, self.max_size)
+        self.counter += n
+
+    # -- sample (reference :114-131) --------------------------------------------------------------
+    def _uniform_indices(self, batch_size: int) -> torch.Tensor:
+        """First ``batch_size`` entries of torch.randperm(self.size), computed on the device from
+        the raw draws torch would consume (sparse forward Fisher-Yates, exact)."""
+        n = self.size
+        b = min(int(batch_size), n)
+        dev = self.storage_device
+        if b == 0:
+            return torch.empty(0, dtype=torch.int64, device=dev)
+        if self.rng == "torch":
+            stream = TorchCpuStream()
+            draws = min(b, n - 1)  # randperm draws once per i in [0, n-2]
+            raw = torch.zeros(b, dtype=torch.int32)
+            if draws:
+                raw[:draws] = stream.draw_u32(draws)
+            if self.exact_rng_advance and n - 1 > draws:
+                stream.skip(n - 1 - draws)
+            stream.commit()
+            raw = raw.to(dev, non_blocking=True)
+        else:
+            with torch.cuda.device(dev):
+                raw = xp.philox_u32(self._philox_seed, self._philox_offset, b, dev)
+            self._philox_offset += (b + 3) // 4
+        with torch.cuda.device(dev):
+            return xp.randperm_prefix(raw, b, 1, n)
+
+    def _gather(self, indices: torch.Tensor) -> TensorBatch:
+        """``storage[indices]`` as fresh copies, every key in one launch."""
+        idx = indices.to(device=self.storage_device, dtype=torch.int64).contiguous().view(-1)
+        B = idx.numel()
+        out = {p: torch.empty((B, *s.shape[1:]), dtype=s.dtype, device=s.device)
+               for p, s in self._leaves.items()}
+        with torch.cuda.device(self.storage_device):
+            xp.gather([(self._leaves[p], out[p]) for p in self._leaves], idx, self.max_size, self._err)
+        return _unflatten(out, [B])
+
+    def sample(self, batch_size: int, return_idx: bool = False) -> TensorBatch:
+        indices = self._uniform_indices(batch_size)
+        samples = self._gather(indices)
+        if return_idx:
+            samples["idxs"] = indices
+        return self._out(samples)
+
+    def clear(self) -> None:
+        self._size = 0
+        self._cursor = 0
+        self._storage = None
+        self._leaves = {}
+        self.initialized = False
+
+
+class MultiStepReplayBuffer(ReplayBuffer):
+    """n-step returns (reference: replay_buffer.py:141-258).  The last ``n_step`` env steps live
+    in a device stage ring; the fold (fp32, product then sum, "any env done" truncation) and the
+    ring insert are one kernel."""
+
+    def __init__(self, max_size: int, n_step: int = 3, gamma: float = 0.99,
+                 device: str | torch.device = "cpu", dtype: torch.dtype = torch.float32,
+                 **kw) -> None:
+        super().__init__(max_size, device, dtype, **kw)
+        self.n_step = n_step
+        self.gamma = gamma
+        self.n_step_buffer: deque[TensorBatch] = deque(maxlen=n_step)
+        self.reward_key = "reward"
+        self.done_key = None
+        self.ns_key = "next_obs"
+        self._stage: dict[tuple, torch.Tensor] = {}
+        self._stage_n = 0
+        self._stage_count = 0
+
+    def _init_stage(self, data: TensorBatch, n: int) -> None:
+        self._stage = {p: torch.zeros((self.n_step * n, *t.shape[1:]), dtype=t.dtype,
+                                      device=self.storage_device)
+                       for p, t in _flatten(data)}
+        self._stage_n = n
+
+    def _detect_keys(self) -> None:
+        first = self.n_step_buffer[0]
+        assert self.reward_key in first, (
+            f"Reward key not found in transition. Expected key: {self.reward_key}")
+        assert self.ns_key in first, (
+            f"Next observation key not found in transition. Expected key: {self.ns_key}")
+        done_key = None
+        expected_keys = ["done", "termination", "terminated"]
+        for key in expected_keys:
+            if key in first:
+                done_key = key
+                break
+        assert done_key is not None, (
+            f"No done/termination key found in transition. Expected keys: {expected_keys}")
+        self.done_key = done_key
+
+    def _fold_into(self, dst: dict[tuple, torch.Tensor], cursor: int, dst_rows: int) -> None:
+        if not self.initialized or self.done_key is None:
+            self._detect_keys()
+        paths = list(self._stage.keys())
+        roles = []
+        for p in paths:
+            if p[0] == self.reward_key:
+                roles.append(nv.XP_ROLE_REWARD)
+            elif p[0] in (self.ns_key, self.done_key):
+                roles.append(nv.XP_ROLE_LAST)
+            else:
+                roles.append(nv.XP_ROLE_FIRST)
+        done_path = (self.done_key,)
+        done_t = self._stage[done_path]
+        if done_t.dtype in (torch.bool, torch.uint8, torch.int8):
+            done_bytes = 1
+        elif done_t.dtype in (torch.float32, torch.int32):
+            done_bytes = 4
+        else:
+            raise TypeError(f"unsupported done dtype {done_t.dtype}")
+        if self._stage[(self.reward_key,)].dtype != torch.float32:
+            raise TypeError("n-step reward must be float32 (Transition casts it, data.py:85-87)")
+        gpow = [float(np.float32(self.gamma**i)) for i in range(self.n_step)]
+        slot0 = self._stage_count % self.n_step  # oldest step (the ring is full here)
+        with torch.cuda.device(self.storage_device):
+            xp.nstep_fold_insert([(self._stage[p], dst[p]) for p in paths], roles,
+                                 paths.index(done_path), done_bytes, self.n_step, slot0, gpow,
+                                 self._stage_n, cursor, dst_rows)
+
+    def add(self, data: DataType) -> TensorBatch | None:
+        data, n = self._prepare(data)
+        if not self._stage:
+            self._init_stage(data, n)
+        if n != self._stage_n:
+            raise ValueError(f"n-step buffer was initialised with {self._stage_n} envs, got {n}")
+        slot = self._stage_count % self.n_step
+        with torch.cuda.device(self.storage_device):
+            xp.ring_insert(self._pairs(data, self._stage), n, slot * n, self.n_step * n)
+        self._stage_count += 1
+        view = _unflatten({p: t[slot * n:(slot + 1) * n] for p, t in self._stage.items()}, [n])
+        self.n_step_buffer.append(view)
+
+        if len(self.n_step_buffer) < self.n_step:
+            return None
+
+        if self._storage is None:
+            if self.done_key is None:
+                self._detect_keys()
+            self._init(view)
+        self._fold_into(self._leaves, self._cursor, self.max_size)
+        self._advance(n)
+        return self.n_step_buffer[0]
+
+    def sample_from_indices(self, idxs: torch.Tensor) -> TensorBatch:
+        idxs = torch.as_tensor(idxs)
+        out = self._gather(idxs)
+        if idxs.ndim > 1:  # storage[idxs] with (B,1) indices gives [B,1,...] in the reference
+            out = out.view(*idxs.shape)
+        return self._out(out)
+
+    def _get_n_step_info(self) -> TensorBatch:
+        """The folded n-step transition for the current window (reference :206-258)."""
+        n = self._stage_n
+        tmp = {p: torch.empty((n, *t.shape[1:]), dtype=t.dtype, device=t.device)
+               for p, t in self._stage.items()}
+        self._fold_into(tmp, 0, n)
+        return _unflatten(tmp, [n])
+
+    def clear(self) -> None:
+        super().clear()
+
+
+class PrioritizedReplayBuffer(ReplayBuffer):
+    """Prioritized replay (reference: replay_buffer.py:261-428) over an interleaved (sum, min)
+    device tree pair; ``max_priority`` is device-resident so add/update never synchronise."""
+
+    def __init__(self, max_size: int, alpha: float = 0.6, device: str | torch.device = "cpu",
+                 dtype: torch.dtype = torch.float32, **kw) -> None:
+        super().__init__(max_size, device, dtype, **kw)
+        self.alpha = alpha
+        self.tree_ptr = 0
+        tree_capacity = 1
+        while tree_capacity < max_size:
+            tree_capacity *= 2
+        self._tree_capacity = tree_capacity
+        self._trees = None
+        self._pending_max_priority = 1.0
+
+    # trees are created on first use so that constructing a buffer needs no GPU
+    def _ensure_trees(self):
+        if self._trees is None:
+            from .segment_tree import make_pair
+
+            s, m, st = make_pair(self._tree_capacity, self.storage_device)
+            self._state = torch.tensor([self._pending_max_priority], dtype=torch.float64,
+                                       device=self.storage_device)
+            self._trees = (s, m, st, st.handle(None))
+        return self._trees
+
+    @property
+    def sum_tree(self):
+        return self._ensure_trees()[0]
+
+    @property
+    def min_tree(self):
+        return self._ensure_trees()[1]
+
+    @property
+    def max_priority(self) -> float:
+        if self._trees is None:
+            return self._pending_max_priority
+        return float(self._state.item())
+
+    @max_priority.setter
+    def max_priority(self, v: float) -> None:
+        if self._trees is None:
+            self._pending_max_priority = float(v)
+        else:
+            self._state.fill_(float(v))
+
+    def add(self, data: DataType) -> None:
+        data, n = self._prepare(data)
+        if self._storage is None:
+            self._init(data)
+        _, _, st, h = self._ensure_trees()
+        with torch.cuda.device(self.storage_device):
+            xp.ring_insert(self._pairs(data, self._leaves), n, self._cursor, self.max_size)
+            # leaves tree_ptr.. := max_priority ** alpha (:306-309), no host round trip
+            xp.per_add(h, self._state, self.tree_ptr, n, self.max_size, self.alpha)
+        self._advance(n)
+        self.tree_ptr = (self.tree_ptr + n) % self.max_size
+
+    def _update_priority(self, idx: int, priority: float) -> None:
+        assert 0 <= idx < self.max_size
+        s, m, st, h = self._ensure_trees()
+        v = torch.tensor([float(priority) ** self.alpha], dtype=torch.float64, device=self.storage_device)
+        i = torch.tensor([int(idx)], dtype=torch.int64, device=self.storage_device)
+        with torch.cuda.device(self.storage_device):
+            xp.tree_set_batch(h, i, v, st.err)
+        self.max_priority = max(self.max_priority, priority)
+
+    def _draw_uniforms(self, batch_size: int) -> torch.Tensor:
+        dev = self.storage_device
+        if self.rng == "torch":
+            # batch_size x torch.rand(1).item() == torch.rand(batch_size) on the same stream
+            return torch.rand(batch_size).to(dev, non_blocking=True)
+        with torch.cuda.device(dev):
+            raw = xp.philox_u32(self._philox_seed, self._philox_offset, batch_size, dev)
+        self._philox_offset += (batch_size + 3) // 4
+        return (raw & 0xFFFFFF).to(torch.float32) * (2.0**-24)
+
+    def _sample_proportional(self, batch_size: int, u: torch.Tensor | None = None) -> torch.Tensor:
+        _, _, st, h = self._ensure_trees()
+        if u is None:
+            u = self._draw_uniforms(batch_size)
+        u = u.to(device=self.storage_device, dtype=torch.float32).contiguous()
+        idx = torch.empty(batch_size, dtype=torch.int64, device=self.storage_device)
+        with torch.cuda.device(self.storage_device):
+            xp.per_sample(h, u, batch_size, 1, self.size, 0.0, idx, None)
+        return idx
+
+    def _calculate_weights(self, indices: torch.Tensor, beta: float) -> torch.Tensor:
+        _, _, st, h = self._ensure_trees()
+        idx = torch.as_tensor(indices).to(device=self.storage_device, dtype=torch.int64).contiguous().view(-1)
+        w = torch.empty(idx.numel(), dtype=torch.float32, device=self.storage_device)
+        with torch.cuda.device(self.storage_device):
+            xp.per_weights(h, idx, self.size, float(beta), w)
+        return w
+
+    def sample(self, batch_size: int, beta: float = 0.4, u: torch.Tensor | None = None) -> TensorBatch:
+        """``u`` (optional): the fp32 uniforms to use instead of drawing them."""
+        _, _, st, h = self._ensure_trees()
+        dev = self.storage_device
+        if u is None:
+            u = self._draw_uniforms(batch_size)
+        u = u.to(device=dev, dtype=torch.float32).contiguous()
+        idx = torch.empty(batch_size, dtype=torch.int64, device=dev)
+        w = torch.empty(batch_size, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            xp.per_sample(h, u, batch_size, 1, self.size, float(beta), idx, w)
+        samples = self._gather(idx)
+        samples["weights"] = w.unsqueeze(1)
+        samples["idxs"] = idx.unsqueeze(1)
+        return self._out(samples)
+
+    def update_priorities(self, indices, priorities, check: bool = True) -> None:
+        """Sequential semantics of :411-428 in one batched pass (last writer wins; every
+        priority, overwritten or not, counts towards ``max_priority``)."""
+        _, _, st, h = self._ensure_trees()
+        dev = self.storage_device
+        idx = torch.as_tensor(indices).to(device=dev, dtype=torch.int64).contiguous().view(-1)
+        pr = torch.as_tensor(priorities)
+        if pr.dtype != torch.float32:
+            # priority.item() of a float64 array keeps fp64; the kernel takes fp32 inputs, which
+            # is what the algorithms produce (dqn_rainbow.py:487-488)
+            pr = pr.to(torch.float32)
+        pr = pr.to(device=dev).contiguous().view(-1)
+        n = min(idx.numel(), pr.numel())  # zip(..., strict=False)
+        with torch.cuda.device(dev):
+            xp.per_update(h, self._state, idx[:n], pr[:n], self.max_size, self.alpha, st.err)
+        if check and int(st.err.item()) != 0:
+            st.err.zero_()
+            raise AssertionError("priority index out of range [0, max_size)")
