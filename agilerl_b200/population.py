@@ -1,0 +1,119 @@
+"""Population sharding across the GPUs of one box (one process per GPU, torch.distributed).
+
+The reference trains the agents of a population sequentially on one device and shares ONE
+replay ``memory`` between them (training/train_off_policy.py:46,249,343-345).  Here:
+
+* each rank owns a contiguous slice of the agents and their RolloutBuffers entirely — GAE / add /
+  minibatching need no communication;
+* the shared off-policy memory is REPLICATED: every rank holds the full storage and both trees.
+  Per env step each rank contributes its agents' new rows; an all-gather in fixed rank-major,
+  agent-major order makes every replica insert the same rows at the same cursor.  PER priority
+  updates are all-gathered as (idx, priority) pairs and applied on every replica in the same
+  canonical order through the same last-writer-wins kernel, so replicas stay bit-identical.
+
+The exchange is device-agnostic (NCCL on GPUs; the CPU tests run it over gloo, world_size 2).
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+
+from .components.tensor_batch import TensorBatch, as_batch
+
+
+@dataclass(frozen=True)
+class ShardPlan:
+    population: int
+    world_size: int
+    rank: int
+
+    def owner(self, agent: int) -> int:
+        """Rank owning ``agent``: contiguous blocks, the first ``population % world_size`` ranks
+        hold one extra agent."""
+        base, extra = divmod(self.population, self.world_size)
+        cut = extra * (base + 1)
+        return agent // (base + 1) if agent < cut else extra + (agent - cut) // max(base, 1)
+
+    def agents_of(self, rank: int) -> range:
+        base, extra = divmod(self.population, self.world_size)
+        start = rank * base + min(rank, extra)
+        return range(start, start + base + (1 if rank < extra else 0))
+
+    @property
+    def local_agents(self) -> range:
+        return self.agents_of(self.rank)
+
+    @property
+    def max_local(self) -> int:
+        return len(self.agents_of(0))
+
+
+def _group_size(group=None) -> int:
+    return dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+
+
+def all_gather_rows(t: torch.Tensor, group=None) -> torch.Tensor:
+    """[n, ...] on every rank -> [world*n, ...], rank-major.  Equal ``n`` on every rank."""
+    world = _group_size(group)
+    if world == 1:
+        return t
+    t = t.contiguous()
+    out = torch.empty((world * t.shape[0], *t.shape[1:]), dtype=t.dtype, device=t.device)
+    if t.dtype == torch.bool:  # NCCL has no bool; ship bytes
+        dist.all_gather_into_tensor(out.view(torch.uint8), t.view(torch.uint8), group=group)
+    else:
+        dist.all_gather_into_tensor(out, t, group=group)
+    return out
+
+
+def all_gather_batch(batch: TensorBatch, group=None) -> TensorBatch:
+    """Every key of a ``[n]`` batch gathered rank-major into a ``[world*n]`` batch."""
+    world = _group_size(group)
+    if world == 1:
+        return batch
+    n = batch.batch_size[0]
+    out = batch._map(lambda t: all_gather_rows(t, group), torch.Size([world * n]))
+    return out
+
+
+class ReplicatedReplay:
+    """A replay buffer replicated on every rank, kept identical by canonical-order exchange.
+
+    ``memory`` is any of the engine's buffers (``ReplayBuffer``, ``PrioritizedReplayBuffer``;
+    for n-step wrap the ``MultiStepReplayBuffer`` whose output feeds the PER buffer).  Each rank
+    calls the methods below collectively with the rows / priorities of ITS agents.
+    """
+
+    def __init__(self, memory, group=None) -> None:
+        self.memory = memory
+        self.group = group
+
+    def add(self, local_rows) -> None:
+        """``local_rows``: the new transitions of this rank's agents, agent-major ``[n]`` (equal
+        ``n`` on every rank).  Every replica inserts all ranks' rows, rank-major."""
+        local = as_batch(local_rows)
+        dev = self.memory.storage_device if _is_cuda_backend(self.group) else None
+        if dev is not None:
+            local = local.to(dev)
+        self.memory.add(all_gather_batch(local, self.group))
+
+    def update_priorities(self, local_idx: torch.Tensor, local_prio: torch.Tensor) -> None:
+        """(idx, priority) pairs of this rank's agents -> applied everywhere in rank-major order
+        (one batched last-writer-wins update per replica)."""
+        dev = self.memory.storage_device if _is_cuda_backend(self.group) else local_idx.device
+        idx = torch.as_tensor(local_idx).to(device=dev, dtype=torch.int64).reshape(-1)
+        pr = torch.as_tensor(local_prio).to(device=dev, dtype=torch.float32).reshape(-1)
+        self.memory.update_priorities(all_gather_rows(idx, self.group), all_gather_rows(pr, self.group))
+
+    def sample(self, *args, **kwargs):
+        """Sampling and gathering are local to a replica."""
+        return self.memory.sample(*args, **kwargs)
+
+
+def _is_cuda_backend(group=None) -> bool:
+    if not (dist.is_available() and dist.is_initialized()):
+        return True
+    return dist.get_backend(group) == "nccl"
