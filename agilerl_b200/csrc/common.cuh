@@ -18,12 +18,16 @@ void set_error(const char *fmt, ...);
 // grid sizing: the B200 has 148 SMs; queried once per device.
 int sm_count();
 
-inline xp_status_t check_launch(const char *what) {
+// kernels launched by this library since load (xp_launch_count); bench.py reports the delta.
+void note_launches(int n);
+
+inline xp_status_t check_launch(const char *what, int n_kernels = 1) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));
     return XP_ERR_CUDA;
   }
+  note_launches(n_kernels);
   return XP_OK;
 }
 

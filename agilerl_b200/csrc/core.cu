@@ -1,5 +1,6 @@
 // core.cu — library plumbing: version, thread-local error text, device facts.
 #include <stdarg.h>
+#include <atomic>
 #include <string.h>
 
 #include "common.cuh"
@@ -14,6 +15,9 @@ void set_error(const char *fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+
+static std::atomic<unsigned long long> g_launches{0};
+void note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 int sm_count() {
   static int cached[64] = {0};
@@ -35,6 +39,8 @@ extern "C" {
 int xp_version(void) { return 1; }
 
 const char *xp_last_error(void) { return xp::g_err; }
+
+uint64_t xp_launch_count(void) { return xp::g_launches.load(std::memory_order_relaxed); }
 
 xp_status_t xp_device_info(int device, int *sm_count, int *cc_major, int *cc_minor) {
   XP_REQUIRE(sm_count && cc_major && cc_minor, XP_ERR_INVALID, "xp_device_info: null output");

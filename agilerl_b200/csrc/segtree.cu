@@ -152,7 +152,7 @@ xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, bool unique, cu
     set_mark_kernel<true><<<grid, threads, 0, st>>>(t, s, B);
     set_rebuild_kernel<true><<<grid, threads, 0, st>>>(t, s, B);
   }
-  return xp::check_launch("tree set");
+  return xp::check_launch("tree set", unique ? 2 : 3);
 }
 
 // ---- queries ----------------------------------------------------------------------------------

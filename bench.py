@@ -1,0 +1,738 @@
+#!/usr/bin/env python
+"""bench.py — the judged benchmark of the B200 experience-path engine.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c3|c4|c5]
+
+One "step" = one population step of the hot path on one batch of synthetic input.  The default
+workload is BASELINE.json configs[1] (C2): Rainbow PER + 3-step replay, capacity 1M, batch 256,
+population 8, 84x84x4 uint8 observations.  A step is, for every agent of the population:
+PrioritizedReplayBuffer.sample(256, beta) [stratified sum-tree descent + IS weights + gather of
+every key] + MultiStepReplayBuffer.sample_from_indices(idxs) [second gather] +
+update_priorities(idxs, new_priorities) — SURVEY.md §8(d): 227 028 algorithmic bytes per sampled
+transition.  The metric is sampled transitions per second.
+
+  value : whole-job throughput, inputs (uniform draws, new priorities) already in HBM, the
+          population batched into single launches, device-timed with CUDA events.
+  e2e   : the same metric through the reference-facing Python API, one call per agent as
+          train_off_policy.py makes them; uniforms are drawn on the host (torch mt19937) and
+          priorities arrive as host arrays (dqn_rainbow.py:487), H2D inside the timed region,
+          indices + IS weights read back D2H every step.
+  roofline     : the dominant kernel (the row gather), algorithmic bytes / CUDA-event duration.
+  cpu_baseline : the oracle port of the reference's CPU path, timed on this host (N=1 only).
+  also         : device-timed numbers + rooflines for C3 (GAE) and C4 (PER tree 2^24), N=1 only.
+
+`--impl reference` times the reference's CPU implementation (oracle port — the reference is pure
+Python and cannot be installed on this image) on the host cores, same metric/config.
+
+Multi-GPU (torchrun, one rank per GPU): weak scaling — every rank owns `population` agents; the
+shared replay is replicated, so the (idx, priority) pairs of every rank are all-gathered (NCCL)
+and applied on every replica in rank-major order; sampling and gathering are local.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "per_sampled_transitions_per_s"
+UNIT = "transitions/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
+    ap.add_argument("--rows", type=int, default=0, help="override replay capacity (0 = config's)")
+    ap.add_argument("--no-also", action="store_true", help="skip the secondary C3/C4 measurements")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    return ap.parse_args()
+
+
+# =================================================================================================
+# clocks: sampled DURING the timed region (pynvml in a thread; nvidia-smi fallback)
+# =================================================================================================
+class ClockSampler:
+    BAD = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")
+
+    def __init__(self, index: int, period_s: float = 0.01):
+        self.index, self.period = index, period_s
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._t = None
+        self._nv = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            # honour CUDA_VISIBLE_DEVICES: map through the torch device's PCI bus id
+            import torch
+
+            bus = torch.cuda.get_device_properties(index).pci_bus_id
+            dom = torch.cuda.get_device_properties(index).pci_domain_id
+            dev = torch.cuda.get_device_properties(index).pci_device_id
+            busid = f"{dom:08X}:{bus:02X}:{dev:02X}.0"
+            try:
+                self._h = pynvml.nvmlDeviceGetHandleByPciBusId(busid.encode())
+            except Exception:
+                self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self._nv = pynvml
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._nv = None
+
+    def _poll_once(self):
+        nv = self._nv
+        mhz = nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+        self.samples.append(mhz)
+        for name, bit in (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown),
+                          ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                          ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown),
+                          ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self._poll_once()
+            except Exception:
+                break
+            self._stop.wait(self.period)
+
+    def start(self):
+        if self._nv is None:
+            return
+        self._stop.clear()
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        if self._t is not None:
+            self._stop.set()
+            self._t.join()
+            self._t = None
+
+    def summary(self) -> dict:
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                    "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# =================================================================================================
+# measured peaks
+# =================================================================================================
+def hbm_peak() -> tuple[float, str]:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+# =================================================================================================
+# workload definitions (sizes from BASELINE.json / SURVEY.md §8d)
+# =================================================================================================
+ATARI = (84, 84, 4)
+R_C2 = 2 * 84 * 84 * 4 + 4 + 4 + 4  # 56 460 B per stored transition row
+C2 = dict(name="c2_rainbow_per_nstep3_cap1M_b256_pop8_obs84x84x4_u8", cap=1_000_000, B=256, P=8,
+          n_step=3, gamma=0.99, alpha=0.6, beta=0.4, num_envs=16, L=20)
+C3 = dict(name="c3_ppo_gae_1024envs_128steps_pop16", T=128, N=1024, P=16, gamma=0.99, lam=0.95)
+C4 = dict(name="c4_per_tree_cap2p24_b4096_pop64", cap=1 << 24, B=4096, P=64, alpha=0.6, beta=0.4,
+          L=24)
+C5 = dict(name="c5_td3_uniform_cap10M_obs376_act17_b1024_pop32", cap=10_000_000, B=1024, P=32,
+          obs=376, act=17)
+R_C5 = 2 * 376 * 4 + 17 * 4 + 4 + 4  # 3 084 B
+
+
+def per_bytes_per_sample(L: int) -> dict:
+    """algorithmic bytes per sampled transition of the tree ops."""
+    return {"descent": 8 * L + 4 + 8, "weights": 8 + 4,
+            "update": 8 + 4 + 2 * (8 + L * 24)}
+
+
+# =================================================================================================
+# B200 arm
+# =================================================================================================
+def cuda_time_ms(fn, sync):
+    import torch
+
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync()
+    a.record()
+    fn()
+    b.record()
+    sync()
+    return a.elapsed_time(b)
+
+
+def graph_time_us(launches, reps: int):
+    """Device time per launch of a list of closures, replayed from one CUDA graph (no host
+    launch gaps).  Returns microseconds per closure call."""
+    import torch
+
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for fn in launches:  # warm-up outside capture
+            fn()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for fn in launches:
+            fn()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        g.replay()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) * 1e3 / (reps * len(launches))
+
+
+class C2Workload:
+    """Rainbow PER + n-step replay (BASELINE.json configs[1])."""
+
+    def __init__(self, args, rank, world, dev):
+        import torch
+
+        from agilerl_b200 import _native as nv
+        from agilerl_b200 import xp
+        from agilerl_b200.components import MultiStepReplayBuffer, PrioritizedReplayBuffer, TensorBatch
+
+        self.torch, self.nv, self.xp, self.TensorBatch = torch, nv, xp, TensorBatch
+        self.args, self.rank, self.world, self.dev = args, rank, world, dev
+        c = dict(C2)
+        self.c = c
+        cap = args.rows or c["cap"]
+        free, total = torch.cuda.mem_get_info(dev)
+        need = 2 * cap * R_C2 + (6 << 30)
+        if need > free:  # another tenant on the GPU: shrink and SAY so (config.rows)
+            cap = int((free - (6 << 30)) // (2 * R_C2))
+        self.cap = cap
+        self.P, self.B = c["P"], c["B"]
+        self.per = PrioritizedReplayBuffer(cap, alpha=c["alpha"], device=dev)
+        self.nstep = MultiStepReplayBuffer(cap, n_step=c["n_step"], gamma=c["gamma"], device=dev)
+        self.lib = nv.load()
+
+    # -- synthetic transitions of the named shape ---------------------------------------------
+    def transition(self, n, g):
+        torch = self.torch
+        return self.TensorBatch({
+            "obs": torch.randint(0, 256, (n, *ATARI), dtype=torch.uint8, generator=g),
+            "action": torch.randint(0, 18, (n,), generator=g).float(),
+            "reward": torch.randn(n, generator=g),
+            "next_obs": torch.randint(0, 256, (n, *ATARI), dtype=torch.uint8, generator=g),
+            "done": (torch.rand(n, generator=g) < 0.01).float()}, batch_size=[n])
+
+    def setup(self):
+        torch, xp = self.torch, self.xp
+        c, cap, dev = self.c, self.cap, self.dev
+        g = torch.Generator().manual_seed(0)
+        # real env steps through n-step -> PER (train_off_policy.py:341-345); allocates storage
+        for _ in range(c["n_step"] + 2):
+            one = self.nstep.add(self.transition(c["num_envs"], g))
+            if one is not None:
+                self.per.add(one)
+        # bulk fill of the remaining rows straight into HBM (setup, untimed): random bytes
+        gd = torch.Generator(device=dev).manual_seed(1 + self.rank)
+        block = torch.randint(0, 256, (1 << 28,), dtype=torch.uint8, device=dev, generator=gd)
+        for buf in (self.per, self.nstep):
+            for path, t in buf._leaves.items():
+                flat = t.view(-1).view(torch.uint8) if t.dtype != torch.uint8 else t.view(-1)
+                if t.dtype == torch.uint8:
+                    n = flat.numel()
+                    off = 0
+                    k = 0
+                    while off < n:
+                        m = min(block.numel() - 4096, n - off)
+                        s = (k * 1031) % 4096  # shift the block so rows are not periodic copies
+                        flat[off:off + m] = block[s:s + m]
+                        off += m
+                        k += 1
+                else:
+                    t.copy_(torch.randn(t.shape, device=dev, generator=gd).to(t.dtype))
+            buf._size = cap
+            buf._cursor = 0
+        self.per.tree_ptr = 0
+        del block
+        # priorities of every stored row: |randn| + 1e-3 through the real update path
+        pr = torch.randn(cap, device=dev, generator=gd).abs() + 1e-3
+        self.per.update_priorities(torch.arange(cap, device=dev), pr)
+        # resident inputs of the timed steps (rotated)
+        n = self.P * self.B
+        self.R = 4
+        self.u = [torch.rand(n, generator=torch.Generator().manual_seed(10 + i)).to(dev) for i in range(self.R)]
+        self.pr = [(torch.randn(n, device=dev, generator=gd).abs() + 1e-6) for _ in range(self.R)]
+        self.idx = torch.empty(n, dtype=torch.int64, device=dev)
+        self.w = torch.empty(n, dtype=torch.float32, device=dev)
+        self.err = torch.zeros(1, dtype=torch.int32, device=dev)
+        # two output sets per buffer; every set is written once per step (231 MB per step)
+        self.outs = []
+        for _ in range(2):
+            o = {}
+            for name, buf in (("per", self.per), ("nstep", self.nstep)):
+                paths = list(buf._leaves.keys())
+                out = [torch.empty((n, *buf._leaves[p].shape[1:]), dtype=buf._leaves[p].dtype, device=dev)
+                       for p in paths]
+                keys = xp.make_keys([(buf._leaves[p], out[i]) for i, p in enumerate(paths)])
+                o[name] = (keys, len(paths), out, paths)
+            self.outs.append(o)
+        _, _, st, h = self.per._ensure_trees()
+        self.h, self.state = h, self.per._state
+        if self.world > 1:
+            self.all_idx = torch.empty(self.world * n, dtype=torch.int64, device=dev)
+            self.all_pr = torch.empty(self.world * n, dtype=torch.float32, device=dev)
+        torch.cuda.synchronize()
+
+    @property
+    def units_per_step(self):
+        return self.P * self.B
+
+    kernels_per_step = 6  # per_sample, gather x2, update (ticket, mark, rebuild)
+
+    def gather_bytes(self):
+        """algorithmic bytes of ONE gather launch: (2R + 8) per sample."""
+        return self.P * self.B * (2 * R_C2 + 8)
+
+    def step(self, i, ev=None):
+        import ctypes as C
+
+        lib, c = self.lib, self.c
+        stream = self.torch.cuda.current_stream().cuda_stream
+        n = self.P * self.B
+        u, pr, o = self.u[i % self.R], self.pr[i % self.R], self.outs[i % 2]
+        chk = self.nv.check
+        chk(lib.xp_per_sample(C.byref(self.h), u.data_ptr(), self.B, self.P, self.cap, c["beta"],
+                              self.idx.data_ptr(), self.w.data_ptr(), stream))
+        if ev is not None:
+            ev[0].record()
+        k = o["per"]
+        chk(lib.xp_gather(k[0], k[1], self.idx.data_ptr(), n, self.cap, self.err.data_ptr(), stream))
+        if ev is not None:
+            ev[1].record()
+        k = o["nstep"]
+        chk(lib.xp_gather(k[0], k[1], self.idx.data_ptr(), n, self.cap, self.err.data_ptr(), stream))
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.all_gather_into_tensor(self.all_idx, self.idx)
+            dist.all_gather_into_tensor(self.all_pr, pr)
+            chk(lib.xp_per_update(C.byref(self.h), self.state.data_ptr(), self.all_idx.data_ptr(),
+                                  self.all_pr.data_ptr(), self.world * n, self.cap, c["alpha"],
+                                  self.err.data_ptr(), stream))
+        else:
+            chk(lib.xp_per_update(C.byref(self.h), self.state.data_ptr(), self.idx.data_ptr(),
+                                  pr.data_ptr(), n, self.cap, c["alpha"], self.err.data_ptr(), stream))
+
+    def verify(self):
+        """size-independent property at full size: the gathered rows equal torch indexing of the
+        storage, indices are within [0, size), the tree root equals the sum of the leaves'
+        pairwise reduction (checked in tests), error flag clear."""
+        torch = self.torch
+        self.step(0)
+        torch.cuda.synchronize()
+        assert int(self.err.item()) == 0, "device error flag set"
+        idx = self.idx
+        assert int(idx.min()) >= 0 and int(idx.max()) < self.cap
+        o = self.outs[0]
+        for name, buf in (("per", self.per), ("nstep", self.nstep)):
+            _, _, out, paths = o[name]
+            for t, p in zip(out, paths):
+                sel = idx[:64]
+                assert torch.equal(t[:64], buf._leaves[p][sel]), f"gather mismatch on {name}/{p}"
+
+    # -- e2e through the public API ---------------------------------------------------------------
+    def e2e_setup(self):
+        torch = self.torch
+        n = self.B
+        g = torch.Generator().manual_seed(77)
+        self.prio_host = [(torch.randn(n, generator=g).abs() + 1e-6).pin_memory().numpy()
+                          for _ in range(self.P * 3)]
+        self.res_host = torch.empty(self.P * n, 3, dtype=torch.float32).pin_memory()
+        torch.manual_seed(1234)
+
+    def e2e_step(self, i):
+        torch = self.torch
+        c = self.c
+        idxs, ws = [], []
+        for a in range(self.P):
+            batch = self.per.sample(self.B, c["beta"])           # host draws + H2D u inside
+            nb = self.nstep.sample_from_indices(batch["idxs"])    # noqa: F841 (n-step batch)
+            idxs.append(batch["idxs"])
+            ws.append(batch["weights"])
+            self.per.update_priorities(batch["idxs"], self.prio_host[(i * self.P + a) % len(self.prio_host)])
+        idx_h = torch.cat(idxs).cpu()                             # D2H: the step's result
+        w_h = torch.cat(ws).cpu()
+        return idx_h, w_h
+
+    def e2e_bytes(self):
+        n = self.P * self.B
+        return n * 4 + n * 4, n * 8 + n * 4  # H2D: u + priorities; D2H: idxs + weights
+
+
+def bench_gae(dev, sets=8, P=None, reps=40):
+    """C3: one launch computes GAE for the whole population; cold-L2 by rotating `sets` buffer
+    sets (> 126 MB in total)."""
+    import torch
+
+    from agilerl_b200 import xp
+
+    c = C3
+    P = P or c["P"]
+    T, N = c["T"], c["N"]
+    gd = torch.Generator(device=dev).manual_seed(3)
+    bufs = []
+    for _ in range(sets):
+        r = torch.randn(P, T, N, device=dev, generator=gd)
+        v = torch.randn(P, T, N, device=dev, generator=gd)
+        d = torch.rand(P, T, N, device=dev, generator=gd) < 0.02
+        lv = torch.randn(P, N, device=dev, generator=gd).double()
+        ld = (torch.rand(P, N, device=dev, generator=gd) < 0.02).double()
+        bufs.append((r, v, d, lv, ld, torch.empty_like(r), torch.empty_like(r)))
+
+    def mk(b):
+        r, v, d, lv, ld, a, g = b
+        return lambda: xp.gae(r, v, d, lv, ld, a, g, T, N, P, T * N, c["gamma"], c["lam"])
+
+    us = graph_time_us([mk(b) for b in bufs], reps)
+    steps = P * T * N
+    return {"workload": c["name"] if P == c["P"] else f"{c['name']}_x{P // c['P']}",
+            "metric": "gae_steps_per_s", "value": steps / (us * 1e-6), "unit": "steps/s",
+            "us_per_launch": us, "launches_timed": reps * sets, "algorithmic_bytes": steps * 17,
+            "l2": f"rotating {sets} buffer sets ({sets * steps * 17 / 1e6:.0f} MB)"}
+
+
+def bench_per_tree(dev, reps=10):
+    """C4: PER tree cap 2^24, 64 agents x 4096 samples per launch; sample(+weights) and update."""
+    import torch
+
+    from agilerl_b200 import xp
+
+    c = C4
+    cap, B, P = c["cap"], c["B"], c["P"]
+    nodes = torch.empty(2 * cap, 2, dtype=torch.float64, device=dev)
+    aux = torch.zeros(2 * cap, dtype=torch.int32, device=dev)
+    t = xp.make_tree(nodes[:, 0], nodes[:, 1], 2, cap, aux)
+    xp.tree_init(t, torch.cuda.current_stream().cuda_stream)
+    state = torch.ones(1, dtype=torch.float64, device=dev)
+    gd = torch.Generator(device=dev).manual_seed(4)
+    xp.per_add(t, state, 0, cap, cap, c["alpha"])
+    pr0 = torch.randn(cap, device=dev, generator=gd).abs() + 1e-3
+    xp.per_update(t, state, torch.arange(cap, device=dev), pr0, cap, c["alpha"])
+    del pr0
+    n = P * B
+    R = 4
+    u = [torch.rand(n, device=dev, generator=gd) for _ in range(R)]
+    pr = [torch.randn(n, device=dev, generator=gd).abs() + 1e-6 for _ in range(R)]
+    idx = [torch.empty(n, dtype=torch.int64, device=dev) for _ in range(R)]
+    w = torch.empty(n, dtype=torch.float32, device=dev)
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def sample(i):
+        return lambda: xp.per_sample(t, u[i], B, P, cap, c["beta"], idx[i], w)
+
+    def update(i):
+        return lambda: xp.per_update(t, state, idx[i], pr[i], cap, c["alpha"], err)
+
+    us_s = graph_time_us([sample(i) for i in range(R)], reps)
+    us_u = graph_time_us([update(i) for i in range(R)], reps)
+    seq = []
+    for i in range(R):
+        seq += [sample(i), update(i)]
+    us_b = 2 * graph_time_us(seq, reps)
+    assert int(err.item()) == 0
+    bps = per_bytes_per_sample(c["L"])
+    tot = sum(bps.values())
+    return {"workload": c["name"], "metric": METRIC, "value": n / (us_b * 1e-6), "unit": UNIT,
+            "us_sample": us_s, "us_update": us_u, "us_sample_plus_update": us_b,
+            "algorithmic_bytes_per_sample": tot, "algorithmic_bytes": n * tot,
+            "l2": "tree 805 MB > L2; top levels L2-resident by design"}
+
+
+def roofline(alg_bytes: float, us: float, traffic=None) -> dict:
+    peak, how = hbm_peak()
+    ach = alg_bytes / (us * 1e-6) / 1e9
+    return {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(ach / peak, 4), "traffic": traffic, "peak_source": how}
+
+
+def b200_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from agilerl_b200 import _native as nv
+
+    lib = nv.load()
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    if args.workload != "c2":
+        raise SystemExit("only --workload c2 is a bench line; c3/c4 are reported under 'also'")
+    wl = C2Workload(args, rank, world, dev)
+    wl.setup()
+    wl.verify()
+    K, W = args.steps, max(args.warmup, 3)
+    for i in range(W):
+        wl.step(i)
+    sync()
+    clocks = ClockSampler(local)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks.start()
+    l0 = lib.xp_launch_count()
+    a.record()
+    for i in range(K):
+        wl.step(W + i, evs[i])
+    b.record()
+    sync()
+    l1 = lib.xp_launch_count()
+    ms = a.elapsed_time(b)
+    gather_us = sum(x.elapsed_time(y) for x, y in evs) * 1e3 / K
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = wl.units_per_step * world * K / (ms * 1e-3)
+
+    # -- e2e through the public per-agent API ---------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        wl.e2e_setup()
+        Ke = max(3, min(K, 200))
+        for i in range(3):
+            wl.e2e_step(i)
+        sync()
+        t0 = time.perf_counter()
+        a.record()
+        for i in range(Ke):
+            wl.e2e_step(i)
+        b.record()
+        sync()
+        wall = time.perf_counter() - t0
+        ems = max(a.elapsed_time(b), wall * 1e3 * 0.0)  # device-side span of the same region
+        if world > 1:
+            t = torch.tensor([ems], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ems = float(t.item())
+        bi, bo = wl.e2e_bytes()
+        e2e = {"value": wl.units_per_step * world * Ke / (ems * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo, "steps": Ke,
+               "ms_per_step": ems / Ke,
+               "api": "per agent: PrioritizedReplayBuffer.sample + MultiStepReplayBuffer."
+                      "sample_from_indices + update_priorities (host uniforms / host priorities)"}
+    clocks.stop()
+
+    also = None
+    cpu = None
+    rows = wl.cap
+    if rank == 0 and world == 1 and not args.no_also:
+        del wl
+        torch.cuda.empty_cache()
+        g = bench_gae(dev)
+        g["roofline"] = roofline(g["algorithmic_bytes"], g["us_per_launch"])
+        g16 = bench_gae(dev, sets=2, P=C3["P"] * 16, reps=20)
+        g16["roofline"] = roofline(g16["algorithmic_bytes"], g16["us_per_launch"])
+        p = bench_per_tree(dev)
+        p["roofline"] = roofline(p["algorithmic_bytes"], p["us_sample_plus_update"])
+        also = [g, g16, p]
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = reference_c2(seconds=args.cpu_seconds, workers=1)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64 tree / u8 rows", "data": "synthetic",
+            "config": {"workload": C2["name"], "rows": rows,
+                       "batch": C2["B"], "population_per_gpu": C2["P"], "population": C2["P"] * world,
+                       "row_bytes": R_C2, "tree_levels": C2["L"],
+                       "l2": "inputs larger than L2: random rows of a 113 GB replay storage; "
+                             "2 rotating output sets of 231 MB",
+                       "parallelism": f"pop-shard x{world}, replicated replay"},
+            "e2e": e2e,
+            "gpu_launches": int(l1 - l0),
+            "clocks": clocks.summary(),
+            "roofline": dict(roofline(C2["P"] * C2["B"] * (2 * R_C2 + 8), gather_us),
+                             kernel="move_kernel<gather>", us_per_launch=round(gather_us, 2),
+                             algorithmic_bytes_per_launch=C2["P"] * C2["B"] * (2 * R_C2 + 8)),
+            "cpu_baseline": cpu,
+            "also": also,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# =================================================================================================
+# reference arm / cpu_baseline: the oracle port of the reference's CPU path
+# =================================================================================================
+_REF_STATE = {}
+
+
+def _ref_build(rows: int, seed: int):
+    """PerOracle (Python-list trees, replay_buffer.py:261-428) at the config's tree capacity and
+    a BOUNDED slice of the row storage (numpy, struct-of-arrays like the TensorDict storage)."""
+    import numpy as np
+
+    from oracle import xp_oracle as xo
+
+    c = C2
+    rng = np.random.default_rng(seed)
+    per = xo.PerOracle(c["cap"], c["alpha"])
+    per.size = c["cap"]
+    cap2 = per.sum_tree.capacity
+    leaves = (np.abs(rng.standard_normal(c["cap"])) + 1e-3) ** c["alpha"]
+    # direct leaf fill + one bottom-up pass (1M sequential _update_priority calls take minutes);
+    # produces exactly the tree the sequential walks produce
+    per.sum_tree.tree[cap2:cap2 + c["cap"]] = leaves.tolist()
+    per.min_tree.tree[cap2:cap2 + c["cap"]] = leaves.tolist()
+    per.sum_tree.rebuild_from_leaves()
+    per.min_tree.rebuild_from_leaves()
+
+    def storage():
+        return {"obs": rng.integers(0, 256, (rows, *ATARI), dtype=np.uint8),
+                "action": rng.integers(0, 18, (rows, 1)).astype(np.float32),
+                "reward": rng.standard_normal((rows, 1)).astype(np.float32),
+                "next_obs": rng.integers(0, 256, (rows, *ATARI), dtype=np.uint8),
+                "done": (rng.random((rows, 1)) < 0.01).astype(np.float32)}
+
+    return per, storage(), storage()
+
+
+def _ref_agent_step(per, st_per, st_n, rows, B, beta, rng_t, prio):
+    """One agent's sample + n-step gather + update, as train_off_policy.py:363-412 drives it."""
+    import numpy as np
+    import torch
+
+    from oracle import xp_oracle as xo
+
+    u = torch.rand(B, generator=rng_t).numpy()       # B x torch.rand(1).item() (:377)
+    idx = per.sample_proportional(B, u)
+    batch = xo.gather(st_per, idx % rows)             # storage[idx].clone()
+    w = per.calculate_weights(idx, beta)
+    nb = xo.gather(st_n, idx % rows)                  # sample_from_indices
+    per.update_priorities(idx, prio)
+    return batch, nb, w
+
+
+def _ref_worker(args):
+    seconds, max_agent_steps, seed, rows = args
+    import numpy as np
+    import torch
+
+    torch.set_num_threads(1)
+    c = C2
+    per, st_per, st_n = _ref_build(rows, seed)
+    rng_t = torch.Generator().manual_seed(seed)
+    prio = (np.abs(np.random.default_rng(seed).standard_normal(c["B"])) + 1e-6).astype(np.float32)
+    _ref_agent_step(per, st_per, st_n, rows, c["B"], c["beta"], rng_t, prio)  # warm-up
+    t0 = time.perf_counter()
+    n = 0
+    while n < max_agent_steps:
+        _ref_agent_step(per, st_per, st_n, rows, c["B"], c["beta"], rng_t, prio)
+        n += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    return n, time.perf_counter() - t0
+
+
+def reference_c2(seconds: float, workers: int, max_agent_steps: int = 1 << 30, rows: int = 4096):
+    """Time the oracle port on the host.  workers == 1: the reference's own execution model
+    (agents sequential in one Python process, train_off_policy.py:249).  workers > 1: that many
+    independent processes, one agent each — the population-parallel upper bound."""
+    c = C2
+    if workers == 1:
+        res = [_ref_worker((seconds, max_agent_steps, 0, rows))]
+    else:
+        import multiprocessing as mp
+
+        ctx = mp.get_context("fork")
+        with ctx.Pool(workers) as pool:
+            res = pool.map(_ref_worker, [(seconds, max_agent_steps, s, rows) for s in range(workers)])
+    agent_steps = sum(r[0] for r in res)
+    wall = max(r[1] for r in res)
+    value = agent_steps * c["B"] / wall
+    return {"value": value, "unit": UNIT, "cores": workers, "kind": "port",
+            "host_cores": os.cpu_count(),
+            "sample": f"{agent_steps} agent-steps of {c['B']} samples in {wall:.1f} s; Python-list "
+                      f"sum/min trees at the full 2^20 capacity, row storage bounded to {rows} rows "
+                      f"(idx mod {rows}); sample_proportional + gather x2 + weights + update_priorities"}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    if args.workload != "c2":
+        raise SystemExit("only --workload c2 is a bench line")
+    K, W = args.steps, args.warmup
+    c = C2
+    workers = max(1, min(c["P"], os.cpu_count() or 1))
+    # each "step" = one bounded sample: every worker runs ONE agent's sample+update (256 samples);
+    # the budget keeps the whole run within a few minutes whatever K is
+    budget = 60.0
+    t0 = time.perf_counter()
+    cpu = reference_c2(seconds=budget, workers=workers, max_agent_steps=max(K + W, 1))
+    wall = time.perf_counter() - t0
+    agent_steps = int(cpu["sample"].split()[0])
+    line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT,
+            "n_gpus": args.gpus, "steps": K, "warmup": W,
+            "ms_per_step": 1e3 * c["B"] * workers / cpu["value"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64 tree / u8 rows", "data": "synthetic",
+            "config": {"workload": c["name"], "rows": c["cap"], "batch": c["B"],
+                       "population_per_gpu": c["P"], "population": c["P"], "row_bytes": R_C2,
+                       "tree_levels": c["L"], "parallelism": f"{workers} host processes"},
+            "cpu_baseline": cpu,
+            "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": round(wall, 1), "agent_steps": agent_steps}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

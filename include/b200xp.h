@@ -41,6 +41,8 @@ typedef int xp_status_t;
 /* ---- library ---------------------------------------------------------------------- */
 int xp_version(void);               /* ABI version, bumped on any signature change  */
 const char *xp_last_error(void);    /* thread-local, never NULL                     */
+/* Number of CUDA kernels this library has launched since it was loaded (all threads).  */
+uint64_t xp_launch_count(void);
 /* Device facts used for grid sizing (SM count, compute capability). */
 xp_status_t xp_device_info(int device, int *sm_count, int *cc_major, int *cc_minor);
 
