@@ -15,9 +15,12 @@ timeout 600 $SMALL > gpurun_out/small_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'move_kernel|per_sample|set_|gae_|tree_|randperm|philox' -c 400 --csv --log-file gpurun_out/launches_bench.csv $SMALL > gpurun_out/ncu_small.log 2>&1
 echo "ncu launches rc=$?"
 timeout 600 $SMALL > gpurun_out/small_plain2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'move_kernel' -s 8 -c 2 -o gpurun_out/prof_gather $SMALL > gpurun_out/ncu_gather.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'move_kernel' -s 14 -c 2 -o gpurun_out/prof_gather $SMALL > gpurun_out/ncu_gather.log 2>&1
 echo "ncu gather rc=$?"
-timeout 600 python tools/quick_bench.py per gae > gpurun_out/quick2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'per_sample|set_|gae_' -s 40 -c 12 -o gpurun_out/prof_tree_gae python tools/quick_bench.py per gae > gpurun_out/ncu_tree.log 2>&1
-echo "ncu tree rc=$?"
+Q="python tools/quick_bench.py per24 gae"
+timeout 600 $Q > gpurun_out/quick2.log 2>&1 && {
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'gae_staged' -s 10 -c 2 -o gpurun_out/prof_gae $Q > gpurun_out/ncu_gae.log 2>&1; echo "ncu gae rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'per_sample_kernel' -s 10 -c 2 -o gpurun_out/prof_sample $Q > gpurun_out/ncu_sample.log 2>&1; echo "ncu sample rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'set_' -s 15 -c 6 -o gpurun_out/prof_update $Q > gpurun_out/ncu_update.log 2>&1; echo "ncu update rc=$?"
+}
 ls -la gpurun_out

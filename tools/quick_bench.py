@@ -106,8 +106,9 @@ if __name__ == "__main__":
     if "gae" in which:
         bench_gae()
         bench_gae(P=256)
-    if "per" in which:
+    if "per" in which or "per20" in which:
         bench_per(20, 256, 8)
+    if "per" in which or "per24" in which:
         bench_per(24, 4096, 64)
     if "gather" in which:
         bench_gather()
