@@ -23,6 +23,7 @@ import torch
 from .. import _native as nv
 from .. import xp
 from .rng import TorchCpuStream
+from .staging import PinnedRing
 from .tensor_batch import TensorBatch, as_batch
 
 DataType = Any
@@ -82,6 +83,12 @@ class ReplayBuffer:
         self._philox_seed = seed
         self._philox_offset = 0
         self._err: torch.Tensor | None = None
+        self._ring: PinnedRing | None = None
+
+    def _stage(self) -> PinnedRing:
+        if self._ring is None:
+            self._ring = PinnedRing(self.storage_device)
+        return self._ring
 
     # -- properties (reference :39-58) ----------------------------------------------------------
     @property
@@ -183,7 +190,8 @@ class ReplayBuffer:
             if self.exact_rng_advance and n - 1 > draws:
                 stream.skip(n - 1 - draws)
             stream.commit()
-            raw = raw.to(dev, non_blocking=True)
+            with torch.cuda.device(dev):
+                raw = self._stage().to_device(raw)
         else:
             with torch.cuda.device(dev):
                 raw = xp.philox_u32(self._philox_seed, self._philox_offset, b, dev)
@@ -402,7 +410,10 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         dev = self.storage_device
         if self.rng == "torch":
             # batch_size x torch.rand(1).item() == torch.rand(batch_size) on the same stream
-            return torch.rand(batch_size).to(dev, non_blocking=True)
+            with torch.cuda.device(dev):
+                slot, host = self._stage().host_view(batch_size, torch.float32)
+                torch.rand(batch_size, out=host)
+                return self._stage().push(slot, host)
         with torch.cuda.device(dev):
             raw = xp.philox_u32(self._philox_seed, self._philox_offset, batch_size, dev)
         self._philox_offset += (batch_size + 3) // 4
@@ -429,6 +440,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
     def sample(self, batch_size: int, beta: float = 0.4, u: torch.Tensor | None = None) -> TensorBatch:
         """``u`` (optional): the fp32 uniforms to use instead of drawing them."""
         _, _, st, h = self._ensure_trees()
+        self._raise_deferred()
         dev = self.storage_device
         if u is None:
             u = self._draw_uniforms(batch_size)
@@ -442,21 +454,58 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         samples["idxs"] = idx.unsqueeze(1)
         return self._out(samples)
 
+    def _raise_deferred(self) -> None:
+        """Out-of-range indices that arrived as DEVICE tensors are detected by the kernel; the
+        flag is read back without blocking and the AssertionError surfaces on the next call."""
+        pend = getattr(self, "_pending_err", None)
+        if pend is not None and pend[1].query():
+            self._pending_err = None
+            if int(pend[0][0]) != 0:
+                self._trees[2].err.zero_()
+                raise AssertionError("priority index out of range [0, max_size)")
+
     def update_priorities(self, indices, priorities, check: bool = True) -> None:
         """Sequential semantics of :411-428 in one batched pass (last writer wins; every
-        priority, overwritten or not, counts towards ``max_priority``)."""
+        priority, overwritten or not, counts towards ``max_priority``).
+
+        Never blocks the host: host-side indices (numpy / CPU tensors) are range-checked on the
+        host (AssertionError as in :319); device-side indices are checked by the kernel and the
+        error is raised on the next call into the buffer."""
         _, _, st, h = self._ensure_trees()
         dev = self.storage_device
-        idx = torch.as_tensor(indices).to(device=dev, dtype=torch.int64).contiguous().view(-1)
-        pr = torch.as_tensor(priorities)
-        if pr.dtype != torch.float32:
-            # priority.item() of a float64 array keeps fp64; the kernel takes fp32 inputs, which
-            # is what the algorithms produce (dqn_rainbow.py:487-488)
-            pr = pr.to(torch.float32)
-        pr = pr.to(device=dev).contiguous().view(-1)
-        n = min(idx.numel(), pr.numel())  # zip(..., strict=False)
+        self._raise_deferred()
+        idx = torch.as_tensor(indices)
+        on_host = not idx.is_cuda
+        if on_host and check and idx.numel():
+            assert 0 <= int(idx.min()) and int(idx.max()) < self.max_size, (
+                "priority index out of range [0, max_size)")
         with torch.cuda.device(dev):
+            if on_host:
+                idx = self._stage().to_device(idx.to(torch.int64).reshape(-1))
+            else:
+                idx = idx.to(device=dev, dtype=torch.int64).contiguous().view(-1)
+            pr = torch.as_tensor(priorities)
+            if pr.dtype != torch.float32:
+                # priority.item() of a float64 array keeps fp64; the kernel takes fp32 inputs,
+                # which is what the algorithms produce (dqn_rainbow.py:487-488)
+                pr = pr.to(torch.float32)
+            if pr.is_cuda:
+                pr = pr.to(device=dev).contiguous().view(-1)
+            else:
+                pr = self._stage().to_device(pr.reshape(-1))
+            n = min(idx.numel(), pr.numel())  # zip(..., strict=False)
             xp.per_update(h, self._state, idx[:n], pr[:n], self.max_size, self.alpha, st.err)
-        if check and int(st.err.item()) != 0:
-            st.err.zero_()
-            raise AssertionError("priority index out of range [0, max_size)")
+            if check and not on_host:
+                if not hasattr(self, "_err_pin"):
+                    self._err_pin = torch.zeros(1, dtype=torch.int32).pin_memory()
+                self._err_pin.copy_(st.err, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                self._pending_err = (self._err_pin, ev)
+
+    def check_errors(self) -> None:
+        """Block until every queued update ran and raise its index error, if any."""
+        pend = getattr(self, "_pending_err", None)
+        if pend is not None:
+            pend[1].synchronize()
+            self._raise_deferred()

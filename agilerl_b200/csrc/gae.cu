@@ -1,19 +1,24 @@
 // gae.cu — reverse-time scans for RolloutBuffer.compute_returns_and_advantages
 // (reference: agilerl/components/rollout_buffer.py:413-481).
 //
-// Parallelism: one lane per (env, agent); time is walked sequentially with an fp64 carry so
-// that the rounding sequence is the reference's (a re-associated parallel-in-time scan is
-// not bit-compatible).  Memory-level parallelism comes from staging [TC x 32 env] tiles of
-// rewards/values/dones through shared memory with cp.async, several stages ahead of the
-// scan (kernel gae_staged), so the whole input of a CTA is in flight long before it is used.
-// A direct kernel (gae_direct) covers shapes the staged one does not (N % 16 != 0).
+// The recurrence carry_t = A_t + K_t * carry_{t+1} must be evaluated in the reference's order
+// with an fp64 carry (a re-associated parallel-in-time scan is not bit-compatible), so the chain
+// itself is one lane per (env, agent).  Everything that does NOT depend on the carry is hoisted
+// out of the chain and done by the whole CTA with full memory-level parallelism:
+//
+//   phase 1 (256 threads): a [TC x 32 env] tile of rewards / values / dones is read with 128-bit
+//           coalesced loads and turned into A_t (fp64), the value v_t and a "terminal" flag in
+//           shared memory;
+//   phase 2 (warp 0, lane = env): the serial chain — per step two dependent fp64 ops fed from
+//           shared memory — writing adv/ret rows (128 B per warp store, coalesced);
+// several CTAs per SM overlap each other's phases.  T > TC is walked in chunks, newest first.
 //
 // Arithmetic (all separately rounded, no FMA contraction):
 //   GAE  (:448-467)  nnt   = 1 - done[t+1]                      (fp64; last_done at t=T-1)
 //                    g_nv  = f64(f32(gamma) * v[t+1])            (fp32 product, t < T-1)
 //                          = gamma * last_value                  (fp64 product, t = T-1)
-//                    delta = (f64(r[t]) + g_nv*nnt) - f64(v[t])
-//                    carry = delta + ((gamma*lambda)*nnt)*carry  (fp64)
+//                    A_t   = (f64(r[t]) + g_nv*nnt) - f64(v[t])  ("delta")
+//                    carry = A_t + ((gamma*lambda)*nnt)*carry    (fp64)
 //                    adv[t] = f32(carry);  ret[t] = adv[t] +f32 v[t]
 //   MC   (:468-477)  G = last_value*(1-last_done);  G = f64(r[t]) + (gamma*G)*(1-done[t])
 //                    ret[t] = f32(G);  adv[t] = ret[t] -f32 v[t]
@@ -38,202 +43,213 @@ struct ScanParams {
   float gamma32;   // f32(gamma): NEP-50 weak-scalar product with a float32 array
 };
 
-// One reverse-time step. `v_next`/`d_next` are v[t+1], done[t+1] (unused at t = T-1).
-template <int MODE>
-__device__ __forceinline__ void scan_step(const ScanParams &p, bool is_last, float r, float v,
-                                          uint8_t d, float v_next, uint8_t d_next, double lv,
-                                          double ld, double &carry, float &adv, float &ret) {
-  if (MODE == kModeGae) {
-    double nnt, g_nv;
-    if (is_last) {
-      nnt = __dsub_rn(1.0, ld);
-      g_nv = __dmul_rn(p.gamma, lv);
-    } else {
-      nnt = __dsub_rn(1.0, d_next ? 1.0 : 0.0);
-      g_nv = (double)__fmul_rn(p.gamma32, v_next);
-    }
-    double delta = __dsub_rn(__dadd_rn((double)r, __dmul_rn(g_nv, nnt)), (double)v);
-    carry = __dadd_rn(delta, __dmul_rn(__dmul_rn(p.gl, nnt), carry));
-    adv = __double2float_rn(carry);
-    ret = __fadd_rn(adv, v);
-  } else {
-    double nt = __dsub_rn(1.0, d ? 1.0 : 0.0);
-    carry = __dadd_rn((double)r, __dmul_rn(__dmul_rn(p.gamma, carry), nt));
-    ret = __double2float_rn(carry);
-    adv = __fsub_rn(ret, v);
-  }
-}
+constexpr int kEnv = 32;       // envs per CTA (one chain warp)
+constexpr int kTC = 128;       // time steps per chunk
+constexpr int kThreads = 256;
 
-// ---- direct kernel: any shape -----------------------------------------------------------
-// lane -> env (coalesced 128 B rows per warp), register prefetch of U time steps.
-template <int MODE, int U>
-__global__ void __launch_bounds__(128) gae_direct(const ScanParams p) {
-  const long long lane_global = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (lane_global >= p.N * p.P) return;
-  const long long agent = lane_global / p.N;
-  const long long env = lane_global - agent * p.N;
-  const long long base = agent * p.agent_stride + env;
-  const float *rw = p.rewards + base;
-  const float *vl = p.values + base;
-  const uint8_t *dn = p.dones + base;
-  float *adv = p.adv + base;
-  float *ret = p.ret + base;
-  const double lv = p.last_value[agent * p.N + env];
-  const double ld = p.last_done[agent * p.N + env];
-
-  double carry = (MODE == kModeGae) ? 0.0 : __dmul_rn(lv, __dsub_rn(1.0, ld));
-  float v_next = 0.f;
-  uint8_t d_next = 0;
-  long long t = p.T - 1;
-  while (t >= 0) {
-    float r[U], v[U];
-    uint8_t d[U];
-#pragma unroll
-    for (int j = 0; j < U; ++j) {
-      long long tt = t - j;
-      if (tt >= 0) {
-        r[j] = __ldg(rw + tt * p.N);
-        v[j] = __ldg(vl + tt * p.N);
-        d[j] = __ldg(dn + tt * p.N);
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < U; ++j) {
-      long long tt = t - j;
-      if (tt >= 0) {
-        float a, g;
-        scan_step<MODE>(p, tt == p.T - 1, r[j], v[j], d[j], v_next, d_next, lv, ld, carry, a, g);
-        adv[tt * p.N] = a;
-        ret[tt * p.N] = g;
-        v_next = v[j];
-        d_next = d[j];
-      }
-    }
-    t -= U;
-  }
-}
-
-// ---- staged kernel: N % 16 == 0 ------------------------------------------------------------
-// One warp per CTA owns 32 consecutive envs of one agent.  Time is cut into chunks of TC
-// steps; a ring of S stages of [TC x 32] tiles (r, v fp32; d u8) is filled with cp.async
-// (16 B for r/v, 4 B for d... both row-contiguous), S-1 chunks ahead of the scan.
-constexpr int kTC = 16;
-constexpr int kStages = 8;
-
-struct __align__(16) StageTile {
-  float r[kTC][32];
-  float v[kTC][32];
-  uint8_t d[kTC][32];
+struct __align__(16) Tile {
+  double a[kTC][kEnv];   // A_t
+  float v[kTC][kEnv];    // v_t
+  uint8_t f[kTC][kEnv];  // GAE: done[t+1] (terminal flag of the NEXT step); MC: done[t]
 };
 
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
-  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
-  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+// A_t for one element.  v_next / d_next are ignored at the global last step.
+template <int MODE>
+__device__ __forceinline__ double make_a(const ScanParams &p, bool is_last, float r, float v,
+                                         float v_next, uint8_t d_next, double lv, double ld) {
+  if (MODE == kModeMc) return (double)r;
+  double nnt, g_nv;
+  if (is_last) {
+    nnt = __dsub_rn(1.0, ld);
+    g_nv = __dmul_rn(p.gamma, lv);
+  } else {
+    nnt = d_next ? 0.0 : 1.0;  // 1.0 - float(done)
+    g_nv = (double)__fmul_rn(p.gamma32, v_next);
+  }
+  return __dsub_rn(__dadd_rn((double)r, __dmul_rn(g_nv, nnt)), (double)v);
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(32) gae_staged(const ScanParams p) {
-  __shared__ StageTile stage[kStages];
-  const int lane = threadIdx.x;
-  const long long tiles_per_agent = p.N / 32;  // N % 32 == 0 guaranteed by the launcher
+template <int MODE, bool VEC>
+__global__ void __launch_bounds__(kThreads, 4) gae_tile_kernel(const ScanParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Tile &tile = *reinterpret_cast<Tile *>(smem_raw);
+  const long long tiles_per_agent = (p.N + kEnv - 1) / kEnv;
   const long long agent = blockIdx.x / tiles_per_agent;
-  const long long env0 = (blockIdx.x - agent * tiles_per_agent) * 32;
+  const long long env0 = (blockIdx.x - agent * tiles_per_agent) * kEnv;
   const long long base = agent * p.agent_stride + env0;
   const float *rw = p.rewards + base;
   const float *vl = p.values + base;
   const uint8_t *dn = p.dones + base;
-  float *adv = p.adv + base + lane;
-  float *ret = p.ret + base + lane;
-  const double lv = p.last_value[agent * p.N + env0 + lane];
-  const double ld = p.last_done[agent * p.N + env0 + lane];
+  const int n_env = (int)((p.N - env0) < kEnv ? (p.N - env0) : kEnv);
 
-  const long long n_chunks = (p.T + kTC - 1) / kTC;
-  // chunk c covers t in [T-1-c*TC-(TC-1), T-1-c*TC] (reverse order), row j <-> t = t_hi - j
+  // chain state (warp 0 only)
+  const int lane = threadIdx.x;
+  double carry = 0.0, lv = 0.0, ld = 0.0;
+  if (threadIdx.x < kEnv && lane < n_env) {
+    lv = p.last_value[agent * p.N + env0 + lane];
+    ld = p.last_done[agent * p.N + env0 + lane];
+    if (MODE == kModeMc) carry = __dmul_rn(lv, __dsub_rn(1.0, ld));
+  }
+  const double k1 = (MODE == kModeGae) ? __dmul_rn(p.gl, 1.0) : 1.0;
+  const double k0 = (MODE == kModeGae) ? __dmul_rn(p.gl, 0.0) : 0.0;
 
-  auto issue = [&](long long c) {
-    if (c < n_chunks) {
-      StageTile &st = stage[c % kStages];
-      const long long t_hi = p.T - 1 - c * kTC;
-      // r, v: TC rows x 128 B = TC*8 16-byte pieces each; 32 lanes -> TC/4 pieces per lane
+  for (long long t_hi = p.T - 1; t_hi >= 0; t_hi -= kTC) {
+    const int rows = (int)((t_hi + 1) < kTC ? (t_hi + 1) : kTC);  // row j <-> t = t_hi - j
+    // ---- phase 1: stage A, v, flag -------------------------------------------------------
+    if (VEC) {
+      // thread -> (row = tid/8 + 32*k, 4 consecutive envs)
+      const int c4 = (threadIdx.x & 7) * 4;
+#pragma unroll 1
+      for (int half = 0; half < 2; ++half) {
+      float4 r4[2], v4[2], vn4[2];
+      uchar4 d4[2];
 #pragma unroll
-      for (int k = 0; k < kTC / 4; ++k) {
-        int piece = k * 32 + lane;
-        int row = piece >> 3, col = (piece & 7) * 4;
-        long long tt = t_hi - row;
-        if (tt >= 0) {
-          cp_async16(&st.r[row][col], rw + tt * p.N + col);
-          cp_async16(&st.v[row][col], vl + tt * p.N + col);
+      for (int k = 0; k < 2; ++k) {
+        const int row = (threadIdx.x >> 3) + 32 * (2 * half + k);
+        const long long t = t_hi - row;
+        r4[k] = v4[k] = vn4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        d4[k] = make_uchar4(0, 0, 0, 0);
+        if (row < rows && c4 < n_env) {
+          r4[k] = __ldcs(reinterpret_cast<const float4 *>(rw + t * p.N + c4));
+          v4[k] = __ldg(reinterpret_cast<const float4 *>(vl + t * p.N + c4));
+          if (MODE == kModeGae) {
+            if (t + 1 < p.T) {
+              vn4[k] = __ldg(reinterpret_cast<const float4 *>(vl + (t + 1) * p.N + c4));
+              d4[k] = __ldg(reinterpret_cast<const uchar4 *>(dn + (t + 1) * p.N + c4));
+            } else {
+              vn4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+              d4[k] = make_uchar4(0, 0, 0, 0);
+            }
+          } else {
+            d4[k] = __ldg(reinterpret_cast<const uchar4 *>(dn + t * p.N + c4));
+          }
         }
       }
-      // d: TC rows x 32 B = TC*8 4-byte pieces
 #pragma unroll
-      for (int k = 0; k < kTC / 4; ++k) {
-        int piece = k * 32 + lane;
-        int row = piece >> 3, col = (piece & 7) * 4;
-        long long tt = t_hi - row;
-        if (tt >= 0) cp_async4(&st.d[row][col], dn + tt * p.N + col);
+      for (int k = 0; k < 2; ++k) {
+        const int row = (threadIdx.x >> 3) + 32 * (2 * half + k);
+        const long long t = t_hi - row;
+        if (row < rows && c4 < n_env) {
+          const bool is_last = (t == p.T - 1);
+          const float rr[4] = {r4[k].x, r4[k].y, r4[k].z, r4[k].w};
+          const float vv[4] = {v4[k].x, v4[k].y, v4[k].z, v4[k].w};
+          const float vn[4] = {vn4[k].x, vn4[k].y, vn4[k].z, vn4[k].w};
+          const uint8_t dd[4] = {d4[k].x, d4[k].y, d4[k].z, d4[k].w};
+          double a[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            double lve = 0.0, lde = 0.0;
+            if (MODE == kModeGae && is_last) {
+              lve = p.last_value[agent * p.N + env0 + c4 + e];
+              lde = p.last_done[agent * p.N + env0 + c4 + e];
+            }
+            a[e] = make_a<MODE>(p, is_last, rr[e], vv[e], vn[e], dd[e], lve, lde);
+          }
+          *reinterpret_cast<double2 *>(&tile.a[row][c4]) = make_double2(a[0], a[1]);
+          *reinterpret_cast<double2 *>(&tile.a[row][c4 + 2]) = make_double2(a[2], a[3]);
+          *reinterpret_cast<float4 *>(&tile.v[row][c4]) = v4[k];
+          *reinterpret_cast<uchar4 *>(&tile.f[row][c4]) = d4[k];
+        }
+      }
+      }
+    } else {
+      // any N / alignment: thread -> (row = tid/32 + 8*k, env = tid%32), 128 B per warp per row
+      const int e = threadIdx.x & 31;
+      for (int row = threadIdx.x >> 5; row < rows; row += kThreads / 32) {
+        const long long t = t_hi - row;
+        if (e < n_env) {
+          const bool is_last = (t == p.T - 1);
+          const float r = __ldg(rw + t * p.N + e);
+          const float v = __ldg(vl + t * p.N + e);
+          float vn = 0.f;
+          uint8_t d = 0;
+          double lve = 0.0, lde = 0.0;
+          if (MODE == kModeGae) {
+            if (!is_last) {
+              vn = __ldg(vl + (t + 1) * p.N + e);
+              d = __ldg(dn + (t + 1) * p.N + e);
+            } else {
+              lve = p.last_value[agent * p.N + env0 + e];
+              lde = p.last_done[agent * p.N + env0 + e];
+            }
+          } else {
+            d = __ldg(dn + t * p.N + e);
+          }
+          tile.a[row][e] = make_a<MODE>(p, is_last, r, v, vn, d, lve, lde);
+          tile.v[row][e] = v;
+          tile.f[row][e] = d;
+        }
       }
     }
-    cp_async_commit();  // empty groups keep the wait_group arithmetic uniform
-  };
-
+    __syncthreads();
+    // ---- phase 2: the chain, lane = env ------------------------------------------------------
+    if (threadIdx.x < kEnv && lane < n_env) {
+      float *adv = p.adv + base + lane;
+      float *ret = p.ret + base + lane;
+      constexpr int U = 8;
+      for (int j0 = 0; j0 < rows; j0 += U) {
+        double a[U];
+        float v[U];
+        uint8_t f[U];
 #pragma unroll
-  for (int c = 0; c < kStages - 1; ++c) issue(c);
-
-  double carry = (MODE == kModeGae) ? 0.0 : __dmul_rn(lv, __dsub_rn(1.0, ld));
-  float v_next = 0.f;
-  uint8_t d_next = 0;
-  for (long long c = 0; c < n_chunks; ++c) {
-    issue(c + kStages - 1);
-    cp_async_wait<kStages - 1>();  // chunk c has landed
-    __syncwarp();
-    const StageTile &st = stage[c % kStages];
-    const long long t_hi = p.T - 1 - c * kTC;
+        for (int u = 0; u < U; ++u) {
+          const int j = (j0 + u < rows) ? j0 + u : rows - 1;
+          a[u] = tile.a[j][lane];
+          v[u] = tile.v[j][lane];
+          f[u] = tile.f[j][lane];
+        }
 #pragma unroll
-    for (int j = 0; j < kTC; ++j) {
-      long long tt = t_hi - j;
-      if (tt >= 0) {
-        float r = st.r[j][lane], v = st.v[j][lane];
-        uint8_t d = st.d[j][lane];
-        float a, g;
-        scan_step<MODE>(p, tt == p.T - 1, r, v, d, v_next, d_next, lv, ld, carry, a, g);
-        __stcs(adv + tt * p.N, a);
-        __stcs(ret + tt * p.N, g);
-        v_next = v;
-        d_next = d;
+        for (int u = 0; u < U; ++u) {
+          const int j = j0 + u;
+          if (j < rows) {
+            const long long t = t_hi - j;
+            float av, rv;
+            if (MODE == kModeGae) {
+              double k = f[u] ? k0 : k1;
+              if (t == p.T - 1) k = __dmul_rn(p.gl, __dsub_rn(1.0, ld));
+              carry = __dadd_rn(a[u], __dmul_rn(k, carry));
+              av = __double2float_rn(carry);
+              rv = __fadd_rn(av, v[u]);
+            } else {
+              const double nt = f[u] ? 0.0 : 1.0;
+              carry = __dadd_rn(a[u], __dmul_rn(__dmul_rn(p.gamma, carry), nt));
+              rv = __double2float_rn(carry);
+              av = __fsub_rn(rv, v[u]);
+            }
+            __stcs(adv + t * p.N, av);
+            __stcs(ret + t * p.N, rv);
+          }
+        }
       }
     }
-    __syncwarp();  // everyone is done with this stage before it is refilled
+    __syncthreads();  // the tile is refilled by the next chunk
   }
-  cp_async_wait<0>();
 }
 
 template <int MODE>
 xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   if (p.T == 0 || p.N == 0 || p.P == 0) return XP_OK;
-  const bool aligned =
-      (p.N % 32 == 0) && (p.agent_stride % 16 == 0) &&
-      ((reinterpret_cast<uintptr_t>(p.rewards) | reinterpret_cast<uintptr_t>(p.values) |
-        reinterpret_cast<uintptr_t>(p.dones)) % 16 == 0);
-  if (aligned) {
-    long long grid = (p.N / 32) * p.P;
-    XP_REQUIRE(grid < (1ll << 31), XP_ERR_INVALID, "xp_gae: grid too large");
-    gae_staged<MODE><<<(unsigned)grid, 32, 0, s>>>(p);
-  } else {
-    long long lanes = p.N * p.P;
-    long long grid = (lanes + 127) / 128;
-    XP_REQUIRE(grid < (1ll << 31), XP_ERR_INVALID, "xp_gae: grid too large");
-    gae_direct<MODE, 8><<<(unsigned)grid, 128, 0, s>>>(p);
+  const bool vec =
+      (p.N % 4 == 0) && (p.agent_stride % 4 == 0) &&
+      (reinterpret_cast<uintptr_t>(p.rewards) % 16 == 0) &&
+      (reinterpret_cast<uintptr_t>(p.values) % 16 == 0) &&
+      (reinterpret_cast<uintptr_t>(p.dones) % 4 == 0);
+  const long long grid = ((p.N + kEnv - 1) / kEnv) * p.P;
+  XP_REQUIRE(grid < (1ll << 31), XP_ERR_INVALID, "xp_gae: grid too large");
+  static bool attr[2][2] = {{false, false}, {false, false}};
+  const void *fn = vec ? (const void *)gae_tile_kernel<MODE, true> : (const void *)gae_tile_kernel<MODE, false>;
+  if (!attr[MODE][vec]) {
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Tile));
+    if (e != cudaSuccess) {
+      xp::set_error("xp_gae: %s", cudaGetErrorString(e));
+      return XP_ERR_CUDA;
+    }
+    attr[MODE][vec] = true;
   }
+  if (vec)
+    gae_tile_kernel<MODE, true><<<(unsigned)grid, kThreads, sizeof(Tile), s>>>(p);
+  else
+    gae_tile_kernel<MODE, false><<<(unsigned)grid, kThreads, sizeof(Tile), s>>>(p);
   return xp::check_launch("xp_gae");
 }
 

@@ -5,29 +5,20 @@
 // buffer interleaves (sum,min) per node (stride 2) so that the two children of a node in both
 // trees are one aligned 32-byte sector.
 //
-// Batched set (B sequential `tree[idx] = val` of the reference, segment_tree.py:81-95):
-//   K1 ticket : atomicMax(aux[cap+idx], i+1)              -> last writer per leaf
-//   K2 mark   : winner writes its leaf, then walks up doing atomicAdd(aux[parent], 1); it stops
-//               at the first parent that was already marked.  aux[p] = number of dirty children.
-//   K3 rebuild: winner walks up again; at each parent atomicSub(aux[p], 1); only the LAST
-//               arriving dirty child (old == 1) recomputes p = op(left, right) from final
-//               children and continues.  aux returns to all-zero.
-// Every touched internal node is recomputed exactly once, after both children are final, so the
-// result is bit-identical to the reference's sequential root walks (same operands, same op).
+// The batched set (B sequential `tree[idx] = val` of the reference, segment_tree.py:81-95) lives
+// in tree_set.cuh: sorted level-synchronous climbs, no global atomics on the tree.
 #include "common.cuh"
 #include "pow.cuh"
+#include "tree_set.cuh"
 
 namespace {
 
-struct Tree {
-  double *sum;
-  double *mn;
-  long long stride;
-  long long cap;
-  int *aux;
-};
-
-__device__ __forceinline__ double py_min(double a, double b) { return (b < a) ? b : a; }
+using xpset::py_min;
+using xpset::SetSrc;
+using xpset::Tree;
+using xpset::kSrcPrio;
+using xpset::kSrcRange;
+using xpset::kSrcVal;
 
 // ---- init ---------------------------------------------------------------------------------
 __global__ void tree_init_kernel(Tree t) {
@@ -38,121 +29,6 @@ __global__ void tree_init_kernel(Tree t) {
     if (t.mn) t.mn[i * t.stride] = __longlong_as_double(0x7ff0000000000000ll);
     if (t.aux) t.aux[i] = 0;
   }
-}
-
-// ---- batched set ------------------------------------------------------------------------------
-// Source of (idx, value) for item i of a batch.
-enum { kSrcVal = 0, kSrcPrio = 1, kSrcRange = 2 };
-struct SetSrc {
-  int kind;
-  const long long *idx;   // kSrcVal / kSrcPrio
-  const double *val;      // kSrcVal
-  const float *prio;      // kSrcPrio: leaf = max(f64(prio), 1e-5) ** alpha
-  double alpha;
-  unsigned long long *max_priority_bits;  // device xp_per_state.max_priority (positive double)
-  long long range_start, range_mod;       // kSrcRange: idx = (start + i) % mod, value = max_priority ** alpha
-  long long limit;                        // valid idx in [0, limit)
-  int *err;
-};
-
-__device__ __forceinline__ long long src_idx(const SetSrc &s, long long i) {
-  if (s.kind == kSrcRange) {
-    long long x = s.range_start + i;
-    return x >= s.range_mod ? x - s.range_mod : x;
-  }
-  return s.idx[i];
-}
-
-__global__ void set_ticket_kernel(Tree t, SetSrc s, long long B) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  double p = 0.0;
-  if (i < B) {
-    const long long idx = s.idx[i];
-    if (idx < 0 || idx >= s.limit) {
-      if (s.err) *s.err = 1;
-    } else {
-      atomicMax(&t.aux[t.cap + idx], (int)(i + 1));
-      if (s.kind == kSrcPrio) {
-        // new_priority = max(priority.item(), 1e-5)  (replay_buffer.py:425); Python max keeps
-        // the first argument unless the second is greater.
-        double q = (double)s.prio[i];
-        p = (1e-5 > q) ? 1e-5 : q;
-      }
-    }
-  }
-  if (s.kind == kSrcPrio) {
-    // max_priority = max(max_priority, p) over every item, overwritten duplicates included (:329)
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) p = fmax(p, __shfl_xor_sync(0xffffffffu, p, o));
-    if ((threadIdx.x & 31) == 0 && p > 0.0)
-      atomicMax(s.max_priority_bits, (unsigned long long)__double_as_longlong(p));
-  }
-}
-
-template <bool UNIQUE>
-__global__ void set_mark_kernel(Tree t, SetSrc s, long long B) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B) return;
-  const long long idx = src_idx(s, i);
-  if (idx < 0 || idx >= s.limit) return;
-  long long n = t.cap + idx;
-  if (!UNIQUE && t.aux[n] != (int)(i + 1)) return;  // a later item overwrites this leaf
-  double v;
-  if (s.kind == kSrcVal) {
-    v = s.val[i];
-  } else if (s.kind == kSrcPrio) {
-    double q = (double)s.prio[i];
-    q = (1e-5 > q) ? 1e-5 : q;
-    v = xp::xp_pow(q, s.alpha);
-  } else {
-    v = xp::xp_pow(__longlong_as_double((long long)*s.max_priority_bits), s.alpha);
-  }
-  if (t.sum) __stcg(&t.sum[n * t.stride], v);
-  if (t.mn) __stcg(&t.mn[n * t.stride], v);
-  while (n > 1) {
-    const long long p = n >> 1;
-    if (atomicAdd(&t.aux[p], 1) != 0) break;  // p (and its ancestors) already marked
-    n = p;
-  }
-}
-
-template <bool UNIQUE>
-__global__ void set_rebuild_kernel(Tree t, SetSrc s, long long B) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B) return;
-  const long long idx = src_idx(s, i);
-  if (idx < 0 || idx >= s.limit) return;
-  long long n = t.cap + idx;
-  if (!UNIQUE) {
-    if (t.aux[n] != (int)(i + 1)) return;
-    t.aux[n] = 0;  // ticket consumed; aux is all-zero again when the kernel ends
-  }
-  while (n > 1) {
-    const long long p = n >> 1;
-    __threadfence();  // publish tree[n] before announcing arrival
-    if (atomicSub(&t.aux[p], 1) != 1) break;  // the other dirty child will finish p
-    __threadfence();
-    const long long l = 2 * p * t.stride, r = (2 * p + 1) * t.stride;
-    if (t.sum) __stcg(&t.sum[p * t.stride], __dadd_rn(__ldcg(&t.sum[l]), __ldcg(&t.sum[r])));
-    if (t.mn) __stcg(&t.mn[p * t.stride], py_min(__ldcg(&t.mn[l]), __ldcg(&t.mn[r])));
-    n = p;
-  }
-}
-
-xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, bool unique, cudaStream_t st) {
-  if (B == 0) return XP_OK;
-  XP_REQUIRE(B < (1ll << 31) - 1, XP_ERR_INVALID, "tree set: batch too large");
-  const int threads = 256;
-  const unsigned grid = (unsigned)((B + threads - 1) / threads);
-  if (!unique) {
-    set_ticket_kernel<<<grid, threads, 0, st>>>(t, s, B);
-    set_mark_kernel<false><<<grid, threads, 0, st>>>(t, s, B);
-    set_rebuild_kernel<false><<<grid, threads, 0, st>>>(t, s, B);
-  } else {
-    set_mark_kernel<true><<<grid, threads, 0, st>>>(t, s, B);
-    set_rebuild_kernel<true><<<grid, threads, 0, st>>>(t, s, B);
-  }
-  return xp::check_launch("tree set", unique ? 2 : 3);
 }
 
 // ---- queries ----------------------------------------------------------------------------------
@@ -294,7 +170,7 @@ xp_status_t xp_tree_set_batch(const xp_tree *tree, const int64_t *idx_dev, const
   s.val = val_dev;
   s.limit = t.cap;
   s.err = err_flag_dev;
-  return run_set(t, s, B, false, (cudaStream_t)stream);
+  return xpset::run_set(t, s, B, (cudaStream_t)stream);
 }
 
 xp_status_t xp_tree_query(const xp_tree *tree, int64_t start, int64_t end, double *out_dev,
@@ -343,7 +219,7 @@ xp_status_t xp_per_add(const xp_tree *tree, xp_per_state *state_dev, int64_t tre
   // n >= max_size touches every leaf of [0,max_size) with one value: same set, no duplicates.
   s.range_start = (n >= max_size) ? 0 : tree_ptr;
   const long long count = (n >= max_size) ? max_size : n;
-  return run_set(t, s, count, true, (cudaStream_t)stream);
+  return xpset::run_set(t, s, count, (cudaStream_t)stream);
 }
 
 xp_status_t xp_per_sample(const xp_tree *tree, const float *u_dev, int64_t B, int64_t P,
@@ -394,7 +270,7 @@ xp_status_t xp_per_update(const xp_tree *tree, xp_per_state *state_dev, const in
   s.max_priority_bits = (unsigned long long *)&state_dev->max_priority;
   s.limit = max_size;
   s.err = err_flag_dev;
-  return run_set(t, s, B, false, (cudaStream_t)stream);
+  return xpset::run_set(t, s, B, (cudaStream_t)stream);
 }
 
 xp_status_t xp_pow_batch(const double *x_dev, double y, double *out_dev, int64_t n, void *stream) {

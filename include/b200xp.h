@@ -90,8 +90,9 @@ typedef struct xp_tree {
   double *min;     /* device; node i at min[i*stride]; init +inf  (segment_tree.py:170) */
   int64_t stride;  /* in doubles                                                        */
   int64_t cap;     /* power of two                                                      */
-  int32_t *aux;    /* device int32[2*cap], zero between calls: leaf slots [cap,2cap) hold
-                      the last-writer ticket, internal slots [1,cap) the pending count   */
+  int32_t *aux;    /* device int32[2*cap] scratch owned by the library after xp_tree_init
+                      (which zeroes it): [cap,2cap) last-writer tickets (zero between calls),
+                      [0,cap) bucket counters / bucketed items of large batches          */
 } xp_tree;
 
 /* fill all nodes with the initial values (SegmentTree.__init__, segment_tree.py:25).    */

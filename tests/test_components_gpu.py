@@ -458,3 +458,16 @@ def test_rollout_arena_one_launch_equals_per_agent(C):
         a, g2 = xo.gae(r["rewards"].cpu().numpy(), r["values"].cpu().numpy(), r["dones"].cpu().numpy(),
                        lv[p], ld[p], 0.99, 0.95)
         assert np.array_equal(arena.buffers[p].buffer["advantages"].cpu().numpy(), a)
+
+
+def test_per_update_device_indices_error_is_deferred_not_lost(C):
+    """Device-resident indices are range-checked by the kernel; the AssertionError of
+    replay_buffer.py:319 surfaces on the next call (or check_errors()) instead of blocking."""
+    b = C.PrioritizedReplayBuffer(max_size=8, alpha=0.6, device="cuda:0")
+    b.add(C.TensorBatch({"obs": torch.zeros(4, 2), "reward": torch.zeros(4)}, batch_size=[4]))
+    bad = torch.tensor([1, 99], device="cuda:0")
+    b.update_priorities(bad, torch.tensor([1.0, 2.0]))
+    with pytest.raises(AssertionError):
+        b.check_errors()
+    b.update_priorities(torch.tensor([1, 2], device="cuda:0"), torch.tensor([1.0, 2.0]))
+    b.check_errors()

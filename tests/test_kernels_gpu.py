@@ -52,7 +52,7 @@ def test_gae_golden_bitwise(xp, cuda_device, seed):
     assert np.array_equal(adv[0], g["adv_mc"]) and np.array_equal(ret[0], g["ret_mc"])
 
 
-@pytest.mark.parametrize("shape", [(3, 50, 96), (2, 1, 32), (1, 7, 1), (4, 130, 64), (2, 33, 40)])
+@pytest.mark.parametrize("shape", [(3, 50, 96), (2, 1, 32), (1, 7, 1), (4, 130, 64), (2, 33, 40), (1, 300, 33), (2, 257, 132)])
 @pytest.mark.parametrize("use_gae", [True, False])
 def test_gae_population_vs_oracle(xp, cuda_device, shape, use_gae):
     P, T, N = shape
@@ -152,8 +152,11 @@ def test_tree_non_pow2_capacity_is_assertion(xp, cuda_device):
         xp.tree_init(bad, 0)
 
 
+# schedules of tree_set.cuh: S (B <= 2048, 1/2/4 items per thread), L (bucketed), D (dense)
 @pytest.mark.parametrize("cap,B,interleaved", [(1, 3, True), (2, 5, False), (64, 40, True),
-                                               (4096, 256, True), (4096, 5000, False), (1 << 16, 20000, True)])
+                                               (4096, 256, True), (4096, 5000, False), (1 << 16, 20000, True),
+                                               (1 << 14, 700, False), (1 << 16, 1500, True), (1 << 16, 2048, True),
+                                               (1 << 18, 3000, True), (1 << 12, 1 << 12, True)])
 def test_tree_set_batch_equals_sequential_reference(xp, cuda_device, cap, B, interleaved):
     rng = np.random.default_rng(cap + B)
     t = DevTree(xp, cuda_device, cap, interleaved)
@@ -169,7 +172,7 @@ def test_tree_set_batch_equals_sequential_reference(xp, cuda_device, cap, B, int
             m[int(i)] = float(x)
         ds, dm = t.arrays()
         assert np.array_equal(ds, np.array(s.tree)) and np.array_equal(dm, np.array(m.tree))
-        assert int(t.aux.abs().sum()) == 0  # scratch returned to zero
+        assert int(t.aux[cap:].abs().sum()) == 0  # last-writer tickets consumed
     # descents: bit-exact indices for random upper bounds, incl. both ends
     total = s.operate()
     ub = np.concatenate([rng.random(512) * total, [0.0, total]])
@@ -182,6 +185,38 @@ def test_tree_set_batch_equals_sequential_reference(xp, cuda_device, cap, B, int
             continue
         q = t.query(int(a), int(b))
         assert q[0] == s.operate(int(a), int(b)) and q[1] == m.operate(int(a), int(b))
+
+
+@pytest.mark.parametrize("pattern", ["sorted", "one_bucket", "one_leaf", "two_leaves_far"])
+@pytest.mark.parametrize("cap,B", [(1 << 10, 300), (1 << 16, 2000), (1 << 16, 9000)])
+def test_tree_set_batch_adversarial_patterns(xp, cuda_device, pattern, cap, B):
+    """sorted input (the PER fast path), every update in one bucket subtree (oversize bucket:
+    several passes), every update on one leaf (one long duplicate run), two far leaves."""
+    rng = np.random.default_rng(cap + B)
+    t = DevTree(xp, cuda_device, cap, True)
+    s, m = xo.SegTree(cap, "sum"), xo.SegTree(cap, "min")
+    base = rng.integers(0, cap, cap // 2)
+    bv = rng.random(cap // 2) + 0.5
+    t.set(base, bv)
+    for i, x in zip(base, bv):
+        s[int(i)] = float(x)
+        m[int(i)] = float(x)
+    if pattern == "sorted":
+        idx = np.sort(rng.integers(0, cap, B))
+    elif pattern == "one_bucket":
+        idx = rng.integers(cap // 2, cap // 2 + 16, B)
+    elif pattern == "one_leaf":
+        idx = np.full(B, cap - 1)
+    else:
+        idx = np.where(rng.random(B) < 0.5, 0, cap - 1)
+    val = rng.random(B) * 3.0 + 1e-3
+    t.set(idx, val)
+    for i, x in zip(idx, val):
+        s[int(i)] = float(x)
+        m[int(i)] = float(x)
+    ds, dm = t.arrays()
+    assert np.array_equal(ds, np.array(s.tree)) and np.array_equal(dm, np.array(m.tree))
+    assert int(t.aux[cap:].abs().sum()) == 0
 
 
 def test_tree_set_out_of_range_flags(xp, cuda_device):
