@@ -226,6 +226,183 @@ __global__ void __launch_bounds__(kThreads, 4) gae_tile_kernel(const ScanParams 
   }
 }
 
+// ---- warp-specialised pipeline (aligned shapes) ---------------------------------------------------
+// 8 loader/storer warps + 1 chain warp per CTA; the [128 x 32] tile is handed over in 4 sub-chunks
+// of 32 time steps through named barriers, so HBM reads (sub-chunk c+1), the serial chain
+// (sub-chunk c) and HBM writes (sub-chunk c-1) overlap inside one CTA.  The chain warp executes
+// only: LDS A_t, LDS flag, select K, DMUL, DADD, STS carry — everything else is off its path.
+constexpr int kSub = 32;
+constexpr int kPipeThreads = 288;
+constexpr int kNumSub = kTC / kSub;
+
+__device__ __forceinline__ void bar_sync(int id, int n) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(int id, int n) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+
+struct LoadRegs {
+  float4 r, v, vn;
+  unsigned d, dn;  // 4 done bytes of this row / of row t+1
+};
+
+template <int MODE>
+__device__ __forceinline__ void pipe_issue(const ScanParams &p, const float *rw, const float *vl,
+                                           const uint8_t *dn, long long t, int c4, bool active,
+                                           bool first_row_of_warp, LoadRegs &L) {
+  L.r = L.v = L.vn = make_float4(0.f, 0.f, 0.f, 0.f);
+  L.d = L.dn = 0u;
+  if (!active) return;
+  L.r = __ldcs(reinterpret_cast<const float4 *>(rw + t * p.N + c4));
+  L.v = __ldcs(reinterpret_cast<const float4 *>(vl + t * p.N + c4));
+  L.d = __ldcs(reinterpret_cast<const unsigned *>(dn + t * p.N + c4));
+  if (MODE == kModeGae && first_row_of_warp && t + 1 < p.T) {  // row t+1 lives in another warp
+    L.vn = __ldg(reinterpret_cast<const float4 *>(vl + (t + 1) * p.N + c4));
+    L.dn = __ldg(reinterpret_cast<const unsigned *>(dn + (t + 1) * p.N + c4));
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kPipeThreads, 4) gae_pipe_kernel(const ScanParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Tile &tile = *reinterpret_cast<Tile *>(smem_raw);
+  const long long tiles_per_agent = (p.N + kEnv - 1) / kEnv;
+  const long long agent = blockIdx.x / tiles_per_agent;
+  const long long env0 = (blockIdx.x - agent * tiles_per_agent) * kEnv;
+  const long long base = agent * p.agent_stride + env0;
+  const int n_env = (int)((p.N - env0) < kEnv ? (p.N - env0) : kEnv);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp < 8) {
+    // ================= loader / storer warps: thread -> (row rl of the sub-chunk, 4 envs) =====
+    const float *rw = p.rewards + base;
+    const float *vl = p.values + base;
+    const uint8_t *dn = p.dones + base;
+    const int rl = threadIdx.x >> 3;
+    const int c4 = (threadIdx.x & 7) * 4;
+    const bool first_row = lane < 8;
+    for (long long t_hi = p.T - 1; t_hi >= 0; t_hi -= kTC) {
+      const int rows = (int)((t_hi + 1) < kTC ? (t_hi + 1) : kTC);
+      LoadRegs L[2];
+      pipe_issue<MODE>(p, rw, vl, dn, t_hi - rl, c4, rl < rows && c4 < n_env, first_row, L[0]);
+#pragma unroll
+      for (int c = 0; c < kNumSub; ++c) {
+        const int row = c * kSub + rl;
+        const long long t = t_hi - row;
+        const bool active = row < rows && c4 < n_env;
+        if (c + 1 < kNumSub) {
+          const int nrow = row + kSub;
+          pipe_issue<MODE>(p, rw, vl, dn, t_hi - nrow, c4, nrow < rows && c4 < n_env, first_row,
+                           L[(c + 1) & 1]);
+        }
+        LoadRegs &R = L[c & 1];
+        if (MODE == kModeGae) {
+          // v[t+1], done[t+1] sit 8 lanes down (the previous row of this warp)
+          const float sx = __shfl_up_sync(0xffffffffu, R.v.x, 8), sy = __shfl_up_sync(0xffffffffu, R.v.y, 8);
+          const float sz = __shfl_up_sync(0xffffffffu, R.v.z, 8), sw = __shfl_up_sync(0xffffffffu, R.v.w, 8);
+          const unsigned sd = __shfl_up_sync(0xffffffffu, R.d, 8);
+          if (!first_row) {
+            R.vn = make_float4(sx, sy, sz, sw);
+            R.dn = sd;
+          }
+        }
+        if (active) {
+          const bool is_last = (t == p.T - 1);
+          const float rr[4] = {R.r.x, R.r.y, R.r.z, R.r.w};
+          const float vv[4] = {R.v.x, R.v.y, R.v.z, R.v.w};
+          const float vn[4] = {R.vn.x, R.vn.y, R.vn.z, R.vn.w};
+          const unsigned flags = (MODE == kModeGae) ? R.dn : R.d;
+          double a[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            double lve = 0.0, lde = 0.0;
+            if (MODE == kModeGae && is_last) {
+              lve = p.last_value[agent * p.N + env0 + c4 + e];
+              lde = p.last_done[agent * p.N + env0 + c4 + e];
+            }
+            a[e] = make_a<MODE>(p, is_last, rr[e], vv[e], vn[e], (uint8_t)((flags >> (8 * e)) & 0xffu), lve, lde);
+          }
+          *reinterpret_cast<double2 *>(&tile.a[row][c4]) = make_double2(a[0], a[1]);
+          *reinterpret_cast<double2 *>(&tile.a[row][c4 + 2]) = make_double2(a[2], a[3]);
+          *reinterpret_cast<float4 *>(&tile.v[row][c4]) = R.v;
+          *reinterpret_cast<unsigned *>(&tile.f[row][c4]) = flags;
+        }
+        bar_arrive(1 + c, kPipeThreads);  // sub-chunk c staged
+      }
+      float *adv = p.adv + base;
+      float *ret = p.ret + base;
+#pragma unroll
+      for (int c = 0; c < kNumSub; ++c) {
+        bar_sync(1 + kNumSub + c, kPipeThreads);  // chain finished sub-chunk c
+        const int row = c * kSub + rl;
+        const long long t = t_hi - row;
+        if (row < rows && c4 < n_env) {
+          const double2 c01 = *reinterpret_cast<const double2 *>(&tile.a[row][c4]);
+          const double2 c23 = *reinterpret_cast<const double2 *>(&tile.a[row][c4 + 2]);
+          const float4 v = *reinterpret_cast<const float4 *>(&tile.v[row][c4]);
+          float4 x, y;
+          x.x = __double2float_rn(c01.x); x.y = __double2float_rn(c01.y);
+          x.z = __double2float_rn(c23.x); x.w = __double2float_rn(c23.y);
+          if (MODE == kModeGae) {  // adv = f32(carry); ret = adv + v
+            y.x = __fadd_rn(x.x, v.x); y.y = __fadd_rn(x.y, v.y);
+            y.z = __fadd_rn(x.z, v.z); y.w = __fadd_rn(x.w, v.w);
+            __stcs(reinterpret_cast<float4 *>(adv + t * p.N + c4), x);
+            __stcs(reinterpret_cast<float4 *>(ret + t * p.N + c4), y);
+          } else {                 // ret = f32(G); adv = ret - v
+            y.x = __fsub_rn(x.x, v.x); y.y = __fsub_rn(x.y, v.y);
+            y.z = __fsub_rn(x.z, v.z); y.w = __fsub_rn(x.w, v.w);
+            __stcs(reinterpret_cast<float4 *>(ret + t * p.N + c4), x);
+            __stcs(reinterpret_cast<float4 *>(adv + t * p.N + c4), y);
+          }
+        }
+      }
+      __syncthreads();  // the tile is refilled by the next 128-step chunk
+    }
+  } else {
+    // ================= chain warp: lane = env ======================================================
+    double carry = 0.0, ld = 0.0;
+    if (lane < n_env) {
+      const double lv = p.last_value[agent * p.N + env0 + lane];
+      ld = p.last_done[agent * p.N + env0 + lane];
+      if (MODE == kModeMc) carry = __dmul_rn(lv, __dsub_rn(1.0, ld));
+    }
+    const double k1 = __dmul_rn(p.gl, 1.0), k0 = __dmul_rn(p.gl, 0.0);
+    const double k_last = __dmul_rn(p.gl, __dsub_rn(1.0, ld));
+    for (long long t_hi = p.T - 1; t_hi >= 0; t_hi -= kTC) {
+      const int rows = (int)((t_hi + 1) < kTC ? (t_hi + 1) : kTC);
+#pragma unroll
+      for (int c = 0; c < kNumSub; ++c) {
+        bar_sync(1 + c, kPipeThreads);
+        const int j1 = (rows - c * kSub) < kSub ? (rows - c * kSub) : kSub;
+        if (lane < n_env && j1 > 0) {
+          double *ap = &tile.a[c * kSub][lane];
+          const uint8_t *fp = &tile.f[c * kSub][lane];
+          int j = 0;
+          if (MODE == kModeGae && c == 0 && t_hi == p.T - 1) {  // bootstrap step uses last_done
+            carry = __dadd_rn(ap[0], __dmul_rn(k_last, carry));
+            ap[0] = carry;
+            j = 1;
+          }
+#pragma unroll 8
+          for (; j < j1; ++j) {
+            const double a = ap[j * kEnv];
+            const uint8_t f = fp[j * kEnv];
+            if (MODE == kModeGae) {
+              carry = __dadd_rn(a, __dmul_rn(f ? k0 : k1, carry));
+            } else {
+              carry = __dadd_rn(a, __dmul_rn(__dmul_rn(p.gamma, carry), f ? 0.0 : 1.0));
+            }
+            ap[j * kEnv] = carry;
+          }
+        }
+        bar_arrive(1 + kNumSub + c, kPipeThreads);
+      }
+      __syncthreads();
+    }
+  }
+}
+
 template <int MODE>
 xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   if (p.T == 0 || p.N == 0 || p.P == 0) return XP_OK;
@@ -237,7 +414,7 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   const long long grid = ((p.N + kEnv - 1) / kEnv) * p.P;
   XP_REQUIRE(grid < (1ll << 31), XP_ERR_INVALID, "xp_gae: grid too large");
   static bool attr[2][2] = {{false, false}, {false, false}};
-  const void *fn = vec ? (const void *)gae_tile_kernel<MODE, true> : (const void *)gae_tile_kernel<MODE, false>;
+  const void *fn = vec ? (const void *)gae_pipe_kernel<MODE> : (const void *)gae_tile_kernel<MODE, false>;
   if (!attr[MODE][vec]) {
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Tile));
     if (e != cudaSuccess) {
@@ -247,7 +424,7 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
     attr[MODE][vec] = true;
   }
   if (vec)
-    gae_tile_kernel<MODE, true><<<(unsigned)grid, kThreads, sizeof(Tile), s>>>(p);
+    gae_pipe_kernel<MODE><<<(unsigned)grid, kPipeThreads, sizeof(Tile), s>>>(p);
   else
     gae_tile_kernel<MODE, false><<<(unsigned)grid, kThreads, sizeof(Tile), s>>>(p);
   return xp::check_launch("xp_gae");

@@ -65,10 +65,16 @@ __device__ __forceinline__ double clamp_prio(float p) {
   return (1e-5 > q) ? 1e-5 : q;
 }
 
+// one out-of-line copy of the (large) glibc pow: the climb kernels are latency- and
+// instruction-cache-bound, not pow-bound
+__device__ __noinline__ double pow_call(double x, double y) { return xp::xp_pow(x, y); }
+
 __device__ __forceinline__ double src_value(const SetSrc &s, long long pos) {
   if (s.kind == kSrcVal) return s.val[pos];
-  if (s.kind == kSrcPrio) return xp::xp_pow(clamp_prio(s.prio[pos]), s.alpha);
-  return xp::xp_pow(__longlong_as_double((long long)*s.max_priority_bits), s.alpha);
+  const double base = (s.kind == kSrcPrio)
+                          ? clamp_prio(s.prio[pos])
+                          : __longlong_as_double((long long)*s.max_priority_bits);
+  return pow_call(base, s.alpha);
 }
 
 // max_priority = max(max_priority, p) over EVERY item, overwritten duplicates included (:329).
@@ -114,20 +120,46 @@ __device__ __forceinline__ int lower_bound(const u64 *keys, int n, u64 target) {
 }
 
 struct ClimbSmem {
-  u64 *key;     // [items] (x << 32) | pos, ascending; kPad beyond n
-  double *vs;   // [items] value of the node this item currently leads (sum tree)
-  double *vm;   // [items] same, min tree
-  int *nxt;     // [items] index of the next leader at the current level
+  u64 *key;      // [items] (x << 32) | pos, ascending; kPad beyond n
+  double2 *val;  // [items] (sum, min) value of the node this item currently leads
+  int *nxt;      // [items] index of the next leader at the current level
 };
-constexpr size_t climb_smem_bytes(int items) { return (size_t)items * (8 + 8 + 8 + 4); }
+constexpr size_t climb_smem_bytes(int items) { return (size_t)items * (8 + 16 + 4); }
 
 __device__ __forceinline__ ClimbSmem carve(unsigned char *base, int items) {
   ClimbSmem s;
-  s.key = reinterpret_cast<u64 *>(base);
-  s.vs = reinterpret_cast<double *>(base + (size_t)items * 8);
-  s.vm = reinterpret_cast<double *>(base + (size_t)items * 16);
+  s.val = reinterpret_cast<double2 *>(base);
+  s.key = reinterpret_cast<u64 *>(base + (size_t)items * 16);
   s.nxt = reinterpret_cast<int *>(base + (size_t)items * 24);
   return s;
+}
+
+// (sum, min) of one node.  PAIRED: the interleaved PER layout (stride 2, min = sum + 1) where a
+// node is one aligned 16-byte pair -> a single 128-bit access.
+template <bool PAIRED>
+__device__ __forceinline__ double2 ld_node(const Tree &t, int node) {
+  if (PAIRED) return __ldcg(reinterpret_cast<const double2 *>(t.sum) + node);
+  double2 r = make_double2(0.0, 0.0);
+  if (t.sum) r.x = __ldcg(&t.sum[(long long)node * t.stride]);
+  if (t.mn) r.y = __ldcg(&t.mn[(long long)node * t.stride]);
+  return r;
+}
+template <bool PAIRED>
+__device__ __forceinline__ void st_node(const Tree &t, int node, double2 v) {
+  if (PAIRED) {
+    __stcg(reinterpret_cast<double2 *>(t.sum) + node, v);
+    return;
+  }
+  if (t.sum) __stcg(&t.sum[(long long)node * t.stride], v.x);
+  if (t.mn) __stcg(&t.mn[(long long)node * t.stride], v.y);
+}
+inline bool is_paired(const Tree &t) {
+  return t.sum && t.mn && t.stride == 2 && t.mn == t.sum + 1 &&
+         (reinterpret_cast<uintptr_t>(t.sum) % 16 == 0);
+}
+
+__device__ __forceinline__ int key_x(const u64 *key, int i) {
+  return reinterpret_cast<const int *>(key)[2 * i + 1];  // high word = leaf index
 }
 
 // ---- level-synchronous sparse climb ---------------------------------------------------------------
@@ -139,33 +171,30 @@ __device__ __forceinline__ ClimbSmem carve(unsigned char *base, int items) {
 //   item i leads heights 0..m_i,   m_i = msb(x_{i-1} ^ x_i)   (item 0 leads every height).
 // A leader that is a left child finds its right sibling, if touched, as the NEXT leader of the
 // level below (nxt[]); a right-child leader's left sibling is untouched by construction.
-template <int ITEMS, int THREADS>
+template <int ITEMS, int THREADS, bool PAIRED>
 __device__ void climb_sorted(const Tree &t, const SetSrc &s, const ClimbSmem &sm, int n, int h_top) {
-  const bool hs = t.sum != nullptr, hm = t.mn != nullptr;
-  long long x[ITEMS];
+  const int cap = (int)t.cap;
+  int x[ITEMS];
   int m[ITEMS];
-  double cs[ITEMS], cm[ITEMS];
+  double2 cv[ITEMS];
 #pragma unroll
   for (int it = 0; it < ITEMS; ++it) {
     const int i = threadIdx.x + it * THREADS;
     m[it] = -1;
     x[it] = 0;
-    cs[it] = cm[it] = 0.0;
+    cv[it] = make_double2(0.0, 0.0);
     if (i < n) {
-      const long long xi = (long long)(sm.key[i] >> 32);
-      const long long prev = i ? (long long)(sm.key[i - 1] >> 32) : -1;
+      const int xi = key_x(sm.key, i);
+      const int prev = i ? key_x(sm.key, i - 1) : -1;
       if (i == 0 || prev != xi) {
-        m[it] = (i == 0) ? 64 : 63 - __clzll(prev ^ xi);
+        m[it] = (i == 0) ? 64 : 31 - __clz(prev ^ xi);
         x[it] = xi;
-        const int j = lower_bound(sm.key, n, (u64)(xi + 1) << 32);  // end of the run of equal x
+        const int j = lower_bound(sm.key, n, (u64)(unsigned)(xi + 1) << 32);  // end of the run of equal x
         const long long pos = (long long)(sm.key[j - 1] & 0xffffffffull);
         const double v = src_value(s, pos);
-        const long long node = t.cap + xi;
-        if (hs) __stcg(&t.sum[node * t.stride], v);
-        if (hm) __stcg(&t.mn[node * t.stride], v);
-        cs[it] = cm[it] = v;
-        sm.vs[i] = v;
-        sm.vm[i] = v;
+        cv[it] = make_double2(v, v);
+        st_node<PAIRED>(t, cap + xi, cv[it]);
+        sm.val[i] = cv[it];
         sm.nxt[i] = j;
       }
     }
@@ -174,18 +203,15 @@ __device__ void climb_sorted(const Tree &t, const SetSrc &s, const ClimbSmem &sm
 
   constexpr int G = 4;  // levels per prefetch group
   for (int k0 = 1; k0 <= h_top; k0 += G) {
-    double ps[ITEMS][G], pm[ITEMS][G];
+    double2 pf[ITEMS][G];
 #pragma unroll
     for (int it = 0; it < ITEMS; ++it) {
 #pragma unroll
       for (int g = 0; g < G; ++g) {
         const int kk = k0 + g;
-        ps[it][g] = pm[it][g] = 0.0;
-        if (kk <= h_top && m[it] >= kk) {
-          const long long sib = ((t.cap >> (kk - 1)) + (x[it] >> (kk - 1))) ^ 1ll;
-          if (hs) ps[it][g] = __ldcg(&t.sum[sib * t.stride]);
-          if (hm) pm[it][g] = __ldcg(&t.mn[sib * t.stride]);
-        }
+        pf[it][g] = make_double2(0.0, 0.0);
+        if (kk <= h_top && m[it] >= kk)
+          pf[it][g] = ld_node<PAIRED>(t, ((cap >> (kk - 1)) + (x[it] >> (kk - 1))) ^ 1);
       }
     }
 #pragma unroll
@@ -197,26 +223,22 @@ __device__ void climb_sorted(const Tree &t, const SetSrc &s, const ClimbSmem &sm
         if (m[it] >= kk) {
           const int i = threadIdx.x + it * THREADS;
           const int j = sm.nxt[i];
-          double ls, lm, rs, rm;
-          const bool merged = (j < n) && (((long long)(sm.key[j] >> 32) >> kk) == (x[it] >> kk));
-          if (merged) {  // i leads the left child, j the right child
-            ls = cs[it]; lm = cm[it];
-            rs = sm.vs[j]; rm = sm.vm[j];
+          const int px = x[it] >> kk;
+          double2 l, r;
+          if (j < n && (key_x(sm.key, j) >> kk) == px) {  // i leads the left child, j the right
+            l = cv[it];
+            r = sm.val[j];
             sm.nxt[i] = sm.nxt[j];
-          } else if ((x[it] >> (kk - 1)) & 1) {  // mine is the right child
-            ls = ps[it][g]; lm = pm[it][g];
-            rs = cs[it]; rm = cm[it];
+          } else if ((x[it] >> (kk - 1)) & 1) {           // mine is the right child
+            l = pf[it][g];
+            r = cv[it];
           } else {
-            ls = cs[it]; lm = cm[it];
-            rs = ps[it][g]; rm = pm[it][g];
+            l = cv[it];
+            r = pf[it][g];
           }
-          cs[it] = __dadd_rn(ls, rs);
-          cm[it] = py_min(lm, rm);
-          const long long node = (t.cap >> kk) + (x[it] >> kk);
-          if (hs) __stcg(&t.sum[node * t.stride], cs[it]);
-          if (hm) __stcg(&t.mn[node * t.stride], cm[it]);
-          sm.vs[i] = cs[it];
-          sm.vm[i] = cm[it];
+          cv[it] = make_double2(__dadd_rn(l.x, r.x), py_min(l.y, r.y));
+          st_node<PAIRED>(t, (cap >> kk) + px, cv[it]);
+          sm.val[i] = cv[it];
         }
       }
       __syncthreads();
@@ -227,7 +249,7 @@ __device__ void climb_sorted(const Tree &t, const SetSrc &s, const ClimbSmem &sm
 constexpr int kSetThreads = 512;
 
 // ---- schedule S: the whole batch in one CTA ------------------------------------------------------
-template <int ITEMS>
+template <int ITEMS, bool PAIRED>
 __global__ void __launch_bounds__(kSetThreads) set_small_kernel(Tree t, SetSrc s, int B, int height) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const ClimbSmem sm = carve(smem_raw, ITEMS * kSetThreads);
@@ -260,7 +282,7 @@ __global__ void __launch_bounds__(kSetThreads) set_small_kernel(Tree t, SetSrc s
   int ok = 1;
   for (int i = threadIdx.x + 1; i < npow2; i += kSetThreads) ok &= (sm.key[i - 1] <= sm.key[i]);
   if (!__syncthreads_and(ok)) bitonic_sort<kSetThreads>(sm.key, npow2);
-  climb_sorted<ITEMS, kSetThreads>(t, s, sm, s_valid, height);
+  climb_sorted<ITEMS, kSetThreads, PAIRED>(t, s, sm, s_valid, height);
 }
 
 // ---- schedule L ----------------------------------------------------------------------------------
@@ -358,6 +380,7 @@ __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long
 // one CTA per bucket subtree: sort its winners, climb to the bucket root (height = shift)
 constexpr int kBucketThreads = 256;
 constexpr int kBucketItems = 2;  // per thread -> chunks of 512 items
+template <bool PAIRED>
 __global__ void __launch_bounds__(kBucketThreads) set_bucket_kernel(Tree t, SetSrc s, Buckets bk) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const ClimbSmem sm = carve(smem_raw, kBucketThreads * kBucketItems);
@@ -372,7 +395,7 @@ __global__ void __launch_bounds__(kBucketThreads) set_bucket_kernel(Tree t, SetS
     for (int i = threadIdx.x; i < npow2; i += kBucketThreads) sm.key[i] = (i < n) ? bk.items[c0 + i] : kPad;
     __syncthreads();
     bitonic_sort<kBucketThreads>(sm.key, npow2);
-    climb_sorted<kBucketItems, kBucketThreads>(t, s, sm, n, bk.shift);
+    climb_sorted<kBucketItems, kBucketThreads, PAIRED>(t, s, sm, n, bk.shift);
   }
   if (threadIdx.x == 0) bk.counts[b] = 0;
 }
@@ -468,17 +491,23 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   XP_REQUIRE(t.cap <= (1ll << 30), XP_ERR_INVALID, "tree set: capacity above 2^30");
   const int L = ilog2(t.cap);
   int launches = 0;
+  const bool paired = is_paired(t);
   if (B <= kMaxItems) {  // schedule S
-    if (B <= kSetThreads) {
-      set_small_kernel<1><<<1, kSetThreads, climb_smem_bytes(kSetThreads), st>>>(t, s, (int)B, L);
-    } else if (B <= 2 * kSetThreads) {
-      set_small_kernel<2><<<1, kSetThreads, climb_smem_bytes(2 * kSetThreads), st>>>(t, s, (int)B, L);
-    } else {
-      static bool attr = false;
-      xp_status_t rc = set_attr_once((const void *)set_small_kernel<4>, climb_smem_bytes(4 * kSetThreads), attr);
+    const int items = B <= kSetThreads ? 1 : (B <= 2 * kSetThreads ? 2 : 4);
+    const size_t smem = climb_smem_bytes(items * kSetThreads);
+    static bool attr[2] = {false, false};
+    if (items == 4) {
+      const void *fn = paired ? (const void *)set_small_kernel<4, true> : (const void *)set_small_kernel<4, false>;
+      xp_status_t rc = set_attr_once(fn, smem, attr[paired]);
       if (rc != XP_OK) return rc;
-      set_small_kernel<4><<<1, kSetThreads, climb_smem_bytes(4 * kSetThreads), st>>>(t, s, (int)B, L);
     }
+#define XP_SMALL(I, P) set_small_kernel<I, P><<<1, kSetThreads, smem, st>>>(t, s, (int)B, L)
+    if (paired) {
+      if (items == 1) XP_SMALL(1, true); else if (items == 2) XP_SMALL(2, true); else XP_SMALL(4, true);
+    } else {
+      if (items == 1) XP_SMALL(1, false); else if (items == 2) XP_SMALL(2, false); else XP_SMALL(4, false);
+    }
+#undef XP_SMALL
     return xp::check_launch("tree set (S)", 1);
   }
   const unsigned grid = (unsigned)((B + 255) / 256);
@@ -489,7 +518,10 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     const Buckets bk = make_buckets(t, (int)nb, shift);
     set_ticket_kernel<true><<<grid, 256, 0, st>>>(t, s, B, bk);
     set_scatter_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
-    set_bucket_kernel<<<(unsigned)nb, kBucketThreads, climb_smem_bytes(kBucketThreads * kBucketItems), st>>>(t, s, bk);
+    if (paired)
+      set_bucket_kernel<true><<<(unsigned)nb, kBucketThreads, climb_smem_bytes(kBucketThreads * kBucketItems), st>>>(t, s, bk);
+    else
+      set_bucket_kernel<false><<<(unsigned)nb, kBucketThreads, climb_smem_bytes(kBucketThreads * kBucketItems), st>>>(t, s, bk);
     launches = 3;
     xp_status_t rc = launch_dense(t, shift, nb, st, launches);
     if (rc != XP_OK) return rc;
