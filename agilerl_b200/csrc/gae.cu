@@ -23,6 +23,10 @@
 //   MC   (:468-477)  G = last_value*(1-last_done);  G = f64(r[t]) + (gamma*G)*(1-done[t])
 //                    ret[t] = f32(G);  adv[t] = ret[t] -f32 v[t]
 #include "common.cuh"
+#include "gae_tma.cuh"
+#ifndef XP_EXP
+#define XP_EXP 0
+#endif
 
 namespace {
 
@@ -69,7 +73,7 @@ __device__ __forceinline__ double make_a(const ScanParams &p, bool is_last, floa
   return __dsub_rn(__dadd_rn((double)r, __dmul_rn(g_nv, nnt)), (double)v);
 }
 
-template <int MODE, bool VEC>
+template <int MODE>
 __global__ void __launch_bounds__(kThreads, 4) gae_tile_kernel(const ScanParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Tile &tile = *reinterpret_cast<Tile *>(smem_raw);
@@ -96,63 +100,7 @@ __global__ void __launch_bounds__(kThreads, 4) gae_tile_kernel(const ScanParams 
   for (long long t_hi = p.T - 1; t_hi >= 0; t_hi -= kTC) {
     const int rows = (int)((t_hi + 1) < kTC ? (t_hi + 1) : kTC);  // row j <-> t = t_hi - j
     // ---- phase 1: stage A, v, flag -------------------------------------------------------
-    if (VEC) {
-      // thread -> (row = tid/8 + 32*k, 4 consecutive envs)
-      const int c4 = (threadIdx.x & 7) * 4;
-#pragma unroll 1
-      for (int half = 0; half < 2; ++half) {
-      float4 r4[2], v4[2], vn4[2];
-      uchar4 d4[2];
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const int row = (threadIdx.x >> 3) + 32 * (2 * half + k);
-        const long long t = t_hi - row;
-        r4[k] = v4[k] = vn4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        d4[k] = make_uchar4(0, 0, 0, 0);
-        if (row < rows && c4 < n_env) {
-          r4[k] = __ldcs(reinterpret_cast<const float4 *>(rw + t * p.N + c4));
-          v4[k] = __ldg(reinterpret_cast<const float4 *>(vl + t * p.N + c4));
-          if (MODE == kModeGae) {
-            if (t + 1 < p.T) {
-              vn4[k] = __ldg(reinterpret_cast<const float4 *>(vl + (t + 1) * p.N + c4));
-              d4[k] = __ldg(reinterpret_cast<const uchar4 *>(dn + (t + 1) * p.N + c4));
-            } else {
-              vn4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-              d4[k] = make_uchar4(0, 0, 0, 0);
-            }
-          } else {
-            d4[k] = __ldg(reinterpret_cast<const uchar4 *>(dn + t * p.N + c4));
-          }
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const int row = (threadIdx.x >> 3) + 32 * (2 * half + k);
-        const long long t = t_hi - row;
-        if (row < rows && c4 < n_env) {
-          const bool is_last = (t == p.T - 1);
-          const float rr[4] = {r4[k].x, r4[k].y, r4[k].z, r4[k].w};
-          const float vv[4] = {v4[k].x, v4[k].y, v4[k].z, v4[k].w};
-          const float vn[4] = {vn4[k].x, vn4[k].y, vn4[k].z, vn4[k].w};
-          const uint8_t dd[4] = {d4[k].x, d4[k].y, d4[k].z, d4[k].w};
-          double a[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            double lve = 0.0, lde = 0.0;
-            if (MODE == kModeGae && is_last) {
-              lve = p.last_value[agent * p.N + env0 + c4 + e];
-              lde = p.last_done[agent * p.N + env0 + c4 + e];
-            }
-            a[e] = make_a<MODE>(p, is_last, rr[e], vv[e], vn[e], dd[e], lve, lde);
-          }
-          *reinterpret_cast<double2 *>(&tile.a[row][c4]) = make_double2(a[0], a[1]);
-          *reinterpret_cast<double2 *>(&tile.a[row][c4 + 2]) = make_double2(a[2], a[3]);
-          *reinterpret_cast<float4 *>(&tile.v[row][c4]) = v4[k];
-          *reinterpret_cast<uchar4 *>(&tile.f[row][c4]) = d4[k];
-        }
-      }
-      }
-    } else {
+    {
       // any N / alignment: thread -> (row = tid/32 + 8*k, env = tid%32), 128 B per warp per row
       const int e = threadIdx.x & 31;
       for (int row = threadIdx.x >> 5; row < rows; row += kThreads / 32) {
@@ -226,207 +174,173 @@ __global__ void __launch_bounds__(kThreads, 4) gae_tile_kernel(const ScanParams 
   }
 }
 
-// ---- warp-specialised pipeline (aligned shapes) ---------------------------------------------------
-// 8 loader/storer warps + 1 chain warp per CTA; the [128 x 32] tile is handed over in 4 sub-chunks
-// of 32 time steps through named barriers, so HBM reads (sub-chunk c+1), the serial chain
-// (sub-chunk c) and HBM writes (sub-chunk c-1) overlap inside one CTA.  The chain warp executes
-// only: LDS A_t, LDS flag, select K, DMUL, DADD, STS carry — everything else is off its path.
-constexpr int kSub = 32;
-constexpr int kPipeThreads = 288;
-constexpr int kNumSub = kTC / kSub;
-
-__device__ __forceinline__ void bar_sync(int id, int n) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
-}
-__device__ __forceinline__ void bar_arrive(int id, int n) {
-  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
-}
-
-struct LoadRegs {
-  float4 r, v, vn;
-  unsigned d, dn;  // 4 done bytes of this row / of row t+1
-};
-
+// ---- TMA-fed kernel (aligned shapes): see gae_tma.cuh -------------------------------------------
 template <int MODE>
-__device__ __forceinline__ void pipe_issue(const ScanParams &p, const float *rw, const float *vl,
-                                           const uint8_t *dn, long long t, int c4, bool active,
-                                           bool first_row_of_warp, LoadRegs &L) {
-  L.r = L.v = L.vn = make_float4(0.f, 0.f, 0.f, 0.f);
-  L.d = L.dn = 0u;
-  if (!active) return;
-  L.r = __ldcs(reinterpret_cast<const float4 *>(rw + t * p.N + c4));
-  L.v = __ldcs(reinterpret_cast<const float4 *>(vl + t * p.N + c4));
-  L.d = __ldcs(reinterpret_cast<const unsigned *>(dn + t * p.N + c4));
-  if (MODE == kModeGae && first_row_of_warp && t + 1 < p.T) {  // row t+1 lives in another warp
-    L.vn = __ldg(reinterpret_cast<const float4 *>(vl + (t + 1) * p.N + c4));
-    L.dn = __ldg(reinterpret_cast<const unsigned *>(dn + (t + 1) * p.N + c4));
+__global__ void __launch_bounds__(32) gae_tma_kernel(const ScanParams p,
+                                                     const __grid_constant__ gaetma::Maps maps) {
+  using namespace gaetma;
+  extern __shared__ __align__(128) unsigned char smem_tma[];
+  Stage *stage = reinterpret_cast<Stage *>(smem_tma);
+  __shared__ __align__(8) unsigned long long bars[kStages];
+  const int lane = threadIdx.x;
+  const int tiles_per_agent = (int)((p.N + kBoxE - 1) / kBoxE);
+  const int agent = blockIdx.x / tiles_per_agent;
+  const int env0 = (blockIdx.x - agent * tiles_per_agent) * kBoxE;
+  const int T = (int)p.T;
+  const int nbox = (T + kBoxT - 1) / kBoxT;  // box b (0 = newest) covers t in [32(nbox-1-b), +32)
+
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) mbar_init(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-}
+  __syncwarp();
+  auto issue = [&](int b) {  // lane 0 only
+    Stage &st = stage[b % kStages];
+    unsigned long long *bar = &bars[b % kStages];
+    const int t0 = kBoxT * (nbox - 1 - b);  // coordinates stay non-negative; the newest box may
+                                            // run past T (zero-filled on load, clipped on store)
+    mbar_expect_tx(bar, kStageBytes);
+    tma_load_3d(&st.r[0][0], &maps.r, env0, t0, agent, bar);
+    tma_load_3d(&st.v[0][0], &maps.v, env0, t0, agent, bar);
+    tma_load_3d(&st.d[0][0], &maps.d, env0, t0, agent, bar);
+  };
+  if (lane == 0) {
+    for (int b = 0; b < kStages && b < nbox; ++b) issue(b);
+  }
 
-template <int MODE>
-__global__ void __launch_bounds__(kPipeThreads, 4) gae_pipe_kernel(const ScanParams p) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  Tile &tile = *reinterpret_cast<Tile *>(smem_raw);
-  const long long tiles_per_agent = (p.N + kEnv - 1) / kEnv;
-  const long long agent = blockIdx.x / tiles_per_agent;
-  const long long env0 = (blockIdx.x - agent * tiles_per_agent) * kEnv;
-  const long long base = agent * p.agent_stride + env0;
-  const int n_env = (int)((p.N - env0) < kEnv ? (p.N - env0) : kEnv);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool env_ok = env0 + lane < p.N;
+  double lv = 0.0, ld = 0.0;
+  if (env_ok) {
+    lv = p.last_value[(long long)agent * p.N + env0 + lane];
+    ld = p.last_done[(long long)agent * p.N + env0 + lane];
+  }
+  double carry = (MODE == kModeMc) ? __dmul_rn(lv, __dsub_rn(1.0, ld)) : 0.0;
+  const double k1 = __dmul_rn(p.gl, 1.0), k0 = __dmul_rn(p.gl, 0.0);
+  float v_next = 0.f;
+  unsigned d_next = 0;
 
-  if (warp < 8) {
-    // ================= loader / storer warps: thread -> (row rl of the sub-chunk, 4 envs) =====
-    const float *rw = p.rewards + base;
-    const float *vl = p.values + base;
-    const uint8_t *dn = p.dones + base;
-    const int rl = threadIdx.x >> 3;
-    const int c4 = (threadIdx.x & 7) * 4;
-    const bool first_row = lane < 8;
-    for (long long t_hi = p.T - 1; t_hi >= 0; t_hi -= kTC) {
-      const int rows = (int)((t_hi + 1) < kTC ? (t_hi + 1) : kTC);
-      LoadRegs L[2];
-      pipe_issue<MODE>(p, rw, vl, dn, t_hi - rl, c4, rl < rows && c4 < n_env, first_row, L[0]);
-#pragma unroll
-      for (int c = 0; c < kNumSub; ++c) {
-        const int row = c * kSub + rl;
-        const long long t = t_hi - row;
-        const bool active = row < rows && c4 < n_env;
-        if (c + 1 < kNumSub) {
-          const int nrow = row + kSub;
-          pipe_issue<MODE>(p, rw, vl, dn, t_hi - nrow, c4, nrow < rows && c4 < n_env, first_row,
-                           L[(c + 1) & 1]);
-        }
-        LoadRegs &R = L[c & 1];
-        if (MODE == kModeGae) {
-          // v[t+1], done[t+1] sit 8 lanes down (the previous row of this warp)
-          const float sx = __shfl_up_sync(0xffffffffu, R.v.x, 8), sy = __shfl_up_sync(0xffffffffu, R.v.y, 8);
-          const float sz = __shfl_up_sync(0xffffffffu, R.v.z, 8), sw = __shfl_up_sync(0xffffffffu, R.v.w, 8);
-          const unsigned sd = __shfl_up_sync(0xffffffffu, R.d, 8);
-          if (!first_row) {
-            R.vn = make_float4(sx, sy, sz, sw);
-            R.dn = sd;
-          }
-        }
-        if (active) {
-          const bool is_last = (t == p.T - 1);
-          const float rr[4] = {R.r.x, R.r.y, R.r.z, R.r.w};
-          const float vv[4] = {R.v.x, R.v.y, R.v.z, R.v.w};
-          const float vn[4] = {R.vn.x, R.vn.y, R.vn.z, R.vn.w};
-          const unsigned flags = (MODE == kModeGae) ? R.dn : R.d;
-          double a[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            double lve = 0.0, lde = 0.0;
-            if (MODE == kModeGae && is_last) {
-              lve = p.last_value[agent * p.N + env0 + c4 + e];
-              lde = p.last_done[agent * p.N + env0 + c4 + e];
-            }
-            a[e] = make_a<MODE>(p, is_last, rr[e], vv[e], vn[e], (uint8_t)((flags >> (8 * e)) & 0xffu), lve, lde);
-          }
-          *reinterpret_cast<double2 *>(&tile.a[row][c4]) = make_double2(a[0], a[1]);
-          *reinterpret_cast<double2 *>(&tile.a[row][c4 + 2]) = make_double2(a[2], a[3]);
-          *reinterpret_cast<float4 *>(&tile.v[row][c4]) = R.v;
-          *reinterpret_cast<unsigned *>(&tile.f[row][c4]) = flags;
-        }
-        bar_arrive(1 + c, kPipeThreads);  // sub-chunk c staged
-      }
-      float *adv = p.adv + base;
-      float *ret = p.ret + base;
-#pragma unroll
-      for (int c = 0; c < kNumSub; ++c) {
-        bar_sync(1 + kNumSub + c, kPipeThreads);  // chain finished sub-chunk c
-        const int row = c * kSub + rl;
-        const long long t = t_hi - row;
-        if (row < rows && c4 < n_env) {
-          const double2 c01 = *reinterpret_cast<const double2 *>(&tile.a[row][c4]);
-          const double2 c23 = *reinterpret_cast<const double2 *>(&tile.a[row][c4 + 2]);
-          const float4 v = *reinterpret_cast<const float4 *>(&tile.v[row][c4]);
-          float4 x, y;
-          x.x = __double2float_rn(c01.x); x.y = __double2float_rn(c01.y);
-          x.z = __double2float_rn(c23.x); x.w = __double2float_rn(c23.y);
-          if (MODE == kModeGae) {  // adv = f32(carry); ret = adv + v
-            y.x = __fadd_rn(x.x, v.x); y.y = __fadd_rn(x.y, v.y);
-            y.z = __fadd_rn(x.z, v.z); y.w = __fadd_rn(x.w, v.w);
-            __stcs(reinterpret_cast<float4 *>(adv + t * p.N + c4), x);
-            __stcs(reinterpret_cast<float4 *>(ret + t * p.N + c4), y);
-          } else {                 // ret = f32(G); adv = ret - v
-            y.x = __fsub_rn(x.x, v.x); y.y = __fsub_rn(x.y, v.y);
-            y.z = __fsub_rn(x.z, v.z); y.w = __fsub_rn(x.w, v.w);
-            __stcs(reinterpret_cast<float4 *>(ret + t * p.N + c4), x);
-            __stcs(reinterpret_cast<float4 *>(adv + t * p.N + c4), y);
-          }
-        }
-      }
-      __syncthreads();  // the tile is refilled by the next 128-step chunk
+  for (int b = 0; b < nbox; ++b) {
+    Stage &st = stage[b % kStages];
+    mbar_wait(&bars[b % kStages], (unsigned)((b / kStages) & 1));
+    const int t0 = kBoxT * (nbox - 1 - b);
+    int row = (T - 1 - t0) < (kBoxT - 1) ? (T - 1 - t0) : (kBoxT - 1);
+    if (MODE == kModeGae && b == 0) {  // t = T-1 bootstraps from last_value / last_done (:451-453)
+      const float r = st.r[row][lane], v = st.v[row][lane];
+      const unsigned d = st.d[row][lane];
+      const double nnt = __dsub_rn(1.0, ld);
+      const double a = __dsub_rn(__dadd_rn((double)r, __dmul_rn(__dmul_rn(p.gamma, lv), nnt)), (double)v);
+      carry = __dadd_rn(a, __dmul_rn(__dmul_rn(p.gl, nnt), carry));
+      const float av = __double2float_rn(carry);
+      st.r[row][lane] = av;
+      st.v[row][lane] = __fadd_rn(av, v);
+      v_next = v;
+      d_next = d;
+      --row;
     }
-  } else {
-    // ================= chain warp: lane = env ======================================================
-    double carry = 0.0, ld = 0.0;
-    if (lane < n_env) {
-      const double lv = p.last_value[agent * p.N + env0 + lane];
-      ld = p.last_done[agent * p.N + env0 + lane];
-      if (MODE == kModeMc) carry = __dmul_rn(lv, __dsub_rn(1.0, ld));
-    }
-    const double k1 = __dmul_rn(p.gl, 1.0), k0 = __dmul_rn(p.gl, 0.0);
-    const double k_last = __dmul_rn(p.gl, __dsub_rn(1.0, ld));
-    for (long long t_hi = p.T - 1; t_hi >= 0; t_hi -= kTC) {
-      const int rows = (int)((t_hi + 1) < kTC ? (t_hi + 1) : kTC);
-#pragma unroll
-      for (int c = 0; c < kNumSub; ++c) {
-        bar_sync(1 + c, kPipeThreads);
-        const int j1 = (rows - c * kSub) < kSub ? (rows - c * kSub) : kSub;
-        if (lane < n_env && j1 > 0) {
-          double *ap = &tile.a[c * kSub][lane];
-          const uint8_t *fp = &tile.f[c * kSub][lane];
-          int j = 0;
-          if (MODE == kModeGae && c == 0 && t_hi == p.T - 1) {  // bootstrap step uses last_done
-            carry = __dadd_rn(ap[0], __dmul_rn(k_last, carry));
-            ap[0] = carry;
-            j = 1;
-          }
 #pragma unroll 8
-          for (; j < j1; ++j) {
-            const double a = ap[j * kEnv];
-            const uint8_t f = fp[j * kEnv];
-            if (MODE == kModeGae) {
-              carry = __dadd_rn(a, __dmul_rn(f ? k0 : k1, carry));
-            } else {
-              carry = __dadd_rn(a, __dmul_rn(__dmul_rn(p.gamma, carry), f ? 0.0 : 1.0));
-            }
-            ap[j * kEnv] = carry;
-          }
-        }
-        bar_arrive(1 + kNumSub + c, kPipeThreads);
+    for (; row >= 0; --row) {
+      const float r = st.r[row][lane], v = st.v[row][lane];
+      const unsigned d = st.d[row][lane];
+      float av, rv;
+      if (MODE == kModeGae) {
+        const double g_nv = (double)__fmul_rn(p.gamma32, v_next);
+        const double a = __dsub_rn(__dadd_rn((double)r, __dmul_rn(g_nv, d_next ? 0.0 : 1.0)), (double)v);
+        carry = __dadd_rn(a, __dmul_rn(d_next ? k0 : k1, carry));
+        av = __double2float_rn(carry);
+        rv = __fadd_rn(av, v);
+      } else {
+        carry = __dadd_rn((double)r, __dmul_rn(__dmul_rn(p.gamma, carry), d ? 0.0 : 1.0));
+        rv = __double2float_rn(carry);
+        av = __fsub_rn(rv, v);
       }
-      __syncthreads();
+      st.r[row][lane] = av;
+      st.v[row][lane] = rv;
+      v_next = v;
+      d_next = d;
     }
+    fence_proxy_async();  // generic-proxy writes above -> visible to the TMA store
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_3d(&maps.adv, env0, t0, agent, &st.r[0][0]);
+      tma_store_3d(&maps.ret, env0, t0, agent, &st.v[0][0]);
+      tma_commit();
+      // the stage box b-1 lived in is free once ITS stores have read shared memory
+      if (b >= 1 && b - 1 + kStages < nbox) {
+        tma_wait_read<1>();
+        issue(b - 1 + kStages);
+      }
+    }
+    __syncwarp();
   }
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// cuTensorMapEncodeTiled through the runtime (no -lcuda): rank-3 maps {env, t, agent}.
+typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                             const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                             CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                             CUtensorMapFloatOOBfill);
+EncodeFn get_encode() {
+  static EncodeFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void *f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeFn)f;
+  }
+  return fn;
+}
+
+bool encode_map(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p) {
+  EncodeFn enc = get_encode();
+  if (!enc) return false;
+  const long long astride = p.P == 1 ? p.T * p.N : p.agent_stride;
+  const cuuint64_t dims[3] = {(cuuint64_t)p.N, (cuuint64_t)p.T, (cuuint64_t)p.P};
+  const cuuint64_t strides[2] = {(cuuint64_t)(p.N * elem_bytes), (cuuint64_t)(astride * elem_bytes)};
+  const cuuint32_t box[3] = {gaetma::kBoxE, gaetma::kBoxT, 1};
+  const cuuint32_t es[3] = {1, 1, 1};
+  const CUresult r = enc(m, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 3,
+                         const_cast<void *>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
 }
 
 template <int MODE>
 xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   if (p.T == 0 || p.N == 0 || p.P == 0) return XP_OK;
-  const bool vec =
-      (p.N % 4 == 0) && (p.agent_stride % 4 == 0) &&
-      (reinterpret_cast<uintptr_t>(p.rewards) % 16 == 0) &&
-      (reinterpret_cast<uintptr_t>(p.values) % 16 == 0) &&
-      (reinterpret_cast<uintptr_t>(p.dones) % 4 == 0);
   const long long grid = ((p.N + kEnv - 1) / kEnv) * p.P;
   XP_REQUIRE(grid < (1ll << 31), XP_ERR_INVALID, "xp_gae: grid too large");
-  static bool attr[2][2] = {{false, false}, {false, false}};
-  const void *fn = vec ? (const void *)gae_pipe_kernel<MODE> : (const void *)gae_tile_kernel<MODE, false>;
-  if (!attr[MODE][vec]) {
-    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Tile));
+  const long long astride = p.P == 1 ? p.T * p.N : p.agent_stride;
+  auto al16 = [](const void *q) { return reinterpret_cast<uintptr_t>(q) % 16 == 0; };
+  // TMA needs 16-byte aligned bases and row / agent strides (the u8 dones are the strict case)
+  const bool tma_ok = (p.N % 16 == 0) && (astride % 16 == 0) && al16(p.rewards) && al16(p.values) &&
+                      al16(p.dones) && al16(p.adv) && al16(p.ret) && p.T < (1ll << 30) &&
+                      p.N < (1ll << 31) && p.P < (1ll << 31);
+  if (tma_ok) {
+    gaetma::Maps maps;
+    if (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
+        encode_map(&maps.d, p.dones, 1, p) && encode_map(&maps.adv, p.adv, 4, p) &&
+        encode_map(&maps.ret, p.ret, 4, p)) {
+      gae_tma_kernel<MODE><<<(unsigned)grid, 32, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps);
+      return xp::check_launch("xp_gae (tma)");
+    }
+  }
+  static bool attr[2] = {false, false};
+  if (!attr[MODE]) {
+    cudaError_t e = cudaFuncSetAttribute((const void *)gae_tile_kernel<MODE>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Tile));
     if (e != cudaSuccess) {
       xp::set_error("xp_gae: %s", cudaGetErrorString(e));
       return XP_ERR_CUDA;
     }
-    attr[MODE][vec] = true;
+    attr[MODE] = true;
   }
-  if (vec)
-    gae_pipe_kernel<MODE><<<(unsigned)grid, kPipeThreads, sizeof(Tile), s>>>(p);
-  else
-    gae_tile_kernel<MODE, false><<<(unsigned)grid, kThreads, sizeof(Tile), s>>>(p);
+  gae_tile_kernel<MODE><<<(unsigned)grid, kThreads, sizeof(Tile), s>>>(p);
   return xp::check_launch("xp_gae");
 }
 

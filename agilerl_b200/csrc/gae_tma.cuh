@@ -1,0 +1,76 @@
+// gae_tma.cuh — TMA-fed reverse-time scan (included by gae.cu; aligned shapes only).
+//
+// One warp per CTA owns 32 envs of one agent.  The [T x 32] strip is walked newest-first in boxes
+// of 32 time steps.  All HBM traffic is issued by the TMA unit:
+//   load : cp.async.bulk.tensor.3d  global -> shared  (rewards, values fp32 [32 t][32 env],
+//          dones u8 [32 t][32 env]), completion on an mbarrier, a ring of kStages boxes in flight;
+//   store: cp.async.bulk.tensor.3d  shared -> global of the advantage / return boxes, which the
+//          chain wrote IN PLACE over the reward / value boxes (bulk-group completion).
+// The 32 lanes only touch shared memory: per step 3 LDS, the carry-independent part of the
+// recurrence (A_t; pipelines freely), the two dependent fp64 ops of the carry, 2 STS.
+// Out-of-range rows/envs are zero-filled on load and clipped on store by the hardware.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace gaetma {
+
+constexpr int kBoxT = 32;    // time steps per box
+constexpr int kBoxE = 32;    // envs per box = lanes
+constexpr int kStages = 4;   // boxes in flight per CTA
+constexpr int kStageBytes = kBoxT * kBoxE * (4 + 4 + 1);  // 9216
+
+struct __align__(128) Stage {
+  float r[kBoxT][kBoxE];    // rewards   -> overwritten with advantages
+  float v[kBoxT][kBoxE];    // values    -> overwritten with returns
+  uint8_t d[kBoxT][kBoxE];  // dones
+};
+
+struct Maps {
+  CUtensorMap r, v, d, adv, ret;
+};
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, int c0, int c1, int c2,
+                                            unsigned long long *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, int c0, int c1, int c2, const void *src) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(map),
+               "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(src))
+               : "memory");
+}
+__device__ __forceinline__ void tma_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+}  // namespace gaetma
