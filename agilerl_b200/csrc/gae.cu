@@ -238,11 +238,8 @@ __global__ void __launch_bounds__(32) gae_tma_kernel(const ScanParams p,
       d_next = d;
       --row;
     }
-#pragma unroll 8
-    for (; row >= 0; --row) {
-      const float r = st.r[row][lane], v = st.v[row][lane];
-      const unsigned d = st.d[row][lane];
-      float av, rv;
+    // one step of the recurrence given the staged inputs of row t and of row t+1
+    auto step = [&](float r, float v, unsigned d, float &av, float &rv) {
       if (MODE == kModeGae) {
         const double g_nv = (double)__fmul_rn(p.gamma32, v_next);
         const double a = __dsub_rn(__dadd_rn((double)r, __dmul_rn(g_nv, d_next ? 0.0 : 1.0)), (double)v);
@@ -254,10 +251,34 @@ __global__ void __launch_bounds__(32) gae_tma_kernel(const ScanParams p,
         rv = __double2float_rn(carry);
         av = __fsub_rn(rv, v);
       }
-      st.r[row][lane] = av;
-      st.v[row][lane] = rv;
       v_next = v;
       d_next = d;
+    };
+    // ragged head (partial newest box / after the bootstrap step): down to a multiple of 8 rows
+    for (; row >= 0 && ((row + 1) & 7) != 0; --row) {
+      float av, rv;
+      step(st.r[row][lane], st.v[row][lane], st.d[row][lane], av, rv);
+      st.r[row][lane] = av;
+      st.v[row][lane] = rv;
+    }
+    // groups of 8 rows staged through registers: 24 independent LDS, then the carry-independent
+    // part of 8 steps pipelines under the 8 x (DMUL -> DADD) carry chain, then 16 STS
+    for (; row >= 7; row -= 8) {
+      float r8[8], v8[8], a8[8], g8[8];
+      unsigned d8[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        r8[u] = st.r[row - u][lane];
+        v8[u] = st.v[row - u][lane];
+        d8[u] = st.d[row - u][lane];
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) step(r8[u], v8[u], d8[u], a8[u], g8[u]);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        st.r[row - u][lane] = a8[u];
+        st.v[row - u][lane] = g8[u];
+      }
     }
     fence_proxy_async();  // generic-proxy writes above -> visible to the TMA store
     __syncwarp();
@@ -295,7 +316,40 @@ EncodeFn get_encode() {
   return fn;
 }
 
+// Encoding costs ~1 us of host time per map; rollout buffers call with the same five arrays every
+// time, so the last few descriptors are kept (keyed by address and shape).
+struct MapKey {
+  const void *base;
+  long long n, t, p, astride;
+  int elem_bytes;
+  bool operator==(const MapKey &o) const {
+    return base == o.base && n == o.n && t == o.t && p == o.p && astride == o.astride && elem_bytes == o.elem_bytes;
+  }
+};
+constexpr int kMapCache = 64;
+thread_local MapKey g_map_keys[kMapCache];
+thread_local CUtensorMap g_map_vals[kMapCache];
+thread_local int g_map_next = 0, g_map_count = 0;
+
+bool encode_map_uncached(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p);
+
 bool encode_map(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p) {
+  const long long astride = p.P == 1 ? p.T * p.N : p.agent_stride;
+  const MapKey key{base, p.N, p.T, p.P, astride, elem_bytes};
+  for (int i = 0; i < g_map_count; ++i)
+    if (g_map_keys[i] == key) {
+      *m = g_map_vals[i];
+      return true;
+    }
+  if (!encode_map_uncached(m, base, elem_bytes, p)) return false;
+  g_map_keys[g_map_next] = key;
+  g_map_vals[g_map_next] = *m;
+  g_map_next = (g_map_next + 1) % kMapCache;
+  if (g_map_count < kMapCache) ++g_map_count;
+  return true;
+}
+
+bool encode_map_uncached(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p) {
   EncodeFn enc = get_encode();
   if (!enc) return false;
   const long long astride = p.P == 1 ? p.T * p.N : p.agent_stride;
