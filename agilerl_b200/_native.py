@@ -130,6 +130,36 @@ def stream_ptr(device=None) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
+class _NoGuard:
+    __slots__ = ()
+
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *a):
+        return False
+
+
+_NO_GUARD = _NoGuard()
+
+
+def raw_stream(index: int) -> int:
+    """cudaStream_t of torch's current stream on device ``index`` (no Python Stream object)."""
+    import torch
+
+    return torch._C._cuda_getCurrentRawStream(index)
+
+
+def on_device(dev):
+    """Device guard that costs nothing when ``dev`` already is the current device (the normal
+    one-process-per-GPU case)."""
+    import torch
+
+    if torch._C._cuda_getDevice() == dev.index:
+        return _NO_GUARD
+    return torch.cuda.device(dev)
+
+
 def require_cuda(device=None):
     """Return the torch CUDA device the engine stores on, or raise loudly."""
     import torch

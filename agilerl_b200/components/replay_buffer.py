@@ -118,10 +118,12 @@ class ReplayBuffer:
 
     def _out(self, batch: TensorBatch) -> TensorBatch:
         """Move a sampled batch to ``self.device`` (no-op when that is the storage device)."""
-        dev = torch.device(self.device)
-        if dev.type == "cuda" and (dev.index is None or dev == self.storage_device):
-            return batch
-        return batch.to(dev)
+        same = getattr(self, "_out_same", None)
+        if same is None:
+            dev = torch.device(self.device)
+            same = dev.type == "cuda" and (dev.index is None or dev == self.storage_device)
+            self._out_same = same
+        return batch if same else batch.to(torch.device(self.device))
 
     # -- add (reference :60-112) ---------------------------------------------------------------
     def _init(self, data: TensorBatch) -> None:
@@ -163,7 +165,7 @@ class ReplayBuffer:
         data, n = self._prepare(data)
         if self._storage is None:
             self._init(data)
-        with torch.cuda.device(self.storage_device):
+        with nv.on_device(self.storage_device):
             xp.ring_insert(self._pairs(data, self._leaves), n, self._cursor, self.max_size)
         self._advance(n)
 
@@ -190,24 +192,62 @@ class ReplayBuffer:
             if self.exact_rng_advance and n - 1 > draws:
                 stream.skip(n - 1 - draws)
             stream.commit()
-            with torch.cuda.device(dev):
+            with nv.on_device(dev):
                 raw = self._stage().to_device(raw)
         else:
-            with torch.cuda.device(dev):
+            with nv.on_device(dev):
                 raw = xp.philox_u32(self._philox_seed, self._philox_offset, b, dev)
             self._philox_offset += (b + 3) // 4
-        with torch.cuda.device(dev):
+        with nv.on_device(dev):
             return xp.randperm_prefix(raw, b, 1, n)
 
-    def _gather(self, indices: torch.Tensor) -> TensorBatch:
-        """``storage[indices]`` as fresh copies, every key in one launch."""
-        idx = indices.to(device=self.storage_device, dtype=torch.int64).contiguous().view(-1)
-        B = idx.numel()
-        out = {p: torch.empty((B, *s.shape[1:]), dtype=s.dtype, device=s.device)
-               for p, s in self._leaves.items()}
-        with torch.cuda.device(self.storage_device):
-            xp.gather([(self._leaves[p], out[p]) for p in self._leaves], idx, self.max_size, self._err)
-        return _unflatten(out, [B])
+    def _gather_plan(self):
+        """Per-storage launch descriptor, built once: the ``xp_key`` array with the source
+        pointers / row sizes filled in, and (tail shape, dtype) of every key."""
+        plan = getattr(self, "_gplan", None)
+        if plan is None or plan[0] is not self._leaves:
+            paths = list(self._leaves.keys())
+            keys = (nv.XpKey * len(paths))()
+            meta = []
+            for i, p in enumerate(paths):
+                t = self._leaves[p]
+                keys[i].src = t.data_ptr()
+                keys[i].row_bytes = xp.row_bytes(t)
+                meta.append((p, tuple(t.shape[1:]), t.dtype))
+            flat = all(len(p) == 1 for p in paths)
+            plan = (self._leaves, keys, meta, flat, nv.load().xp_gather)
+            self._gplan = plan
+        return plan
+
+    def _gather(self, indices: torch.Tensor, lead: tuple | None = None) -> TensorBatch:
+        """``storage[indices]`` as fresh copies, every key in one launch.  ``lead``: leading
+        shape of the result (the shape of ``indices`` in the reference's ``storage[idxs]``)."""
+        dev = self.storage_device
+        idx = indices
+        if idx.device != dev or idx.dtype != torch.int64:
+            idx = idx.to(device=dev, dtype=torch.int64)
+        if idx.dim() != 1 or not idx.is_contiguous():
+            idx = idx.contiguous().view(-1)
+        B = idx.shape[0]
+        if lead is None:
+            lead = (B,)
+        _, keys, meta, flat, fn = self._gather_plan()
+        out = {}
+        with nv.on_device(dev):
+            for i, (p, tail, dt) in enumerate(meta):
+                o = torch.empty((*lead, *tail), dtype=dt, device=dev)
+                keys[i].dst = o.data_ptr()
+                out[p] = o
+            if B:
+                nv.check(fn(keys, len(meta), idx.data_ptr(), B, self.max_size, self._err.data_ptr(),
+                            nv.raw_stream(dev.index)), "xp_gather")
+        if flat:  # no nested keys: build the batch directly
+            tb = TensorBatch.__new__(TensorBatch)
+            tb._d = {p[0]: t for p, t in out.items()}
+            tb._non_tensor = {}
+            tb.batch_size = torch.Size(lead)
+            return tb
+        return _unflatten(out, list(lead))
 
     def sample(self, batch_size: int, return_idx: bool = False) -> TensorBatch:
         indices = self._uniform_indices(batch_size)
@@ -289,7 +329,7 @@ class MultiStepReplayBuffer(ReplayBuffer):
             raise TypeError("n-step reward must be float32 (Transition casts it, data.py:85-87)")
         gpow = [float(np.float32(self.gamma**i)) for i in range(self.n_step)]
         slot0 = self._stage_count % self.n_step  # oldest step (the ring is full here)
-        with torch.cuda.device(self.storage_device):
+        with nv.on_device(self.storage_device):
             xp.nstep_fold_insert([(self._stage[p], dst[p]) for p in paths], roles,
                                  paths.index(done_path), done_bytes, self.n_step, slot0, gpow,
                                  self._stage_n, cursor, dst_rows)
@@ -301,7 +341,7 @@ class MultiStepReplayBuffer(ReplayBuffer):
         if n != self._stage_n:
             raise ValueError(f"n-step buffer was initialised with {self._stage_n} envs, got {n}")
         slot = self._stage_count % self.n_step
-        with torch.cuda.device(self.storage_device):
+        with nv.on_device(self.storage_device):
             xp.ring_insert(self._pairs(data, self._stage), n, slot * n, self.n_step * n)
         self._stage_count += 1
         view = _unflatten({p: t[slot * n:(slot + 1) * n] for p, t in self._stage.items()}, [n])
@@ -319,11 +359,10 @@ class MultiStepReplayBuffer(ReplayBuffer):
         return self.n_step_buffer[0]
 
     def sample_from_indices(self, idxs: torch.Tensor) -> TensorBatch:
-        idxs = torch.as_tensor(idxs)
-        out = self._gather(idxs)
-        if idxs.ndim > 1:  # storage[idxs] with (B,1) indices gives [B,1,...] in the reference
-            out = out.view(*idxs.shape)
-        return self._out(out)
+        if not isinstance(idxs, torch.Tensor):
+            idxs = torch.as_tensor(idxs)
+        # storage[idxs] with (B,1) indices gives [B,1,...] in the reference
+        return self._out(self._gather(idxs, tuple(idxs.shape) if idxs.ndim > 1 else None))
 
     def _get_n_step_info(self) -> TensorBatch:
         """The folded n-step transition for the current window (reference :206-258)."""
@@ -352,6 +391,10 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         self._tree_capacity = tree_capacity
         self._trees = None
         self._pending_max_priority = 1.0
+        self._pending_err = None
+        self._err_pin = None
+        self._err_ev = None
+        self._updates_since_poll = 0
 
     # trees are created on first use so that constructing a buffer needs no GPU
     def _ensure_trees(self):
@@ -362,6 +405,10 @@ class PrioritizedReplayBuffer(ReplayBuffer):
             self._state = torch.tensor([self._pending_max_priority], dtype=torch.float64,
                                        device=self.storage_device)
             self._trees = (s, m, st, st.handle(None))
+            import ctypes as _C
+
+            self._lib = nv.load()
+            self._href = _C.byref(self._trees[3])
         return self._trees
 
     @property
@@ -390,7 +437,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         if self._storage is None:
             self._init(data)
         _, _, st, h = self._ensure_trees()
-        with torch.cuda.device(self.storage_device):
+        with nv.on_device(self.storage_device):
             xp.ring_insert(self._pairs(data, self._leaves), n, self._cursor, self.max_size)
             # leaves tree_ptr.. := max_priority ** alpha (:306-309), no host round trip
             xp.per_add(h, self._state, self.tree_ptr, n, self.max_size, self.alpha)
@@ -402,7 +449,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         s, m, st, h = self._ensure_trees()
         v = torch.tensor([float(priority) ** self.alpha], dtype=torch.float64, device=self.storage_device)
         i = torch.tensor([int(idx)], dtype=torch.int64, device=self.storage_device)
-        with torch.cuda.device(self.storage_device):
+        with nv.on_device(self.storage_device):
             xp.tree_set_batch(h, i, v, st.err)
         self.max_priority = max(self.max_priority, priority)
 
@@ -410,11 +457,11 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         dev = self.storage_device
         if self.rng == "torch":
             # batch_size x torch.rand(1).item() == torch.rand(batch_size) on the same stream
-            with torch.cuda.device(dev):
+            with nv.on_device(dev):
                 slot, host = self._stage().host_view(batch_size, torch.float32)
                 torch.rand(batch_size, out=host)
                 return self._stage().push(slot, host)
-        with torch.cuda.device(dev):
+        with nv.on_device(dev):
             raw = xp.philox_u32(self._philox_seed, self._philox_offset, batch_size, dev)
         self._philox_offset += (batch_size + 3) // 4
         return (raw & 0xFFFFFF).to(torch.float32) * (2.0**-24)
@@ -425,7 +472,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
             u = self._draw_uniforms(batch_size)
         u = u.to(device=self.storage_device, dtype=torch.float32).contiguous()
         idx = torch.empty(batch_size, dtype=torch.int64, device=self.storage_device)
-        with torch.cuda.device(self.storage_device):
+        with nv.on_device(self.storage_device):
             xp.per_sample(h, u, batch_size, 1, self.size, 0.0, idx, None)
         return idx
 
@@ -433,36 +480,49 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         _, _, st, h = self._ensure_trees()
         idx = torch.as_tensor(indices).to(device=self.storage_device, dtype=torch.int64).contiguous().view(-1)
         w = torch.empty(idx.numel(), dtype=torch.float32, device=self.storage_device)
-        with torch.cuda.device(self.storage_device):
+        with nv.on_device(self.storage_device):
             xp.per_weights(h, idx, self.size, float(beta), w)
         return w
 
     def sample(self, batch_size: int, beta: float = 0.4, u: torch.Tensor | None = None) -> TensorBatch:
         """``u`` (optional): the fp32 uniforms to use instead of drawing them."""
         _, _, st, h = self._ensure_trees()
-        self._raise_deferred()
+        if self._pending_err is not None:
+            self._raise_deferred()
         dev = self.storage_device
         if u is None:
             u = self._draw_uniforms(batch_size)
-        u = u.to(device=dev, dtype=torch.float32).contiguous()
-        idx = torch.empty(batch_size, dtype=torch.int64, device=dev)
-        w = torch.empty(batch_size, dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
-            xp.per_sample(h, u, batch_size, 1, self.size, float(beta), idx, w)
-        samples = self._gather(idx)
-        samples["weights"] = w.unsqueeze(1)
-        samples["idxs"] = idx.unsqueeze(1)
+        if u.device != dev or u.dtype != torch.float32 or not u.is_contiguous():
+            u = u.to(device=dev, dtype=torch.float32).contiguous()
+        with nv.on_device(dev):
+            idx = torch.empty((batch_size, 1), dtype=torch.int64, device=dev)
+            w = torch.empty((batch_size, 1), dtype=torch.float32, device=dev)
+            nv.check(self._lib.xp_per_sample(self._href, u.data_ptr(), batch_size, 1, self._size,
+                                             float(beta), idx.data_ptr(), w.data_ptr(),
+                                             nv.raw_stream(dev.index)), "xp_per_sample")
+        samples = self._gather(idx.view(-1))
+        samples._d["weights"] = w
+        samples._d["idxs"] = idx
         return self._out(samples)
 
     def _raise_deferred(self) -> None:
-        """Out-of-range indices that arrived as DEVICE tensors are detected by the kernel; the
-        flag is read back without blocking and the AssertionError surfaces on the next call."""
-        pend = getattr(self, "_pending_err", None)
+        """Out-of-range indices that arrived as DEVICE tensors are detected by the kernel (a sticky
+        device flag); the flag is read back without blocking and the AssertionError surfaces on
+        a later call into the buffer (``check_errors()`` forces it)."""
+        pend = self._pending_err
         if pend is not None and pend[1].query():
             self._pending_err = None
             if int(pend[0][0]) != 0:
                 self._trees[2].err.zero_()
                 raise AssertionError("priority index out of range [0, max_size)")
+
+    def _poll_err_async(self) -> None:
+        if self._err_pin is None:
+            self._err_pin = torch.zeros(1, dtype=torch.int32).pin_memory()
+            self._err_ev = torch.cuda.Event()
+        self._err_pin.copy_(self._trees[2].err, non_blocking=True)
+        self._err_ev.record()
+        self._pending_err = (self._err_pin, self._err_ev)
 
     def update_priorities(self, indices, priorities, check: bool = True) -> None:
         """Sequential semantics of :411-428 in one batched pass (last writer wins; every
@@ -470,21 +530,24 @@ class PrioritizedReplayBuffer(ReplayBuffer):
 
         Never blocks the host: host-side indices (numpy / CPU tensors) are range-checked on the
         host (AssertionError as in :319); device-side indices are checked by the kernel and the
-        error is raised on the next call into the buffer."""
+        error is raised on a later call into the buffer."""
         _, _, st, h = self._ensure_trees()
         dev = self.storage_device
-        self._raise_deferred()
-        idx = torch.as_tensor(indices)
+        if self._pending_err is not None:
+            self._raise_deferred()
+        idx = indices if isinstance(indices, torch.Tensor) else torch.as_tensor(indices)
         on_host = not idx.is_cuda
         if on_host and check and idx.numel():
             assert 0 <= int(idx.min()) and int(idx.max()) < self.max_size, (
                 "priority index out of range [0, max_size)")
-        with torch.cuda.device(dev):
+        with nv.on_device(dev):
             if on_host:
                 idx = self._stage().to_device(idx.to(torch.int64).reshape(-1))
             else:
-                idx = idx.to(device=dev, dtype=torch.int64).contiguous().view(-1)
-            pr = torch.as_tensor(priorities)
+                if idx.device != dev or idx.dtype != torch.int64:
+                    idx = idx.to(device=dev, dtype=torch.int64)
+                idx = idx.view(-1) if idx.is_contiguous() else idx.contiguous().view(-1)
+            pr = priorities if isinstance(priorities, torch.Tensor) else torch.as_tensor(priorities)
             if pr.dtype != torch.float32:
                 # priority.item() of a float64 array keeps fp64; the kernel takes fp32 inputs,
                 # which is what the algorithms produce (dqn_rainbow.py:487-488)
@@ -493,19 +556,22 @@ class PrioritizedReplayBuffer(ReplayBuffer):
                 pr = pr.to(device=dev).contiguous().view(-1)
             else:
                 pr = self._stage().to_device(pr.reshape(-1))
-            n = min(idx.numel(), pr.numel())  # zip(..., strict=False)
-            xp.per_update(h, self._state, idx[:n], pr[:n], self.max_size, self.alpha, st.err)
+            n = min(idx.shape[0], pr.shape[0])  # zip(..., strict=False)
+            nv.check(self._lib.xp_per_update(self._href, self._state.data_ptr(), idx.data_ptr(),
+                                             pr.data_ptr(), n, self.max_size, self.alpha,
+                                             st.err.data_ptr(), nv.raw_stream(dev.index)),
+                     "xp_per_update")
             if check and not on_host:
-                if not hasattr(self, "_err_pin"):
-                    self._err_pin = torch.zeros(1, dtype=torch.int32).pin_memory()
-                self._err_pin.copy_(st.err, non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record()
-                self._pending_err = (self._err_pin, ev)
+                self._updates_since_poll += 1
+                if self._updates_since_poll >= 32 and self._pending_err is None:
+                    self._updates_since_poll = 0
+                    self._poll_err_async()
 
     def check_errors(self) -> None:
         """Block until every queued update ran and raise its index error, if any."""
-        pend = getattr(self, "_pending_err", None)
-        if pend is not None:
-            pend[1].synchronize()
-            self._raise_deferred()
+        if self._trees is None:
+            return
+        with nv.on_device(self.storage_device):
+            self._poll_err_async()
+        self._pending_err[1].synchronize()
+        self._raise_deferred()

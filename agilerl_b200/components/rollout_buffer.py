@@ -224,7 +224,7 @@ class RolloutBuffer:
                 # PPO hands (layers, num_envs, size); stored as (num_envs, layers, size) (:381-392)
                 put(("hidden_states", key), torch.as_tensor(t).permute(1, 0, 2))
 
-        with torch.cuda.device(self._sdev):
+        with nv.on_device(self._sdev):
             xp.ring_insert(pairs_as_rows(pairs), 1, self.pos, self.capacity)
 
         self.pos += 1
@@ -237,7 +237,7 @@ class RolloutBuffer:
         lv = _as_f64(last_value, self.num_envs, self._sdev)
         ld = _as_f64(last_done, self.num_envs, self._sdev)
         L = self._leaves
-        with torch.cuda.device(self._sdev):
+        with nv.on_device(self._sdev):
             xp.gae(L[("rewards",)], L[("values",)], L[("dones",)], lv, ld, L[("advantages",)],
                    L[("returns",)], buffer_size, self.num_envs, 1, self.capacity * self.num_envs,
                    float(self.gamma), float(self.gae_lambda), bool(self.use_gae))
@@ -253,7 +253,7 @@ class RolloutBuffer:
         out = OrderedDict((p, torch.empty((B, *s.shape[1:]), dtype=s.dtype, device=s.device))
                           for p, s in flat.items())
         n_rows = next(iter(flat.values())).shape[0]
-        with torch.cuda.device(self._sdev):
+        with nv.on_device(self._sdev):
             xp.gather([(flat[p], out[p]) for p in flat], idx, n_rows)
         return out
 
@@ -265,7 +265,7 @@ class RolloutBuffer:
         if draws:
             raw[:draws] = stream.draw_u32(draws)
         stream.commit()
-        with torch.cuda.device(self._sdev):
+        with nv.on_device(self._sdev):
             return chunked_randperm_prefix(raw.to(self._sdev), batch_size, total)
 
     def get_tensor_batch(self, batch_size: int | None = None, device: str | None = None):
@@ -412,7 +412,7 @@ class RolloutArena:
         lv = _as_f64(last_values, P * N, self._sdev)
         ld = _as_f64(last_dones, P * N, self._sdev)
         S = self.slab
-        with torch.cuda.device(self._sdev):
+        with nv.on_device(self._sdev):
             xp.gae(S[("rewards",)], S[("values",)], S[("dones",)], lv, ld, S[("advantages",)],
                    S[("returns",)], T, N, P, self.capacity * N, float(self.gamma),
                    float(self.gae_lambda), bool(self.use_gae))

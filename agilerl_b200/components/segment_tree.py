@@ -31,7 +31,7 @@ class _TreeStorage:
         self.device = nv.require_cuda(device)
         self.capacity = capacity
         self.paired = paired
-        with torch.cuda.device(self.device):
+        with nv.on_device(self.device):
             if paired:
                 self.nodes = torch.empty(2 * capacity, 2, dtype=torch.float64, device=self.device)
             else:
@@ -102,7 +102,7 @@ class SegmentTree:
             self._storage = _TreeStorage(capacity, device, paired=False)
             self._col = self._storage.column(0)
             self._t = self._storage.handle(self._kind)
-            with torch.cuda.device(self._storage.device):
+            with nv.on_device(self._storage.device):
                 xp.tree_init(self._t, torch.cuda.current_stream().cuda_stream)
         else:
             self._storage = _storage
@@ -117,7 +117,7 @@ class SegmentTree:
 
     def operate(self, start: int = 0, end: int = 0) -> float:
         out = self._storage.scratch
-        with torch.cuda.device(self.device):
+        with nv.on_device(self.device):
             xp.tree_query(self._t, int(start), int(end), out)
         return float(out[0 if self._kind == "sum" else 1].item())
 
@@ -135,7 +135,7 @@ class SegmentTree:
         """Sequential ``tree[idx[i]] = val[i]`` for the whole batch in one pass (last writer wins)."""
         idx = idx.to(device=self.device, dtype=torch.int64).contiguous().view(-1)
         val = val.to(device=self.device, dtype=torch.float64).contiguous().view(-1)
-        with torch.cuda.device(self.device):
+        with nv.on_device(self.device):
             xp.tree_set_batch(self._t, idx, val, self._storage.err)
         if check and int(self._storage.err.item()) != 0:
             self._storage.err.zero_()
@@ -164,7 +164,7 @@ class SumSegmentTree(SegmentTree):
 
     def retrieve_batch(self, upperbound: torch.Tensor) -> torch.Tensor:
         ub = upperbound.to(device=self.device, dtype=torch.float64).contiguous().view(-1)
-        with torch.cuda.device(self.device):
+        with nv.on_device(self.device):
             return xp.tree_retrieve(self._t, ub)
 
 
@@ -185,6 +185,6 @@ def make_pair(capacity: int, device=None) -> tuple[SumSegmentTree, MinSegmentTre
     """An interleaved (sum, min) pair sharing one node array: the two children of a node in
     both trees are one aligned 32-byte sector (PrioritizedReplayBuffer, replay_buffer.py:292-294)."""
     st = _TreeStorage(capacity, device, paired=True)
-    with torch.cuda.device(st.device):
+    with nv.on_device(st.device):
         xp.tree_init(st.handle(None), torch.cuda.current_stream().cuda_stream)
     return SumSegmentTree(capacity, _storage=st), MinSegmentTree(capacity, _storage=st), st

@@ -21,7 +21,7 @@ class PinnedRing:
     def _slot(self, nbytes: int) -> dict:
         s = self._slots[self._next]
         self._next = (self._next + 1) % len(self._slots)
-        if s["ev"] is not None:
+        if s["ev"] is not None and not s["ev"].query():
             s["ev"].synchronize()  # normally long complete
         if s["buf"] is None or s["buf"].numel() < nbytes:
             s["buf"] = torch.empty(max(nbytes, 4096), dtype=torch.uint8).pin_memory()
@@ -38,7 +38,7 @@ class PinnedRing:
         """Enqueue host -> device on the current stream; returns the device tensor."""
         out = torch.empty(host.shape, dtype=host.dtype, device=self.device)
         out.copy_(host, non_blocking=True)
-        slot["ev"].record(torch.cuda.current_stream(self.device))
+        slot["ev"].record()
         return out
 
     def to_device(self, t: torch.Tensor) -> torch.Tensor:

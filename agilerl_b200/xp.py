@@ -16,7 +16,7 @@ from ._native import XpKey, XpTree, check, ptr
 
 
 def _stream(t: torch.Tensor) -> int:
-    return torch.cuda.current_stream(t.device).cuda_stream
+    return torch._C._cuda_getCurrentRawStream(t.device.index)
 
 
 def _need(t: torch.Tensor, dtype, name: str) -> torch.Tensor:

@@ -1,0 +1,29 @@
+"""Host-side profile of the per-agent API loop (bench.py e2e leg) on a small buffer."""
+import cProfile, pstats, sys, os, time, io
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+sys.argv = ["bench.py", "--rows", "65536"]
+import bench, torch
+args = bench.parse_args()
+dev = torch.device("cuda", 0)
+wl = bench.C2Workload(args, 0, 1, dev)
+wl.setup(); wl.e2e_setup()
+for i in range(5): wl.e2e_step(i)
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for i in range(50): wl.e2e_step(i)
+torch.cuda.synchronize()
+print("e2e ms/step", (time.perf_counter() - t0) / 50 * 1e3)
+# per-call host time (no sync inside)
+import collections
+acc = collections.Counter()
+for i in range(50):
+    for a in range(wl.P):
+        t = time.perf_counter(); b = wl.per.sample(wl.B, 0.4); acc["sample"] += time.perf_counter() - t
+        t = time.perf_counter(); nb = wl.nstep.sample_from_indices(b["idxs"]); acc["nstep"] += time.perf_counter() - t
+        t = time.perf_counter(); wl.per.update_priorities(b["idxs"], wl.prio_host[a]); acc["update"] += time.perf_counter() - t
+    t = time.perf_counter(); torch.cuda.synchronize(); acc["sync"] += time.perf_counter() - t
+for k, v in acc.items(): print(f"{k:8s} {v / 50 / (wl.P if k != 'sync' else 1) * 1e6:8.1f} us per call")
+pr = cProfile.Profile(); pr.enable()
+for i in range(50): wl.e2e_step(i)
+torch.cuda.synchronize(); pr.disable()
+s = io.StringIO(); pstats.Stats(pr, stream=s).sort_stats("tottime").print_stats(28); print(s.getvalue()[:6000])
