@@ -458,9 +458,10 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         if self.rng == "torch":
             # batch_size x torch.rand(1).item() == torch.rand(batch_size) on the same stream
             with nv.on_device(dev):
-                slot, host = self._stage().host_view(batch_size, torch.float32)
+                ring = self._stage()
+                slot, host, dv = ring.views(batch_size, torch.float32)
                 torch.rand(batch_size, out=host)
-                return self._stage().push(slot, host)
+                return ring.push(slot, host, dv)
         with nv.on_device(dev):
             raw = xp.philox_u32(self._philox_seed, self._philox_offset, batch_size, dev)
         self._philox_offset += (batch_size + 3) // 4

@@ -4,46 +4,71 @@ The reference hands the buffers host data on every call: ``torch.rand`` draws fo
 (replay_buffer.py:377) and priorities as numpy arrays (algorithms/dqn_rainbow.py:487).  A plain
 ``.to(device)`` of pageable memory blocks the host until the copy is done; going through a small
 ring of pinned buffers keeps every call asynchronous (the copy is enqueued on the current stream,
-the host moves on).  A slot is reused only after the copy that read it has completed.
+the host moves on).  Every slot owns a pinned host buffer AND a device buffer; a slot is reused
+only after the copy that read its host side has completed, and its device side is only ever
+touched by stream-ordered work (copy, then the kernel that consumes it), so reuse is safe as long
+as the consumer runs on the same stream — which is how the buffers use it.
 """
 
 from __future__ import annotations
 
 import torch
 
+_SLOT_BYTES = 1 << 16
+
+
+class _Slot:
+    __slots__ = ("host", "dev", "ev", "views")
+
+    def __init__(self, nbytes: int, device: torch.device) -> None:
+        self.host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+        self.dev = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        self.ev = torch.cuda.Event()
+        self.views: dict = {}
+
 
 class PinnedRing:
     def __init__(self, device: torch.device, slots: int = 16) -> None:
         self.device = device
-        self._slots: list[dict] = [{"buf": None, "ev": None} for _ in range(slots)]
+        self._n = slots
+        self._slots: list[_Slot | None] = [None] * slots
         self._next = 0
+        self._used = [False] * slots
 
-    def _slot(self, nbytes: int) -> dict:
-        s = self._slots[self._next]
-        self._next = (self._next + 1) % len(self._slots)
-        if s["ev"] is not None and not s["ev"].query():
-            s["ev"].synchronize()  # normally long complete
-        if s["buf"] is None or s["buf"].numel() < nbytes:
-            s["buf"] = torch.empty(max(nbytes, 4096), dtype=torch.uint8).pin_memory()
-        if s["ev"] is None:
-            s["ev"] = torch.cuda.Event()
+    def _slot(self, nbytes: int) -> _Slot:
+        i = self._next
+        self._next = (i + 1) % self._n
+        s = self._slots[i]
+        if s is None or s.host.numel() < nbytes:
+            if s is not None and self._used[i]:
+                s.ev.synchronize()
+            s = _Slot(max(nbytes, _SLOT_BYTES), self.device)
+            self._slots[i] = s
+            self._used[i] = False
+        elif self._used[i] and not s.ev.query():
+            s.ev.synchronize()  # normally long complete
         return s
 
-    def host_view(self, n: int, dtype: torch.dtype):
-        """(slot, pinned tensor [n] of dtype) to be filled by the caller, then ``push``ed."""
+    def views(self, n: int, dtype: torch.dtype):
+        """(slot, pinned host view [n], device view [n]) — fill the host view, then ``push``."""
         s = self._slot(n * dtype.itemsize)
-        return s, s["buf"][: n * dtype.itemsize].view(dtype)
+        v = s.views.get((n, dtype))
+        if v is None:
+            nb = n * dtype.itemsize
+            v = (s.host[:nb].view(dtype), s.dev[:nb].view(dtype))
+            s.views[(n, dtype)] = v
+        return s, v[0], v[1]
 
-    def push(self, slot: dict, host: torch.Tensor) -> torch.Tensor:
-        """Enqueue host -> device on the current stream; returns the device tensor."""
-        out = torch.empty(host.shape, dtype=host.dtype, device=self.device)
-        out.copy_(host, non_blocking=True)
-        slot["ev"].record()
-        return out
+    def push(self, slot: _Slot, host: torch.Tensor, dev: torch.Tensor) -> torch.Tensor:
+        """Enqueue host -> device on the current stream; returns the device view (valid for
+        stream-ordered consumers until the ring wraps around)."""
+        dev.copy_(host, non_blocking=True)
+        slot.ev.record()
+        self._used[self._slots.index(slot)] = True
+        return dev
 
     def to_device(self, t: torch.Tensor) -> torch.Tensor:
-        """Asynchronous copy of a (small) CPU tensor."""
-        t = t.contiguous()
-        slot, host = self.host_view(t.numel(), t.dtype)
-        host.copy_(t.view(-1))
-        return self.push(slot, host).view(t.shape)
+        """Asynchronous copy of a (small, flat) CPU tensor."""
+        slot, host, dev = self.views(t.numel(), t.dtype)
+        host.copy_(t.reshape(-1))
+        return self.push(slot, host, dev)

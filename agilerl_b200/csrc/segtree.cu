@@ -32,18 +32,75 @@ __global__ void tree_init_kernel(Tree t) {
 }
 
 // ---- queries ----------------------------------------------------------------------------------
-// SegmentTree._operate_helper (segment_tree.py:28-62), same recursion => same association.
+// SegmentTree._operate_helper (segment_tree.py:28-62) without recursion (device stacks are small;
+// a 2^20-leaf tree is 20 frames deep) but with the SAME association order:
+//   walk down to the node where [start,end] splits;
+//   left part  = suffix query of the left child  = op(op(op(deepest, R_k), ...), R_1)   (left-deep)
+//   right part = prefix query of the right child = op(L_1, op(L_2, ... op(L_k, deepest))) (right-deep)
+//   result     = op(left part, right part).
+template <bool IS_SUM>
+__device__ __forceinline__ double q_op(double a, double b) { return IS_SUM ? __dadd_rn(a, b) : py_min(a, b); }
+
+template <bool IS_SUM>
+__device__ double q_suffix(const double *base, long long stride, long long start, long long node,
+                           long long ns, long long ne) {
+  long long sib[40];
+  int k = 0;
+  while (start != ns) {
+    const long long mid = (ns + ne) / 2;
+    if (mid + 1 <= start) {
+      node = 2 * node + 1;
+      ns = mid + 1;
+    } else {
+      sib[k++] = 2 * node + 1;  // the whole right child is inside the range
+      node = 2 * node;
+      ne = mid;
+    }
+  }
+  double v = base[node * stride];
+  while (k > 0) v = q_op<IS_SUM>(v, base[sib[--k] * stride]);
+  return v;
+}
+
+template <bool IS_SUM>
+__device__ double q_prefix(const double *base, long long stride, long long end, long long node,
+                           long long ns, long long ne) {
+  long long sib[40];
+  int k = 0;
+  while (end != ne) {
+    const long long mid = (ns + ne) / 2;
+    if (end <= mid) {
+      node = 2 * node;
+      ne = mid;
+    } else {
+      sib[k++] = 2 * node;  // the whole left child is inside the range
+      node = 2 * node + 1;
+      ns = mid + 1;
+    }
+  }
+  double v = base[node * stride];
+  while (k > 0) v = q_op<IS_SUM>(base[sib[--k] * stride], v);
+  return v;
+}
+
 template <bool IS_SUM>
 __device__ double operate_helper(const double *base, long long stride, long long start,
                                  long long end, long long node, long long ns, long long ne) {
-  if (start == ns && end == ne) return base[node * stride];
-  const long long mid = (ns + ne) / 2;
-  if (end <= mid) return operate_helper<IS_SUM>(base, stride, start, end, 2 * node, ns, mid);
-  if (mid + 1 <= start)
-    return operate_helper<IS_SUM>(base, stride, start, end, 2 * node + 1, mid + 1, ne);
-  const double a = operate_helper<IS_SUM>(base, stride, start, mid, 2 * node, ns, mid);
-  const double b = operate_helper<IS_SUM>(base, stride, mid + 1, end, 2 * node + 1, mid + 1, ne);
-  return IS_SUM ? __dadd_rn(a, b) : py_min(a, b);
+  while (!(start == ns && end == ne)) {
+    const long long mid = (ns + ne) / 2;
+    if (end <= mid) {
+      node = 2 * node;
+      ne = mid;
+    } else if (mid + 1 <= start) {
+      node = 2 * node + 1;
+      ns = mid + 1;
+    } else {
+      const double a = q_suffix<IS_SUM>(base, stride, start, 2 * node, ns, mid);
+      const double b = q_prefix<IS_SUM>(base, stride, end, 2 * node + 1, mid + 1, ne);
+      return q_op<IS_SUM>(a, b);
+    }
+  }
+  return base[node * stride];
 }
 
 __global__ void tree_query_kernel(Tree t, long long start, long long end, double *out) {

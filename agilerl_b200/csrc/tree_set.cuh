@@ -5,19 +5,17 @@
 // any schedule that recomputes each touched ancestor once after both children are final is
 // bit-identical to the sequential loop.
 //
-// Three schedules, chosen by batch size (none uses a global atomic in the climb):
-//   S  B <= 2048          one CTA: sort (leaf, pos) keys in shared memory, resolve duplicates,
-//                         then a level-synchronous SPARSE climb.  In sorted order the touched
-//                         nodes of a level are runs of equal prefixes; the first item of a run
-//                         ("leader") owns the node, its sibling is either the next leader of the
-//                         level below (value passed through shared memory) or untouched (read
-//                         from global, prefetched 4 levels ahead).  One __syncthreads per level.
-//   L  B <= cap/4         tickets (last writer per leaf) + histogram over <= 2048 bucket subtrees
-//                         -> scatter winners into buckets -> one CTA per bucket runs schedule S
-//                         inside its subtree -> one CTA rebuilds the (<= 2048-leaf) top densely.
-//   D  otherwise          tickets -> winners write leaves -> dense bottom-up rebuild, coalesced.
-// `aux` (int32[2*cap], zero between calls): [cap, 2cap) last-writer tickets; [0, cap) scratch
-// of schedule L (bucket counters, offsets, cursors, bucketed items).
+// The tree is cut into nb = 2^k bucket subtrees with ~8 batch items each; ONE WARP climbs a bucket
+// (warp_climb: register sort by (leaf, pos), duplicate resolution, level loop over shuffles — no
+// shared memory, block barrier or tree atomic), then the nb-leaf top is rebuilt densely.
+// Three schedules, chosen by batch size:
+//   M  B <= 8192    one launch: every warp filters the whole (L2-resident) batch for its bucket,
+//                   climbs it; the last CTA to finish rebuilds the top.
+//   L  larger B     histogram(+scan) -> scatter into per-bucket slices -> one warp per bucket ->
+//                   dense top (256-node chunks).
+//   D  B ~ cap      tickets -> winners write leaves -> dense coalesced bottom-up rebuild.
+// `aux` (int32[2*cap]): [cap, 2cap) last-writer tickets (zero between calls; schedule D and
+// oversize buckets); [0, cap) scratch (done counter, bucket counters/offsets/cursors, items).
 #pragma once
 #include "common.cuh"
 #include "pow.cuh"
@@ -48,6 +46,7 @@ struct SetSrc {
   long long range_start, range_mod;       // kSrcRange: idx = (start + i) % mod, value = max_priority ** alpha
   long long limit;                        // valid idx in [0, limit)
   int *err;
+  const double *pre;                      // optional: leaf values precomputed per batch position
 };
 
 __device__ __forceinline__ long long src_idx(const SetSrc &s, long long i) {
@@ -71,6 +70,7 @@ __device__ __noinline__ double pow_call(double x, double y) { return xp::xp_pow(
 
 __device__ __forceinline__ double src_value(const SetSrc &s, long long pos) {
   if (s.kind == kSrcVal) return s.val[pos];
+  if (s.pre) return __ldcg(&s.pre[pos]);
   const double base = (s.kind == kSrcPrio)
                           ? clamp_prio(s.prio[pos])
                           : __longlong_as_double((long long)*s.max_priority_bits);
@@ -86,53 +86,6 @@ __device__ __forceinline__ void fold_max_priority(const SetSrc &s, double p) {
     atomicMax(s.max_priority_bits, (unsigned long long)__double_as_longlong(p));
 }
 
-constexpr u64 kPad = ~0ull;
-constexpr int kMaxItems = 2048;  // items one CTA climbs at a time
-
-// ---- shared-memory bitonic sort (ascending), npow2 <= kMaxItems --------------------------------
-template <int THREADS>
-__device__ void bitonic_sort(u64 *keys, int npow2) {
-  for (int k = 2; k <= npow2; k <<= 1) {
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int p = threadIdx.x; p < (npow2 >> 1); p += THREADS) {
-        const int i = ((p & ~(j - 1)) << 1) | (p & (j - 1));
-        const int q = i | j;
-        const u64 a = keys[i], b = keys[q];
-        const bool up = ((i & k) == 0);
-        if ((a > b) == up) {
-          keys[i] = b;
-          keys[q] = a;
-        }
-      }
-      __syncthreads();
-    }
-  }
-}
-
-// first index in keys[0..n) whose key is >= target (keys ascending)
-__device__ __forceinline__ int lower_bound(const u64 *keys, int n, u64 target) {
-  int lo = 0, hi = n;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (keys[mid] < target) lo = mid + 1; else hi = mid;
-  }
-  return lo;
-}
-
-struct ClimbSmem {
-  u64 *key;      // [items] (x << 32) | pos, ascending; kPad beyond n
-  double2 *val;  // [items] (sum, min) value of the node this item currently leads
-  int *nxt;      // [items] index of the next leader at the current level
-};
-constexpr size_t climb_smem_bytes(int items) { return (size_t)items * (8 + 16 + 4); }
-
-__device__ __forceinline__ ClimbSmem carve(unsigned char *base, int items) {
-  ClimbSmem s;
-  s.val = reinterpret_cast<double2 *>(base);
-  s.key = reinterpret_cast<u64 *>(base + (size_t)items * 16);
-  s.nxt = reinterpret_cast<int *>(base + (size_t)items * 24);
-  return s;
-}
 
 // (sum, min) of one node.  PAIRED: the interleaved PER layout (stride 2, min = sum + 1) where a
 // node is one aligned 16-byte pair -> a single 128-bit access.
@@ -158,134 +111,224 @@ inline bool is_paired(const Tree &t) {
          (reinterpret_cast<uintptr_t>(t.sum) % 16 == 0);
 }
 
-__device__ __forceinline__ int key_x(const u64 *key, int i) {
-  return reinterpret_cast<const int *>(key)[2 * i + 1];  // high word = leaf index
-}
+constexpr u64 kPad = ~0ull;
 
-// ---- level-synchronous sparse climb ---------------------------------------------------------------
-// On entry key[0..n) is ascending, x = key >> 32 is a leaf index; duplicates of x are adjacent and
-// the LAST of a run carries the winning batch position (largest pos).  All THREADS threads call.
-// Writes the touched leaves from src_value(pos) and recomputes their ancestors up to height h_top
-// (node id at height h: (cap >> h) + (x >> h)).
-//   leader of a node at height k  = first item (in sorted order) below that node;
-//   item i leads heights 0..m_i,   m_i = msb(x_{i-1} ^ x_i)   (item 0 leads every height).
-// A leader that is a left child finds its right sibling, if touched, as the NEXT leader of the
-// level below (nxt[]); a right-child leader's left sibling is untouched by construction.
-template <int ITEMS, int THREADS, bool PAIRED>
-__device__ void climb_sorted(const Tree &t, const SetSrc &s, const ClimbSmem &sm, int n, int h_top) {
+// ---- warp-level sparse climb --------------------------------------------------------------------
+// One warp owns one bucket subtree (2^h_top leaves) and at most 32 items of it, one per lane:
+// key = (leaf << 32) | batch position, kPad for "no item".  Everything is warp-synchronous —
+// a register bitonic sort and the level loop exchange values with shuffles; there is no shared
+// memory, no block barrier and no atomic.
+//   * sorted by (leaf, pos), duplicates of a leaf are adjacent and the LAST of a run carries the
+//     winning position (sequential last-writer-wins, segment_tree.py:81-95);
+//   * leader of a node at height k = first lane (in sorted order) below that node; lane i leads
+//     heights 0..m_i with m_i = msb(x_prev ^ x_i) (lane 0 leads every height);
+//   * a leader that is a left child finds its right sibling, if touched, as the NEXT leader of the
+//     level below (nxt), else the sibling is untouched and read from global memory (prefetched
+//     four levels ahead); a right-child leader's left sibling is untouched by construction.
+// Every touched node is recomputed once from its final children with the reference's operand
+// order (left, right), hence bit-identical to the sequential loop.
+template <bool PAIRED>
+__device__ __forceinline__ void warp_climb(const Tree &t, const SetSrc &s, u64 key, int h_top) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
   const int cap = (int)t.cap;
-  int x[ITEMS];
-  int m[ITEMS];
-  double2 cv[ITEMS];
+  // bitonic sort of the 32 keys (ascending across lanes)
 #pragma unroll
-  for (int it = 0; it < ITEMS; ++it) {
-    const int i = threadIdx.x + it * THREADS;
-    m[it] = -1;
-    x[it] = 0;
-    cv[it] = make_double2(0.0, 0.0);
-    if (i < n) {
-      const int xi = key_x(sm.key, i);
-      const int prev = i ? key_x(sm.key, i - 1) : -1;
-      if (i == 0 || prev != xi) {
-        m[it] = (i == 0) ? 64 : 31 - __clz(prev ^ xi);
-        x[it] = xi;
-        const int j = lower_bound(sm.key, n, (u64)(unsigned)(xi + 1) << 32);  // end of the run of equal x
-        const long long pos = (long long)(sm.key[j - 1] & 0xffffffffull);
-        const double v = src_value(s, pos);
-        cv[it] = make_double2(v, v);
-        st_node<PAIRED>(t, cap + xi, cv[it]);
-        sm.val[i] = cv[it];
-        sm.nxt[i] = j;
-      }
+  for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      const u64 o = __shfl_xor_sync(FULL, key, j);
+      const bool up = ((lane & k) == 0);
+      const bool lower = ((lane & j) == 0);
+      const u64 lo = key < o ? key : o, hi = key < o ? o : key;
+      key = (lower == up) ? lo : hi;
     }
   }
-  __syncthreads();
-
-  constexpr int G = 4;  // levels per prefetch group
+  const bool valid = key != kPad;
+  const int n = __popc(__ballot_sync(FULL, valid));
+  const int x = (int)(key >> 32);
+  const unsigned pos = (unsigned)(key & 0xffffffffull);
+  const int xprev = __shfl_up_sync(FULL, x, 1);
+  const bool leader = valid && (lane == 0 || xprev != x);
+  const unsigned lmask = __ballot_sync(FULL, leader);
+  const unsigned higher = (lane == 31) ? 0u : (lmask & ~((2u << lane) - 1u));
+  int nxt = higher ? (__ffs(higher) - 1) : n;  // next leader (= end of this run of equal leaves)
+  const unsigned pos_last = __shfl_sync(FULL, pos, (nxt - 1) & 31);
+  const int m = leader ? (lane == 0 ? 64 : 31 - __clz(xprev ^ x)) : -1;
+  double2 cv = make_double2(0.0, 0.0);
+  if (leader) {
+    const double v = src_value(s, (long long)pos_last);
+    cv = make_double2(v, v);
+    st_node<PAIRED>(t, cap + x, cv);
+  }
+  constexpr int G = 4;
   for (int k0 = 1; k0 <= h_top; k0 += G) {
-    double2 pf[ITEMS][G];
+    double2 pf[G];
 #pragma unroll
-    for (int it = 0; it < ITEMS; ++it) {
-#pragma unroll
-      for (int g = 0; g < G; ++g) {
-        const int kk = k0 + g;
-        pf[it][g] = make_double2(0.0, 0.0);
-        if (kk <= h_top && m[it] >= kk)
-          pf[it][g] = ld_node<PAIRED>(t, ((cap >> (kk - 1)) + (x[it] >> (kk - 1))) ^ 1);
-      }
+    for (int g = 0; g < G; ++g) {
+      const int kk = k0 + g;
+      pf[g] = make_double2(0.0, 0.0);
+      if (kk <= h_top && m >= kk) pf[g] = ld_node<PAIRED>(t, ((cap >> (kk - 1)) + (x >> (kk - 1))) ^ 1);
     }
 #pragma unroll
     for (int g = 0; g < G; ++g) {
       const int kk = k0 + g;
-      if (kk > h_top) break;  // uniform across the CTA
+      if (kk > h_top) break;  // warp-uniform
+      const int jj = nxt & 31;
+      const int xj = __shfl_sync(FULL, x, jj);
+      const double rs = __shfl_sync(FULL, cv.x, jj);
+      const double rm = __shfl_sync(FULL, cv.y, jj);
+      const int nj = __shfl_sync(FULL, nxt, jj);
+      if (m >= kk) {
+        const int px = x >> kk;
+        double2 l, r;
+        if (nxt < n && (xj >> kk) == px) {     // this lane leads the left child, lane nxt the right
+          l = cv;
+          r = make_double2(rs, rm);
+          nxt = nj;
+        } else if ((x >> (kk - 1)) & 1) {      // mine is the right child
+          l = pf[g];
+          r = cv;
+        } else {
+          l = cv;
+          r = pf[g];
+        }
+        cv = make_double2(__dadd_rn(l.x, r.x), py_min(l.y, r.y));
+        st_node<PAIRED>(t, (cap >> kk) + px, cv);
+      }
+    }
+  }
+}
+
+// A bucket with more than 32 items (skewed batches): resolve the last writer per leaf with
+// tickets in aux[cap + leaf] (only this warp touches this bucket's leaves), then climb the
+// winners 32 at a time — each pass leaves the subtree consistent, so any pass order is right.
+// `fetch(i)` returns the i-th candidate key of this bucket or kPad; `count` candidates.
+template <bool PAIRED, typename Fetch>
+__device__ void warp_climb_large(const Tree &t, const SetSrc &s, Fetch fetch, long long count, int h_top) {
+  const int lane = threadIdx.x & 31;
+  for (long long i0 = 0; i0 < count; i0 += 32) {
+    const u64 key = (i0 + lane < count) ? fetch(i0 + lane) : kPad;
+    if (key != kPad) atomicMax(&t.aux[t.cap + (long long)(key >> 32)], (int)(key & 0xffffffffull) + 1);
+  }
+  __threadfence();
+  __syncwarp();
+  for (long long i0 = 0; i0 < count; i0 += 32) {
+    u64 key = (i0 + lane < count) ? fetch(i0 + lane) : kPad;
+    if (key != kPad) {
+      int *tk = &t.aux[t.cap + (long long)(key >> 32)];
+      if (__ldcg(tk) == (int)(key & 0xffffffffull) + 1) {
+        __stcg(tk, 0);  // ticket consumed
+      } else {
+        key = kPad;     // a later item overwrites this leaf
+      }
+    }
+    if (__ballot_sync(0xffffffffu, key != kPad)) {
+      warp_climb<PAIRED>(t, s, key, h_top);
+      __threadfence();  // this pass's nodes are the next pass's untouched siblings
+      __syncwarp();
+    }
+  }
+}
+
+__device__ __forceinline__ u64 item_key(const SetSrc &s, long long i, long long &leaf_out) {
+  const long long leaf = src_idx(s, i);
+  leaf_out = leaf;
+  if (leaf < 0 || leaf >= s.limit) return kPad;
+  return ((u64)leaf << 32) | (u64)i;
+}
+
+// dense rebuild of the top of the tree by ONE CTA: `width` (power of two) nodes at height h0 are
+// loaded into a shared-memory heap and reduced; recomputing an untouched node from unchanged
+// children gives the value it already has (every node is op(children) by construction).
+template <bool PAIRED>
+__device__ void cta_dense_top(const Tree &t, int h0, int width, double2 *heap) {
+  for (int i = threadIdx.x; i < width; i += blockDim.x)
+    heap[width + i] = ld_node<PAIRED>(t, (int)(t.cap >> h0) + i);
+  __syncthreads();
+  int h = h0;
+  for (int w = width >> 1; w >= 1; w >>= 1) {
+    ++h;
+    for (int q = threadIdx.x; q < w; q += blockDim.x) {
+      const double2 l = heap[2 * (w + q)], r = heap[2 * (w + q) + 1];
+      const double2 v = make_double2(__dadd_rn(l.x, r.x), py_min(l.y, r.y));
+      heap[w + q] = v;
+      st_node<PAIRED>(t, (int)(t.cap >> h) + q, v);
+    }
+    __syncthreads();
+  }
+}
+
+// ---- schedule M (B <= 8192): ONE launch ---------------------------------------------------------
+// Warp w owns bucket subtree w of nb = 2^k buckets: it scans the whole batch (a few KB, L2
+// resident), keeps the items whose leaf falls in its bucket, climbs to the bucket root; the last
+// CTA to finish rebuilds the nb-leaf top densely.
+constexpr int kMidWarps = 4;
+template <bool PAIRED>
+__global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc s, int B, int nb, int shift) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ u64 s_list[kMidWarps][32];
+  __shared__ int s_last;
+  const unsigned FULL = 0xffffffffu;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (b < nb) {
+    int cnt = 0;
+    double pmax = 0.0;
+    constexpr int U = 8;  // independent loads in flight per lane
+    for (int i0 = 0; i0 < B; i0 += 32 * U) {
+      u64 keys[U];
+      long long leaves[U];
 #pragma unroll
-      for (int it = 0; it < ITEMS; ++it) {
-        if (m[it] >= kk) {
-          const int i = threadIdx.x + it * THREADS;
-          const int j = sm.nxt[i];
-          const int px = x[it] >> kk;
-          double2 l, r;
-          if (j < n && (key_x(sm.key, j) >> kk) == px) {  // i leads the left child, j the right
-            l = cv[it];
-            r = sm.val[j];
-            sm.nxt[i] = sm.nxt[j];
-          } else if ((x[it] >> (kk - 1)) & 1) {           // mine is the right child
-            l = pf[it][g];
-            r = cv[it];
-          } else {
-            l = cv[it];
-            r = pf[it][g];
+      for (int u = 0; u < U; ++u) {
+        const int i = i0 + u * 32 + lane;
+        keys[u] = kPad;
+        leaves[u] = 0;
+        if (i < B) {
+          keys[u] = item_key(s, i, leaves[u]);
+          if (b == 0) {
+            if (keys[u] == kPad && s.err) *s.err = 1;
+            if (s.kind == kSrcPrio) pmax = fmax(pmax, clamp_prio(s.prio[i]));
           }
-          cv[it] = make_double2(__dadd_rn(l.x, r.x), py_min(l.y, r.y));
-          st_node<PAIRED>(t, (cap >> kk) + px, cv[it]);
-          sm.val[i] = cv[it];
         }
       }
-      __syncthreads();
-    }
-  }
-}
-
-constexpr int kSetThreads = 512;
-
-// ---- schedule S: the whole batch in one CTA ------------------------------------------------------
-template <int ITEMS, bool PAIRED>
-__global__ void __launch_bounds__(kSetThreads) set_small_kernel(Tree t, SetSrc s, int B, int height) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const ClimbSmem sm = carve(smem_raw, ITEMS * kSetThreads);
-  __shared__ int s_valid;
-  if (threadIdx.x == 0) s_valid = 0;
-  int npow2 = 1;
-  while (npow2 < B) npow2 <<= 1;
-  if (npow2 < 2) npow2 = 2;
-  __syncthreads();
-  int valid = 0;
-  double pmax = 0.0;
-  for (int i = threadIdx.x; i < npow2; i += kSetThreads) {
-    u64 key = kPad;
-    if (i < B) {
-      const long long leaf = src_idx(s, i);
-      if (leaf < 0 || leaf >= s.limit) {
-        if (s.err) *s.err = 1;
-      } else {
-        key = ((u64)leaf << 32) | (u64)i;
-        ++valid;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const bool mine = keys[u] != kPad && (int)(leaves[u] >> shift) == b;
+        const unsigned mask = __ballot_sync(FULL, mine);
+        const int slot = cnt + __popc(mask & ((1u << lane) - 1u));
+        if (mine && slot < 32) s_list[warp][slot] = keys[u];
+        cnt += __popc(mask);
       }
-      if (s.kind == kSrcPrio) pmax = fmax(pmax, clamp_prio(s.prio[i]));
     }
-    sm.key[i] = key;
+    if (b == 0 && s.kind == kSrcPrio) fold_max_priority(s, pmax);
+    __syncwarp();
+    if (cnt <= 32) {
+      if (cnt > 0) warp_climb<PAIRED>(t, s, lane < cnt ? s_list[warp][lane] : kPad, shift);
+    } else {
+      auto fetch = [&](long long i) -> u64 {
+        long long leaf;
+        const u64 key = item_key(s, i, leaf);
+        return (key != kPad && (int)(leaf >> shift) == b) ? key : kPad;
+      };
+      warp_climb_large<PAIRED>(t, s, fetch, B, shift);
+    }
   }
-  if (s.kind == kSrcPrio) fold_max_priority(s, pmax);
-  if (valid) atomicAdd(&s_valid, valid);
+  if (nb == 1) return;
+  __threadfence();  // bucket roots visible before this CTA counts itself done
   __syncthreads();
-  // PER indices of one agent arrive ascending (stratified sampling): skip the sort when sorted
-  int ok = 1;
-  for (int i = threadIdx.x + 1; i < npow2; i += kSetThreads) ok &= (sm.key[i - 1] <= sm.key[i]);
-  if (!__syncthreads_and(ok)) bitonic_sort<kSetThreads>(sm.key, npow2);
-  climb_sorted<ITEMS, kSetThreads, PAIRED>(t, s, sm, s_valid, height);
+  if (threadIdx.x == 0) {
+    const int done = atomicAdd(&t.aux[0], 1);
+    s_last = (done == (int)gridDim.x - 1);
+    if (s_last) t.aux[0] = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  cta_dense_top<PAIRED>(t, shift, nb, reinterpret_cast<double2 *>(smem_raw));
 }
 
-// ---- schedule L ----------------------------------------------------------------------------------
+// ---- schedule L (large B): histogram+scan -> scatter -> one warp per bucket -> dense top --------
 // aux scratch layout (ints): [0] done counter, [16, 16+NB) counts, then offsets[NB+1], cursors[NB],
 // then (8-byte aligned) items u64[B].
 struct Buckets {
@@ -293,9 +336,10 @@ struct Buckets {
   int shift;       // leaves per bucket = 1 << shift
   int *counts, *offsets, *cursors;
   u64 *items;
+  double *vals;    // kSrcPrio only: leaf value per batch position (else NULL)
 };
 
-__host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift) {
+__host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift, long long B, bool want_vals) {
   Buckets b;
   b.nb = nb;
   b.shift = shift;
@@ -305,99 +349,119 @@ __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift
   long long off = 16 + 3ll * nb + 1;
   off = (off + 1) & ~1ll;
   b.items = reinterpret_cast<u64 *>(t.aux + off);
+  b.vals = want_vals ? reinterpret_cast<double *>(t.aux + off + 2 * B) : nullptr;
   return b;
 }
 
-// tickets: aux[cap + leaf] = max(pos + 1) = the last writer (segment_tree.py:81-95 applied in
-// order); optional bucket histogram; the last CTA to finish scans the histogram.
-template <bool HIST>
-__global__ void __launch_bounds__(256) set_ticket_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
+// per-bucket item counts (duplicates included); the last CTA to finish turns them into offsets
+__global__ void __launch_bounds__(256) set_hist_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   double p = 0.0;
   if (i < B) {
-    const long long leaf = src_idx(s, i);
-    if (leaf < 0 || leaf >= s.limit) {
+    long long leaf;
+    if (item_key(s, i, leaf) == kPad) {
       if (s.err) *s.err = 1;
     } else {
-      atomicMax(&t.aux[t.cap + leaf], (int)(i + 1));
-      if (HIST) atomicAdd(&bk.counts[leaf >> bk.shift], 1);
+      atomicAdd(&bk.counts[leaf >> bk.shift], 1);
     }
     if (s.kind == kSrcPrio) p = clamp_prio(s.prio[i]);
   }
   if (s.kind == kSrcPrio) fold_max_priority(s, p);
-  if (!HIST) return;
-  __shared__ int s_last;
-  __shared__ int s_part[256];
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(&t.aux[0], 1) == (int)gridDim.x - 1);
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  // exclusive scan of counts[nb] (an upper bound: duplicates are counted) -> offsets, cursors
-  const int per = (bk.nb + 255) / 256;
+}
+
+// exclusive scan of counts[nb] -> offsets[nb+1], cursors[nb]; one CTA of 32 warps, warp w owns a
+// contiguous segment, coalesced 32-wide loads, shuffle scans.
+__global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
+  __shared__ int s_warp[32];
+  const unsigned FULL = 0xffffffffu;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int seg = (bk.nb + 31) / 32;  // elements per warp
+  const int base = warp * seg;
   int sum = 0;
-  for (int k = 0; k < per; ++k) {
-    const int b = threadIdx.x * per + k;
-    if (b < bk.nb) sum += __ldcg(&bk.counts[b]);
-  }
-  s_part[threadIdx.x] = sum;
+  for (int i = lane; i < seg; i += 32)
+    if (base + i < bk.nb) sum += __ldcg(&bk.counts[base + i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(FULL, sum, o);
+  if (lane == 0) s_warp[warp] = sum;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int run = 0;
-    for (int k = 0; k < 256; ++k) {
-      const int v = s_part[k];
-      s_part[k] = run;
-      run += v;
+  if (warp == 0) {
+    const int v = s_warp[lane];
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(FULL, inc, o);
+      if (lane >= o) inc += n;
     }
-    bk.offsets[bk.nb] = run;
-    t.aux[0] = 0;
+    s_warp[lane] = inc - v;
+    if (lane == 31) bk.offsets[bk.nb] = inc;
   }
   __syncthreads();
-  int run = s_part[threadIdx.x];
-  for (int k = 0; k < per; ++k) {
-    const int b = threadIdx.x * per + k;
-    if (b < bk.nb) {
-      bk.offsets[b] = run;
-      bk.cursors[b] = run;
-      run += __ldcg(&bk.counts[b]);
+  int run = s_warp[warp];
+  for (int i0 = 0; i0 < seg; i0 += 32) {
+    const int i = base + i0 + lane;
+    const int v = (i0 + lane < seg && i < bk.nb) ? __ldcg(&bk.counts[i]) : 0;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(FULL, inc, o);
+      if (lane >= o) inc += n;
     }
+    if (i0 + lane < seg && i < bk.nb) {
+      bk.offsets[i] = run + inc - v;
+      bk.cursors[i] = run + inc - v;
+    }
+    run += __shfl_sync(FULL, inc, 31);
   }
 }
 
-// winners move into their bucket's slice of items[]; tickets are consumed (aux back to zero)
+// every valid item goes into its bucket's slice; the leaf value (pow) is computed HERE, with all
+// lanes busy, and parked by batch position for the bucket warp that will need it
 __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B) return;
-  const long long leaf = src_idx(s, i);
-  if (leaf < 0 || leaf >= s.limit) return;
-  if (t.aux[t.cap + leaf] != (int)(i + 1)) return;  // a later item overwrites this leaf
-  t.aux[t.cap + leaf] = 0;
+  long long leaf;
+  const u64 key = item_key(s, i, leaf);
+  if (key == kPad) return;
   const int slot = atomicAdd(&bk.cursors[leaf >> bk.shift], 1);
-  bk.items[slot] = ((u64)leaf << 32) | (u64)i;
+  bk.items[slot] = key;
+  if (bk.vals) bk.vals[i] = pow_call(clamp_prio(s.prio[i]), s.alpha);
 }
 
-// one CTA per bucket subtree: sort its winners, climb to the bucket root (height = shift)
-constexpr int kBucketThreads = 256;
-constexpr int kBucketItems = 2;  // per thread -> chunks of 512 items
+constexpr int kBucketWarps = 8;
 template <bool PAIRED>
-__global__ void __launch_bounds__(kBucketThreads) set_bucket_kernel(Tree t, SetSrc s, Buckets bk) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const ClimbSmem sm = carve(smem_raw, kBucketThreads * kBucketItems);
-  const int b = blockIdx.x;
+__global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * kBucketWarps + (threadIdx.x >> 5);
+  if (b >= bk.nb) return;
   const int begin = bk.offsets[b];
-  const int end = bk.cursors[b];
-  constexpr int kChunk = kBucketThreads * kBucketItems;
-  for (int c0 = begin; c0 < end; c0 += kChunk) {  // oversize buckets: several passes, any order
-    const int n = min(kChunk, end - c0);
-    int npow2 = 2;
-    while (npow2 < n) npow2 <<= 1;
-    for (int i = threadIdx.x; i < npow2; i += kBucketThreads) sm.key[i] = (i < n) ? bk.items[c0 + i] : kPad;
-    __syncthreads();
-    bitonic_sort<kBucketThreads>(sm.key, npow2);
-    climb_sorted<kBucketItems, kBucketThreads, PAIRED>(t, s, sm, n, bk.shift);
+  const int n = bk.cursors[b] - begin;
+  if (n == 0) return;
+  if (lane == 0) bk.counts[b] = 0;  // scratch back to zero for the next call
+  const u64 *items = bk.items + begin;
+  s.pre = bk.vals;
+  if (n <= 32) {
+    warp_climb<PAIRED>(t, s, lane < n ? __ldcg(&items[lane]) : kPad, bk.shift);
+  } else {
+    auto fetch = [&](long long i) -> u64 { return __ldcg(&items[i]); };
+    warp_climb_large<PAIRED>(t, s, fetch, n, bk.shift);
   }
-  if (threadIdx.x == 0) bk.counts[b] = 0;
+}
+
+// ---- schedule D helpers ----------------------------------------------------------------------------
+// tickets: aux[cap + leaf] = max(pos + 1) = the last writer of the leaf
+__global__ void __launch_bounds__(256) set_ticket_kernel(Tree t, SetSrc s, long long B) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  double p = 0.0;
+  if (i < B) {
+    long long leaf;
+    if (item_key(s, i, leaf) == kPad) {
+      if (s.err) *s.err = 1;
+    } else {
+      atomicMax(&t.aux[t.cap + leaf], (int)(i + 1));
+    }
+    if (s.kind == kSrcPrio) p = clamp_prio(s.prio[i]);
+  }
+  if (s.kind == kSrcPrio) fold_max_priority(s, p);
 }
 
 // ---- schedule D: winners write leaves, then a dense coalesced bottom-up rebuild -----------------
@@ -470,12 +534,15 @@ inline xp_status_t set_attr_once(const void *fn, size_t bytes, bool &done) {
   return XP_OK;
 }
 
-inline xp_status_t launch_dense(const Tree &t, int h0, long long width, cudaStream_t st, int &launches) {
+
+inline xp_status_t launch_dense(const Tree &t, int h0, long long width, int max_logc, cudaStream_t st,
+                                int &launches) {
   static bool attr = false;
   xp_status_t rc = set_attr_once((const void *)set_dense_kernel, (size_t)4 * (1 << kDenseLogC) * 8, attr);
   if (rc != XP_OK) return rc;
   while (width > 1) {
-    const int logC = (int)(ilog2(width) < kDenseLogC ? ilog2(width) : kDenseLogC);
+    const int lw = ilog2(width);
+    const int logC = lw < max_logc ? lw : max_logc;
     const long long grid = width >> logC;
     set_dense_kernel<<<(unsigned)grid, kDenseThreads, (size_t)4 * (1 << logC) * 8, st>>>(t, h0, logC);
     ++launches;
@@ -490,48 +557,47 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   XP_REQUIRE(B < (1ll << 31) - 1, XP_ERR_INVALID, "tree set: batch too large");
   XP_REQUIRE(t.cap <= (1ll << 30), XP_ERR_INVALID, "tree set: capacity above 2^30");
   const int L = ilog2(t.cap);
-  int launches = 0;
   const bool paired = is_paired(t);
-  if (B <= kMaxItems) {  // schedule S
-    const int items = B <= kSetThreads ? 1 : (B <= 2 * kSetThreads ? 2 : 4);
-    const size_t smem = climb_smem_bytes(items * kSetThreads);
-    static bool attr[2] = {false, false};
-    if (items == 4) {
-      const void *fn = paired ? (const void *)set_small_kernel<4, true> : (const void *)set_small_kernel<4, false>;
-      xp_status_t rc = set_attr_once(fn, smem, attr[paired]);
-      if (rc != XP_OK) return rc;
-    }
-#define XP_SMALL(I, P) set_small_kernel<I, P><<<1, kSetThreads, smem, st>>>(t, s, (int)B, L)
-    if (paired) {
-      if (items == 1) XP_SMALL(1, true); else if (items == 2) XP_SMALL(2, true); else XP_SMALL(4, true);
-    } else {
-      if (items == 1) XP_SMALL(1, false); else if (items == 2) XP_SMALL(2, false); else XP_SMALL(4, false);
-    }
-#undef XP_SMALL
-    return xp::check_launch("tree set (S)", 1);
+  int launches = 0;
+  if (B <= 8192) {  // schedule M: one launch
+    long long nb = 1;
+    while (nb * 8 < B && nb < 1024 && nb * 2 <= t.cap) nb <<= 1;
+    const int shift = L - ilog2(nb);
+    const int warps = nb < kMidWarps ? (int)nb : kMidWarps;
+    const unsigned grid = (unsigned)(nb / warps);
+    const size_t smem = nb > 1 ? (size_t)2 * nb * sizeof(double2) : 0;
+    if (paired)
+      set_mid_kernel<true><<<grid, warps * 32, smem, st>>>(t, s, (int)B, (int)nb, shift);
+    else
+      set_mid_kernel<false><<<grid, warps * 32, smem, st>>>(t, s, (int)B, (int)nb, shift);
+    return xp::check_launch("tree set (M)", 1);
   }
   const unsigned grid = (unsigned)((B + 255) / 256);
-  const long long nb = t.cap >> 3 < 2048 ? t.cap >> 3 : 2048;
-  const long long need = 16 + 3 * nb + 2 + 2 * B;
-  if (nb >= 2 && need <= t.cap) {  // schedule L
+  long long nb = 1;
+  while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;
+  const bool want_vals = s.kind == kSrcPrio;
+  const long long need = 16 + 3 * nb + 2 + (want_vals ? 4 : 2) * B;
+  if (need <= t.cap) {  // schedule L
     const int shift = L - ilog2(nb);
-    const Buckets bk = make_buckets(t, (int)nb, shift);
-    set_ticket_kernel<true><<<grid, 256, 0, st>>>(t, s, B, bk);
+    const Buckets bk = make_buckets(t, (int)nb, shift, B, want_vals);
+    set_hist_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
+    set_scan_kernel<<<1, 1024, 0, st>>>(bk);
     set_scatter_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
+    const unsigned bgrid = (unsigned)((nb + kBucketWarps - 1) / kBucketWarps);
     if (paired)
-      set_bucket_kernel<true><<<(unsigned)nb, kBucketThreads, climb_smem_bytes(kBucketThreads * kBucketItems), st>>>(t, s, bk);
+      set_wbucket_kernel<true><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk);
     else
-      set_bucket_kernel<false><<<(unsigned)nb, kBucketThreads, climb_smem_bytes(kBucketThreads * kBucketItems), st>>>(t, s, bk);
-    launches = 3;
-    xp_status_t rc = launch_dense(t, shift, nb, st, launches);
+      set_wbucket_kernel<false><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk);
+    launches = 4;
+    xp_status_t rc = launch_dense(t, shift, nb, 8, st, launches);
     if (rc != XP_OK) return rc;
     return xp::check_launch("tree set (L)", launches);
   }
   // schedule D
-  set_ticket_kernel<false><<<grid, 256, 0, st>>>(t, s, B, Buckets{});
+  set_ticket_kernel<<<grid, 256, 0, st>>>(t, s, B);
   set_leafwrite_kernel<<<grid, 256, 0, st>>>(t, s, B);
   launches = 2;
-  xp_status_t rc = launch_dense(t, 0, t.cap, st, launches);
+  xp_status_t rc = launch_dense(t, 0, t.cap, kDenseLogC, st, launches);
   if (rc != XP_OK) return rc;
   return xp::check_launch("tree set (D)", launches);
 }

@@ -152,11 +152,12 @@ def test_tree_non_pow2_capacity_is_assertion(xp, cuda_device):
         xp.tree_init(bad, 0)
 
 
-# schedules of tree_set.cuh: S (B <= 2048, 1/2/4 items per thread), L (bucketed), D (dense)
+# schedules of tree_set.cuh: M (B <= 8192, one launch), L (bucketed, large B), D (dense rebuild)
 @pytest.mark.parametrize("cap,B,interleaved", [(1, 3, True), (2, 5, False), (64, 40, True),
                                                (4096, 256, True), (4096, 5000, False), (1 << 16, 20000, True),
                                                (1 << 14, 700, False), (1 << 16, 1500, True), (1 << 16, 2048, True),
-                                               (1 << 18, 3000, True), (1 << 12, 1 << 12, True)])
+                                               (1 << 18, 3000, True), (1 << 12, 1 << 12, True), (1 << 14, 20000, True),
+                                               (1 << 18, 8192, False), (1 << 18, 30000, True), (1 << 20, 100000, True)])
 def test_tree_set_batch_equals_sequential_reference(xp, cuda_device, cap, B, interleaved):
     rng = np.random.default_rng(cap + B)
     t = DevTree(xp, cuda_device, cap, interleaved)
@@ -188,7 +189,7 @@ def test_tree_set_batch_equals_sequential_reference(xp, cuda_device, cap, B, int
 
 
 @pytest.mark.parametrize("pattern", ["sorted", "one_bucket", "one_leaf", "two_leaves_far"])
-@pytest.mark.parametrize("cap,B", [(1 << 10, 300), (1 << 16, 2000), (1 << 16, 9000)])
+@pytest.mark.parametrize("cap,B", [(1 << 10, 300), (1 << 16, 2000), (1 << 16, 9000), (1 << 18, 40000)])
 def test_tree_set_batch_adversarial_patterns(xp, cuda_device, pattern, cap, B):
     """sorted input (the PER fast path), every update in one bucket subtree (oversize bucket:
     several passes), every update on one leaf (one long duplicate run), two far leaves."""
