@@ -144,17 +144,21 @@ __device__ __forceinline__ float is_weight(const Tree &t, long long leaf, double
 }
 
 // _sample_proportional (+ _calculate_weights) for P agents x B strata, one thread per sample.
+// Thread order is stratum-major / agent-minor: the lanes of a warp draw in the SAME stratum for
+// different agents, so their descents share every node down to where the stratum splits
+// (identical addresses coalesce into one transaction) and then stay inside one small subtree.
 __global__ void __launch_bounds__(256) per_sample_kernel(Tree t, const float *u, long long B,
-                                                         long long total_samples, double size,
-                                                         double neg_beta, long long *idx_out,
-                                                         float *w_out) {
+                                                         long long P, long long total_samples,
+                                                         double size, double neg_beta,
+                                                         long long *idx_out, float *w_out) {
   __shared__ double s_max_w;
   const double total = __ldg(&t.sum[t.stride]);  // sum_tree.sum() == tree[1]
   if (w_out && threadIdx.x == 0) s_max_w = is_max_weight(t, total, size, neg_beta);
   if (w_out) __syncthreads();
-  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= total_samples) return;
-  const long long i = j % B;
+  const long long tt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tt >= total_samples) return;
+  const long long i = tt / P;                 // stratum
+  const long long j = (tt - i * P) * B + i;   // sample slot: agent-major like the reference loop
   const double seg = __ddiv_rn(total, (double)B);
   const double a = __dmul_rn(seg, (double)i);
   const double b = __dmul_rn(seg, (double)(i + 1));
@@ -292,7 +296,7 @@ xp_status_t xp_per_sample(const xp_tree *tree, const float *u_dev, int64_t B, in
   if (total == 0) return XP_OK;
   XP_REQUIRE(u_dev && idx_out_dev, XP_ERR_INVALID, "xp_per_sample: null pointer");
   per_sample_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      t, u_dev, B, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
+      t, u_dev, B, P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
   return xp::check_launch("xp_per_sample");
 }
 

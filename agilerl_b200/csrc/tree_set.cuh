@@ -19,6 +19,7 @@
 #pragma once
 #include "common.cuh"
 #include "pow.cuh"
+#include <stdlib.h>
 
 namespace xpset {
 
@@ -127,34 +128,39 @@ constexpr u64 kPad = ~0ull;
 //     four levels ahead); a right-child leader's left sibling is untouched by construction.
 // Every touched node is recomputed once from its final children with the reference's operand
 // order (left, right), hence bit-identical to the sequential loop.
-template <bool PAIRED>
+// WIDTH = 32: the warp climbs one bucket; WIDTH = 16: each half-warp climbs its own bucket (two
+// buckets of <= 16 items per warp — most of the per-level cost is per warp, not per item).
+template <bool PAIRED, int WIDTH>
 __device__ __forceinline__ void warp_climb(const Tree &t, const SetSrc &s, u64 key, int h_top) {
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
+  const int l = lane & (WIDTH - 1);         // lane inside the group
+  const int gbase = lane & ~(WIDTH - 1);    // first lane of the group
+  const unsigned gmask = WIDTH == 32 ? FULL : ((1u << WIDTH) - 1u);
   const int cap = (int)t.cap;
-  // bitonic sort of the 32 keys (ascending across lanes)
+  // bitonic sort of the group's keys (ascending across its lanes)
 #pragma unroll
-  for (int k = 2; k <= 32; k <<= 1) {
+  for (int k = 2; k <= WIDTH; k <<= 1) {
 #pragma unroll
     for (int j = k >> 1; j > 0; j >>= 1) {
       const u64 o = __shfl_xor_sync(FULL, key, j);
-      const bool up = ((lane & k) == 0);
-      const bool lower = ((lane & j) == 0);
+      const bool up = ((l & k) == 0);
+      const bool lower = ((l & j) == 0);
       const u64 lo = key < o ? key : o, hi = key < o ? o : key;
       key = (lower == up) ? lo : hi;
     }
   }
   const bool valid = key != kPad;
-  const int n = __popc(__ballot_sync(FULL, valid));
+  const int n = __popc((__ballot_sync(FULL, valid) >> gbase) & gmask);
   const int x = (int)(key >> 32);
   const unsigned pos = (unsigned)(key & 0xffffffffull);
-  const int xprev = __shfl_up_sync(FULL, x, 1);
-  const bool leader = valid && (lane == 0 || xprev != x);
-  const unsigned lmask = __ballot_sync(FULL, leader);
-  const unsigned higher = (lane == 31) ? 0u : (lmask & ~((2u << lane) - 1u));
+  const int xprev = __shfl_up_sync(FULL, x, 1, WIDTH);
+  const bool leader = valid && (l == 0 || xprev != x);
+  const unsigned lmask = (__ballot_sync(FULL, leader) >> gbase) & gmask;
+  const unsigned higher = (l == 31) ? 0u : (lmask & ~((2u << l) - 1u));
   int nxt = higher ? (__ffs(higher) - 1) : n;  // next leader (= end of this run of equal leaves)
-  const unsigned pos_last = __shfl_sync(FULL, pos, (nxt - 1) & 31);
-  const int m = leader ? (lane == 0 ? 64 : 31 - __clz(xprev ^ x)) : -1;
+  const unsigned pos_last = __shfl_sync(FULL, pos, (nxt - 1) & (WIDTH - 1), WIDTH);
+  const int m = leader ? (l == 0 ? 64 : 31 - __clz(xprev ^ x)) : -1;
   double2 cv = make_double2(0.0, 0.0);
   if (leader) {
     const double v = src_value(s, (long long)pos_last);
@@ -174,26 +180,31 @@ __device__ __forceinline__ void warp_climb(const Tree &t, const SetSrc &s, u64 k
     for (int g = 0; g < G; ++g) {
       const int kk = k0 + g;
       if (kk > h_top) break;  // warp-uniform
-      const int jj = nxt & 31;
-      const int xj = __shfl_sync(FULL, x, jj);
-      const double rs = __shfl_sync(FULL, cv.x, jj);
-      const double rm = __shfl_sync(FULL, cv.y, jj);
-      const int nj = __shfl_sync(FULL, nxt, jj);
+      const int jj = nxt & (WIDTH - 1);
+      const int px = x >> kk;
+      const int xj = __shfl_sync(FULL, x, jj, WIDTH);
+      const bool merge = (m >= kk) && nxt < n && (xj >> kk) == px;
+      double rs = 0.0, rm = 0.0;
+      int nj = 0;
+      if (__ballot_sync(FULL, merge)) {  // warp-uniform: nobody merges on most of the lower levels
+        rs = __shfl_sync(FULL, cv.x, jj, WIDTH);
+        rm = __shfl_sync(FULL, cv.y, jj, WIDTH);
+        nj = __shfl_sync(FULL, nxt, jj, WIDTH);
+      }
       if (m >= kk) {
-        const int px = x >> kk;
-        double2 l, r;
-        if (nxt < n && (xj >> kk) == px) {     // this lane leads the left child, lane nxt the right
-          l = cv;
-          r = make_double2(rs, rm);
+        double2 lft, rgt;
+        if (merge) {                           // this lane leads the left child, lane nxt the right
+          lft = cv;
+          rgt = make_double2(rs, rm);
           nxt = nj;
         } else if ((x >> (kk - 1)) & 1) {      // mine is the right child
-          l = pf[g];
-          r = cv;
+          lft = pf[g];
+          rgt = cv;
         } else {
-          l = cv;
-          r = pf[g];
+          lft = cv;
+          rgt = pf[g];
         }
-        cv = make_double2(__dadd_rn(l.x, r.x), py_min(l.y, r.y));
+        cv = make_double2(__dadd_rn(lft.x, rgt.x), py_min(lft.y, rgt.y));
         st_node<PAIRED>(t, (cap >> kk) + px, cv);
       }
     }
@@ -224,7 +235,7 @@ __device__ void warp_climb_large(const Tree &t, const SetSrc &s, Fetch fetch, lo
       }
     }
     if (__ballot_sync(0xffffffffu, key != kPad)) {
-      warp_climb<PAIRED>(t, s, key, h_top);
+      warp_climb<PAIRED, 32>(t, s, key, h_top);
       __threadfence();  // this pass's nodes are the next pass's untouched siblings
       __syncwarp();
     }
@@ -304,7 +315,7 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
     if (b == 0 && s.kind == kSrcPrio) fold_max_priority(s, pmax);
     __syncwarp();
     if (cnt <= 32) {
-      if (cnt > 0) warp_climb<PAIRED>(t, s, lane < cnt ? s_list[warp][lane] : kPad, shift);
+      if (cnt > 0) warp_climb<PAIRED, 32>(t, s, lane < cnt ? s_list[warp][lane] : kPad, shift);
     } else {
       auto fetch = [&](long long i) -> u64 {
         long long leaf;
@@ -369,48 +380,62 @@ __global__ void __launch_bounds__(256) set_hist_kernel(Tree t, SetSrc s, long lo
   if (s.kind == kSrcPrio) fold_max_priority(s, p);
 }
 
-// exclusive scan of counts[nb] -> offsets[nb+1], cursors[nb]; one CTA of 32 warps, warp w owns a
-// contiguous segment, coalesced 32-wide loads, shuffle scans.
+// exclusive scan of counts[nb] -> offsets[nb+1], cursors[nb] by one CTA of 32 warps:
+// coalesced 32-wide rows scanned with shuffles (row-local exclusive values parked in shared
+// memory), a block scan of the <= 1024 row totals, then one coalesced write pass.
+__device__ __forceinline__ int warp_inclusive(int v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += n;
+  }
+  return v;
+}
 __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
+  extern __shared__ int s_excl[];   // [nb] exclusive prefix inside each 32-row
+  __shared__ int s_row[1024];       // row totals -> exclusive row offsets
   __shared__ int s_warp[32];
-  const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int seg = (bk.nb + 31) / 32;  // elements per warp
-  const int base = warp * seg;
-  int sum = 0;
-  for (int i = lane; i < seg; i += 32)
-    if (base + i < bk.nb) sum += __ldcg(&bk.counts[base + i]);
+  const int nb = bk.nb;
+  const int rows = (nb + 31) >> 5;
+  constexpr int kRowsPerWarp = 32;  // nb <= 32768
+  int vals[kRowsPerWarp];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(FULL, sum, o);
-  if (lane == 0) s_warp[warp] = sum;
-  __syncthreads();
-  if (warp == 0) {
-    const int v = s_warp[lane];
-    int inc = v;
+  for (int k = 0; k < kRowsPerWarp; ++k) {  // every load of this warp in flight at once
+    const int i = (warp + 32 * k) * 32 + lane;
+    vals[k] = (warp + 32 * k < rows && i < nb) ? __ldcg(&bk.counts[i]) : 0;
+  }
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int n = __shfl_up_sync(FULL, inc, o);
-      if (lane >= o) inc += n;
+  for (int k = 0; k < kRowsPerWarp; ++k) {
+    const int r = warp + 32 * k;
+    if (r < rows) {
+      const int i = r * 32 + lane;
+      const int inc = warp_inclusive(vals[k], lane);
+      if (i < nb) s_excl[i] = inc - vals[k];
+      if (lane == 31) s_row[r] = inc;
     }
-    s_warp[lane] = inc - v;
-    if (lane == 31) bk.offsets[bk.nb] = inc;
   }
   __syncthreads();
-  int run = s_warp[warp];
-  for (int i0 = 0; i0 < seg; i0 += 32) {
-    const int i = base + i0 + lane;
-    const int v = (i0 + lane < seg && i < bk.nb) ? __ldcg(&bk.counts[i]) : 0;
-    int inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int n = __shfl_up_sync(FULL, inc, o);
-      if (lane >= o) inc += n;
+  const int rv = threadIdx.x < rows ? s_row[threadIdx.x] : 0;
+  const int rinc = warp_inclusive(rv, lane);
+  if (lane == 31) s_warp[warp] = rinc;
+  __syncthreads();
+  if (warp == 0) {
+    const int w = s_warp[lane];
+    const int winc = warp_inclusive(w, lane);
+    s_warp[lane] = winc - w;
+    if (lane == 31) bk.offsets[nb] = winc;
+  }
+  __syncthreads();
+  if (threadIdx.x < rows) s_row[threadIdx.x] = s_warp[warp] + rinc - rv;
+  __syncthreads();
+  for (int r = warp; r < rows; r += 32) {
+    const int i = r * 32 + lane;
+    if (i < nb) {
+      const int off = s_row[r] + s_excl[i];
+      bk.offsets[i] = off;
+      bk.cursors[i] = off;
     }
-    if (i0 + lane < seg && i < bk.nb) {
-      bk.offsets[i] = run + inc - v;
-      bk.cursors[i] = run + inc - v;
-    }
-    run += __shfl_sync(FULL, inc, 31);
   }
 }
 
@@ -427,23 +452,40 @@ __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long
   if (bk.vals) bk.vals[i] = pow_call(clamp_prio(s.prio[i]), s.alpha);
 }
 
+// one warp per PAIR of buckets: both <= 16 items -> the two half-warps climb them side by side;
+// otherwise one after the other with the whole warp.
 constexpr int kBucketWarps = 8;
 template <bool PAIRED>
-__global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk) {
+__global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk, int use_half) {
   const int lane = threadIdx.x & 31;
-  const int b = blockIdx.x * kBucketWarps + (threadIdx.x >> 5);
-  if (b >= bk.nb) return;
-  const int begin = bk.offsets[b];
-  const int n = bk.cursors[b] - begin;
-  if (n == 0) return;
-  if (lane == 0) bk.counts[b] = 0;  // scratch back to zero for the next call
-  const u64 *items = bk.items + begin;
+  const int b0 = 2 * (blockIdx.x * kBucketWarps + (threadIdx.x >> 5));
+  if (b0 >= bk.nb) return;
   s.pre = bk.vals;
-  if (n <= 32) {
-    warp_climb<PAIRED>(t, s, lane < n ? __ldcg(&items[lane]) : kPad, bk.shift);
-  } else {
-    auto fetch = [&](long long i) -> u64 { return __ldcg(&items[i]); };
-    warp_climb_large<PAIRED>(t, s, fetch, n, bk.shift);
+  const int has1 = (b0 + 1 < bk.nb);
+  const int beg0 = bk.offsets[b0], n0 = bk.cursors[b0] - beg0;
+  const int beg1 = has1 ? bk.offsets[b0 + 1] : 0, n1 = has1 ? bk.cursors[b0 + 1] - beg1 : 0;
+  if (n0 == 0 && n1 == 0) return;
+  if (lane == 0) {  // scratch back to zero for the next call
+    bk.counts[b0] = 0;
+    if (has1) bk.counts[b0 + 1] = 0;
+  }
+  if (use_half && n0 <= 16 && n1 <= 16) {
+    const int half = lane >> 4, l = lane & 15;
+    const int beg = half ? beg1 : beg0, n = half ? n1 : n0;
+    warp_climb<PAIRED, 16>(t, s, l < n ? __ldcg(&bk.items[beg + l]) : kPad, bk.shift);
+    return;
+  }
+#pragma unroll 1
+  for (int h = 0; h < 2; ++h) {
+    const int beg = h ? beg1 : beg0, n = h ? n1 : n0;
+    if (n == 0) continue;
+    const u64 *items = bk.items + beg;
+    if (n <= 32) {
+      warp_climb<PAIRED, 32>(t, s, lane < n ? __ldcg(&items[lane]) : kPad, bk.shift);
+    } else {
+      auto fetch = [&](long long i) -> u64 { return __ldcg(&items[i]); };
+      warp_climb_large<PAIRED>(t, s, fetch, n, bk.shift);
+    }
   }
 }
 
@@ -483,37 +525,55 @@ __global__ void __launch_bounds__(256) set_leafwrite_kernel(Tree t, SetSrc s, lo
 // the value it already has (every node is op(children) by construction), so dense == sparse.
 constexpr int kDenseThreads = 512;
 constexpr int kDenseLogC = 12;
-__global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0, int logC) {
+__global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0, int logC, int finish) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int s_last;
   const int C = 1 << logC;
   double *S = reinterpret_cast<double *>(smem_raw);
   double *M = S + 2 * C;
   const bool hs = t.sum != nullptr, hm = t.mn != nullptr;
-  const long long chunk = blockIdx.x;
-  const long long base = (t.cap >> h0) + chunk * C;
-  for (int i = threadIdx.x; i < C; i += kDenseThreads) {
-    if (hs) S[C + i] = __ldcg(&t.sum[(base + i) * t.stride]);
-    if (hm) M[C + i] = __ldcg(&t.mn[(base + i) * t.stride]);
-  }
-  __syncthreads();
-  for (int r = 1; r <= logC; ++r) {
-    const int w = C >> r;
-    const long long lvl = (t.cap >> (h0 + r)) + chunk * w;
-    for (int q = threadIdx.x; q < w; q += kDenseThreads) {
-      const int n = w + q;
-      if (hs) {
-        const double v = __dadd_rn(S[2 * n], S[2 * n + 1]);
-        S[n] = v;
-        __stcg(&t.sum[(lvl + q) * t.stride], v);
-      }
-      if (hm) {
-        const double v = py_min(M[2 * n], M[2 * n + 1]);
-        M[n] = v;
-        __stcg(&t.mn[(lvl + q) * t.stride], v);
-      }
+  // reduce `n` (power of two <= C) nodes at height h starting at node id `base`; level r above
+  // them starts at node id lvl0(r)
+  auto reduce = [&](long long base, int n, int h, long long chunk) {
+    for (int i = threadIdx.x; i < n; i += kDenseThreads) {
+      if (hs) S[n + i] = __ldcg(&t.sum[(base + i) * t.stride]);
+      if (hm) M[n + i] = __ldcg(&t.mn[(base + i) * t.stride]);
     }
     __syncthreads();
+    int r = 0;
+    for (int w = n >> 1; w >= 1; w >>= 1) {
+      ++r;
+      const long long lvl = (t.cap >> (h + r)) + chunk * w;
+      for (int q = threadIdx.x; q < w; q += kDenseThreads) {
+        const int m = w + q;
+        if (hs) {
+          const double v = __dadd_rn(S[2 * m], S[2 * m + 1]);
+          S[m] = v;
+          __stcg(&t.sum[(lvl + q) * t.stride], v);
+        }
+        if (hm) {
+          const double v = py_min(M[2 * m], M[2 * m + 1]);
+          M[m] = v;
+          __stcg(&t.mn[(lvl + q) * t.stride], v);
+        }
+      }
+      __syncthreads();
+    }
+  };
+  const long long chunk = blockIdx.x;
+  reduce((t.cap >> h0) + chunk * C, C, h0, chunk);
+  if (!finish || gridDim.x == 1) return;
+  // the last CTA to finish reduces the gridDim.x chunk roots (a power of two <= C) to the root
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    s_last = (atomicAdd(&t.aux[1], 1) == (int)gridDim.x - 1);
+    if (s_last) t.aux[1] = 0;
   }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  reduce(t.cap >> (h0 + logC), (int)gridDim.x, h0 + logC, 0);
 }
 
 // ---- host: pick a schedule -------------------------------------------------------------------------
@@ -544,8 +604,10 @@ inline xp_status_t launch_dense(const Tree &t, int h0, long long width, int max_
     const int lw = ilog2(width);
     const int logC = lw < max_logc ? lw : max_logc;
     const long long grid = width >> logC;
-    set_dense_kernel<<<(unsigned)grid, kDenseThreads, (size_t)4 * (1 << logC) * 8, st>>>(t, h0, logC);
+    const int finish = grid <= (1ll << logC) ? 1 : 0;  // the chunk roots fit one CTA's heap
+    set_dense_kernel<<<(unsigned)grid, kDenseThreads, (size_t)4 * (1 << logC) * 8, st>>>(t, h0, logC, finish);
     ++launches;
+    if (finish) break;
     h0 += logC;
     width >>= logC;
   }
@@ -574,20 +636,26 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   }
   const unsigned grid = (unsigned)((B + 255) / 256);
   long long nb = 1;
-  while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;
+  const int use_half = 1;
+  while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;  // ~16 items per bucket
   const bool want_vals = s.kind == kSrcPrio;
   const long long need = 16 + 3 * nb + 2 + (want_vals ? 4 : 2) * B;
   if (need <= t.cap) {  // schedule L
     const int shift = L - ilog2(nb);
     const Buckets bk = make_buckets(t, (int)nb, shift, B, want_vals);
     set_hist_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
-    set_scan_kernel<<<1, 1024, 0, st>>>(bk);
+    static bool scan_attr = false;
+    {
+      xp_status_t rc = set_attr_once((const void *)set_scan_kernel, (size_t)32768 * 4, scan_attr);
+      if (rc != XP_OK) return rc;
+    }
+    set_scan_kernel<<<1, 1024, (size_t)nb * 4, st>>>(bk);
     set_scatter_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
-    const unsigned bgrid = (unsigned)((nb + kBucketWarps - 1) / kBucketWarps);
+    const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps) / kBucketWarps);
     if (paired)
-      set_wbucket_kernel<true><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk);
+      set_wbucket_kernel<true><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk, use_half);
     else
-      set_wbucket_kernel<false><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk);
+      set_wbucket_kernel<false><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk, use_half);
     launches = 4;
     xp_status_t rc = launch_dense(t, shift, nb, 8, st, launches);
     if (rc != XP_OK) return rc;
