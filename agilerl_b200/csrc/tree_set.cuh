@@ -19,7 +19,6 @@
 #pragma once
 #include "common.cuh"
 #include "pow.cuh"
-#include <stdlib.h>
 
 namespace xpset {
 
