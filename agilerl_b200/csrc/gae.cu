@@ -3,15 +3,14 @@
 //
 // The recurrence carry_t = A_t + K_t * carry_{t+1} must be evaluated in the reference's order
 // with an fp64 carry (a re-associated parallel-in-time scan is not bit-compatible), so the chain
-// itself is one lane per (env, agent).  Everything that does NOT depend on the carry is hoisted
-// out of the chain and done by the whole CTA with full memory-level parallelism:
+// itself is one lane per (env, agent).  Two kernels:
 //
-//   phase 1 (256 threads): a [TC x 32 env] tile of rewards / values / dones is read with 128-bit
-//           coalesced loads and turned into A_t (fp64), the value v_t and a "terminal" flag in
-//           shared memory;
-//   phase 2 (warp 0, lane = env): the serial chain — per step two dependent fp64 ops fed from
-//           shared memory — writing adv/ret rows (128 B per warp store, coalesced);
-// several CTAs per SM overlap each other's phases.  T > TC is walked in chunks, newest first.
+//   gae_tma_kernel  (gae_tma.cuh; shapes whose strides are 16-byte multiples): one warp per CTA,
+//           all HBM traffic issued by the TMA unit into / out of a 4-stage shared-memory ring;
+//           the lanes run the chain from shared memory and write results in place;
+//   gae_tile_kernel (any shape): 256 threads stage a [TC x 32 env] tile (A_t in fp64, v_t and a
+//           terminal flag) with coalesced loads, warp 0 runs the chain and stores 128-byte rows.
+// T longer than a tile / box is walked in chunks, newest first.
 //
 // Arithmetic (all separately rounded, no FMA contraction):
 //   GAE  (:448-467)  nnt   = 1 - done[t+1]                      (fp64; last_done at t=T-1)
@@ -24,9 +23,6 @@
 //                    ret[t] = f32(G);  adv[t] = ret[t] -f32 v[t]
 #include "common.cuh"
 #include "gae_tma.cuh"
-#ifndef XP_EXP
-#define XP_EXP 0
-#endif
 
 namespace {
 

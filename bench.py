@@ -311,7 +311,6 @@ class C2Workload:
     def units_per_step(self):
         return self.P * self.B
 
-    kernels_per_step = 6  # per_sample, gather x2, update (ticket, mark, rebuild)
 
     def gather_bytes(self):
         """algorithmic bytes of ONE gather launch: (2R + 8) per sample."""

@@ -1,5 +1,5 @@
 // Standalone timing harness for xp_gae (no Python): rotating buffer sets, CUDA events.
-// nvcc ... -DXP_EXP=<n> selects experiment variants guarded inside gae.cu.
+// Standalone timing of the GAE launch (includes gae.cu directly).
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -27,7 +27,7 @@ int main(int argc, char **argv) {
     }
     cudaEventRecord(e1); cudaDeviceSynchronize();
     float ms; cudaEventElapsedTime(&ms, e0, e1);
-    printf("XP_EXP=%d P=%lld sets=%d: %.2f us/launch  %.0f GB/s\n", XP_EXP, P, sets, ms * 1e3 / iters, n * 17.0 / (ms * 1e-3 / iters) / 1e9);
+    printf("P=%lld sets=%d: %.2f us/launch  %.0f GB/s\n", P, sets, ms * 1e3 / iters, n * 17.0 / (ms * 1e-3 / iters) / 1e9);
   }
   printf("%s\n", cudaGetErrorString(cudaGetLastError()));
   return 0;
