@@ -3,7 +3,7 @@
 // :206-258 (_get_n_step_info).
 //
 // A table is struct-of-arrays: one [rows, row_bytes] array per key.  All keys move in ONE
-// launch (blockIdx.y = key).  Rows are cut into 128-bit vectors when pointer and row size
+// launch (flat grid, each key owns a CTA range).  Rows are cut into 128-bit vectors when pointer and row size
 // allow (else 8/4/2/1-byte), consecutive lanes take consecutive vectors of the same row, so
 // both the HBM read of the source row and the write of the packed output row are coalesced;
 // each thread keeps 4 independent 128-bit loads in flight.
@@ -22,6 +22,9 @@ struct KeyDesc {
   int vec_bytes;        // 16, 8, 4, 2 or 1
   long long vpr;        // vectors per row
   long long chunks;     // wide path: CTAs per row; narrow path: 0
+  long long per_chunk;  // wide path: vectors per chunk (even split, multiple of 32)
+  long long cta0;       // first CTA of this key in the flat grid
+  long long ctas;       // CTAs assigned to this key
   int role;             // n-step role
 };
 
@@ -129,14 +132,15 @@ __device__ __forceinline__ bool map_rows(const MoveParams &p, const KeyDesc &kd,
 }
 
 template <int OP, int W>
-__device__ __forceinline__ void move_key(const MoveParams &p, const KeyDesc &kd, int m) {
+__device__ __forceinline__ void move_key(const MoveParams &p, const KeyDesc &kd, int m, long long cta) {
   using V = typename VecT<W>::type;
   if (kd.chunks > 0) {
     // wide rows: one CTA per (row, chunk); no per-thread division
     const long long total = p.n_rows * kd.chunks;
-    for (long long w = blockIdx.x; w < total; w += gridDim.x) {
+    for (long long w = cta; w < total; w += kd.ctas) {
       const long long row = w / kd.chunks;
-      const long long v0 = (w - row * kd.chunks) * kVecPerCta;
+      const long long v0 = (w - row * kd.chunks) * kd.per_chunk;
+      const long long v_end = min(v0 + kd.per_chunk, kd.vpr);
       long long src_row, dst_row;
       const bool ok = map_rows<OP>(p, kd, row, m, src_row, dst_row);
       const char *s = kd.src + src_row * kd.row_bytes;
@@ -145,19 +149,18 @@ __device__ __forceinline__ void move_key(const MoveParams &p, const KeyDesc &kd,
 #pragma unroll
       for (int j = 0; j < kUnroll; ++j) {
         const long long v = v0 + threadIdx.x + j * kThreads;
-        if (v < kd.vpr) buf[j] = ok ? ld_vec<W>(s + v * W) : zero_vec<W>();
+        if (v < v_end) buf[j] = ok ? ld_vec<W>(s + v * W) : zero_vec<W>();
       }
 #pragma unroll
       for (int j = 0; j < kUnroll; ++j) {
         const long long v = v0 + threadIdx.x + j * kThreads;
-        if (v < kd.vpr) st_vec<W>(d + v * W, buf[j]);
+        if (v < v_end) st_vec<W>(d + v * W, buf[j]);
       }
     }
   } else {
     // narrow rows: flat (row, vector) space, consecutive lanes write consecutive bytes
     const long long total = p.n_rows * kd.vpr;
-    for (long long e = (long long)blockIdx.x * kThreads + threadIdx.x; e < total;
-         e += (long long)gridDim.x * kThreads) {
+    for (long long e = cta * kThreads + threadIdx.x; e < total; e += kd.ctas * kThreads) {
       const long long row = e / kd.vpr;
       const long long v = e - row * kd.vpr;
       long long src_row, dst_row;
@@ -169,13 +172,12 @@ __device__ __forceinline__ void move_key(const MoveParams &p, const KeyDesc &kd,
 }
 
 // n-step reward fold (replay_buffer.py:237-256): fp32, product then sum, forward order.
-__device__ __forceinline__ void fold_reward(const MoveParams &p, const KeyDesc &kd, int m) {
+__device__ __forceinline__ void fold_reward(const MoveParams &p, const KeyDesc &kd, int m, long long cta) {
   const long long epr = kd.row_bytes / 4;
   const long long total = p.n_rows * epr;
   const float *stage = reinterpret_cast<const float *>(kd.src);
   float *dst = reinterpret_cast<float *>(kd.dst);
-  for (long long e = (long long)blockIdx.x * kThreads + threadIdx.x; e < total;
-       e += (long long)gridDim.x * kThreads) {
+  for (long long e = cta * kThreads + threadIdx.x; e < total; e += kd.ctas * kThreads) {
     const long long row = e / epr, c = e - row * epr;
     float R = stage[(long long)(p.slot0 % p.n_step) * total + e];
     for (int i = 1; i <= m; ++i) {
@@ -188,21 +190,25 @@ __device__ __forceinline__ void fold_reward(const MoveParams &p, const KeyDesc &
 
 template <int OP>
 __global__ void __launch_bounds__(kThreads) move_kernel(const __grid_constant__ MoveParams p) {
-  const KeyDesc &kd = p.k[blockIdx.y];
+  // flat grid: key k owns CTAs [cta0_k, cta0_k + ctas_k)
+  int key = 0;
+  while (key + 1 < p.n_keys && (long long)blockIdx.x >= p.k[key + 1].cta0) ++key;
+  const KeyDesc &kd = p.k[key];
+  const long long cta = (long long)blockIdx.x - kd.cta0;
   int m = 0;
   if (OP == kOpNstep) {
     m = nstep_last_index(p);
     if (kd.role == XP_ROLE_REWARD) {
-      fold_reward(p, kd, m);
+      fold_reward(p, kd, m, cta);
       return;
     }
   }
   switch (kd.vec_bytes) {
-    case 16: move_key<OP, 16>(p, kd, m); break;
-    case 8: move_key<OP, 8>(p, kd, m); break;
-    case 4: move_key<OP, 4>(p, kd, m); break;
-    case 2: move_key<OP, 2>(p, kd, m); break;
-    default: move_key<OP, 1>(p, kd, m); break;
+    case 16: move_key<OP, 16>(p, kd, m, cta); break;
+    case 8: move_key<OP, 8>(p, kd, m, cta); break;
+    case 4: move_key<OP, 4>(p, kd, m, cta); break;
+    case 2: move_key<OP, 2>(p, kd, m, cta); break;
+    default: move_key<OP, 1>(p, kd, m, cta); break;
   }
 }
 
@@ -216,13 +222,14 @@ int pick_vec(const void *a, const void *b, long long row_bytes) {
 }
 
 xp_status_t fill_keys(MoveParams &p, const xp_key *keys, const int *roles, int n_keys,
-                      long long n_rows, long long &max_ctas, const char *what) {
+                      long long n_rows, long long &grid_ctas, const char *what) {
   XP_REQUIRE(n_keys >= 0 && n_keys <= XP_MAX_KEYS, XP_ERR_INVALID, "%s: n_keys %d not in [0,%d]",
              what, n_keys, XP_MAX_KEYS);
   XP_REQUIRE(n_keys == 0 || keys, XP_ERR_INVALID, "%s: null keys", what);
   p.n_keys = n_keys;
   p.n_rows = n_rows;
-  max_ctas = 1;
+  grid_ctas = 0;
+  const long long cap = (long long)xp::sm_count() * 32;  // per key; grid-stride beyond that
   for (int i = 0; i < n_keys; ++i) {
     XP_REQUIRE(keys[i].row_bytes > 0, XP_ERR_INVALID, "%s: key %d row_bytes <= 0", what, i);
     XP_REQUIRE(n_rows == 0 || (keys[i].src && keys[i].dst), XP_ERR_INVALID, "%s: key %d null pointer", what, i);
@@ -240,17 +247,14 @@ xp_status_t fill_keys(MoveParams &p, const xp_key *keys, const int *roles, int n
     } else {
       k.chunks = (k.vpr >= 128) ? (k.vpr + kVecPerCta - 1) / kVecPerCta : 0;
     }
+    k.per_chunk = k.chunks > 0 ? ((k.vpr + k.chunks - 1) / k.chunks + 31) / 32 * 32 : 0;
     long long ctas = k.chunks > 0 ? n_rows * k.chunks : (n_rows * k.vpr + kThreads - 1) / kThreads;
     if (k.role == XP_ROLE_REWARD) ctas = (n_rows * (k.row_bytes / 4) + kThreads - 1) / kThreads;
-    if (ctas > max_ctas) max_ctas = ctas;
+    k.ctas = ctas < 1 ? 1 : (ctas > cap ? cap : ctas);
+    k.cta0 = grid_ctas;
+    grid_ctas += k.ctas;
   }
   return XP_OK;
-}
-
-unsigned grid_x(long long ctas) {
-  // enough CTAs to fill the machine several times over, grid-stride beyond that
-  const long long cap = (long long)xp::sm_count() * 32;
-  return (unsigned)(ctas < cap ? (ctas < 1 ? 1 : ctas) : cap);
 }
 
 }  // namespace
@@ -271,7 +275,7 @@ xp_status_t xp_ring_insert(const xp_key *keys, int n_keys, int64_t n_rows, int64
   if (st != XP_OK) return st;
   p.cursor = cursor;
   p.max_size = max_size;
-  dim3 grid(grid_x(ctas), (unsigned)n_keys);
+  dim3 grid((unsigned)ctas);
   move_kernel<kOpInsert><<<grid, kThreads, 0, (cudaStream_t)stream>>>(p);
   return xp::check_launch("xp_ring_insert");
 }
@@ -288,7 +292,7 @@ xp_status_t xp_gather(const xp_key *keys, int n_keys, const int64_t *idx_dev, in
   p.idx = (const long long *)idx_dev;
   p.n_src_rows = n_src_rows;
   p.err = err_flag_dev;
-  dim3 grid(grid_x(ctas), (unsigned)n_keys);
+  dim3 grid((unsigned)ctas);
   move_kernel<kOpGather><<<grid, kThreads, 0, (cudaStream_t)stream>>>(p);
   return xp::check_launch("xp_gather");
 }
@@ -315,7 +319,7 @@ xp_status_t xp_nstep_fold_insert(const xp_key *keys, const int *roles, int n_key
   p.done_key = done_key;
   p.done_elem_bytes = done_elem_bytes;
   for (int i = 0; i < n_step; ++i) p.gpow[i] = gpow[i];
-  dim3 grid(grid_x(ctas), (unsigned)n_keys);
+  dim3 grid((unsigned)ctas);
   move_kernel<kOpNstep><<<grid, kThreads, 0, (cudaStream_t)stream>>>(p);
   return xp::check_launch("xp_nstep_fold_insert");
 }
