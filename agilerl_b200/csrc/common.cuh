@@ -57,4 +57,5 @@ __device__ __forceinline__ void st_stream_v4(int4 *p, const int4 &v) {
                : "memory");
 }
 
+
 }  // namespace xp

@@ -125,6 +125,59 @@ __device__ __forceinline__ long long descend(const double *sum, long long stride
   return idx - cap;
 }
 
+// The same walk, D levels per memory round trip: all left children of the next D levels below the
+// current node (2^D - 1 nodes, contiguous per level in heap order) are requested at once, then the
+// D comparisons run from registers.  Same comparisons and subtractions in the same order =>
+// identical result; ~4x the sectors of the plain walk, so only for small (latency-bound) batches.
+// `leaf_val` receives sum[cap + leaf] (the right sibling is fetched with the last group).
+template <int D>
+__device__ __forceinline__ long long descend_wide(const double *sum, long long stride, long long cap,
+                                                  double ub, double *leaf_val) {
+  long long idx = 1;
+  int rem = 63 - __clzll(cap);
+  double last = 0.0;
+  if (rem == 0) last = __ldg(&sum[stride]);
+  while (rem > 0) {
+    const int d = rem < D ? rem : D;
+    double v[(1 << D) - 1];  // v[q]: level k = floor(log2(q+1)) + 1 below idx, m-th left child
+#pragma unroll
+    for (int q = 0; q < (1 << D) - 1; ++q) {
+      const int k = 32 - __builtin_clz((unsigned)(q + 1));
+      const int m = q + 1 - (1 << (k - 1));
+      v[q] = (k <= d) ? __ldg(&sum[((idx << k) + 2 * m) * stride]) : 0.0;
+    }
+    double vr[1 << (D - 1)];  // right siblings at the leaf level (last group only)
+#pragma unroll
+    for (int m = 0; m < (1 << (D - 1)); ++m)
+      vr[m] = (rem == d && m < (1 << (d - 1))) ? __ldg(&sum[((idx << d) + 2 * m + 1) * stride]) : 0.0;
+    int o = 0;
+#pragma unroll
+    for (int k = 1; k <= D; ++k) {
+      if (k <= d) {
+        double lv = v[(1 << (k - 1)) - 1];
+#pragma unroll
+        for (int m = 1; m < (1 << (k - 1)); ++m) lv = (o == m) ? v[(1 << (k - 1)) - 1 + m] : lv;
+        if (k == d) {
+          double rv = vr[0];
+#pragma unroll
+          for (int m = 1; m < (1 << (D - 1)); ++m) rv = (o == m) ? vr[m] : rv;
+          last = (lv > ub) ? lv : rv;
+        }
+        if (lv > ub) {
+          o = 2 * o;
+        } else {
+          ub = __dsub_rn(ub, lv);
+          o = 2 * o + 1;
+        }
+      }
+    }
+    idx = (idx << d) + o;
+    rem -= d;
+  }
+  *leaf_val = last;
+  return idx - cap;
+}
+
 __global__ void tree_retrieve_kernel(Tree t, const double *ub, long long B, long long *out) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B) out[i] = descend(t.sum, t.stride, t.cap, ub[i]);
@@ -136,25 +189,33 @@ __device__ __forceinline__ double is_max_weight(const Tree &t, double total, dou
   const double p_min = __ddiv_rn(__ldg(&t.mn[t.stride]), total);
   return xp::xp_pow(__dmul_rn(p_min, size), neg_beta);
 }
-__device__ __forceinline__ float is_weight(const Tree &t, long long leaf, double total,
-                                           double size, double neg_beta, double max_w) {
-  const double p = __ddiv_rn(__ldg(&t.sum[(t.cap + leaf) * t.stride]), total);
+__device__ __forceinline__ float is_weight_of(double leaf_val, double total, double size,
+                                              double neg_beta, double max_w) {
+  const double p = __ddiv_rn(leaf_val, total);
   const double w = xp::xp_pow(__dmul_rn(p, size), neg_beta);
   return __double2float_rn(__ddiv_rn(w, max_w));
+}
+__device__ __forceinline__ float is_weight(const Tree &t, long long leaf, double total,
+                                           double size, double neg_beta, double max_w) {
+  return is_weight_of(__ldg(&t.sum[(t.cap + leaf) * t.stride]), total, size, neg_beta, max_w);
 }
 
 // _sample_proportional (+ _calculate_weights) for P agents x B strata, one thread per sample.
 // Thread order is stratum-major / agent-minor: the lanes of a warp draw in the SAME stratum for
 // different agents, so their descents share every node down to where the stratum splits
 // (identical addresses coalesce into one transaction) and then stay inside one small subtree.
+template <bool WIDE>
 __global__ void __launch_bounds__(256) per_sample_kernel(Tree t, const float *u, long long B,
                                                          long long P, long long total_samples,
                                                          double size, double neg_beta,
                                                          long long *idx_out, float *w_out) {
+  constexpr bool wide = WIDE;
   __shared__ double s_max_w;
   const double total = __ldg(&t.sum[t.stride]);  // sum_tree.sum() == tree[1]
-  if (w_out && threadIdx.x == 0) s_max_w = is_max_weight(t, total, size, neg_beta);
-  if (w_out) __syncthreads();
+  if (!wide) {
+    if (w_out && threadIdx.x == 0) s_max_w = is_max_weight(t, total, size, neg_beta);
+    if (w_out) __syncthreads();
+  }
   const long long tt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (tt >= total_samples) return;
   const long long i = tt / P;                 // stratum
@@ -164,6 +225,18 @@ __global__ void __launch_bounds__(256) per_sample_kernel(Tree t, const float *u,
   const double b = __dmul_rn(seg, (double)(i + 1));
   // torch.rand(1).item() widens fp32 -> fp64 exactly; u*(b-a)+a in three rounded ops (:377)
   const double ub = __dadd_rn(__dmul_rn((double)u[j], __dsub_rn(b, a)), a);
+  if (wide) {
+    // small batch: latency-bound — wide descent, and every thread derives max_w itself (no barrier)
+    const double mn = w_out ? __ldg(&t.mn[t.stride]) : 0.0;
+    double leaf_val;
+    const long long leaf = descend_wide<4>(t.sum, t.stride, t.cap, ub, &leaf_val);
+    idx_out[j] = leaf;
+    if (w_out) {
+      const double max_w = xp::xp_pow(__dmul_rn(__ddiv_rn(mn, total), size), neg_beta);
+      w_out[j] = is_weight_of(leaf_val, total, size, neg_beta, max_w);
+    }
+    return;
+  }
   const long long leaf = descend(t.sum, t.stride, t.cap, ub);
   idx_out[j] = leaf;
   if (w_out) w_out[j] = is_weight(t, leaf, total, size, neg_beta, s_max_w);
@@ -295,8 +368,15 @@ xp_status_t xp_per_sample(const xp_tree *tree, const float *u_dev, int64_t B, in
   const long long total = B * P;
   if (total == 0) return XP_OK;
   XP_REQUIRE(u_dev && idx_out_dev, XP_ERR_INVALID, "xp_per_sample: null pointer");
-  per_sample_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      t, u_dev, B, P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
+  const int wide = total <= 16384;  // latency-bound: 4 levels per round trip, small CTAs on many SMs
+  const int threads = wide ? 64 : 256;
+  const unsigned grid = (unsigned)((total + threads - 1) / threads);
+  if (wide)
+    per_sample_kernel<true><<<grid, threads, 0, (cudaStream_t)stream>>>(
+        t, u_dev, B, P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
+  else
+    per_sample_kernel<false><<<grid, threads, 0, (cudaStream_t)stream>>>(
+        t, u_dev, B, P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
   return xp::check_launch("xp_per_sample");
 }
 

@@ -270,9 +270,10 @@ __device__ void cta_dense_top(const Tree &t, int h0, int width, double2 *heap) {
 }
 
 // ---- schedule M (B <= 8192): ONE launch ---------------------------------------------------------
-// Warp w owns bucket subtree w of nb = 2^k buckets: it scans the whole batch (a few KB, L2
-// resident), keeps the items whose leaf falls in its bucket, climbs to the bucket root; the last
-// CTA to finish rebuilds the nb-leaf top densely.
+// The CTA stages the whole batch's leaf numbers in shared memory with every load in flight at
+// once (a few KB, L2 resident); warp w then owns bucket subtree w of nb = 2^k buckets: it keeps
+// the items whose leaf falls in its bucket and climbs to the bucket root; the last CTA to finish
+// rebuilds the nb-leaf top densely (its heap re-uses the staging memory).
 constexpr int kMidWarps = 4;
 template <bool PAIRED>
 __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc s, int B, int nb, int shift) {
@@ -282,44 +283,52 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
   const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * (blockDim.x >> 5) + warp;
-  if (b < nb) {
-    int cnt = 0;
+  int *s_leaf = reinterpret_cast<int *>(smem_raw);  // [B]; -1 = out of range
+  {
+    constexpr int U = 8;  // independent loads in flight per thread (no branch on a loaded value)
+    const bool fold = blockIdx.x == 0 && s.kind == kSrcPrio;
     double pmax = 0.0;
-    constexpr int U = 8;  // independent loads in flight per lane
-    for (int i0 = 0; i0 < B; i0 += 32 * U) {
-      u64 keys[U];
-      long long leaves[U];
+    for (int i0 = 0; i0 < B; i0 += (int)blockDim.x * U) {
+      long long raw[U];
+      float pr[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const int i = i0 + u * 32 + lane;
-        keys[u] = kPad;
-        leaves[u] = 0;
+        const int i = min(i0 + u * (int)blockDim.x + (int)threadIdx.x, B - 1);
+        raw[u] = (s.kind == kSrcRange) ? src_idx(s, i) : __ldg(s.idx + i);
+        pr[u] = fold ? __ldg(s.prio + i) : 0.0f;
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int i = i0 + u * (int)blockDim.x + (int)threadIdx.x;
         if (i < B) {
-          keys[u] = item_key(s, i, leaves[u]);
-          if (b == 0) {
-            if (keys[u] == kPad && s.err) *s.err = 1;
-            if (s.kind == kSrcPrio) pmax = fmax(pmax, clamp_prio(s.prio[i]));
-          }
+          const bool bad = raw[u] < 0 || raw[u] >= s.limit;
+          s_leaf[i] = bad ? -1 : (int)raw[u];
+          if (bad && blockIdx.x == 0 && s.err) *s.err = 1;
+          if (fold) pmax = fmax(pmax, clamp_prio(pr[u]));
         }
       }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const bool mine = keys[u] != kPad && (int)(leaves[u] >> shift) == b;
-        const unsigned mask = __ballot_sync(FULL, mine);
-        const int slot = cnt + __popc(mask & ((1u << lane) - 1u));
-        if (mine && slot < 32) s_list[warp][slot] = keys[u];
-        cnt += __popc(mask);
-      }
     }
-    if (b == 0 && s.kind == kSrcPrio) fold_max_priority(s, pmax);
+    if (fold) fold_max_priority(s, pmax);
+  }
+  __syncthreads();
+  if (b < nb) {
+    int cnt = 0;
+    for (int i0 = 0; i0 < B; i0 += 32) {
+      const int i = i0 + lane;
+      const int leaf = i < B ? s_leaf[i] : -1;
+      const bool mine = leaf >= 0 && (leaf >> shift) == b;
+      const unsigned mask = __ballot_sync(FULL, mine);
+      const int slot = cnt + __popc(mask & ((1u << lane) - 1u));
+      if (mine && slot < 32) s_list[warp][slot] = ((u64)(unsigned)leaf << 32) | (u64)(unsigned)i;
+      cnt += __popc(mask);
+    }
     __syncwarp();
     if (cnt <= 32) {
       if (cnt > 0) warp_climb<PAIRED, 32>(t, s, lane < cnt ? s_list[warp][lane] : kPad, shift);
     } else {
       auto fetch = [&](long long i) -> u64 {
-        long long leaf;
-        const u64 key = item_key(s, i, leaf);
-        return (key != kPad && (int)(leaf >> shift) == b) ? key : kPad;
+        const int leaf = s_leaf[i];
+        return (leaf >= 0 && (leaf >> shift) == b) ? (((u64)(unsigned)leaf << 32) | (u64)i) : kPad;
       };
       warp_climb_large<PAIRED>(t, s, fetch, B, shift);
     }
@@ -626,7 +635,8 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     const int shift = L - ilog2(nb);
     const int warps = nb < kMidWarps ? (int)nb : kMidWarps;
     const unsigned grid = (unsigned)(nb / warps);
-    const size_t smem = nb > 1 ? (size_t)2 * nb * sizeof(double2) : 0;
+    const size_t heap = nb > 1 ? (size_t)2 * nb * sizeof(double2) : 0;
+    const size_t smem = heap > (size_t)B * 4 ? heap : (size_t)B * 4;
     if (paired)
       set_mid_kernel<true><<<grid, warps * 32, smem, st>>>(t, s, (int)B, (int)nb, shift);
     else

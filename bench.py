@@ -330,10 +330,12 @@ class C2Workload:
             ev[0].record()
         k = o["per"]
         chk(lib.xp_gather(k[0], k[1], self.idx.data_ptr(), n, self.cap, self.err.data_ptr(), stream))
-        if ev is not None:
-            ev[1].record()
+        if ev is not None and len(ev) > 2:
+            ev[2].record()
         k = o["nstep"]
         chk(lib.xp_gather(k[0], k[1], self.idx.data_ptr(), n, self.cap, self.err.data_ptr(), stream))
+        if ev is not None:
+            ev[1].record()
         if self.world > 1:
             import torch.distributed as dist
 
@@ -345,6 +347,8 @@ class C2Workload:
         else:
             chk(lib.xp_per_update(C.byref(self.h), self.state.data_ptr(), self.idx.data_ptr(),
                                   pr.data_ptr(), n, self.cap, c["alpha"], self.err.data_ptr(), stream))
+        if ev is not None and len(ev) > 3:
+            ev[3].record()
 
     def verify(self):
         """size-independent property at full size: the gathered rows equal torch indexing of the
@@ -522,12 +526,24 @@ def b200_arm(args):
     sync()
     l1 = lib.xp_launch_count()
     ms = a.elapsed_time(b)
-    gather_us = sum(x.elapsed_time(y) for x, y in evs) * 1e3 / K
+    # the two gather launches (PER table, n-step table; same indices) sit between one event pair
+    gather_us = sum(x.elapsed_time(y) for x, y in evs) * 1e3 / K / 2
     if world > 1:
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = wl.units_per_step * world * K / (ms * 1e-3)
+
+    # per-kernel breakdown of the step (separate untimed pass; events between every launch)
+    Kb = min(K, 50)
+    bev = [[torch.cuda.Event(enable_timing=True) for _ in range(5)] for _ in range(Kb)]
+    for i in range(Kb):
+        bev[i][4].record()
+        wl.step(W + i, bev[i])
+    sync()
+    breakdown = {n: round(sum(e[x].elapsed_time(e[y]) for e in bev) * 1e3 / Kb, 2)
+                 for n, x, y in (("per_sample_us", 4, 0), ("gather_per_table_us", 0, 2),
+                                 ("gather_nstep_table_us", 2, 1), ("per_update_us", 1, 3))}
 
     # -- e2e through the public per-agent API ---------------------------------------------------
     e2e = None
@@ -589,7 +605,9 @@ def b200_arm(args):
             "clocks": clocks.summary(),
             "roofline": dict(roofline(C2["P"] * C2["B"] * (2 * R_C2 + 8), gather_us),
                              kernel="move_kernel<gather>", us_per_launch=round(gather_us, 2),
-                             algorithmic_bytes_per_launch=C2["P"] * C2["B"] * (2 * R_C2 + 8)),
+                             algorithmic_bytes_per_launch=C2["P"] * C2["B"] * (2 * R_C2 + 8),
+                             launches_timed=2 * K),
+            "step_breakdown": breakdown,
             "cpu_baseline": cpu,
             "also": also,
         }
