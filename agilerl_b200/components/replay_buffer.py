@@ -203,19 +203,20 @@ class ReplayBuffer:
 
     def _gather_plan(self):
         """Per-storage launch descriptor, built once: the ``xp_key`` array with the source
-        pointers / row sizes filled in, and (tail shape, dtype) of every key."""
+        pointers / row sizes filled in, and the keys grouped by (tail shape, dtype) — the outputs
+        of a group are carved from ONE allocation (fewer allocator round trips per sample)."""
         plan = getattr(self, "_gplan", None)
         if plan is None or plan[0] is not self._leaves:
             paths = list(self._leaves.keys())
             keys = (nv.XpKey * len(paths))()
-            meta = []
+            groups: dict = {}
             for i, p in enumerate(paths):
                 t = self._leaves[p]
                 keys[i].src = t.data_ptr()
                 keys[i].row_bytes = xp.row_bytes(t)
-                meta.append((p, tuple(t.shape[1:]), t.dtype))
+                groups.setdefault((tuple(t.shape[1:]), t.dtype), []).append((i, p, xp.row_bytes(t)))
             flat = all(len(p) == 1 for p in paths)
-            plan = (self._leaves, keys, meta, flat, nv.load().xp_gather)
+            plan = (self._leaves, keys, list(groups.items()), flat, nv.load().xp_gather, len(paths))
             self._gplan = plan
         return plan
 
@@ -231,23 +232,31 @@ class ReplayBuffer:
         B = idx.shape[0]
         if lead is None:
             lead = (B,)
-        _, keys, meta, flat, fn = self._gather_plan()
+        _, keys, groups, flat, fn, n_keys = self._gather_plan()
         out = {}
         with nv.on_device(dev):
-            for i, (p, tail, dt) in enumerate(meta):
-                o = torch.empty((*lead, *tail), dtype=dt, device=dev)
-                keys[i].dst = o.data_ptr()
-                out[p] = o
+            for (tail, dt), members in groups:
+                if len(members) == 1:
+                    i, p, _ = members[0]
+                    o = torch.empty((*lead, *tail), dtype=dt, device=dev)
+                    keys[i].dst = o.data_ptr()
+                    out[p] = o
+                else:
+                    slab = torch.empty((len(members), *lead, *tail), dtype=dt, device=dev)
+                    base = slab.data_ptr()
+                    for j, ((i, p, rb), o) in enumerate(zip(members, slab.unbind(0))):
+                        keys[i].dst = base + j * B * rb
+                        out[p] = o
             if B:
-                nv.check(fn(keys, len(meta), idx.data_ptr(), B, self.max_size, self._err.data_ptr(),
+                nv.check(fn(keys, n_keys, idx.data_ptr(), B, self.max_size, self._err.data_ptr(),
                             nv.raw_stream(dev.index)), "xp_gather")
-        if flat:  # no nested keys: build the batch directly
+        if flat:  # no nested keys: build the batch directly (in storage key order)
             tb = TensorBatch.__new__(TensorBatch)
-            tb._d = {p[0]: t for p, t in out.items()}
+            tb._d = {p[0]: out[p] for p in self._leaves}
             tb._non_tensor = {}
             tb.batch_size = torch.Size(lead)
             return tb
-        return _unflatten(out, list(lead))
+        return _unflatten({p: out[p] for p in self._leaves}, list(lead))
 
     def sample(self, batch_size: int, return_idx: bool = False) -> TensorBatch:
         indices = self._uniform_indices(batch_size)

@@ -54,4 +54,28 @@ xp_status_t xp_device_info(int device, int *sm_count, int *cc_major, int *cc_min
   return XP_OK;
 }
 
+xp_status_t xp_copy_to_device(void *dst_dev, const void *src_host, int64_t nbytes, void *stream) {
+  XP_REQUIRE(nbytes >= 0, XP_ERR_INVALID, "xp_copy_to_device: negative size");
+  if (nbytes == 0) return XP_OK;
+  XP_REQUIRE(dst_dev && src_host, XP_ERR_INVALID, "xp_copy_to_device: null pointer");
+  cudaError_t e = cudaMemcpyAsync(dst_dev, src_host, (size_t)nbytes, cudaMemcpyHostToDevice, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    xp::set_error("xp_copy_to_device: %s", cudaGetErrorString(e));
+    return XP_ERR_CUDA;
+  }
+  return XP_OK;
+}
+
+xp_status_t xp_copy_to_host(void *dst_host, const void *src_dev, int64_t nbytes, void *stream) {
+  XP_REQUIRE(nbytes >= 0, XP_ERR_INVALID, "xp_copy_to_host: negative size");
+  if (nbytes == 0) return XP_OK;
+  XP_REQUIRE(dst_host && src_dev, XP_ERR_INVALID, "xp_copy_to_host: null pointer");
+  cudaError_t e = cudaMemcpyAsync(dst_host, src_dev, (size_t)nbytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    xp::set_error("xp_copy_to_host: %s", cudaGetErrorString(e));
+    return XP_ERR_CUDA;
+  }
+  return XP_OK;
+}
+
 }  // extern "C"

@@ -46,6 +46,14 @@ uint64_t xp_launch_count(void);
 /* Device facts used for grid sizing (SM count, compute capability). */
 xp_status_t xp_device_info(int device, int *sm_count, int *cc_major, int *cc_minor);
 
+/* Host staging: asynchronous copy of a small host array to device memory (or back) on `stream`.
+ * Replaces the `.to(device)` of the per-call host inputs of the reference: the torch.rand draws
+ * (replay_buffer.py:377), the priorities / indices that arrive as numpy arrays (:411-428,
+ * algorithms/dqn_rainbow.py:487-488).  Truly asynchronous only for pinned host memory; the
+ * caller keeps the host array alive and unmodified until the stream has passed this point.  */
+xp_status_t xp_copy_to_device(void *dst_dev, const void *src_host, int64_t nbytes, void *stream);
+xp_status_t xp_copy_to_host(void *dst_host, const void *src_dev, int64_t nbytes, void *stream);
+
 /* ---- keys: one column of a transition table ---------------------------------------- */
 /* A replay storage is struct-of-arrays: one [max_size, row_bytes] device array per key
  * (replay_buffer.py:60-70).  `src`/`dst` meaning depends on the op.                     */
