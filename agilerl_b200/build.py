@@ -90,6 +90,43 @@ def build(verbose: bool = False, force: bool = False) -> Path:
     return LIB
 
 
+HOSTACCEL_SRC = CSRC / "hostaccel.cpp"
+HOSTACCEL = LIB_DIR / "_hostaccel.so"
+
+
+def build_hostaccel(force: bool = False) -> Path:
+    """Compile the optional torch/pybind11 host fast path (g++, no CUDA code of its own)."""
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension as ce
+
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    h = hashlib.sha256()
+    h.update(HOSTACCEL_SRC.read_bytes())
+    h.update((ROOT / "include" / "b200xp.h").read_bytes())
+    h.update(torch.__version__.encode())
+    stamp = OBJ_DIR / "hostaccel.sha"
+    OBJ_DIR.mkdir(parents=True, exist_ok=True)
+    if HOSTACCEL.exists() and stamp.exists() and stamp.read_text() == h.hexdigest() and not force:
+        return HOSTACCEL
+    cuda_home = os.path.dirname(os.path.dirname(_nvcc()))
+    inc = ce.include_paths() + [sysconfig.get_paths()["include"], os.path.join(cuda_home, "include"),
+                                str(ROOT / "include")]
+    lib = ce.library_paths()[0]
+    cmd = ["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-w", str(HOSTACCEL_SRC), "-o", str(HOSTACCEL),
+           "-DTORCH_EXTENSION_NAME=_hostaccel", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
+           *[f"-I{i}" for i in inc], f"-L{lib}", "-ltorch", "-ltorch_cpu", "-ltorch_python", "-lc10",
+           "-lc10_cuda", "-ltorch_cuda", f"-Wl,-rpath,{lib}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"g++ failed for hostaccel.cpp:\n{r.stdout}\n{r.stderr}")
+    stamp.write_text(h.hexdigest())
+    return HOSTACCEL
+
+
 if __name__ == "__main__":
     p = build(verbose="-v" in sys.argv, force="-f" in sys.argv)
     print(p)
+    print(build_hostaccel(force="-f" in sys.argv))

@@ -20,6 +20,7 @@ from typing import Any
 import numpy as np
 import torch
 
+from .. import _hostaccel
 from .. import _native as nv
 from .. import xp
 from .rng import TorchCpuStream
@@ -220,6 +221,21 @@ class ReplayBuffer:
             self._gplan = plan
         return plan
 
+    def _fast_table(self):
+        """Native host fast path for ``storage[idx]`` (flat key sets on the current device), or
+        None.  Rebuilt when the storage is re-allocated."""
+        ft = getattr(self, "_ftab", None)
+        if ft is None or ft[0] is not self._leaves:
+            acc = _hostaccel.load()
+            obj = None
+            if (acc is not None and self._leaves and len(self._leaves) <= 24
+                    and all(len(p) == 1 and t.is_cuda for p, t in self._leaves.items())):
+                obj = acc.FastGather(list(self._leaves.values()), [p[0] for p in self._leaves],
+                                     self.max_size, self._err)
+            ft = (self._leaves, obj)
+            self._ftab = ft
+        return ft[1]
+
     def _gather(self, indices: torch.Tensor, lead: tuple | None = None) -> TensorBatch:
         """``storage[indices]`` as fresh copies, every key in one launch.  ``lead``: leading
         shape of the result (the shape of ``indices`` in the reference's ``storage[idxs]``)."""
@@ -232,6 +248,13 @@ class ReplayBuffer:
         B = idx.shape[0]
         if lead is None:
             lead = (B,)
+        fast = self._fast_table()
+        if fast is not None and torch._C._cuda_getDevice() == dev.index:
+            tb = TensorBatch.__new__(TensorBatch)
+            tb._d = fast.gather(idx, lead)
+            tb._non_tensor = {}
+            tb.batch_size = torch.Size(lead)
+            return tb
         _, keys, groups, flat, fn, n_keys = self._gather_plan()
         out = {}
         with nv.on_device(dev):
@@ -500,6 +523,17 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         if self._pending_err is not None:
             self._raise_deferred()
         dev = self.storage_device
+        fp = self._fast_per()
+        if fp is not None and torch._C._cuda_getDevice() == dev.index:
+            if u is None and self.rng != "torch":
+                u = self._draw_uniforms(batch_size)
+            if u is None or (u.is_cuda and u.device == dev and u.dtype == torch.float32
+                             and u.is_contiguous() and u.numel() == batch_size):
+                tb = TensorBatch.__new__(TensorBatch)
+                tb._d = fp.sample(batch_size, float(beta), self._size, u)
+                tb._non_tensor = {}
+                tb.batch_size = torch.Size((batch_size,))
+                return self._out(tb)
         if u is None:
             u = self._draw_uniforms(batch_size)
         if u.device != dev or u.dtype != torch.float32 or not u.is_contiguous():
@@ -514,6 +548,22 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         samples._d["weights"] = w
         samples._d["idxs"] = idx
         return self._out(samples)
+
+    def _fast_per(self):
+        """Native host fast path of sample / update_priorities, or None."""
+        tab = self._fast_table()
+        if tab is None:
+            return None
+        fp = getattr(self, "_fper", None)
+        if fp is None or fp[0] is not tab or fp[1] is not self._trees:
+            import ctypes as _C
+
+            _, _, st, h = self._ensure_trees()
+            obj = _hostaccel.load().FastPer(tab, _C.addressof(h), st.nodes, st.aux, self._state, st.err,
+                                            self.max_size, float(self.alpha))
+            fp = (tab, self._trees, obj)
+            self._fper = fp
+        return fp[2]
 
     def _raise_deferred(self) -> None:
         """Out-of-range indices that arrived as DEVICE tensors are detected by the kernel (a sticky
@@ -550,6 +600,19 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         if on_host and check and idx.numel():
             assert 0 <= int(idx.min()) and int(idx.max()) < self.max_size, (
                 "priority index out of range [0, max_size)")
+        if not on_host and torch._C._cuda_getDevice() == dev.index:
+            fp = self._fast_per()
+            pr = priorities if isinstance(priorities, torch.Tensor) else torch.as_tensor(priorities)
+            if (fp is not None and idx.device == dev and idx.dtype == torch.int64 and idx.is_contiguous()
+                    and pr.dtype == torch.float32 and pr.is_contiguous()
+                    and (not pr.is_cuda or pr.device == dev)):
+                fp.update(idx, pr)
+                if check:
+                    self._updates_since_poll += 1
+                    if self._updates_since_poll >= 32 and self._pending_err is None:
+                        self._updates_since_poll = 0
+                        self._poll_err_async()
+                return
         with nv.on_device(dev):
             if on_host:
                 idx = self._stage().to_device(idx.to(torch.int64).reshape(-1))

@@ -1,0 +1,257 @@
+// hostaccel.cpp — native fast path of the PYTHON host mirror (agilerl_b200.components).
+//
+// Not part of the C-ABI: libb200xp.so stays torch-free.  This is a small CPython/torch extension
+// that does, in one call, what the Python host does in ~15 interpreter round trips per buffer
+// method: allocate the fresh output tensors (replay_buffer.py:126 `storage[idx]` copies), stage
+// the host inputs through a pinned ring, and call the C-ABI entry points on torch's current
+// stream.  The Python classes use it when it is built and the inputs are in canonical form, and
+// fall back to their own (identical, slower) code otherwise; results are the same either way —
+// every byte is still produced by libb200xp.so kernels.
+#include <ATen/cuda/CUDAEvent.h>
+#include <c10/cuda/CUDAStream.h>
+#include <torch/extension.h>
+
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "b200xp.h"
+
+namespace py = pybind11;
+
+namespace {
+
+using gather_fn = xp_status_t (*)(const xp_key *, int, const int64_t *, int64_t, int64_t, int *, void *);
+using sample_fn = xp_status_t (*)(const xp_tree *, const float *, int64_t, int64_t, int64_t, double,
+                                  int64_t *, float *, void *);
+using update_fn = xp_status_t (*)(const xp_tree *, xp_per_state *, const int64_t *, const float *,
+                                  int64_t, int64_t, double, int *, void *);
+using copy_fn = xp_status_t (*)(void *, const void *, int64_t, void *);
+
+struct Fns {
+  gather_fn gather = nullptr;
+  sample_fn per_sample = nullptr;
+  update_fn per_update = nullptr;
+  copy_fn copy_to_device = nullptr;
+  py::object check;  // agilerl_b200._native.check(status, what): raises the mapped exception
+} g;
+
+void bind(uint64_t gather, uint64_t per_sample, uint64_t per_update, uint64_t copy_to_device,
+          py::object check) {
+  g.gather = reinterpret_cast<gather_fn>(gather);
+  g.per_sample = reinterpret_cast<sample_fn>(per_sample);
+  g.per_update = reinterpret_cast<update_fn>(per_update);
+  g.copy_to_device = reinterpret_cast<copy_fn>(copy_to_device);
+  g.check = std::move(check);
+}
+
+inline void ok(xp_status_t rc, const char *what) {
+  if (rc != XP_OK) g.check((int)rc, what);  // raises in Python
+}
+
+// ---- pinned staging ring (same protocol as components/staging.py) ------------------------------
+struct Slot {
+  at::Tensor host, dev;
+  char *hp = nullptr, *dp = nullptr;
+  int64_t nbytes = 0;
+};
+
+class Ring {
+ public:
+  Ring(c10::DeviceIndex index, int slots) : index_(index), slots_(slots), half_(slots / 2) {}
+
+  Slot &acquire(int64_t nbytes) {
+    const int i = next_;
+    if (i % half_ == 0) {
+      const int h = i / half_;
+      if (pending_[h]) {
+        if (!ev_[h].query()) ev_[h].synchronize();
+        pending_[h] = false;
+      }
+    }
+    Slot &s = slots_[i];
+    if (s.nbytes < nbytes) {
+      if (s.nbytes) c10::cuda::getCurrentCUDAStream(index_).synchronize();
+      const int64_t n = std::max<int64_t>(nbytes, 1 << 16);
+      s.host = at::empty({n}, at::TensorOptions().dtype(at::kByte).pinned_memory(true));
+      s.dev = at::empty({n}, at::TensorOptions().dtype(at::kByte).device(c10::Device(c10::kCUDA, index_)));
+      s.hp = static_cast<char *>(s.host.data_ptr());
+      s.dp = static_cast<char *>(s.dev.data_ptr());
+      s.nbytes = n;
+    }
+    return s;
+  }
+
+  // host -> device of the first nbytes of the acquired slot, on the current stream
+  void push(Slot &s, int64_t nbytes, c10::cuda::CUDAStream st) {
+    if (have_last_ && st.stream() != last_) c10::cuda::device_synchronize();
+    last_ = st.stream();
+    have_last_ = true;
+    ok(g.copy_to_device(s.dp, s.hp, nbytes, st.stream()), "xp_copy_to_device");
+    const int i = next_;
+    next_ = (i + 1) % (int)slots_.size();
+    if ((i + 1) % half_ == 0) {
+      const int h = i / half_;
+      ev_[h].record(st);
+      pending_[h] = true;
+    }
+  }
+
+ private:
+  c10::DeviceIndex index_;
+  std::vector<Slot> slots_;
+  int half_, next_ = 0;
+  at::cuda::CUDAEvent ev_[2];
+  bool pending_[2] = {false, false};
+  cudaStream_t last_ = nullptr;
+  bool have_last_ = false;
+};
+
+// ---- storage[idx] for every key of a table ------------------------------------------------------
+struct KeyMeta {
+  std::string name;
+  std::vector<int64_t> tail;
+  at::ScalarType dtype;
+};
+
+class FastGather {
+ public:
+  FastGather(std::vector<at::Tensor> leaves, std::vector<std::string> names, int64_t max_size,
+             at::Tensor err)
+      : leaves_(std::move(leaves)), max_size_(max_size), err_(std::move(err)) {
+    TORCH_CHECK(leaves_.size() == names.size() && !leaves_.empty() && leaves_.size() <= XP_MAX_KEYS);
+    index_ = leaves_[0].device().index();
+    keys_.resize(leaves_.size());
+    for (size_t i = 0; i < leaves_.size(); ++i) {
+      const at::Tensor &t = leaves_[i];
+      TORCH_CHECK(t.is_cuda() && t.is_contiguous() && t.dim() >= 1);
+      keys_[i].src = t.data_ptr();
+      keys_[i].dst = nullptr;
+      int64_t per_row = 1;
+      for (int64_t d = 1; d < t.dim(); ++d) per_row *= t.size(d);
+      keys_[i].row_bytes = per_row * (int64_t)t.element_size();
+      KeyMeta m;
+      m.name = names[i];
+      m.tail.assign(t.sizes().begin() + 1, t.sizes().end());
+      m.dtype = t.scalar_type();
+      meta_.push_back(std::move(m));
+    }
+  }
+
+  // idx: int64 CUDA contiguous; lead: leading shape of the outputs (numel(lead) == idx.numel())
+  py::dict gather(const at::Tensor &idx, const std::vector<int64_t> &lead) {
+    py::dict out;
+    gather_into(out, idx.data_ptr<int64_t>(), idx.numel(), lead, c10::cuda::getCurrentCUDAStream(index_));
+    return out;
+  }
+
+  void gather_into(py::dict &out, const int64_t *idx, int64_t B, const std::vector<int64_t> &lead,
+                   c10::cuda::CUDAStream st) {
+    const auto dev = c10::Device(c10::kCUDA, index_);
+    std::vector<int64_t> shape;
+    for (size_t i = 0; i < keys_.size(); ++i) {
+      shape.assign(lead.begin(), lead.end());
+      shape.insert(shape.end(), meta_[i].tail.begin(), meta_[i].tail.end());
+      at::Tensor o = at::empty(shape, at::TensorOptions().dtype(meta_[i].dtype).device(dev));
+      keys_[i].dst = o.data_ptr();
+      out[py::str(meta_[i].name)] = o;
+    }
+    if (B > 0)
+      ok(g.gather(keys_.data(), (int)keys_.size(), idx, B, max_size_, err_.data_ptr<int>(), st.stream()),
+         "xp_gather");
+  }
+
+  c10::DeviceIndex index() const { return index_; }
+
+ private:
+  std::vector<at::Tensor> leaves_;
+  std::vector<xp_key> keys_;
+  std::vector<KeyMeta> meta_;
+  int64_t max_size_;
+  at::Tensor err_;
+  c10::DeviceIndex index_;
+};
+
+// ---- PrioritizedReplayBuffer.sample / update_priorities (replay_buffer.py:331-428) --------------
+class FastPer {
+ public:
+  FastPer(std::shared_ptr<FastGather> table, uint64_t tree_struct_addr, at::Tensor nodes,
+          at::Tensor aux, at::Tensor state, at::Tensor tree_err, int64_t max_size, double alpha)
+      : table_(std::move(table)), nodes_(std::move(nodes)), aux_(std::move(aux)),
+        state_(std::move(state)), tree_err_(std::move(tree_err)), max_size_(max_size), alpha_(alpha),
+        ring_(table_->index(), 32) {
+    std::memcpy(&tree_, reinterpret_cast<const void *>(tree_struct_addr), sizeof(xp_tree));
+  }
+
+  // sample(batch_size, beta) with the torch CPU generator's draws (u == None) or given fp32
+  // uniforms already on the device.  Returns {keys..., "weights" (B,1) f32, "idxs" (B,1) i64}.
+  py::dict sample(int64_t B, double beta, int64_t size, const c10::optional<at::Tensor> &u_dev) {
+    const auto index = table_->index();
+    const auto dev = c10::Device(c10::kCUDA, index);
+    auto st = c10::cuda::getCurrentCUDAStream(index);
+    const float *u = nullptr;
+    if (u_dev.has_value()) {
+      u = u_dev->data_ptr<float>();
+    } else {
+      // batch_size x torch.rand(1).item() == torch.rand(batch_size) == uniform_(0,1) on the
+      // default CPU generator (replay_buffer.py:377), drawn straight into pinned memory
+      Slot &s = ring_.acquire(B * 4);
+      at::Tensor hv = at::from_blob(s.hp, {B}, at::TensorOptions().dtype(at::kFloat));
+      hv.uniform_(0.0, 1.0);
+      ring_.push(s, B * 4, st);
+      u = reinterpret_cast<const float *>(s.dp);
+    }
+    at::Tensor idx = at::empty({B, 1}, at::TensorOptions().dtype(at::kLong).device(dev));
+    at::Tensor w = at::empty({B, 1}, at::TensorOptions().dtype(at::kFloat).device(dev));
+    ok(g.per_sample(&tree_, u, B, 1, size, beta, idx.data_ptr<int64_t>(), w.data_ptr<float>(), st.stream()),
+       "xp_per_sample");
+    py::dict out;
+    table_->gather_into(out, idx.data_ptr<int64_t>(), B, {B}, st);
+    out["weights"] = w;
+    out["idxs"] = idx;
+    return out;
+  }
+
+  // update_priorities(indices, priorities): idx int64 CUDA contiguous; prio fp32 contiguous on the
+  // host (staged through the pinned ring) or on the device.
+  void update(const at::Tensor &idx, const at::Tensor &prio) {
+    const auto index = table_->index();
+    auto st = c10::cuda::getCurrentCUDAStream(index);
+    const int64_t n = std::min<int64_t>(idx.numel(), prio.numel());
+    const float *p = nullptr;
+    if (prio.is_cuda()) {
+      p = prio.data_ptr<float>();
+    } else {
+      Slot &s = ring_.acquire(n * 4);
+      std::memcpy(s.hp, prio.data_ptr<float>(), (size_t)n * 4);
+      ring_.push(s, n * 4, st);
+      p = reinterpret_cast<const float *>(s.dp);
+    }
+    ok(g.per_update(&tree_, reinterpret_cast<xp_per_state *>(state_.data_ptr()), idx.data_ptr<int64_t>(), p, n,
+                    max_size_, alpha_, tree_err_.data_ptr<int>(), st.stream()),
+       "xp_per_update");
+  }
+
+ private:
+  std::shared_ptr<FastGather> table_;
+  xp_tree tree_;
+  at::Tensor nodes_, aux_, state_, tree_err_;  // keep the device memory behind tree_ alive
+  int64_t max_size_;
+  double alpha_;
+  Ring ring_;
+};
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.doc() = "native fast path of the agilerl_b200 Python host (calls libb200xp.so)";
+  m.def("bind", &bind);
+  py::class_<FastGather, std::shared_ptr<FastGather>>(m, "FastGather")
+      .def(py::init<std::vector<at::Tensor>, std::vector<std::string>, int64_t, at::Tensor>())
+      .def("gather", &FastGather::gather);
+  py::class_<FastPer>(m, "FastPer")
+      .def(py::init<std::shared_ptr<FastGather>, uint64_t, at::Tensor, at::Tensor, at::Tensor, at::Tensor,
+                    int64_t, double>())
+      .def("sample", &FastPer::sample)
+      .def("update", &FastPer::update);
+}

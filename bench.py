@@ -374,7 +374,11 @@ class C2Workload:
         g = torch.Generator().manual_seed(77)
         self.prio_host = [(torch.randn(n, generator=g).abs() + 1e-6).pin_memory().numpy()
                           for _ in range(self.P * 3)]
-        self.res_host = torch.empty(self.P * n, 3, dtype=torch.float32).pin_memory()
+        self.res_idx_dev = torch.empty(self.P * n, 1, dtype=torch.int64, device=self.dev)
+        self.res_w_dev = torch.empty(self.P * n, 1, dtype=torch.float32, device=self.dev)
+        self.res_idx_host = torch.empty(self.P * n, 1, dtype=torch.int64).pin_memory()
+        self.res_w_host = torch.empty(self.P * n, 1, dtype=torch.float32).pin_memory()
+        self.res_ev = torch.cuda.Event()
         torch.manual_seed(1234)
 
     def e2e_step(self, i):
@@ -387,9 +391,15 @@ class C2Workload:
             idxs.append(batch["idxs"])
             ws.append(batch["weights"])
             self.per.update_priorities(batch["idxs"], self.prio_host[(i * self.P + a) % len(self.prio_host)])
-        idx_h = torch.cat(idxs).cpu()                             # D2H: the step's result
-        w_h = torch.cat(ws).cpu()
-        return idx_h, w_h
+        # D2H: the step's result (sampled indices + IS weights of all agents) into pinned memory
+        n = self.P * self.B
+        torch.cat(idxs, out=self.res_idx_dev)
+        torch.cat(ws, out=self.res_w_dev)
+        self.res_idx_host.copy_(self.res_idx_dev, non_blocking=True)
+        self.res_w_host.copy_(self.res_w_dev, non_blocking=True)
+        self.res_ev.record()
+        self.res_ev.synchronize()
+        return self.res_idx_host, self.res_w_host
 
     def e2e_bytes(self):
         n = self.P * self.B
