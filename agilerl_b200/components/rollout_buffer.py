@@ -317,6 +317,149 @@ class RolloutBuffer:
                 np_dict[key] = value.cpu().numpy()
         return np_dict
 
+    # -- truncated-BPTT sequences (reference :627-922) ----------------------------------------------
+    @staticmethod
+    def _pad_sequences(sequences, target_length: int | None = None):
+        """Zero-pad a list of [len_i, ...] tensors (or batches of them) to [B, T, ...] (:627-675).
+        Host-level utility kept for API parity; ``prepare_sequence_tensors`` pads inside the row
+        gather instead."""
+        if isinstance(sequences[0], TensorBatch):
+            keys = list(sequences[0].keys())
+            return TensorBatch({k: RolloutBuffer._pad_sequences([s[k] for s in sequences], target_length)
+                                for k in keys})
+        if target_length is not None:
+            out = []
+            for seq in sequences:
+                pad = target_length - seq.size(0)
+                out.append(torch.nn.functional.pad(seq, [0, 0] * (seq.dim() - 1) + [0, pad]))
+            return torch.stack(out)
+        return torch.nn.utils.rnn.pad_sequence(sequences, batch_first=True, padding_value=0)
+
+    def _get_complete_sequences(self, data, episode_done_indices):
+        """Split ``data`` [T, num_envs, ...] into per-episode sequences (:677-722); API parity
+        helper over plain indexing (the batched path is ``xp_bptt_plan``)."""
+        msl = self.max_seq_len
+        sequences, max_length = [], 1
+        for env_idx in range(self.num_envs):
+            start = 0
+            for done_index in episode_done_indices[env_idx]:
+                episode = data[start:done_index + 1, env_idx]
+                n = len(episode)
+                if msl is not None and n >= msl:
+                    sequences.extend(_cut_episode(episode, msl, self.bptt_sequence_type))
+                else:
+                    sequences.append(episode)
+                max_length = max(max_length, n)
+                start = done_index + 1
+        return sequences, max_length
+
+    def prepare_sequence_tensors(self, device: str | None = None) -> None:
+        """All sequences of the buffer, zero-padded to a common length (:724-846): fills
+        ``padded_data`` (batch [num_sequences * max_sequence_length]: observations, actions,
+        [action_masks], pad_mask + non-tensor ``initial_hidden_states``), ``unpadded_data``
+        (log_probs, advantages, values, returns, flat t-major) and ``unpadded_slices``."""
+        if not self.recurrent:
+            raise ValueError("prepare_sequence_tensors() is only supported when recurrent=True.")
+        if self.size() == 0:
+            raise ValueError("Attempting to prepare sequences with empty buffer.")
+        target_device = device or self.device
+        buffer_size = self.capacity if self.full else self.pos
+        N = self.num_envs
+        msl = self.max_seq_len
+        kind = BPTTSequenceType(self.bptt_sequence_type).value
+        if msl is not None:
+            assert msl > 0, "max_seq_len must be greater than 0"
+            if kind == "fifty_percent_overlap" and msl == 1:
+                raise ValueError("range() arg 3 must not be zero")
+        flat = self._flat_views(buffer_size)
+        with nv.on_device(self._sdev):
+            desc, off, header = xp.bptt_plan(self._leaves[("dones",)], buffer_size, N, msl, kind)
+            # output shapes depend on the data: one small read-back (the reference's
+            # dones.nonzero().tolist() per env is the same dependency)
+            S, L, max_ep, total = (int(x) for x in header.cpu())
+            pad_idx, pad_mask, unp_idx, first = xp.bptt_indices(desc, off, S, L, N, total)
+            self._seq_desc = desc[:, :S].cpu().numpy()  # host copy (t0, env, len) for the minibatch plans
+            pad_paths = [p for p in flat if p[0] in ("observations", "actions")]
+            pad_paths += [p for p in flat if p[0] == "action_masks"]
+            n_rows = buffer_size * N
+            padded = OrderedDict((p, torch.empty((S * L, *flat[p].shape[1:]), dtype=flat[p].dtype,
+                                                 device=self._sdev)) for p in pad_paths)
+            xp.gather([(flat[p], padded[p]) for p in pad_paths], pad_idx, n_rows)  # -1 rows -> zeros
+            hid_paths = [p for p in flat if p[0] == "hidden_states"]
+            init = OrderedDict((p, torch.empty((S, *flat[p].shape[1:]), dtype=flat[p].dtype, device=self._sdev))
+                               for p in hid_paths)
+            if hid_paths:
+                xp.gather([(flat[p], init[p]) for p in hid_paths], first, n_rows)
+            unp = OrderedDict((p, flat[p].clone()) for p in
+                              (("log_probs",), ("advantages",), ("values",), ("returns",)))
+        padded[("pad_mask",)] = pad_mask
+        self.unpadded_slices = _LazySlices(self._seq_desc, N)
+        self.max_sequence_length = min(max_ep, msl) if msl is not None else max_ep
+        self.num_sequences = S
+        pd = self._to_target(_nest(padded, [S * L]), target_device)
+        if hid_paths:
+            pd.set_non_tensor("initial_hidden_states",
+                              OrderedDict((p[1], t.to(pd.device)) for p, t in init.items()))
+        self.padded_data = pd
+        self.unpadded_data = self._to_target(_nest(unp, [n_rows]), target_device)
+
+    def get_minibatch_sequences(self, batch_size: int):
+        """Yield (padded, unpadded) minibatches of whole sequences (:848-922); the sequence order
+        is ``torch.randperm(num_sequences)`` from torch's CPU generator, as in the reference."""
+        if self.unpadded_slices is None:
+            raise ValueError("Attempting to fetch minibatches before preparing sequences. "
+                             "Call prepare_sequence_tensors() first.")
+        S, L, N = self.num_sequences, self.max_sequence_length, self.num_envs
+        if batch_size > S:
+            warnings.warn(f"Batch size {batch_size} is larger than the number of sequences "
+                          f"({S}), using batch_size = {S}.", stacklevel=2)
+            batch_size = S
+        sequence_indices = torch.randperm(S)
+        sel_host = sequence_indices.numpy()
+        t0, env, ln = (self._seq_desc[i].astype(np.int64) for i in range(3))
+        pdata, udata = self.padded_data, self.unpadded_data
+        pdev = pdata.device if pdata.device is not None else self._sdev
+        on_dev = torch.device(pdev).type == "cuda"
+        p_leaves = OrderedDict(_flat(pdata))
+        u_leaves = OrderedDict(_flat(udata))
+        init = pdata.get_non_tensor("initial_hidden_states", None)
+        sel_dev = sequence_indices.to(pdev) if on_dev else sequence_indices
+        for start in range(0, S, batch_size):
+            end = min(start + batch_size, S)
+            sel = sel_host[start:end]
+            k = end - start
+            lens = ln[sel]
+            # flat (t * N + env) steps of the selected sequences, concatenated (:889-900)
+            first = np.repeat(t0[sel] * N + env[sel], lens)
+            within = np.arange(int(lens.sum())) - np.repeat(np.cumsum(lens) - lens, lens)
+            unp_idx = torch.from_numpy(first + within * N)
+            if on_dev:
+                with nv.on_device(self._sdev):
+                    sd = sel_dev[start:end]
+                    rows = OrderedDict((p, t.view(S, -1)) for p, t in p_leaves.items())
+                    out = OrderedDict((p, torch.empty((k * L, *t.shape[1:]), dtype=t.dtype, device=t.device))
+                                      for p, t in p_leaves.items())
+                    xp.gather([(rows[p], out[p].view(k, -1)) for p in rows], sd, S)
+                    padded = _nest(out, [k * L])
+                    if init is not None:
+                        hs = OrderedDict((h, torch.empty((k, *t.shape[1:]), dtype=t.dtype, device=t.device))
+                                         for h, t in init.items())
+                        xp.gather([(init[h], hs[h]) for h in init], sd, S)
+                        padded.set_non_tensor("initial_hidden_states", dict(hs))
+                    ui = unp_idx.to(self._sdev, non_blocking=True)
+                    uo = OrderedDict((p, torch.empty((ui.numel(), *t.shape[1:]), dtype=t.dtype, device=t.device))
+                                     for p, t in u_leaves.items())
+                    xp.gather([(u_leaves[p], uo[p]) for p in u_leaves], ui, next(iter(u_leaves.values())).shape[0])
+                    unpadded = _nest(uo, [ui.numel()])
+            else:  # data was requested on the host: plain indexing of the host copies
+                sq = sequence_indices[start:end]
+                pidx = (sq.view(-1, 1) * L + torch.arange(L)).view(-1)
+                padded = pdata[pidx]
+                if init is not None:
+                    padded.set_non_tensor("initial_hidden_states", {h: t[sq].clone() for h, t in init.items()})
+                unpadded = udata[unp_idx]
+            yield padded, unpadded
+
     # -- pickling (reference :924-970; clone() deep-copies the buffer) ------------------------------
     def __getstate__(self) -> dict[str, Any]:
         state = self.__dict__.copy()
@@ -331,6 +474,42 @@ class RolloutBuffer:
         self._sdev = nv.require_cuda(state.get("_sdev"))
         self._leaves = OrderedDict((p, t.to(self._sdev)) for p, t in state["_leaves"].items())
         self.buffer = _nest(self._leaves, [self.capacity, self.num_envs])
+
+
+def _cut_episode(episode, max_seq_len: int, sequence_type):
+    """extract_sequences_from_episode (utils/algo_utils.py:214-265) on one episode."""
+    n = len(episode)
+    assert max_seq_len > 0, "max_seq_len must be greater than 0"
+    assert n > 0, "episode must be non-empty"
+    assert max_seq_len <= n, "max_seq_len must be less than or equal to the length of the episode"
+    kind = BPTTSequenceType(sequence_type)
+    if kind == BPTTSequenceType.CHUNKED:
+        starts = range(0, max(1, n // max_seq_len) * max_seq_len, max_seq_len)
+    elif kind == BPTTSequenceType.MAXIMUM:
+        starts = range(n - max_seq_len + 1)
+    else:
+        starts = range(0, n - max_seq_len + 1, max_seq_len // 2)
+    return [episode[s:s + max_seq_len] for s in starts]
+
+
+class _LazySlices:
+    """``unpadded_slices`` (:752-762): per sequence, the flat ``t * num_envs + env`` indices of its
+    steps — materialised on demand from the (t0, env, len) descriptors."""
+
+    def __init__(self, desc: np.ndarray, num_envs: int) -> None:
+        self._d, self._n = desc, num_envs
+
+    def __len__(self) -> int:
+        return self._d.shape[1]
+
+    def __getitem__(self, i: int) -> torch.Tensor:
+        if not -len(self) <= i < len(self):
+            raise IndexError(i)
+        t0, env, ln = (int(x) for x in self._d[:, i])
+        return torch.arange(t0, t0 + ln) * self._n + env
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
 
 
 def pairs_as_rows(pairs):

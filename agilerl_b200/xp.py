@@ -196,3 +196,40 @@ def gae(rewards, values, dones, last_value, last_done, adv, ret, T: int, N: int,
         check(lib.xp_mc_returns(rewards.data_ptr(), values.data_ptr(), dones.data_ptr(),
                                 last_value.data_ptr(), last_done.data_ptr(), adv.data_ptr(),
                                 ret.data_ptr(), T, N, P, agent_stride, gamma, s), "xp_mc_returns")
+
+
+# ---- truncated-BPTT sequence preparation ------------------------------------------------------------
+BPTT_TYPES = {"chunked": 0, "maximum": 1, "fifty_percent_overlap": 2}
+
+
+def bptt_plan(dones: torch.Tensor, T: int, N: int, max_seq_len: int | None, seq_type: str):
+    """Cut the first ``T`` stored steps of ``dones`` [>=T, N] (CUDA bool/uint8) into sequences.
+    Returns (desc int32 [3, T*N] = rows t0/env/len, seq_off int64 [T*N], header int64 [4] =
+    {num_sequences, longest sequence, longest episode, total unpadded steps}) — all on device."""
+    if dones.dtype not in (torch.bool, torch.uint8) or not dones.is_cuda or not dones.is_contiguous():
+        raise TypeError("dones must be a contiguous CUDA bool/uint8 tensor")
+    dev = dones.device
+    n = T * N
+    desc = torch.empty((3, n), dtype=torch.int32, device=dev)
+    off = torch.empty(n, dtype=torch.int64, device=dev)
+    scratch = torch.empty(2 * N + 2, dtype=torch.int32, device=dev)
+    header = torch.empty(4, dtype=torch.int64, device=dev)
+    check(nv.load().xp_bptt_plan(dones.data_ptr(), T, N, int(max_seq_len or 0), BPTT_TYPES[seq_type],
+                                 scratch.data_ptr(), desc[0].data_ptr(), desc[1].data_ptr(),
+                                 desc[2].data_ptr(), off.data_ptr(), header.data_ptr(), _stream(dones)),
+          "xp_bptt_plan")
+    return desc, off, header
+
+
+def bptt_indices(desc: torch.Tensor, off: torch.Tensor, num_seq: int, pad_len: int, N: int, total: int):
+    """(pad_idx int64 [S*L] with -1 padding, pad_mask bool [S*L], unp_idx int64 [total],
+    first_idx int64 [S]) for the sequences described by ``bptt_plan``."""
+    dev = desc.device
+    pad_idx = torch.empty(num_seq * pad_len, dtype=torch.int64, device=dev)
+    pad_mask = torch.empty(num_seq * pad_len, dtype=torch.bool, device=dev)
+    unp_idx = torch.empty(total, dtype=torch.int64, device=dev)
+    first = torch.empty(num_seq, dtype=torch.int64, device=dev)
+    check(nv.load().xp_bptt_indices(desc[0].data_ptr(), desc[1].data_ptr(), desc[2].data_ptr(), off.data_ptr(),
+                                    num_seq, pad_len, N, pad_idx.data_ptr(), pad_mask.data_ptr(),
+                                    unp_idx.data_ptr(), first.data_ptr(), _stream(desc)), "xp_bptt_indices")
+    return pad_idx, pad_mask, unp_idx, first

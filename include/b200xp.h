@@ -184,6 +184,36 @@ xp_status_t xp_mc_returns(const float *rewards, const float *values, const uint8
                           float *ret, int64_t T, int64_t N, int64_t P, int64_t agent_stride,
                           double gamma, void *stream);
 
+/* ---- truncated-BPTT sequence preparation (RolloutBuffer.prepare_sequence_tensors) ------ */
+/* replaces the per-env Python walk of rollout_buffer.py:736-762 + _get_complete_sequences
+ * (:677-722) + extract_sequences_from_episode (utils/algo_utils.py:214-265).
+ * dones u8 [T][N] (the first T = buffer_size stored steps).  An episode ends where a done flag
+ * is set and at step T-1.  An episode of len >= max_seq_len (max_seq_len > 0) is cut into
+ * sequences of max_seq_len steps: CHUNKED max(1, len / max_seq_len) non-overlapping chunks (the
+ * remainder is dropped, as in the reference), MAXIMUM every window, FIFTY_PERCENT_OVERLAP windows
+ * every max_seq_len / 2 steps; shorter episodes (or max_seq_len == 0, "None") are one sequence.
+ * Sequences are numbered env-major, then by start step.  Outputs (device):
+ *   seq_t0/seq_env/seq_len int32[>= T*N], seq_off int64[>= T*N] (offset of the sequence in the
+ *   concatenated unpadded step list), header int64[4] = {num_sequences, longest sequence,
+ *   longest episode, total unpadded steps}; env_scratch int32[2N + 2].                          */
+#define XP_BPTT_CHUNKED 0
+#define XP_BPTT_MAXIMUM 1
+#define XP_BPTT_FIFTY_PERCENT_OVERLAP 2
+xp_status_t xp_bptt_plan(const uint8_t *dones_dev, int64_t T, int64_t N, int64_t max_seq_len,
+                         int seq_type, int32_t *env_scratch_dev, int32_t *seq_t0_dev,
+                         int32_t *seq_env_dev, int32_t *seq_len_dev, int64_t *seq_off_dev,
+                         int64_t *header_dev, void *stream);
+/* The padded layout as row indices for xp_gather (replaces _pad_sequences, :627-675):
+ *   pad_idx int64[num_seq][pad_len] = flat step t*N + env, or -1 where the sequence is shorter
+ *   (xp_gather writes zero rows for negative indices == the reference's zero padding);
+ *   pad_mask u8 same shape (:767-770); unp_idx int64[total unpadded steps] = the concatenated
+ *   `unpadded_slices` (:752-762); first_idx int64[num_seq] (may be NULL) = first step of every
+ *   sequence (initial hidden states, :818-826).                                              */
+xp_status_t xp_bptt_indices(const int32_t *seq_t0_dev, const int32_t *seq_env_dev,
+                            const int32_t *seq_len_dev, const int64_t *seq_off_dev, int64_t num_seq,
+                            int64_t pad_len, int64_t N, int64_t *pad_idx_dev, uint8_t *pad_mask_dev,
+                            int64_t *unp_idx_dev, int64_t *first_idx_dev, void *stream);
+
 /* ---- host-side RNG mirror (no GPU needed) -------------------------------------------- */
 /* torch's CPU generator is mt19937; these reproduce the raw 32-bit stream so that the
  * engine consumes "identical uniform draws" (replay_buffer.py:125,377).

@@ -132,8 +132,29 @@ def gen_rng():
     save("torch_rng", **rec)
 
 
+def gen_bptt():
+    """Sequence cutting + padding by the extracted reference functions (ref_loader.reference_bptt)."""
+    cases = [(0, 12, 3, None, "chunked", 0.2), (1, 12, 3, 3, "chunked", 0.2), (2, 12, 3, 3, "maximum", 0.2),
+             (3, 16, 4, 4, "fifty_percent_overlap", 0.15), (4, 40, 7, 5, "chunked", 0.05),
+             (5, 40, 7, 8, "maximum", 0.0), (6, 33, 5, 1, "chunked", 0.3), (7, 9, 2, 20, "chunked", 0.1),
+             (8, 64, 33, 6, "fifty_percent_overlap", 0.08)]
+    for seed, T, N, msl, tp, pd in cases:
+        g = torch.Generator().manual_seed(100 + seed)
+        d = (torch.rand(T, N, generator=g) < pd).numpy()
+        x = torch.randn(T, N, 3, generator=g).numpy()
+        slices, padded, mask, L, S = ref_loader.reference_bptt(d, x, msl, tp)
+        save(f"bptt_s{seed}", dones=d, data=x, max_seq_len=np.array(-1 if msl is None else msl),
+             seq_type=np.array(tp), unpadded=np.concatenate(slices),
+             lengths=np.array([len(s) for s in slices]), padded=padded, pad_mask=mask,
+             max_sequence_length=np.array(L), num_sequences=np.array(S))
+
+
 if __name__ == "__main__":
+    if sys.argv[1:] == ["bptt"]:
+        gen_bptt()
+        sys.exit(0)
     gen_gae()
     gen_per()
     gen_ring_nstep()
     gen_rng()
+    gen_bptt()

@@ -209,3 +209,73 @@ def reference_gae(rewards, values, dones, last_value, last_done, gamma, gae_lamb
     )
     f(self_like, last_value, last_done)
     return self_like.buffer["advantages"].numpy().copy(), self_like.buffer["returns"].numpy().copy()
+
+
+def _extract(path: str, names: list[str], cls: str | None = None) -> dict[str, str]:
+    """Source text of top-level defs/classes (or methods of ``cls``) called ``names``."""
+    src = open(path).read()
+    tree = ast.parse(src)
+    out = {}
+    body = tree.body
+    if cls is not None:
+        body = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == cls).body
+    for node in body:
+        if isinstance(node, (ast.FunctionDef, ast.ClassDef)) and node.name in names:
+            out[node.name] = textwrap.dedent(ast.get_source_segment(src, node))
+    missing = set(names) - set(out)
+    assert not missing, f"not found in {path}: {missing}"
+    return out
+
+
+def load_reference_bptt():
+    """The UNMODIFIED sequence-cutting code of the reference, extracted by name:
+    ``BPTTSequenceType`` (agilerl/typing.py:160), ``extract_sequences_from_episode``
+    (utils/algo_utils.py:214-265), ``RolloutBuffer._get_complete_sequences`` (:677-722) and the
+    tensor branch of ``RolloutBuffer._pad_sequences`` (:627-675).  Returns a namespace."""
+    if "bptt" in _cache:
+        return _cache["bptt"]
+    import enum
+
+    g = {"np": np, "torch": torch, "Enum": enum.Enum, "TensorDict": dict,
+         "is_tensor_collection": lambda x: False}
+    exec(_extract(os.path.join(REF_PKG, "typing.py"), ["BPTTSequenceType"])["BPTTSequenceType"], g)
+    exec(_extract(os.path.join(REF_PKG, "utils", "algo_utils.py"),
+                  ["extract_sequences_from_episode"])["extract_sequences_from_episode"], g)
+    m = _extract(os.path.join(REF_PKG, "components", "rollout_buffer.py"),
+                 ["_get_complete_sequences", "_pad_sequences"], cls="RolloutBuffer")
+    exec(m["_get_complete_sequences"], g)
+    exec(m["_pad_sequences"].replace("@staticmethod", ""), g)
+    g["RolloutBuffer"] = types.SimpleNamespace(_pad_sequences=g["_pad_sequences"])
+    _cache["bptt"] = types.SimpleNamespace(**{k: g[k] for k in (
+        "BPTTSequenceType", "extract_sequences_from_episode", "_get_complete_sequences", "_pad_sequences")})
+    return _cache["bptt"]
+
+
+def reference_bptt(dones, data, max_seq_len, seq_type: str):
+    """Drive the extracted reference functions the way prepare_sequence_tensors does
+    (rollout_buffer.py:736-800) on ``dones`` bool [T,N] and ONE data field ``data`` [T,N,...].
+    Returns (unpadded_slices list[np.ndarray], padded np [S,L,...], pad_mask np [S,L],
+    max_sequence_length, num_sequences)."""
+    ns = load_reference_bptt()
+    T, N = dones.shape
+    d = torch.from_numpy(np.ascontiguousarray(dones))
+    self_like = types.SimpleNamespace(num_envs=N, max_seq_len=max_seq_len,
+                                      bptt_sequence_type=ns.BPTTSequenceType(seq_type))
+    # the done-index loop of prepare_sequence_tensors (:738-750), statement for statement
+    episode_done_indices = []
+    for env_idx in range(N):
+        env_dones = d[:, env_idx]
+        lst = env_dones.nonzero().squeeze(-1).tolist()
+        episode_done_indices.append(lst)
+        if len(episode_done_indices[env_idx]) == 0 or episode_done_indices[env_idx][-1] != T - 1:
+            episode_done_indices[env_idx].append(T - 1)
+    flat = torch.arange(T * N).reshape(T, N)
+    slices, _ = ns._get_complete_sequences(self_like, flat, episode_done_indices)
+    x = torch.from_numpy(np.ascontiguousarray(data))
+    seqs, max_len = ns._get_complete_sequences(self_like, x, episode_done_indices)
+    padded = ns._pad_sequences(seqs, target_length=None)
+    ones = torch.ones(T, N, dtype=torch.bool)
+    mseqs, _ = ns._get_complete_sequences(self_like, ones, episode_done_indices)
+    mask = ns._pad_sequences(mseqs, target_length=None)
+    msl = min(max_len, max_seq_len) if max_seq_len is not None else max_len
+    return [s.numpy().copy() for s in slices], padded.numpy(), mask.numpy(), int(msl), len(seqs)

@@ -285,3 +285,63 @@ def gae_scalar(rewards, values, dones, last_value, last_done, gamma: float, gae_
 def pow_cpython(x: float, y: float) -> float:
     """float ** float in CPython = libm pow (replay_buffer.py:322,401,406)."""
     return math.pow(x, y)
+
+
+# =================================================================================================
+# truncated-BPTT sequence preparation — rollout_buffer.py:627-800, utils/algo_utils.py:214-265
+# =================================================================================================
+def bptt_sequences(dones, max_seq_len, seq_type: str = "chunked"):
+    """dones bool [T,N] -> ([(env, t0, len), ...] in reference order, longest episode).
+
+    Episodes end at every done flag and at the last stored step (:738-750); an episode of
+    len >= max_seq_len is cut by extract_sequences_from_episode (algo_utils.py:243-259), shorter
+    ones (or max_seq_len None) are one sequence (:696-712)."""
+    dones = np.asarray(dones).astype(bool)
+    T, N = dones.shape
+    seqs, max_ep = [], 1
+    for env in range(N):
+        ends = np.nonzero(dones[:, env])[0].tolist()
+        if not ends or ends[-1] != T - 1:
+            ends.append(T - 1)
+        start = 0
+        for e in ends:
+            n = e - start + 1
+            if max_seq_len is not None and n >= max_seq_len:
+                if seq_type == "chunked":
+                    for c in range(max(1, n // max_seq_len)):
+                        seqs.append((env, start + c * max_seq_len, max_seq_len))
+                elif seq_type == "maximum":
+                    for s in range(n - max_seq_len + 1):
+                        seqs.append((env, start + s, max_seq_len))
+                elif seq_type == "fifty_percent_overlap":
+                    for s in range(0, n - max_seq_len + 1, max_seq_len // 2):  # step 0 -> ValueError
+                        seqs.append((env, start + s, max_seq_len))
+                else:
+                    raise NotImplementedError(seq_type)
+            else:
+                seqs.append((env, start, n))
+            max_ep = max(max_ep, n)
+            start = e + 1
+    return seqs, max_ep
+
+
+def bptt_prepare(dones, fields: dict, max_seq_len, seq_type: str = "chunked"):
+    """prepare_sequence_tensors (:724-846) on numpy arrays: ``fields`` name -> [T,N,...].
+    Returns dict(num_sequences, max_sequence_length, unpadded_slices (list of flat t*N+env index
+    arrays), pad_mask [S,L], padded {name: [S,L,...]}, first_idx [S])."""
+    dones = np.asarray(dones)
+    T, N = dones.shape
+    seqs, max_ep = bptt_sequences(dones, max_seq_len, seq_type)
+    S = len(seqs)
+    L = max(n for _, _, n in seqs)  # pad_sequence pads to the longest sequence (:669-675)
+    slices = [(np.arange(t0, t0 + n) * N + env).astype(np.int64) for env, t0, n in seqs]
+    mask = np.zeros((S, L), dtype=bool)
+    padded = {k: np.zeros((S, L, *np.asarray(v).shape[2:]), dtype=np.asarray(v).dtype) for k, v in fields.items()}
+    for s, (env, t0, n) in enumerate(seqs):
+        mask[s, :n] = True
+        for k, v in fields.items():
+            padded[k][s, :n] = np.asarray(v)[t0:t0 + n, env]
+    msl = min(max_ep, max_seq_len) if max_seq_len is not None else max_ep  # :806-810
+    return {"num_sequences": S, "max_sequence_length": int(msl), "unpadded_slices": slices,
+            "pad_mask": mask, "padded": padded,
+            "first_idx": np.array([t0 * N + env for env, t0, _ in seqs], dtype=np.int64)}

@@ -471,3 +471,131 @@ def test_per_update_device_indices_error_is_deferred_not_lost(C):
         b.check_errors()
     b.update_priorities(torch.tensor([1, 2], device="cuda:0"), torch.tensor([1.0, 2.0]))
     b.check_errors()
+
+
+# ---- truncated-BPTT sequences (reference test_rollout_buffer.py:924-1830) ---------------------------
+def _recurrent_buffer(C, T, N, msl, kind="chunked", obs_dim=3, dones=None, seed=0, device="cuda"):
+    from agilerl_b200.components import spaces
+    from agilerl_b200.components.rollout_buffer import BPTTSequenceType
+
+    g = torch.Generator().manual_seed(seed)
+    b = C.RolloutBuffer(capacity=T, observation_space=spaces.Box(-1, 1, (obs_dim,), np.float32),
+                        action_space=spaces.Discrete(2), num_envs=N, device=device, recurrent=True,
+                        hidden_state_architecture={"h_actor": (1, N, 4), "h_critic": (2, N, 8)},
+                        max_seq_len=msl, bptt_sequence_type=BPTTSequenceType(kind))
+    data = torch.randn(T, N, obs_dim, generator=g)
+    hid = {"h_actor": torch.randn(T, 1, N, 4, generator=g), "h_critic": torch.randn(T, 2, N, 8, generator=g)}
+    for t in range(T):
+        b.add(data[t].numpy(), np.arange(N) % 2, np.ones(N) * t, dones[t], np.full(N, 0.5), np.full(N, 0.1),
+              hidden_state={k: v[t] for k, v in hid.items()})
+    b.compute_returns_and_advantages(np.zeros(N), np.ones(N))
+    return b, data.numpy(), hid
+
+
+@pytest.mark.parametrize("seed", range(9))
+def test_bptt_prepare_matches_reference_golden(C, seed):
+    z = load_golden(f"bptt_s{seed}")
+    msl = int(z["max_seq_len"])
+    msl = None if msl < 0 else msl
+    dones = z["dones"]
+    T, N = dones.shape
+    b, _, hid = _recurrent_buffer(C, T, N, msl, str(z["seq_type"]), obs_dim=3, dones=dones, seed=seed)
+    # overwrite the observations with the golden data field so that `padded` is comparable
+    b._leaves[("observations",)].copy_(torch.from_numpy(z["data"]))
+    b.prepare_sequence_tensors()
+    S, L = int(z["num_sequences"]), z["padded"].shape[1]
+    assert b.num_sequences == S and b.max_sequence_length == int(z["max_sequence_length"])
+    pd = b.padded_data
+    assert pd.batch_size == torch.Size([S * L])
+    assert np.array_equal(pd["observations"].cpu().numpy().reshape(S, L, 3), z["padded"])
+    assert np.array_equal(pd["pad_mask"].cpu().numpy().reshape(S, L), z["pad_mask"])
+    assert pd["pad_mask"].dtype == torch.bool
+    assert np.array_equal(np.concatenate([s.numpy() for s in b.unpadded_slices]), z["unpadded"])
+    assert [len(s) for s in b.unpadded_slices] == z["lengths"].tolist()
+    # initial hidden states = hidden state stored at the first step of every sequence (:818-826)
+    first = np.array([int(s[0]) for s in b.unpadded_slices])
+    init = pd.get_non_tensor("initial_hidden_states")
+    for k, v in hid.items():
+        flat = v.permute(0, 2, 1, 3).reshape(T * N, v.shape[1], v.shape[3]).numpy()
+        assert np.array_equal(init[k].cpu().numpy(), flat[first]), k
+    assert "hidden_states" not in pd
+    for k in ("log_probs", "advantages", "values", "returns"):
+        assert torch.equal(b.unpadded_data[k], b._leaves[(k,)][:T].reshape(-1))
+
+
+@pytest.mark.parametrize("kind,msl", [("chunked", 5), ("maximum", 7), ("fifty_percent_overlap", 6), ("chunked", None)])
+def test_bptt_prepare_matches_oracle_large(C, kind, msl):
+    T, N = 257, 130
+    g = torch.Generator().manual_seed(11)
+    dones = (torch.rand(T, N, generator=g) < 0.03).numpy()
+    b, data, _ = _recurrent_buffer(C, T, N, msl, kind, dones=dones, seed=4)
+    b.prepare_sequence_tensors()
+    r = xo.bptt_prepare(dones, {"observations": data}, msl, kind)
+    S = r["num_sequences"]
+    L = r["pad_mask"].shape[1]
+    assert b.num_sequences == S and b.max_sequence_length == r["max_sequence_length"]
+    assert np.array_equal(b.padded_data["observations"].cpu().numpy().reshape(S, L, -1), r["padded"]["observations"])
+    assert np.array_equal(b.padded_data["pad_mask"].cpu().numpy().reshape(S, L), r["pad_mask"])
+    assert all(np.array_equal(a.numpy(), e) for a, e in zip(b.unpadded_slices, r["unpadded_slices"]))
+
+
+def test_bptt_minibatches_cover_every_sequence_once(C):
+    # :1065-1147, :1722-1775 — whole sequences, shuffled by torch.randperm on the CPU generator
+    T, N, msl = 40, 6, 4
+    g = torch.Generator().manual_seed(2)
+    dones = (torch.rand(T, N, generator=g) < 0.1).numpy()
+    b, data, hid = _recurrent_buffer(C, T, N, msl, "chunked", dones=dones, seed=1)
+    b.prepare_sequence_tensors()
+    S, L = b.num_sequences, b.max_sequence_length
+    torch.manual_seed(77)
+    order = torch.randperm(S)
+    torch.manual_seed(77)
+    seen, n_unp = [], 0
+    init_all = b.padded_data.get_non_tensor("initial_hidden_states")
+    for i, (padded, unpadded) in enumerate(b.get_minibatch_sequences(5)):
+        sel = order[i * 5:(i + 1) * 5]
+        k = len(sel)
+        assert padded.batch_size == torch.Size([k * L])
+        rows = (sel.view(-1, 1) * L + torch.arange(L)).view(-1).cuda()
+        assert torch.equal(padded["observations"], b.padded_data["observations"][rows])
+        assert torch.equal(padded["pad_mask"], b.padded_data["pad_mask"][rows])
+        ih = padded.get_non_tensor("initial_hidden_states")
+        assert torch.equal(ih["h_critic"], init_all["h_critic"][sel.cuda()])
+        uidx = torch.cat([b.unpadded_slices[int(s)] for s in sel]).cuda()
+        for key in ("log_probs", "advantages", "values", "returns"):
+            assert torch.equal(unpadded[key], b.unpadded_data[key][uidx])
+        assert int(padded["pad_mask"].sum()) == uidx.numel()
+        seen += sel.tolist()
+        n_unp += uidx.numel()
+    assert sorted(seen) == list(range(S))
+    with pytest.warns(UserWarning):
+        assert len(list(b.get_minibatch_sequences(10 * S))) == 1
+
+
+def test_bptt_errors_and_helpers(C):
+    from agilerl_b200.components import spaces
+
+    nb = C.RolloutBuffer(capacity=4, observation_space=spaces.Box(-1, 1, (2,), np.float32),
+                         action_space=spaces.Discrete(2), num_envs=1, device="cuda")
+    with pytest.raises(ValueError):
+        nb.prepare_sequence_tensors()  # recurrent=False (:737-741)
+    dones = np.zeros((6, 2), dtype=bool)
+    b, _, _ = _recurrent_buffer(C, 6, 2, 3, dones=dones)
+    with pytest.raises(ValueError):
+        list(b.get_minibatch_sequences(2))  # before preparation (:1149-1168)
+    b.reset()
+    with pytest.raises(ValueError):
+        b.prepare_sequence_tensors()  # empty buffer
+    # _pad_sequences (:1170-1216)
+    seqs = [torch.tensor([[1, 2], [3, 4]]), torch.tensor([[5, 6], [7, 8], [9, 10]]), torch.tensor([[11, 12]])]
+    assert C.RolloutBuffer._pad_sequences(seqs).shape == (3, 3, 2)
+    assert C.RolloutBuffer._pad_sequences(seqs, target_length=5).shape == (3, 5, 2)
+    # _get_complete_sequences (:1512-1558)
+    out, mx = b._get_complete_sequences(torch.arange(20).reshape(10, 2), [[3, 7, 9], [4, 9]])
+    assert mx == 5 and [len(s) for s in out] == [3, 3, 2, 3, 3]
+    # host-side data on request (:1466-1507)
+    b2, _, _ = _recurrent_buffer(C, 6, 2, 3, dones=dones)
+    b2.prepare_sequence_tensors(device="cpu")
+    assert b2.padded_data["observations"].device.type == "cpu"
+    p, u = next(iter(b2.get_minibatch_sequences(2)))
+    assert p["observations"].device.type == "cpu" and u["returns"].device.type == "cpu"

@@ -203,3 +203,31 @@ def test_randperm_prefix_is_torch_randperm():
     for k, (seed, n, B) in enumerate(g["cases"]):
         raw = xo.mt19937_raw(int(seed), int(B))
         assert np.array_equal(xo.randperm_prefix(raw, int(B), int(n)), g[f"perm_{k}"]), (seed, n, B)
+
+
+# ---- truncated-BPTT sequence preparation ---------------------------------------------------------
+@pytest.mark.parametrize("seed", range(9))
+def test_bptt_oracle_matches_reference_golden(seed):
+    z = load_golden(f"bptt_s{seed}")
+    msl = int(z["max_seq_len"])
+    msl = None if msl < 0 else msl
+    r = xo.bptt_prepare(z["dones"], {"x": z["data"]}, msl, str(z["seq_type"]))
+    assert r["num_sequences"] == int(z["num_sequences"])
+    assert r["max_sequence_length"] == int(z["max_sequence_length"])
+    assert np.array_equal(np.concatenate(r["unpadded_slices"]), z["unpadded"])
+    assert np.array_equal(np.array([len(s) for s in r["unpadded_slices"]]), z["lengths"])
+    assert np.array_equal(r["pad_mask"], z["pad_mask"])
+    assert np.array_equal(r["padded"]["x"], z["padded"])
+
+
+def test_bptt_reference_kats():
+    # tests/test_components/test_rollout_buffer.py:1218-1270: one 12-step episode, max_seq_len 4
+    d = np.zeros((12, 1), dtype=bool)
+    d[11] = True
+    assert len(xo.bptt_sequences(d, 4, "chunked")[0]) == 12 // 4
+    assert len(xo.bptt_sequences(d, 4, "maximum")[0]) == 12 - 4 + 1
+    # chunking drops the remainder of an episode (algo_utils.py:243-248)
+    d = np.zeros((10, 1), dtype=bool)
+    assert [s[1:] for s in xo.bptt_sequences(d, 4, "chunked")[0]] == [(0, 4), (4, 4)]
+    with pytest.raises(ValueError):
+        xo.bptt_sequences(d, 1, "fifty_percent_overlap")
