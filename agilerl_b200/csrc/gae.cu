@@ -172,13 +172,13 @@ __global__ void __launch_bounds__(kThreads, 4) gae_tile_kernel(const ScanParams 
 
 // ---- TMA-fed kernel (aligned shapes): see gae_tma.cuh -------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(32) gae_tma_kernel(const ScanParams p,
+__global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams p,
                                                      const __grid_constant__ gaetma::Maps maps) {
   using namespace gaetma;
   extern __shared__ __align__(128) unsigned char smem_tma[];
   Stage *stage = reinterpret_cast<Stage *>(smem_tma);
   __shared__ __align__(8) unsigned long long bars[kStages];
-  const int lane = threadIdx.x;
+  const int lane = threadIdx.x;  // env within the 64-wide box
   const int tiles_per_agent = (int)((p.N + kBoxE - 1) / kBoxE);
   const int agent = blockIdx.x / tiles_per_agent;
   const int env0 = (blockIdx.x - agent * tiles_per_agent) * kBoxE;
@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(32) gae_tma_kernel(const ScanParams p,
     for (int s = 0; s < kStages; ++s) mbar_init(&bars[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncwarp();
+  __syncthreads();
   auto issue = [&](int b) {  // lane 0 only
     Stage &st = stage[b % kStages];
     unsigned long long *bar = &bars[b % kStages];
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(32) gae_tma_kernel(const ScanParams p,
       }
     }
     fence_proxy_async();  // generic-proxy writes above -> visible to the TMA store
-    __syncwarp();
+    __syncthreads();      // both warps are done with the box
     if (lane == 0) {
       tma_store_3d(&maps.adv, env0, t0, agent, &st.r[0][0]);
       tma_store_3d(&maps.ret, env0, t0, agent, &st.v[0][0]);
@@ -288,9 +288,10 @@ __global__ void __launch_bounds__(32) gae_tma_kernel(const ScanParams p,
         issue(b - 1 + kStages);
       }
     }
-    __syncwarp();
   }
-  if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  // the CTA may retire once the stores have READ shared memory; their global writes complete on
+  // their own (kernel completion orders them)
+  if (lane == 0) tma_wait_read<0>();
 }
 
 // cuTensorMapEncodeTiled through the runtime (no -lcuda): rank-3 maps {env, t, agent}.
@@ -363,7 +364,8 @@ bool encode_map_uncached(CUtensorMap *m, const void *base, int elem_bytes, const
 template <int MODE>
 xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   if (p.T == 0 || p.N == 0 || p.P == 0) return XP_OK;
-  const long long grid = ((p.N + kEnv - 1) / kEnv) * p.P;
+  const long long grid = ((p.N + kEnv - 1) / kEnv) * p.P;  // tile kernel
+  const long long grid_tma = ((p.N + gaetma::kBoxE - 1) / gaetma::kBoxE) * p.P;
   XP_REQUIRE(grid < (1ll << 31), XP_ERR_INVALID, "xp_gae: grid too large");
   const long long astride = p.P == 1 ? p.T * p.N : p.agent_stride;
   auto al16 = [](const void *q) { return reinterpret_cast<uintptr_t>(q) % 16 == 0; };
@@ -376,7 +378,20 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
     if (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
         encode_map(&maps.d, p.dones, 1, p) && encode_map(&maps.adv, p.adv, 4, p) &&
         encode_map(&maps.ret, p.ret, 4, p)) {
-      gae_tma_kernel<MODE><<<(unsigned)grid, 32, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps);
+      static bool tma_attr[2] = {false, false};
+      if (!tma_attr[MODE]) {
+        cudaError_t e = cudaFuncSetAttribute((const void *)gae_tma_kernel<MODE>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)(sizeof(gaetma::Stage) * gaetma::kStages));
+        if (e != cudaSuccess) {
+          xp::set_error("xp_gae: %s", cudaGetErrorString(e));
+          return XP_ERR_CUDA;
+        }
+        tma_attr[MODE] = true;
+      }
+      // (programmatic dependent launch was measured and dropped: early-resident CTAs of the next
+      // launch slowed the running one, 11.5 vs 11.0 us at C3)
+      gae_tma_kernel<MODE><<<(unsigned)grid_tma, gaetma::kBoxE, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps);
       return xp::check_launch("xp_gae (tma)");
     }
   }

@@ -353,6 +353,7 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
 struct Buckets {
   int nb;          // number of bucket subtrees (power of two)
   int shift;       // leaves per bucket = 1 << shift
+  int top;         // height at which the sparse climb stops (<= shift); the dense rebuild starts there
   int *counts, *offsets, *cursors;
   u64 *items;
   double *vals;    // kSrcPrio only: leaf value per batch position (else NULL)
@@ -362,6 +363,7 @@ __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift
   Buckets b;
   b.nb = nb;
   b.shift = shift;
+  b.top = shift;
   b.counts = t.aux + 16;
   b.offsets = b.counts + nb;
   b.cursors = b.offsets + nb + 1;
@@ -480,7 +482,7 @@ __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, 
   if (use_half && n0 <= 16 && n1 <= 16) {
     const int half = lane >> 4, l = lane & 15;
     const int beg = half ? beg1 : beg0, n = half ? n1 : n0;
-    warp_climb<PAIRED, 16>(t, s, l < n ? __ldcg(&bk.items[beg + l]) : kPad, bk.shift);
+    warp_climb<PAIRED, 16>(t, s, l < n ? __ldcg(&bk.items[beg + l]) : kPad, bk.top);
     return;
   }
 #pragma unroll 1
@@ -489,10 +491,10 @@ __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, 
     if (n == 0) continue;
     const u64 *items = bk.items + beg;
     if (n <= 32) {
-      warp_climb<PAIRED, 32>(t, s, lane < n ? __ldcg(&items[lane]) : kPad, bk.shift);
+      warp_climb<PAIRED, 32>(t, s, lane < n ? __ldcg(&items[lane]) : kPad, bk.top);
     } else {
       auto fetch = [&](long long i) -> u64 { return __ldcg(&items[i]); };
-      warp_climb_large<PAIRED>(t, s, fetch, n, bk.shift);
+      warp_climb_large<PAIRED>(t, s, fetch, n, bk.top);
     }
   }
 }
@@ -651,7 +653,14 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   const long long need = 16 + 3 * nb + 2 + (want_vals ? 4 : 2) * B;
   if (need <= t.cap) {  // schedule L
     const int shift = L - ilog2(nb);
-    const Buckets bk = make_buckets(t, (int)nb, shift, B, want_vals);
+    Buckets bk = make_buckets(t, (int)nb, shift, B, want_vals);
+    // The sparse climb costs ~2 scattered sector requests per item per level; a dense coalesced
+    // rebuild of everything above height `top` costs 32 B per node of that level.  Measured at
+    // cap 2^24, B 2^18: the two meet where the level holds ~2 B nodes (update 88 -> 83 us).
+    int top = L - ilog2(B) - 1;
+    if (top < 1) top = 1;
+    if (top > shift) top = shift;
+    bk.top = top;
     set_hist_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
     static bool scan_attr = false;
     {
@@ -666,7 +675,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     else
       set_wbucket_kernel<false><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk, use_half);
     launches = 4;
-    xp_status_t rc = launch_dense(t, shift, nb, 8, st, launches);
+    xp_status_t rc = launch_dense(t, bk.top, t.cap >> bk.top, bk.top == shift ? 8 : 10, st, launches);
     if (rc != XP_OK) return rc;
     return xp::check_launch("tree set (L)", launches);
   }

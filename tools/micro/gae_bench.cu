@@ -2,6 +2,7 @@
 // Standalone timing of the GAE launch (includes gae.cu directly).
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <vector>
 #include "../../agilerl_b200/csrc/core.cu"
 #include "../../agilerl_b200/csrc/gae.cu"
