@@ -485,6 +485,35 @@ def bench_per_tree(dev, reps=10):
             "l2": "tree 805 MB > L2; top levels L2-resident by design"}
 
 
+def ncu_traffic(kernel_substr: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of a kernel, from the newest
+    committed ``profiles/r*_ncu_*.txt`` summary that contains it (tools/ncu_summary.py output of an
+    ``ncu --set full`` capture); None when no capture is on disk."""
+    import glob
+    import re
+
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    root = os.path.dirname(os.path.abspath(__file__))
+    for path in sorted(glob.glob(os.path.join(root, "profiles", "r*_ncu_*.txt")), reverse=True):
+        cur, rd, wr = None, None, None
+        for ln in open(path, errors="replace"):
+            if ln.startswith("Kernel Name"):
+                if cur and rd is not None and wr is not None:
+                    break
+                cur, rd, wr = (kernel_substr in ln), None, None
+            elif cur:
+                m = re.match(r"dram__bytes_(read|write)\.sum\s+([0-9.]+)\s+(\w+)", ln)
+                if m:
+                    v = float(m.group(2)) * unit.get(m.group(3), 1.0)
+                    if m.group(1) == "read":
+                        rd = v
+                    else:
+                        wr = v
+        if cur and rd is not None and wr is not None:
+            return {"bytes": rd + wr, "source": os.path.relpath(path, root)}
+    return None
+
+
 def roofline(alg_bytes: float, us: float, traffic=None) -> dict:
     peak, how = hbm_peak()
     ach = alg_bytes / (us * 1e-6) / 1e9
@@ -613,10 +642,12 @@ def b200_arm(args):
             "e2e": e2e,
             "gpu_launches": int(l1 - l0),
             "clocks": clocks.summary(),
-            "roofline": dict(roofline(C2["P"] * C2["B"] * (2 * R_C2 + 8), gather_us),
+            "roofline": dict(roofline(C2["P"] * C2["B"] * (2 * R_C2 + 8), gather_us,
+                                      (ncu_traffic("move_kernel<0>") or {}).get("bytes")),
                              kernel="move_kernel<gather>", us_per_launch=round(gather_us, 2),
                              algorithmic_bytes_per_launch=C2["P"] * C2["B"] * (2 * R_C2 + 8),
-                             launches_timed=2 * K),
+                             launches_timed=2 * K,
+                             traffic_source=(ncu_traffic("move_kernel<0>") or {}).get("source")),
             "step_breakdown": breakdown,
             "cpu_baseline": cpu,
             "also": also,
@@ -755,6 +786,12 @@ def reference_arm(args):
 
 def main():
     args = parse_args()
+    # stdout carries exactly ONE JSON line: anything native libraries print there (NCCL's version
+    # banner, for one) is sent to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if args.impl == "reference":
         reference_arm(args)
     else:
