@@ -149,7 +149,86 @@ def gen_bptt():
              max_sequence_length=np.array(L), num_sequences=np.array(S))
 
 
+def marb_scenario(seed: int):
+    """Deterministic multi-agent scenario: (memory_size, fields, agents, list of save calls,
+    list of sample batch sizes).  Shared by the golden generator and the GPU parity test."""
+    rng = np.random.default_rng(1000 + seed)
+    agents = ["agent_0", "agent_1", "other"]
+    fields = ["state", "action", "reward", "next_state", "done"]
+    cap = [16, 40, 9][seed]
+    vect = seed == 1
+    n_env = 4
+    saves = []
+    for step in range([25, 14, 30][seed]):
+        def obs(a):
+            lead = (n_env,) if vect else ()
+            if a == "other" and seed != 1:
+                return {"img": rng.integers(0, 256, (*lead, 2, 3, 3)).astype(np.uint8),
+                        "vec": rng.standard_normal((*lead, 5)).astype(np.float32)}
+            if a == "agent_1" and seed == 2:
+                return (rng.standard_normal((*lead, 2)), rng.integers(0, 9, (*lead, 1)))
+            return rng.standard_normal((*lead, 4)).astype(np.float32)
+        state = {a: obs(a) for a in agents}
+        nstate = {a: obs(a) for a in agents}
+        if vect:
+            action = {a: rng.integers(0, 5, (n_env,)) for a in agents}
+            reward = {a: rng.standard_normal(n_env) for a in agents}
+            done = {a: rng.random(n_env) < 0.2 for a in agents}
+        else:
+            action = {a: int(rng.integers(0, 5)) if a != "other" else rng.standard_normal(2) for a in agents}
+            reward = {a: float(rng.standard_normal()) for a in agents}
+            done = {a: bool(rng.random() < 0.2) for a in agents}
+        saves.append(((state, action, reward, nstate, done), vect))
+    return cap, fields, agents, saves, [3, 7, 1, 8]
+
+
+def flatten_marb(sample, fields, agents):
+    out = {}
+    for f, per_agent in zip(fields, sample):
+        for a in agents:
+            v = per_agent[a]
+            if isinstance(v, dict):
+                for k, t in v.items():
+                    out[f"{f}|{a}|d:{k}"] = t
+            elif isinstance(v, tuple):
+                for i, t in enumerate(v):
+                    out[f"{f}|{a}|t:{i}"] = t
+            else:
+                out[f"{f}|{a}"] = v
+    return out
+
+
+def gen_marb():
+    """MultiAgentReplayBuffer: the unmodified reference class through save_to_memory / sample."""
+    import random
+
+    M = ref_loader.load_reference_marb()
+    for seed in range(3):
+        cap, fields, agents, saves, batches = marb_scenario(seed)
+        buf = M(cap, fields, agents, device="cpu")
+        arrays = {}
+        random.seed(500 + seed)
+        k = 0
+        for i, (args, vect) in enumerate(saves):
+            buf.save_to_memory(*args, is_vectorised=vect)
+            if i in (len(saves) // 3, len(saves) - 1):
+                for bs in batches:
+                    if bs <= len(buf):
+                        s = flatten_marb(buf.sample(bs), fields, agents)
+                        for name, t in s.items():
+                            assert t.dtype == torch.float32
+                            arrays[f"s{k}|{name}"] = t.numpy()
+                        k += 1
+        arrays["n_samples"] = np.array(k)
+        arrays["final_len"] = np.array(len(buf))
+        arrays["counter"] = np.array(buf.counter)
+        save(f"marb_s{seed}", **arrays)
+
+
 if __name__ == "__main__":
+    if sys.argv[1:] == ["marb"]:
+        gen_marb()
+        sys.exit(0)
     if sys.argv[1:] == ["bptt"]:
         gen_bptt()
         sys.exit(0)
@@ -158,3 +237,4 @@ if __name__ == "__main__":
     gen_ring_nstep()
     gen_rng()
     gen_bptt()
+    gen_marb()

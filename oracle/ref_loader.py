@@ -279,3 +279,41 @@ def reference_bptt(dones, data, max_seq_len, seq_type: str):
     mask = ns._pad_sequences(mseqs, target_length=None)
     msl = min(max_len, max_seq_len) if max_seq_len is not None else max_len
     return [s.numpy().copy() for s in slices], padded.numpy(), mask.numpy(), int(msl), len(seqs)
+
+
+def load_reference_marb():
+    """The UNMODIFIED ``MultiAgentReplayBuffer`` (components/multi_agent_replay_buffer.py), loaded
+    by path with two stub modules: ``agilerl.typing`` (a type alias only) and
+    ``agilerl.utils.algo_utils`` holding the reference's own ``obs_to_tensor`` (AST-extracted,
+    utils/algo_utils.py:746-773)."""
+    if "marb" in _cache:
+        return _cache["marb"]
+    from numbers import Number
+
+    names = ("agilerl", "agilerl.components", "agilerl.typing", "agilerl.utils", "agilerl.utils.algo_utils",
+             "agilerl.components.multi_agent_replay_buffer")
+    saved = {k: sys.modules.get(k) for k in names}
+    try:
+        for n in ("agilerl", "agilerl.components", "agilerl.utils"):
+            pkg = types.ModuleType(n)
+            pkg.__path__ = []
+            sys.modules[n] = pkg
+        ty = types.ModuleType("agilerl.typing")
+        ty.NumpyObsType = object
+        sys.modules["agilerl.typing"] = ty
+        au = types.ModuleType("agilerl.utils.algo_utils")
+        g = {"np": np, "torch": torch, "Number": Number, "TensorDict": ShimTensorDict,
+             "ObservationType": object, "TorchObsType": object}
+        exec(_extract(os.path.join(REF_PKG, "utils", "algo_utils.py"), ["obs_to_tensor"])["obs_to_tensor"], g)
+        au.obs_to_tensor = g["obs_to_tensor"]
+        sys.modules["agilerl.utils.algo_utils"] = au
+        mod = _load("agilerl.components.multi_agent_replay_buffer",
+                    os.path.join(REF_PKG, "components", "multi_agent_replay_buffer.py"))
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+    _cache["marb"] = mod.MultiAgentReplayBuffer
+    return _cache["marb"]

@@ -345,3 +345,77 @@ def bptt_prepare(dones, fields: dict, max_seq_len, seq_type: str = "chunked"):
     return {"num_sequences": S, "max_sequence_length": int(msl), "unpadded_slices": slices,
             "pad_mask": mask, "padded": padded,
             "first_idx": np.array([t0 * N + env for env, t0, _ in seqs], dtype=np.int64)}
+
+
+# =================================================================================================
+# MultiAgentReplayBuffer — components/multi_agent_replay_buffer.py:16-242
+# =================================================================================================
+class MarbOracle:
+    """deque of per-step tuples of {agent: value}; sample = random.sample + numpy stacking +
+    ``.float()`` (:108-162, utils/algo_utils.py:746-773).  Returns numpy fp32 arrays."""
+
+    BINARY = ("done", "termination", "terminated", "truncation", "truncated")
+
+    def __init__(self, memory_size: int, field_names, agent_ids):
+        from collections import deque
+
+        self.memory = deque(maxlen=memory_size)
+        self.field_names, self.agent_ids = list(field_names), list(agent_ids)
+        self.counter = 0
+
+    def __len__(self):
+        return len(self.memory)
+
+    def save(self, *args, is_vectorised=False):
+        if not is_vectorised:  # :164-173
+            self.memory.append(args)
+            self.counter += 1
+            return
+        n = len(next(iter(args[0].values())))  # :199
+
+        def row(v, i):
+            if isinstance(v, dict):
+                return {k: np.asarray(x[i]) for k, x in v.items()}
+            if isinstance(v, tuple):
+                return tuple(np.asarray(x[i]) for x in v)
+            return np.asarray(v[i])
+
+        for i in range(n):  # :200-226
+            self.memory.append(tuple({a: row(v, i) for a, v in arg.items()} for arg in args))
+            self.counter += 1
+
+    @staticmethod
+    def _stack(items):  # stack_transitions :58-96
+        def st(xs):
+            a = np.array(xs)
+            return a[:, None] if a.ndim == 1 else a
+
+        if isinstance(items[0], dict):
+            return {k: st([np.array(it[k]) for it in items]) for k in items[0]}
+        if isinstance(items[0], tuple):
+            return tuple(st([np.array(it[i]) for it in items]) for i in range(len(items[0])))
+        return st(items)
+
+    def sample(self, batch_size: int):
+        import random
+
+        exps = random.sample(self.memory, k=batch_size)  # :160
+
+        def f32(x):
+            return np.asarray(x).astype(np.float32)
+
+        out = []
+        for fi, f in enumerate(self.field_names):
+            per = {}
+            for a in self.agent_ids:
+                ts = self._stack([e[fi][a] for e in exps])
+                if f in self.BINARY and not isinstance(ts, (dict, tuple)) and not np.isnan(ts).any():
+                    ts = ts.astype(np.uint8)  # :137-138
+                if isinstance(ts, dict):
+                    per[a] = {k: f32(v) for k, v in ts.items()}
+                elif isinstance(ts, tuple):
+                    per[a] = tuple(f32(v) for v in ts)
+                else:
+                    per[a] = f32(ts)
+            out.append(per)
+        return tuple(out)

@@ -231,3 +231,28 @@ def test_bptt_reference_kats():
     assert [s[1:] for s in xo.bptt_sequences(d, 4, "chunked")[0]] == [(0, 4), (4, 4)]
     with pytest.raises(ValueError):
         xo.bptt_sequences(d, 1, "fifty_percent_overlap")
+
+
+# ---- MultiAgentReplayBuffer ----------------------------------------------------------------------------
+@pytest.mark.parametrize("seed", range(3))
+def test_marb_oracle_matches_reference_golden(seed):
+    import random
+
+    from oracle.make_golden import flatten_marb, marb_scenario
+
+    z = load_golden(f"marb_s{seed}")
+    cap, fields, agents, saves, batches = marb_scenario(seed)
+    buf = xo.MarbOracle(cap, fields, agents)
+    random.seed(500 + seed)
+    k = 0
+    for i, (args, vect) in enumerate(saves):
+        buf.save(*args, is_vectorised=vect)
+        if i in (len(saves) // 3, len(saves) - 1):
+            for bs in batches:
+                if bs <= len(buf):
+                    s = flatten_marb(buf.sample(bs), fields, agents)
+                    for name, t in s.items():
+                        assert t.dtype == np.float32
+                        assert np.array_equal(t, z[f"s{k}|{name}"], equal_nan=True), (k, name)
+                    k += 1
+    assert k == int(z["n_samples"]) and len(buf) == int(z["final_len"]) and buf.counter == int(z["counter"])
