@@ -16,7 +16,9 @@ def install() -> None:
     from . import components as c
 
     mods = {
-        "agilerl.components": ("ReplayBuffer", "MultiStepReplayBuffer", "PrioritizedReplayBuffer"),
+        "agilerl.components": ("ReplayBuffer", "MultiStepReplayBuffer", "PrioritizedReplayBuffer",
+                               "MultiAgentReplayBuffer", "RolloutBuffer", "Sampler"),
+        "agilerl.components.multi_agent_replay_buffer": ("MultiAgentReplayBuffer",),
         "agilerl.components.replay_buffer": ("ReplayBuffer", "MultiStepReplayBuffer", "PrioritizedReplayBuffer"),
         "agilerl.components.segment_tree": ("SumSegmentTree", "MinSegmentTree"),
         "agilerl.components.rollout_buffer": ("RolloutBuffer",),
