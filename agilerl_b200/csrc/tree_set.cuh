@@ -269,24 +269,35 @@ __device__ void cta_dense_top(const Tree &t, int h0, int width, double2 *heap) {
   }
 }
 
-// ---- schedule M (B <= 8192): ONE launch ---------------------------------------------------------
-// The CTA stages the whole batch's leaf numbers in shared memory with every load in flight at
-// once (a few KB, L2 resident); warp w then owns bucket subtree w of nb = 2^k buckets: it keeps
-// the items whose leaf falls in its bucket and climbs to the bucket root; the last CTA to finish
-// rebuilds the nb-leaf top densely (its heap re-uses the staging memory).
+// ---- schedule M (B <= 16384): ONE launch ----------------------------------------------------------
+// Warp w of a CTA owns bucket subtree w of nb = 2^k buckets; the last CTA to finish rebuilds the
+// nb-leaf top densely (its heap re-uses the staging memory).  Finding a bucket's items:
+//   small batches: the CTA stages every leaf number of the batch in shared memory (all loads in
+//           flight at once, no branch on a loaded value) and each warp filters that array;
+//   larger batches: while staging, the CTA keeps only the items of ITS buckets (a compact key list,
+//           shared-memory atomic append), so the per-warp filter walks tens of keys instead of the
+//           whole batch; a list overflow (skewed batch) falls back to the full array.
 constexpr int kMidWarps = 4;
+constexpr int kMidListCap = 1024;   // compact list capacity per CTA (keys)
+constexpr int kMidCompactFrom = 1024;
 template <bool PAIRED>
 __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc s, int B, int nb, int shift) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ u64 s_list[kMidWarps][32];
-  __shared__ int s_last;
+  __shared__ int s_last, s_cnt;
   const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.x * (blockDim.x >> 5) + warp;
+  const int nwarps = blockDim.x >> 5;
+  const int b = blockIdx.x * nwarps + warp;
   int *s_leaf = reinterpret_cast<int *>(smem_raw);  // [B]; -1 = out of range
-  {
-    constexpr int U = 8;  // independent loads in flight per thread (no branch on a loaded value)
-    const bool fold = blockIdx.x == 0 && s.kind == kSrcPrio;
+  u64 *s_keys = reinterpret_cast<u64 *>(smem_raw);  // [kMidListCap] (compact mode)
+  bool compact = B > kMidCompactFrom;
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  for (int pass = 0; pass < 2; ++pass) {
+    constexpr int U = 8;  // independent loads in flight per thread
+    const bool fold = pass == 0 && blockIdx.x == 0 && s.kind == kSrcPrio;
+    const int b_lo = blockIdx.x * nwarps, b_hi = b_lo + nwarps;
     double pmax = 0.0;
     for (int i0 = 0; i0 < B; i0 += (int)blockDim.x * U) {
       long long raw[U];
@@ -302,35 +313,51 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
         const int i = i0 + u * (int)blockDim.x + (int)threadIdx.x;
         if (i < B) {
           const bool bad = raw[u] < 0 || raw[u] >= s.limit;
-          s_leaf[i] = bad ? -1 : (int)raw[u];
+          if (compact) {
+            const int bk = (int)(raw[u] >> shift);
+            if (!bad && bk >= b_lo && bk < b_hi) {
+              const int slot = atomicAdd(&s_cnt, 1);
+              if (slot < kMidListCap) s_keys[slot] = ((u64)(unsigned)raw[u] << 32) | (u64)(unsigned)i;
+            }
+          } else {
+            s_leaf[i] = bad ? -1 : (int)raw[u];
+          }
           if (bad && blockIdx.x == 0 && s.err) *s.err = 1;
           if (fold) pmax = fmax(pmax, clamp_prio(pr[u]));
         }
       }
     }
     if (fold) fold_max_priority(s, pmax);
+    __syncthreads();
+    if (!compact || s_cnt <= kMidListCap) break;
+    compact = false;  // skewed batch: stage the whole array instead
+    __syncthreads();
   }
-  __syncthreads();
   if (b < nb) {
+    const int n = compact ? s_cnt : B;
+    auto fetch = [&](long long i) -> u64 {
+      if (compact) {
+        const u64 key = s_keys[i];
+        return ((int)(key >> 32) >> shift) == b ? key : kPad;
+      }
+      const int leaf = s_leaf[i];
+      return (leaf >= 0 && (leaf >> shift) == b) ? (((u64)(unsigned)leaf << 32) | (u64)i) : kPad;
+    };
     int cnt = 0;
-    for (int i0 = 0; i0 < B; i0 += 32) {
+    for (int i0 = 0; i0 < n; i0 += 32) {
       const int i = i0 + lane;
-      const int leaf = i < B ? s_leaf[i] : -1;
-      const bool mine = leaf >= 0 && (leaf >> shift) == b;
+      const u64 key = i < n ? fetch(i) : kPad;
+      const bool mine = key != kPad;
       const unsigned mask = __ballot_sync(FULL, mine);
       const int slot = cnt + __popc(mask & ((1u << lane) - 1u));
-      if (mine && slot < 32) s_list[warp][slot] = ((u64)(unsigned)leaf << 32) | (u64)(unsigned)i;
+      if (mine && slot < 32) s_list[warp][slot] = key;
       cnt += __popc(mask);
     }
     __syncwarp();
     if (cnt <= 32) {
       if (cnt > 0) warp_climb<PAIRED, 32>(t, s, lane < cnt ? s_list[warp][lane] : kPad, shift);
     } else {
-      auto fetch = [&](long long i) -> u64 {
-        const int leaf = s_leaf[i];
-        return (leaf >= 0 && (leaf >> shift) == b) ? (((u64)(unsigned)leaf << 32) | (u64)i) : kPad;
-      };
-      warp_climb_large<PAIRED>(t, s, fetch, B, shift);
+      warp_climb_large<PAIRED>(t, s, fetch, n, shift);
     }
   }
   if (nb == 1) return;
@@ -631,14 +658,19 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   const int L = ilog2(t.cap);
   const bool paired = is_paired(t);
   int launches = 0;
-  if (B <= 8192) {  // schedule M: one launch
+  if (B <= 16384) {  // schedule M: one launch
     long long nb = 1;
-    while (nb * 8 < B && nb < 1024 && nb * 2 <= t.cap) nb <<= 1;
+    while (nb * 8 < B && nb < 2048 && nb * 2 <= t.cap) nb <<= 1;
     const int shift = L - ilog2(nb);
     const int warps = nb < kMidWarps ? (int)nb : kMidWarps;
     const unsigned grid = (unsigned)(nb / warps);
     const size_t heap = nb > 1 ? (size_t)2 * nb * sizeof(double2) : 0;
-    const size_t smem = heap > (size_t)B * 4 ? heap : (size_t)B * 4;
+    size_t smem = heap > (size_t)B * 4 ? heap : (size_t)B * 4;
+    if (B > kMidCompactFrom && smem < (size_t)kMidListCap * 8) smem = (size_t)kMidListCap * 8;
+    static bool mid_attr[2] = {false, false};
+    xp_status_t rc = set_attr_once(paired ? (const void *)set_mid_kernel<true> : (const void *)set_mid_kernel<false>,
+                                   (size_t)65536, mid_attr[paired ? 1 : 0]);
+    if (rc != XP_OK) return rc;
     if (paired)
       set_mid_kernel<true><<<grid, warps * 32, smem, st>>>(t, s, (int)B, (int)nb, shift);
     else

@@ -106,6 +106,16 @@ class ReplicatedReplay:
         dev = self.memory.storage_device if _is_cuda_backend(self.group) else local_idx.device
         idx = torch.as_tensor(local_idx).to(device=dev, dtype=torch.int64).reshape(-1)
         pr = torch.as_tensor(local_prio).to(device=dev, dtype=torch.float32).reshape(-1)
+        world = _group_size(self.group)
+        if world > 1 and _is_cuda_backend(self.group):
+            # both all-gathers in ONE NCCL launch
+            all_idx = torch.empty(world * idx.shape[0], dtype=idx.dtype, device=dev)
+            all_pr = torch.empty(world * pr.shape[0], dtype=pr.dtype, device=dev)
+            with dist._coalescing_manager(group=self.group, device=torch.device(dev)):
+                dist.all_gather_into_tensor(all_idx, idx.contiguous(), group=self.group)
+                dist.all_gather_into_tensor(all_pr, pr.contiguous(), group=self.group)
+            self.memory.update_priorities(all_idx, all_pr)
+            return
         self.memory.update_priorities(all_gather_rows(idx, self.group), all_gather_rows(pr, self.group))
 
     def sample(self, *args, **kwargs):

@@ -302,9 +302,23 @@ class C2Workload:
             self.outs.append(o)
         _, _, st, h = self.per._ensure_trees()
         self.h, self.state = h, self.per._state
+        self.px = None
         if self.world > 1:
             self.all_idx = torch.empty(self.world * n, dtype=torch.int64, device=dev)
             self.all_pr = torch.empty(self.world * n, dtype=torch.float32, device=dev)
+            from agilerl_b200 import peer
+
+            if peer.available() and os.environ.get("XP_BENCH_NCCL") != "1":
+                try:
+                    # every rank's (indices, priorities) live in NVLink peer-mapped memory; the
+                    # exchange is the library's own one-kernel all-gather (xp_peer_allgather)
+                    self.px = peer.PeerExchange(12 * n, [(0, 8 * n, torch.int64), (8 * n, 4 * n, torch.float32)], dev)
+                    self.idx_blk = [self.px.view(k, 0, n, torch.int64) for k in (0, 1)]
+                    for k in (0, 1):  # the learner's new priorities are produced straight into the block
+                        self.px.view(k, 8 * n, n, torch.float32).copy_(self.pr[k])
+                except Exception as e:  # pragma: no cover - depends on the box
+                    sys.stderr.write(f"bench.py: peer exchange unavailable ({e}); using NCCL all-gather\n")
+                    self.px = None
         torch.cuda.synchronize()
 
     @property
@@ -324,6 +338,8 @@ class C2Workload:
         n = self.P * self.B
         u, pr, o = self.u[i % self.R], self.pr[i % self.R], self.outs[i % 2]
         chk = self.nv.check
+        if self.px is not None:
+            self.idx = self.idx_blk[self.px.current]  # sampled indices land in the peer-mapped block
         chk(lib.xp_per_sample(C.byref(self.h), u.data_ptr(), self.B, self.P, self.cap, c["beta"],
                               self.idx.data_ptr(), self.w.data_ptr(), stream))
         if ev is not None:
@@ -336,11 +352,18 @@ class C2Workload:
         chk(lib.xp_gather(k[0], k[1], self.idx.data_ptr(), n, self.cap, self.err.data_ptr(), stream))
         if ev is not None:
             ev[1].record()
-        if self.world > 1:
+        if self.px is not None:
+            all_idx, all_pr = self.px.allgather()
+            chk(lib.xp_per_update(C.byref(self.h), self.state.data_ptr(), all_idx.data_ptr(),
+                                  all_pr.data_ptr(), self.world * n, self.cap, c["alpha"],
+                                  self.err.data_ptr(), stream))
+        elif self.world > 1:
             import torch.distributed as dist
 
-            dist.all_gather_into_tensor(self.all_idx, self.idx)
-            dist.all_gather_into_tensor(self.all_pr, pr)
+            # both all-gathers in ONE NCCL launch (ncclGroupStart/End)
+            with dist._coalescing_manager(device=self.dev):
+                dist.all_gather_into_tensor(self.all_idx, self.idx)
+                dist.all_gather_into_tensor(self.all_pr, pr)
             chk(lib.xp_per_update(C.byref(self.h), self.state.data_ptr(), self.all_idx.data_ptr(),
                                   self.all_pr.data_ptr(), self.world * n, self.cap, c["alpha"],
                                   self.err.data_ptr(), stream))
@@ -615,6 +638,9 @@ def b200_arm(args):
     also = None
     cpu = None
     rows = wl.cap
+    exchange = "peer" if wl.px is not None else "nccl"
+    if wl.px is not None:
+        wl.px.check()
     if rank == 0 and world == 1 and not args.no_also:
         del wl
         torch.cuda.empty_cache()
@@ -638,7 +664,9 @@ def b200_arm(args):
                        "row_bytes": R_C2, "tree_levels": C2["L"],
                        "l2": "inputs larger than L2: random rows of a 113 GB replay storage; "
                              "2 rotating output sets of 231 MB",
-                       "parallelism": f"pop-shard x{world}, replicated replay"},
+                       "parallelism": f"pop-shard x{world}, replicated replay"
+                                      + ("" if world == 1 else (", exchange: xp_peer_allgather over NVLink peer memory"
+                                                                if exchange == "peer" else ", exchange: NCCL all-gather"))},
             "e2e": e2e,
             "gpu_launches": int(l1 - l0),
             "clocks": clocks.summary(),

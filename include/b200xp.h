@@ -214,6 +214,28 @@ xp_status_t xp_bptt_indices(const int32_t *seq_t0_dev, const int32_t *seq_env_de
                             int64_t pad_len, int64_t N, int64_t *pad_idx_dev, uint8_t *pad_mask_dev,
                             int64_t *unp_idx_dev, int64_t *first_idx_dev, void *stream);
 
+/* ---- replicated-replay exchange over NVLink peer memory ---------------------------------- */
+/* replaces the broadcast of sampled indices + gather of new priorities of the distributed
+ * off-policy loop (training/train_off_policy.py:363-381) when every rank is one GPU of an NVLink
+ * domain.  Rank r keeps its block in peer-mapped memory at peer_base[r]; peer_flags[r] is a
+ * uint32[world] array in r's peer-mapped memory (zero before the first call).  The kernel signals
+ * `epoch` to every peer, waits for every peer's `epoch`, and copies segment k of every rank's
+ * block (peer_base[r] + src_off, `bytes` long) to segs[k].dst + r*bytes (local memory): a
+ * rank-major all-gather.  Call with epoch = 1, 2, 3, ... on every rank, and alternate between two
+ * source blocks so that a block is not rewritten while a slower peer may still read it.
+ * peer_base / peer_flags / segs are HOST arrays.  A peer that does not arrive within ~2 s sets
+ * *err_flag_dev instead of hanging.                                                          */
+#define XP_MAX_PEERS 16
+#define XP_MAX_PEER_SEGS 4
+typedef struct xp_peer_seg {
+  int64_t src_off; /* byte offset of the segment inside every rank's block */
+  void *dst;       /* local device memory, world * bytes long              */
+  int64_t bytes;   /* per rank                                             */
+} xp_peer_seg;
+xp_status_t xp_peer_allgather(const void *const *peer_base, void *const *peer_flags, int rank,
+                              int world, uint32_t epoch, const xp_peer_seg *segs, int n_segs,
+                              int *err_flag_dev, void *stream);
+
 /* ---- host-side RNG mirror (no GPU needed) -------------------------------------------- */
 /* torch's CPU generator is mt19937; these reproduce the raw 32-bit stream so that the
  * engine consumes "identical uniform draws" (replay_buffer.py:125,377).

@@ -152,12 +152,13 @@ def test_tree_non_pow2_capacity_is_assertion(xp, cuda_device):
         xp.tree_init(bad, 0)
 
 
-# schedules of tree_set.cuh: M (B <= 8192, one launch), L (bucketed, large B), D (dense rebuild)
+# schedules of tree_set.cuh: M (B <= 16384, one launch), L (bucketed, large B), D (dense rebuild)
 @pytest.mark.parametrize("cap,B,interleaved", [(1, 3, True), (2, 5, False), (64, 40, True),
                                                (4096, 256, True), (4096, 5000, False), (1 << 16, 20000, True),
                                                (1 << 14, 700, False), (1 << 16, 1500, True), (1 << 16, 2048, True),
                                                (1 << 18, 3000, True), (1 << 12, 1 << 12, True), (1 << 14, 20000, True),
-                                               (1 << 18, 8192, False), (1 << 18, 30000, True), (1 << 20, 100000, True)])
+                                               (1 << 18, 8192, False), (1 << 18, 30000, True), (1 << 20, 100000, True),
+                                               (1 << 18, 16384, True), (1 << 20, 12000, True), (1 << 18, 16385, True)])
 def test_tree_set_batch_equals_sequential_reference(xp, cuda_device, cap, B, interleaved):
     rng = np.random.default_rng(cap + B)
     t = DevTree(xp, cuda_device, cap, interleaved)
