@@ -90,6 +90,9 @@ class ReplicatedReplay:
     def __init__(self, memory, group=None) -> None:
         self.memory = memory
         self.group = group
+        self._px = None      # peer.PeerExchange, created on the first CUDA update
+        self._px_n = 0
+        self._peer_ok = None
 
     def add(self, local_rows) -> None:
         """``local_rows``: the new transitions of this rank's agents, agent-major ``[n]`` (equal
@@ -107,6 +110,30 @@ class ReplicatedReplay:
         idx = torch.as_tensor(local_idx).to(device=dev, dtype=torch.int64).reshape(-1)
         pr = torch.as_tensor(local_prio).to(device=dev, dtype=torch.float32).reshape(-1)
         world = _group_size(self.group)
+        if world > 1 and _is_cuda_backend(self.group) and self._peer_ok is not False:
+            # NVLink peer-memory exchange: one kernel signals, waits and pulls every rank's block
+            n = idx.shape[0]
+            try:
+                if self._px is None or self._px_n != n:
+                    from . import peer
+
+                    if not peer.available(self.group):
+                        raise RuntimeError("symmetric memory unavailable")
+                    self._px = peer.PeerExchange(12 * n, [(0, 8 * n, torch.int64), (8 * n, 4 * n, torch.float32)],
+                                                 torch.device(dev), self.group)
+                    self._px_n = n
+                    self._peer_ok = True
+            except Exception:
+                if self._peer_ok:  # it worked before: a real error, not an unsupported box
+                    raise
+                self._peer_ok = False
+            if self._peer_ok:
+                k = self._px.current
+                self._px.view(k, 0, n, torch.int64).copy_(idx)
+                self._px.view(k, 8 * n, n, torch.float32).copy_(pr)
+                all_idx, all_pr = self._px.allgather()
+                self.memory.update_priorities(all_idx, all_pr)
+                return
         if world > 1 and _is_cuda_backend(self.group):
             # both all-gathers in ONE NCCL launch
             all_idx = torch.empty(world * idx.shape[0], dtype=idx.dtype, device=dev)

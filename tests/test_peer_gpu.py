@@ -65,3 +65,40 @@ def test_peer_allgather_two_gpus(tmp_path):
     r1 = torch.load(tmp_path / "r1.pt", weights_only=False)
     assert r0["ok"] and r1["ok"]
     assert torch.equal(r0["tree"], r1["tree"]) and r0["maxp"] == r1["maxp"]  # replicas stay bit-identical
+
+
+def _worker_rr(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from agilerl_b200.components import PrioritizedReplayBuffer, TensorBatch
+    from agilerl_b200.population import ReplicatedReplay
+
+    mem = PrioritizedReplayBuffer(1024, alpha=0.6, device=dev)
+    rep = ReplicatedReplay(mem)
+    g = torch.Generator().manual_seed(7 + rank)
+    for _ in range(3):
+        rep.add(TensorBatch({"obs": torch.randn(8, 3, generator=g), "reward": torch.randn(8, generator=g)}, batch_size=[8]))
+    for step in range(5):
+        idx = torch.randint(0, 48, (16,), generator=g)
+        rep.update_priorities(idx, torch.rand(16, generator=g) + 0.05)
+    mem.check_errors()
+    torch.save({"peer": rep._peer_ok, "tree": mem._trees[2].nodes.cpu(), "obs": mem._leaves[("obs",)][:48].cpu()},
+               os.path.join(out_dir, f"q{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_replicated_replay_uses_peer_exchange(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    world = 2
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_worker_rr, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    q0 = torch.load(tmp_path / "q0.pt", weights_only=False)
+    q1 = torch.load(tmp_path / "q1.pt", weights_only=False)
+    assert q0["peer"] is True and q1["peer"] is True
+    assert torch.equal(q0["tree"], q1["tree"]) and torch.equal(q0["obs"], q1["obs"])
