@@ -277,7 +277,7 @@ __device__ void cta_dense_top(const Tree &t, int h0, int width, double2 *heap) {
 //   larger batches: while staging, the CTA keeps only the items of ITS buckets (a compact key list,
 //           shared-memory atomic append), so the per-warp filter walks tens of keys instead of the
 //           whole batch; a list overflow (skewed batch) falls back to the full array.
-constexpr int kMidWarps = 4;
+constexpr int kMidWarps = 16;  // at most; small batches launch 4 warps per CTA
 constexpr int kMidListCap = 1024;   // compact list capacity per CTA (keys)
 constexpr int kMidCompactFrom = 1024;
 template <bool PAIRED>
@@ -662,7 +662,9 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     long long nb = 1;
     while (nb * 8 < B && nb < 2048 && nb * 2 <= t.cap) nb <<= 1;
     const int shift = L - ilog2(nb);
-    const int warps = nb < kMidWarps ? (int)nb : kMidWarps;
+    // every CTA reads the whole batch once: wider CTAs for larger batches keep that O(B * nb / warps)
+    int warps = B > 4096 ? 16 : B > 2048 ? 8 : 4;
+    if (warps > nb) warps = (int)nb;
     const unsigned grid = (unsigned)(nb / warps);
     const size_t heap = nb > 1 ? (size_t)2 * nb * sizeof(double2) : 0;
     size_t smem = heap > (size_t)B * 4 ? heap : (size_t)B * 4;
