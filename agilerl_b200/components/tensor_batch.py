@@ -21,6 +21,9 @@ def _is_batch(x) -> bool:
     return isinstance(x, TensorBatch)
 
 
+_RINGS: dict = {}  # device -> PinnedRing for index vectors
+
+
 class TensorBatch:
     __slots__ = ("_d", "batch_size", "_non_tensor")
 
@@ -124,6 +127,60 @@ class TensorBatch:
             real = torch.empty(tuple(self.batch_size) + (0,))
             return real[idx].shape[:-1]
 
+    def _leaf_items(self, prefix=()):
+        for k, v in self._d.items():
+            if _is_batch(v):
+                yield from v._leaf_items(prefix + (k,))
+            else:
+                yield prefix + (k,), v
+
+    def _gather_rows(self, idx: torch.Tensor):
+        """``batch[idx]`` for a host integer index vector over a CUDA-resident batch: every key in
+        ONE ``xp_gather`` launch (the reference's PPO minibatch slicing, algorithms/ppo.py:846-848,
+        indexes each key separately).  Returns None when the fast path does not apply."""
+        if len(self.batch_size) != 1 or idx.dim() != 1 or idx.is_cuda or idx.dtype not in (torch.int64, torch.int32):
+            return None
+        n = self.batch_size[0]
+        leaves = list(self._leaf_items())
+        if not leaves or n == 0:
+            return None
+        dev = leaves[0][1].device
+        if dev.type != "cuda":
+            return None
+        for _, t in leaves:
+            if t.device != dev or not t.is_contiguous() or t.dim() < 1 or t.shape[0] != n:
+                return None
+        m = idx.numel()
+        if m == 0:
+            return None
+        lo, hi = int(idx.min()), int(idx.max())
+        if hi >= n or lo < -n:  # what CPU indexing raises; a device gather would only assert
+            raise IndexError(f"index {hi if hi >= n else lo} is out of bounds for dimension 0 with size {n}")
+        if lo < 0:
+            return None  # negative (from-the-end) indices: torch's own indexing handles them
+        from .. import _native as nv
+        from .. import xp
+        from .staging import PinnedRing
+
+        ring = _RINGS.get(dev)
+        if ring is None:
+            ring = _RINGS[dev] = PinnedRing(dev)
+        with nv.on_device(dev):
+            idx_dev = ring.to_device(idx if idx.dtype == torch.int64 else idx.to(torch.int64))
+            outs = [torch.empty((m, *t.shape[1:]), dtype=t.dtype, device=dev) for _, t in leaves]
+            for k in range(0, len(leaves), 24):
+                xp.gather([(t, o) for (_, t), o in zip(leaves[k:k + 24], outs[k:k + 24])], idx_dev, n)
+        root = TensorBatch({}, batch_size=[m])
+        root._non_tensor = dict(self._non_tensor)
+        for (path, _), o in zip(leaves, outs):
+            node = root
+            for key in path[:-1]:
+                if key not in node._d:
+                    node._d[key] = TensorBatch({}, batch_size=[m])
+                node = node._d[key]
+            node._d[path[-1]] = o
+        return root
+
     def __getitem__(self, idx):
         if isinstance(idx, str):
             if idx in self._d:
@@ -133,6 +190,10 @@ class TensorBatch:
             raise KeyError(idx)
         if isinstance(idx, np.ndarray):
             idx = torch.from_numpy(idx)
+        if isinstance(idx, torch.Tensor):
+            fast = self._gather_rows(idx)
+            if fast is not None:
+                return fast
         new_bs = self._index_batch_size(idx)
 
         def take(t):

@@ -599,3 +599,40 @@ def test_bptt_errors_and_helpers(C):
     assert b2.padded_data["observations"].device.type == "cpu"
     p, u = next(iter(b2.get_minibatch_sequences(2)))
     assert p["observations"].device.type == "cpu" and u["returns"].device.type == "cpu"
+
+
+# ---- PPO minibatch slicing (algorithms/ppo.py:838-848): buffer_td[minibatch_indices] --------------------
+def test_tensor_batch_row_indexing_by_host_indices_is_one_gather(C):
+    from agilerl_b200 import _native as nv
+    from agilerl_b200.components import spaces
+
+    T, N = 12, 5
+    b = C.RolloutBuffer(capacity=T, observation_space=spaces.Dict({"a": spaces.Box(-1, 1, (3,), np.float32),
+                                                                  "b": spaces.Box(-1, 1, (2, 2), np.float32)}),
+                        action_space=spaces.Discrete(3), num_envs=N, device="cuda")
+    g = torch.Generator().manual_seed(0)
+    for t in range(T):
+        b.add({"a": torch.randn(N, 3, generator=g).numpy(), "b": torch.randn(N, 2, 2, generator=g).numpy()},
+              np.arange(N) % 3, np.ones(N), np.zeros(N), np.full(N, 0.5), np.full(N, 0.1))
+    b.compute_returns_and_advantages(np.zeros(N), np.zeros(N))
+    td = b.get_tensor_batch(device="cuda")
+    adv = td.get("advantages")
+    td["advantages"] = (adv - adv.mean()) / (adv.std() + 1e-8)   # :832-836, plain torch on device
+    indices = np.arange(T * N)
+    np.random.default_rng(1).shuffle(indices)
+    lib = nv.load()
+    for start in range(0, T * N, 16):
+        mb_idx = indices[start:start + 16]
+        l0 = lib.xp_launch_count()
+        mb = td[mb_idx]
+        assert lib.xp_launch_count() - l0 == 1  # every key in one launch
+        ref = torch.from_numpy(mb_idx).cuda()
+        assert mb.batch_size == torch.Size([len(mb_idx)])
+        assert torch.equal(mb["observations"]["b"], td["observations"]["b"][ref])
+        assert torch.equal(mb["advantages"], td["advantages"][ref])
+        assert torch.equal(mb["dones"], td["dones"][ref]) and mb["dones"].dtype == torch.bool
+    # negative / boolean / device indices keep torch's semantics
+    assert torch.equal(td[np.array([-1, 0])]["returns"], td["returns"][torch.tensor([-1, 0]).cuda()])
+    assert td[torch.tensor([1, 2]).cuda()].batch_size == torch.Size([2])
+    with pytest.raises(IndexError):
+        td[np.array([T * N])]
