@@ -66,6 +66,8 @@ _SIGNATURES = {
                                        C.c_int, C.c_int, C.POINTER(C.c_float), c_i64, c_i64, c_i64, c_vp]),
     "xp_gae": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64,
                          C.c_double, C.c_double, c_vp]),
+    "xp_gae_f32": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64,
+                             C.c_double, C.c_double, c_vp]),
     "xp_mc_returns": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64,
                                 C.c_double, c_vp]),
     "xp_mt19937_seed": (None, [C.POINTER(XpMt19937), C.c_uint32]),

@@ -361,6 +361,50 @@ bool encode_map_uncached(CUtensorMap *m, const void *base, int elem_bytes, const
   return r == CUDA_SUCCESS;
 }
 
+// ---- all-fp32 GAE of the legacy "experiences" path (algorithms/ppo.py:686-713, ippo.py:703-720) --------
+// torch evaluates that loop with fp32 tensors and Python-float scalars: every op is a separately
+// rounded fp32 op, gamma and gamma*lambda enter as fp32.  thread = (agent, env); rows are read
+// coalesced across envs, 8 steps staged ahead of the chain.
+__global__ void __launch_bounds__(128) gae32_kernel(const float *rewards, const float *values, const uint8_t *dones,
+                                                    const float *next_value, const float *next_done, float *adv,
+                                                    float *ret, long long T, long long N, long long P,
+                                                    long long astride, float g32, float gl32) {
+  const long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N * P) return;
+  const long long agent = c / N, env = c - agent * N;
+  const long long base = agent * astride + env;
+  const float *r = rewards + base, *v = values + base;
+  const uint8_t *d = dones + base;
+  float *a = adv + base, *g = ret + base;
+  float nv = next_value[agent * N + env];
+  float nnt = __fsub_rn(1.0f, next_done[agent * N + env]);
+  float carry = 0.0f;
+  constexpr int U = 8;
+  for (long long t_hi = T - 1; t_hi >= 0; t_hi -= U) {
+    float r8[U], v8[U];
+    uint8_t d8[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long t = t_hi - u >= 0 ? t_hi - u : 0;
+      r8[u] = __ldg(r + t * N);
+      v8[u] = __ldg(v + t * N);
+      d8[u] = __ldg(d + t * N);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long t = t_hi - u;
+      if (t >= 0) {
+        const float delta = __fsub_rn(__fadd_rn(r8[u], __fmul_rn(__fmul_rn(g32, nv), nnt)), v8[u]);
+        carry = __fadd_rn(delta, __fmul_rn(__fmul_rn(gl32, nnt), carry));
+        __stcs(a + t * N, carry);
+        __stcs(g + t * N, __fadd_rn(carry, v8[u]));
+        nv = v8[u];
+        nnt = d8[u] ? 0.0f : 1.0f;  // 1.0 - dones[t].long()
+      }
+    }
+  }
+}
+
 template <int MODE>
 xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   if (p.T == 0 || p.N == 0 || p.P == 0) return XP_OK;
@@ -452,6 +496,23 @@ xp_status_t xp_gae(const float *rewards, const float *values, const uint8_t *don
                                P, agent_stride, gamma, gl);
   if (st != XP_OK) return st;
   return launch_scan<kModeGae>(p, (cudaStream_t)stream);
+}
+
+xp_status_t xp_gae_f32(const float *rewards, const float *values, const uint8_t *dones,
+                       const float *next_value, const float *next_done, float *adv, float *ret, int64_t T,
+                       int64_t N, int64_t P, int64_t agent_stride, double gamma, double gae_lambda,
+                       void *stream) {
+  XP_REQUIRE(T >= 0 && N >= 0 && P >= 0, XP_ERR_INVALID, "xp_gae_f32: negative extent");
+  if (T == 0 || N == 0 || P == 0) return XP_OK;
+  XP_REQUIRE(rewards && values && dones && next_value && next_done && adv && ret, XP_ERR_INVALID,
+             "xp_gae_f32: null pointer");
+  XP_REQUIRE(P == 1 || agent_stride >= T * N, XP_ERR_INVALID, "xp_gae_f32: agent_stride < T*N");
+  volatile double gl = gamma * gae_lambda;  // one Python-float product, then rounded to fp32 by the tensor op
+  const long long chains = N * P;
+  gae32_kernel<<<(unsigned)((chains + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      rewards, values, dones, next_value, next_done, adv, ret, T, N, P, P == 1 ? T * N : agent_stride,
+      (float)gamma, (float)gl);
+  return xp::check_launch("xp_gae_f32");
 }
 
 xp_status_t xp_mc_returns(const float *rewards, const float *values, const uint8_t *dones,

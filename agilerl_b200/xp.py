@@ -198,6 +198,20 @@ def gae(rewards, values, dones, last_value, last_done, adv, ret, T: int, N: int,
                                 ret.data_ptr(), T, N, P, agent_stride, gamma, s), "xp_mc_returns")
 
 
+def gae_f32(rewards, values, dones, next_value, next_done, adv, ret, T: int, N: int, P: int,
+            agent_stride: int, gamma: float, gae_lambda: float) -> None:
+    """The all-fp32 GAE of the legacy experiences path: everything fp32 except dones (bool/uint8)."""
+    for name, t in (("rewards", rewards), ("values", values), ("adv", adv), ("ret", ret),
+                    ("next_value", next_value), ("next_done", next_done)):
+        _need(t, torch.float32, name)
+    if dones.dtype not in (torch.bool, torch.uint8) or not dones.is_cuda:
+        raise TypeError("dones must be a CUDA bool/uint8 tensor")
+    check(nv.load().xp_gae_f32(rewards.data_ptr(), values.data_ptr(), dones.data_ptr(),
+                               next_value.data_ptr(), next_done.data_ptr(), adv.data_ptr(),
+                               ret.data_ptr(), T, N, P, agent_stride, gamma, gae_lambda,
+                               _stream(rewards)), "xp_gae_f32")
+
+
 # ---- truncated-BPTT sequence preparation ------------------------------------------------------------
 BPTT_TYPES = {"chunked": 0, "maximum": 1, "fifty_percent_overlap": 2}
 

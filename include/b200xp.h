@@ -178,6 +178,14 @@ xp_status_t xp_gae(const float *rewards, const float *values, const uint8_t *don
                    const double *last_value, const double *last_done, float *adv, float *ret,
                    int64_t T, int64_t N, int64_t P, int64_t agent_stride, double gamma,
                    double gae_lambda, void *stream);
+/* replaces the all-fp32 GAE loop of the legacy "experiences" learn path (algorithms/ppo.py:686-713,
+ * algorithms/ippo.py:703-720): torch fp32 tensors with Python-float scalars, i.e. every op rounded
+ * in fp32, gamma and gamma*lambda entering as fp32; next_value / next_done fp32 [P][N] bootstrap
+ * t = T-1; dones u8 (the reference's dones.long()).  ret = adv + values.                       */
+xp_status_t xp_gae_f32(const float *rewards, const float *values, const uint8_t *dones,
+                       const float *next_value, const float *next_done, float *adv, float *ret,
+                       int64_t T, int64_t N, int64_t P, int64_t agent_stride, double gamma,
+                       double gae_lambda, void *stream);
 /* replaces the Monte-Carlo branch (rollout_buffer.py:468-477). */
 xp_status_t xp_mc_returns(const float *rewards, const float *values, const uint8_t *dones,
                           const double *last_value, const double *last_done, float *adv,

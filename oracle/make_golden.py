@@ -41,6 +41,22 @@ def gen_gae():
              gamma=0.99, gae_lambda=0.95, adv=adv, ret=ret, adv_mc=adv_mc, ret_mc=ret_mc)
 
 
+def gen_gae32():
+    # the legacy experiences path: both sibling sites (ppo.py / ippo.py), fractional next_done included
+    for seed, (T, N, site) in [(0, (16, 8, "ppo")), (1, (128, 64, "ppo")), (2, (37, 33, "ippo")),
+                               (3, (1, 5, "ippo")), (4, (64, 1, "ppo"))]:
+        g = torch.Generator().manual_seed(100 + seed)
+        r = torch.randn(T, N, generator=g).numpy()
+        v = torch.randn(T, N, generator=g).numpy()
+        d = (torch.rand(T, N, generator=g) < 0.05).numpy()
+        nv = torch.randn(N, generator=g).numpy()
+        nd = (torch.rand(N, generator=g) < 0.2).float().numpy()
+        gamma, lam = (0.99, 0.95) if seed != 2 else (0.997, 0.9)
+        adv, ret = ref_loader.reference_gae_f32(r, v, d, nv, nd, gamma, lam, site=site)
+        save(f"gae32_s{seed}", rewards=r, values=v, dones=d, next_value=nv, next_done=nd,
+             gamma=gamma, gae_lambda=lam, adv=adv, ret=ret)
+
+
 def gen_per():
     ref = ref_loader.load_reference()
     TD = ref.TensorDict
@@ -229,10 +245,14 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["marb"]:
         gen_marb()
         sys.exit(0)
+    if sys.argv[1:] == ["gae32"]:
+        gen_gae32()
+        sys.exit(0)
     if sys.argv[1:] == ["bptt"]:
         gen_bptt()
         sys.exit(0)
     gen_gae()
+    gen_gae32()
     gen_per()
     gen_ring_nstep()
     gen_rng()

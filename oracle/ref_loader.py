@@ -317,3 +317,51 @@ def load_reference_marb():
                 sys.modules[k] = v
     _cache["marb"] = mod.MultiAgentReplayBuffer
     return _cache["marb"]
+
+
+def _reference_gae_loop(path: str, method: str, cls: str):
+    """Source of the ``for t in reversed(range(num_steps))`` statement inside ``cls.method`` —
+    the all-fp32 GAE loop of the legacy experiences path (algorithms/ppo.py:693-711,
+    algorithms/ippo.py:705-720) — extracted unmodified."""
+    src = open(path).read()
+    tree = ast.parse(src)
+    klass = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == cls)
+    fn = next(n for n in klass.body if isinstance(n, ast.FunctionDef) and n.name == method)
+    for node in ast.walk(fn):
+        if (isinstance(node, ast.For) and isinstance(node.target, ast.Name) and node.target.id == "t"
+                and "last_gae_lambda" in ast.get_source_segment(src, node)):
+            return textwrap.dedent(" " * node.col_offset + ast.get_source_segment(src, node))
+    raise AssertionError(f"GAE loop not found in {path}:{cls}.{method}")
+
+
+def reference_gae_f32(rewards, values, dones, next_value, next_done, gamma, gae_lambda, site="ppo"):
+    """Run the reference's own loop statement (site 'ppo' = PPO._deprecated_learn_from_experiences,
+    'ippo' = IPPO._learn_individual) on fp32 torch CPU tensors, with the few assignments that
+    precede it in the reference (ppo.py:688-692) restated.  rewards/values fp32 [T,N], dones 0/1
+    [T,N], next_value fp32 [N], next_done fp32 [N].  Returns (advantages, returns) fp32 numpy."""
+    key = "gae32_" + site
+    if key not in _cache:
+        if site == "ppo":
+            _cache[key] = _reference_gae_loop(os.path.join(REF_PKG, "algorithms", "ppo.py"),
+                                              "_deprecated_learn_from_experiences", "PPO")
+        else:
+            _cache[key] = _reference_gae_loop(os.path.join(REF_PKG, "algorithms", "ippo.py"),
+                                              "_learn_individual", "IPPO")
+    rewards = torch.from_numpy(np.ascontiguousarray(rewards, dtype=np.float32))
+    values = torch.from_numpy(np.ascontiguousarray(values, dtype=np.float32))
+    d = torch.from_numpy(np.ascontiguousarray(dones))
+    g = {
+        "torch": torch,
+        "self": types.SimpleNamespace(gamma=gamma, gae_lambda=gae_lambda),
+        "rewards": rewards, "values": values,
+        "dones": d.long() if site == "ppo" else d.float(),
+        "next_done": torch.from_numpy(np.ascontiguousarray(next_done, dtype=np.float32)).reshape(1, -1),
+        "next_value": torch.from_numpy(np.ascontiguousarray(next_value, dtype=np.float32)).reshape(1, -1),
+        "num_steps": rewards.size(0),
+        "advantages": torch.zeros_like(rewards).float(),
+        "last_gae_lambda": 0,
+    }
+    with torch.no_grad():
+        exec(_cache[key], g)
+    adv = g["advantages"]
+    return adv.numpy().copy(), (adv + values).numpy().copy()

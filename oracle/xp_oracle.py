@@ -282,6 +282,31 @@ def gae_scalar(rewards, values, dones, last_value, last_done, gamma: float, gae_
     return adv, adv + values
 
 
+def gae_f32(rewards, values, dones, next_value, next_done, gamma: float, gae_lambda: float):
+    """The all-fp32 GAE loop of the legacy experiences path (algorithms/ppo.py:693-713,
+    algorithms/ippo.py:705-724).  torch evaluates it on fp32 tensors with Python-float scalars,
+    i.e. every scalar enters as fp32 and every op rounds to fp32.  rewards/values fp32 [T,N],
+    dones 0/1 [T,N], next_value/next_done fp32 [N]."""
+    f = np.float32
+    T, N = rewards.shape
+    rewards = np.asarray(rewards, dtype=f)
+    values = np.asarray(values, dtype=f)
+    g32, gl32 = f(gamma), f(gamma * gae_lambda)
+    adv = np.zeros((T, N), dtype=f)
+    carry = np.zeros(N, dtype=f)
+    for t in reversed(range(T)):
+        if t == T - 1:
+            nnt = f(1.0) - np.asarray(next_done, dtype=f).reshape(N)
+            nv = np.asarray(next_value, dtype=f).reshape(N)
+        else:
+            nnt = f(1.0) - np.asarray(dones[t + 1]).astype(f)
+            nv = values[t + 1]
+        delta = (rewards[t] + (g32 * nv) * nnt) - values[t]
+        adv[t] = carry = delta + (gl32 * nnt) * carry
+    assert adv.dtype == f
+    return adv, adv + values
+
+
 def pow_cpython(x: float, y: float) -> float:
     """float ** float in CPython = libm pow (replay_buffer.py:322,401,406)."""
     return math.pow(x, y)

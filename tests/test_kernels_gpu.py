@@ -97,6 +97,54 @@ def test_gae_full_size_properties(xp, cuda_device):
     assert np.array_equal(adv[5], a) and np.array_equal(ret[5], g2)
 
 
+# ---- all-fp32 GAE of the legacy experiences path (ppo.py:686-713, ippo.py:703-724) ------------------
+@pytest.mark.parametrize("seed", [0, 1, 2, 3, 4])
+def test_gae_f32_golden_bitwise(cuda_device, seed):
+    from agilerl_b200.returns import gae_from_experiences
+
+    g = load_golden(f"gae32_s{seed}")
+    adv, ret = gae_from_experiences(g["rewards"], g["values"], g["dones"], g["next_value"], g["next_done"],
+                                    float(g["gamma"]), float(g["gae_lambda"]))
+    assert adv.is_cuda and adv.dtype == torch.float32 and tuple(adv.shape) == g["adv"].shape
+    assert np.array_equal(adv.cpu().numpy(), g["adv"]) and np.array_equal(ret.cpu().numpy(), g["ret"])
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1), (3, 50, 96), (2, 9, 33), (16, 128, 1024), (1, 300, 7)])
+def test_gae_f32_population_vs_oracle(cuda_device, shape):
+    from agilerl_b200.returns import gae_from_experiences
+
+    P, T, N = shape
+    rng = np.random.default_rng(P * 77 + T)
+    r = rng.standard_normal((P, T, N)).astype(np.float32)
+    v = rng.standard_normal((P, T, N)).astype(np.float32)
+    d = rng.random((P, T, N)) < 0.05
+    nv = rng.standard_normal((P, N)).astype(np.float32)
+    nd = (rng.random((P, N)) < 0.2).astype(np.float32)
+    adv, ret = gae_from_experiences(r, v, d.astype(np.int64), nv, nd, 0.99, 0.95)
+    adv, ret = adv.cpu().numpy(), ret.cpu().numpy()
+    for p in range(0, P, max(1, P // 3)):
+        a, g = xo.gae_f32(r[p], v[p], d[p], nv[p], nd[p], 0.99, 0.95)
+        assert np.array_equal(adv[p], a) and np.array_equal(ret[p], g)
+
+
+def test_gae_f32_single_env_and_errors(cuda_device):
+    from agilerl_b200.returns import gae_from_experiences
+
+    rng = np.random.default_rng(0)
+    r, v = rng.standard_normal(40).astype(np.float32), rng.standard_normal(40).astype(np.float32)
+    d = rng.random(40) < 0.1
+    adv, ret = gae_from_experiences(r, v, d, np.float32(0.3), np.float32(0.0), 0.9, 0.8)
+    a, g = xo.gae_f32(r[:, None], v[:, None], d[:, None], [0.3], [0.0], 0.9, 0.8)
+    assert adv.shape == (40,) and np.array_equal(adv.cpu().numpy(), a[:, 0]) and np.array_equal(ret.cpu().numpy(), g[:, 0])
+    with pytest.raises(ValueError):
+        gae_from_experiences(r, v[:-1], d, 0.3, 0.0, 0.9, 0.8)
+    with pytest.raises(ValueError):
+        gae_from_experiences(r[:, None], v[:, None], d[:, None], [0.3, 0.1], [0.0], 0.9, 0.8)
+    e = torch.empty(0, 4)
+    adv, ret = gae_from_experiences(e, e, e, torch.zeros(4), torch.zeros(4), 0.9, 0.8)
+    assert adv.shape == (0, 4)
+
+
 # ---- trees --------------------------------------------------------------------------------------
 class DevTree:
     """(sum,min) interleaved device tree driven through the C-ABI."""

@@ -29,6 +29,16 @@ def test_gae_scalar_restatement_is_the_same_rounding_sequence(seed):
     assert np.array_equal(adv, g["adv"]) and np.array_equal(ret, g["ret"])
 
 
+@pytest.mark.parametrize("seed", [0, 1, 2, 3, 4])
+def test_gae_f32_matches_reference_loop_bitwise(seed):
+    """The all-fp32 loop of ppo.py:693-713 / ippo.py:705-724 (fixtures from the extracted loop)."""
+    g = load_golden(f"gae32_s{seed}")
+    adv, ret = xo.gae_f32(g["rewards"], g["values"], g["dones"], g["next_value"], g["next_done"],
+                          float(g["gamma"]), float(g["gae_lambda"]))
+    assert adv.dtype == np.float32
+    assert np.array_equal(adv, g["adv"]) and np.array_equal(ret, g["ret"])
+
+
 # ---- segment tree KATs (reference tests/test_components/test_segment_tree.py:39-129) -----------
 def test_tree_set_and_sum_kat():
     t = xo.SegTree(4, "sum")
