@@ -33,7 +33,10 @@ struct Fns {
   sample_fn per_sample = nullptr;
   update_fn per_update = nullptr;
   copy_fn copy_to_device = nullptr;
-  py::object check;  // agilerl_b200._native.check(status, what): raises the mapped exception
+  // agilerl_b200._native.check(status, what): raises the mapped exception.  A borrowed handle whose
+  // reference is deliberately never released: this struct is destroyed by the C runtime's exit
+  // handlers, after the interpreter has been finalised, where a Py_DECREF would touch freed memory.
+  py::handle check;
 } g;
 
 void bind(uint64_t gather, uint64_t per_sample, uint64_t per_update, uint64_t copy_to_device,
@@ -42,7 +45,7 @@ void bind(uint64_t gather, uint64_t per_sample, uint64_t per_update, uint64_t co
   g.per_sample = reinterpret_cast<sample_fn>(per_sample);
   g.per_update = reinterpret_cast<update_fn>(per_update);
   g.copy_to_device = reinterpret_cast<copy_fn>(copy_to_device);
-  g.check = std::move(check);
+  g.check = check.release();  // leaked on purpose, see Fns::check
 }
 
 inline void ok(xp_status_t rc, const char *what) {
