@@ -170,6 +170,13 @@ class ReplayBuffer:
             xp.ring_insert(self._pairs(data, self._leaves), n, self._cursor, self.max_size)
         self._advance(n)
 
+    def _add_rows_with(self, n: int, insert) -> None:
+        """``add`` of ``n`` rows whose movement into the ring is done by ``insert(cursor)`` — the fused
+        exchange + insert of the replicated shared memory (``population.ReplicatedReplay``)."""
+        with nv.on_device(self.storage_device):
+            insert(self._cursor)
+        self._advance(n)
+
     def _advance(self, n: int) -> None:
         self._cursor = (self._cursor + n) % self.max_size
         self._size = min(self._size + n, self.max_size)
@@ -472,6 +479,14 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         with nv.on_device(self.storage_device):
             xp.ring_insert(self._pairs(data, self._leaves), n, self._cursor, self.max_size)
             # leaves tree_ptr.. := max_priority ** alpha (:306-309), no host round trip
+            xp.per_add(h, self._state, self.tree_ptr, n, self.max_size, self.alpha)
+        self._advance(n)
+        self.tree_ptr = (self.tree_ptr + n) % self.max_size
+
+    def _add_rows_with(self, n: int, insert) -> None:
+        _, _, st, h = self._ensure_trees()
+        with nv.on_device(self.storage_device):
+            insert(self._cursor)
             xp.per_add(h, self._state, self.tree_ptr, n, self.max_size, self.alpha)
         self._advance(n)
         self.tree_ptr = (self.tree_ptr + n) % self.max_size

@@ -9,7 +9,9 @@
 //   2. waits until each peer has said the same (acquire loads of its own flag array),
 //   3. copies each peer's block straight out of the peer's memory into the local rank-major
 //      arrays that xp_per_update consumes.
-// CTA r talks to peer r, so the waits and the copies of different peers overlap.  No NCCL call,
+// CTA r talks to peer r, so the waits and the copies of different peers overlap.  The same
+// handshake fronts xp_peer_ring_insert, which drops every rank's new transitions straight into
+// the local replica's ring (the per-step insert broadcast of the shared memory).  No NCCL call,
 // no host synchronisation; a peer that never arrives is reported through the error flag after a
 // bounded wait instead of hanging the GPU.
 #include "common.cuh"
@@ -35,56 +37,123 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
   return v;
 }
 
+// Signal "rank p.rank reached `epoch`" to peer r (when `signal`), then wait for peer r's epoch.
+// Called by one thread of the CTA; returns false after a bounded wait (the error flag is set).
+template <class P>
+__device__ __forceinline__ bool peer_sync(const P &p, int r, bool signal) {
+  if (r == p.rank) return true;
+  if (signal) {
+    __threadfence_system();                          // this rank's block is visible system-wide
+    st_release_sys(p.flags[r] + p.rank, p.epoch);    // "rank p.rank reached epoch" in r's array
+  }
+  const long long t0 = clock64();
+  // epochs only grow; the signed difference survives wrap-around
+  while ((int)(ld_acquire_sys(p.flags[p.rank] + r) - p.epoch) < 0) {
+    if (clock64() - t0 > p.timeout_cycles) {
+      if (p.err) *p.err = 1;
+      return false;
+    }
+    __nanosleep(64);
+  }
+  return true;
+}
+
+// Copy `bytes` from peer-mapped `src` to local `dst` with W-byte system-scope loads, U of them in
+// flight per thread (NVLink round trips are ~2 us); the CTA handles vectors [v0, v1).
+template <int W>
+__device__ __forceinline__ void pull_vec(const char *src, char *dst, long long v0, long long v1) {
+  constexpr int U = 8;
+  for (long long b0 = v0; b0 < v1; b0 += (long long)blockDim.x * U) {
+    if constexpr (W == 16) {
+      int4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = b0 + (long long)u * blockDim.x + threadIdx.x;
+        if (i < v1)
+          asm volatile("ld.relaxed.sys.global.v4.s32 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w)
+                       : "l"(src + (i << 4)));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = b0 + (long long)u * blockDim.x + threadIdx.x;
+        if (i < v1) *reinterpret_cast<int4 *>(dst + (i << 4)) = v[u];
+      }
+    } else if constexpr (W == 4) {
+      int v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = b0 + (long long)u * blockDim.x + threadIdx.x;
+        if (i < v1) asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(v[u]) : "l"(src + (i << 2)));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = b0 + (long long)u * blockDim.x + threadIdx.x;
+        if (i < v1) *reinterpret_cast<int *>(dst + (i << 2)) = v[u];
+      }
+    } else {
+      for (long long i = b0 + threadIdx.x; i < v1 && i < b0 + (long long)blockDim.x * U; i += blockDim.x)
+        dst[i] = *reinterpret_cast<const volatile char *>(src + i);
+    }
+  }
+}
+
+// Part `part` of `parts` of a [src, src+bytes) -> dst copy, widest vector the alignment allows.
+__device__ __forceinline__ void pull(const char *src, char *dst, long long bytes, int part, int parts) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | (uintptr_t)bytes;
+  const int sh = (a & 15) == 0 ? 4 : (a & 3) == 0 ? 2 : 0;
+  const long long n = bytes >> sh;
+  const long long per = (n + parts - 1) / parts;
+  const long long v0 = per * part, v1 = v0 + per < n ? v0 + per : n;
+  if (v0 >= v1) return;
+  if (sh == 4) pull_vec<16>(src, dst, v0, v1);
+  else if (sh == 2) pull_vec<4>(src, dst, v0, v1);
+  else pull_vec<1>(src, dst, v0, v1);
+}
+
 __global__ void __launch_bounds__(256) peer_allgather_kernel(const __grid_constant__ PeerParams p) {
   const int r = blockIdx.x;  // the peer this CTA serves
   __shared__ int s_ok;
-  if (threadIdx.x == 0) {
-    s_ok = 1;
-    if (r != p.rank) {
-      __threadfence_system();                          // this rank's block is visible system-wide
-      st_release_sys(p.flags[r] + p.rank, p.epoch);    // "rank p.rank reached epoch" in r's array
-      const long long t0 = clock64();
-      // epochs only grow; the signed difference survives wrap-around
-      while ((int)(ld_acquire_sys(p.flags[p.rank] + r) - p.epoch) < 0) {
-        if (clock64() - t0 > p.timeout_cycles) {
-          s_ok = 0;
-          if (p.err) *p.err = 1;
-          break;
-        }
-        __nanosleep(64);
-      }
-    }
-  }
+  if (threadIdx.x == 0) s_ok = peer_sync(p, r, true) ? 1 : 0;
   __syncthreads();
   if (!s_ok) return;
   for (int k = 0; k < p.n_segs; ++k) {
     const xp_peer_seg &sg = p.seg[k];
+    pull(p.base[r] + sg.src_off, static_cast<char *>(sg.dst) + (long long)r * sg.bytes, sg.bytes, 0, 1);
+  }
+}
+
+// ---- exchange + ring insert in one kernel --------------------------------------------------
+// Every rank's n_rows new rows per key sit in its peer-mapped block; rank-major row q = r*n_rows+i
+// lands in local ring slot (cursor + q) % ring_rows — ReplayBuffer.add of the concatenated batch
+// (replay_buffer.py:100-107) on every replica, without materialising the concatenation.
+// grid = (ctas_per_peer, world): CTA (c, r) moves the c-th share of peer r's rows; CTA (0, r)
+// sends this rank's signal to peer r, every CTA of row r waits for peer r's.
+struct PeerRingParams {
+  const char *base[XP_MAX_PEERS];
+  unsigned *flags[XP_MAX_PEERS];
+  xp_peer_ring_seg seg[XP_MAX_PEER_RING_SEGS];
+  int n_segs, rank, world;
+  unsigned epoch;
+  int *err;
+  long long timeout_cycles;
+  long long n_rows, cursor, ring_rows;
+};
+
+__global__ void __launch_bounds__(256) peer_ring_insert_kernel(const __grid_constant__ PeerRingParams p) {
+  const int r = blockIdx.y, c = blockIdx.x, parts = gridDim.x;
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) s_ok = peer_sync(p, r, c == 0) ? 1 : 0;
+  __syncthreads();
+  if (!s_ok) return;
+  const long long start = (p.cursor + (long long)r * p.n_rows) % p.ring_rows;
+  const long long first = p.n_rows < p.ring_rows - start ? p.n_rows : p.ring_rows - start;  // rows before the wrap
+  for (int k = 0; k < p.n_segs; ++k) {
+    const xp_peer_ring_seg &sg = p.seg[k];
     const char *src = p.base[r] + sg.src_off;
-    char *dst = static_cast<char *>(sg.dst) + (long long)r * sg.bytes;
-    if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | (uintptr_t)sg.bytes) & 15) == 0) {
-      const long long n16 = sg.bytes >> 4;
-      constexpr int U = 8;  // NVLink round trips are ~2 us: keep 8 loads per thread in flight
-      for (long long b0 = 0; b0 < n16; b0 += (long long)blockDim.x * U) {
-        int4 v[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const long long i = b0 + (long long)u * blockDim.x + threadIdx.x;
-          if (i < n16)
-            asm volatile("ld.relaxed.sys.global.v4.s32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w)
-                         : "l"(src + (i << 4)));
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const long long i = b0 + (long long)u * blockDim.x + threadIdx.x;
-          if (i < n16) *reinterpret_cast<int4 *>(dst + (i << 4)) = v[u];
-        }
-      }
-    } else {
-      for (long long i = threadIdx.x; i < sg.bytes; i += blockDim.x) {
-        dst[i] = *reinterpret_cast<const volatile char *>(src + i);
-      }
-    }
+    char *dst = static_cast<char *>(sg.dst);
+    pull(src, dst + start * sg.row_bytes, first * sg.row_bytes, c, parts);
+    if (first < p.n_rows) pull(src + first * sg.row_bytes, dst, (p.n_rows - first) * sg.row_bytes, c, parts);
   }
 }
 
@@ -120,6 +189,51 @@ xp_status_t xp_peer_allgather(const void *const *peer_base, void *const *peer_fl
   p.timeout_cycles = 4000000000ll;  // ~2 s at 2 GHz: report, do not hang
   peer_allgather_kernel<<<world, 256, 0, (cudaStream_t)stream>>>(p);
   return xp::check_launch("xp_peer_allgather");
+}
+
+xp_status_t xp_peer_ring_insert(const void *const *peer_base, void *const *peer_flags, int rank, int world,
+                                uint32_t epoch, const xp_peer_ring_seg *segs, int n_segs, int64_t n_rows,
+                                int64_t cursor, int64_t ring_rows, int *err_flag_dev, void *stream) {
+  XP_REQUIRE(world >= 1 && world <= XP_MAX_PEERS, XP_ERR_INVALID, "xp_peer_ring_insert: world %d not in [1,%d]",
+             world, XP_MAX_PEERS);
+  XP_REQUIRE(rank >= 0 && rank < world, XP_ERR_INVALID, "xp_peer_ring_insert: bad rank");
+  XP_REQUIRE(n_segs >= 1 && n_segs <= XP_MAX_PEER_RING_SEGS, XP_ERR_INVALID,
+             "xp_peer_ring_insert: n_segs %d not in [1,%d]", n_segs, XP_MAX_PEER_RING_SEGS);
+  XP_REQUIRE(peer_base && peer_flags && segs, XP_ERR_INVALID, "xp_peer_ring_insert: null pointer");
+  XP_REQUIRE(ring_rows > 0 && cursor >= 0 && cursor < ring_rows, XP_ERR_INVALID, "xp_peer_ring_insert: bad cursor");
+  XP_REQUIRE(n_rows >= 0 && n_rows * world <= ring_rows, XP_ERR_INVALID,
+             "xp_peer_ring_insert: %lld rows x %d ranks exceed the ring (%lld)", (long long)n_rows, world,
+             (long long)ring_rows);
+  PeerRingParams p{};
+  long long bytes = 0;
+  for (int r = 0; r < world; ++r) {
+    XP_REQUIRE(peer_base[r] && peer_flags[r], XP_ERR_INVALID, "xp_peer_ring_insert: null peer pointer");
+    p.base[r] = static_cast<const char *>(peer_base[r]);
+    p.flags[r] = static_cast<unsigned *>(peer_flags[r]);
+  }
+  for (int k = 0; k < n_segs; ++k) {
+    XP_REQUIRE(segs[k].row_bytes > 0 && segs[k].src_off >= 0 && segs[k].dst, XP_ERR_INVALID,
+               "xp_peer_ring_insert: bad segment %d", k);
+    p.seg[k] = segs[k];
+    bytes += segs[k].row_bytes * n_rows;
+  }
+  p.n_segs = n_segs;
+  p.rank = rank;
+  p.world = world;
+  p.epoch = epoch;
+  p.err = err_flag_dev;
+  p.timeout_cycles = 4000000000ll;
+  p.n_rows = n_rows;
+  p.cursor = cursor;
+  p.ring_rows = ring_rows;
+  // one CTA per 64 KB of a peer's rows, and never more CTAs than stay resident together (the
+  // signalling CTAs must not queue behind waiting ones)
+  long long parts = (bytes + 65535) / 65536;
+  const long long cap = 128 / world;
+  if (parts > cap) parts = cap;
+  if (parts < 1) parts = 1;
+  peer_ring_insert_kernel<<<dim3((unsigned)parts, (unsigned)world), 256, 0, (cudaStream_t)stream>>>(p);
+  return xp::check_launch("xp_peer_ring_insert");
 }
 
 }  // extern "C"

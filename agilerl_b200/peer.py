@@ -2,6 +2,8 @@
 
 ``PeerExchange`` owns, on every rank, a block of peer-mapped ("symmetric") memory that the other
 ranks of the group can read directly, plus a small flag array the peers signal through.
+``ring_insert()`` launches ONE kernel (``xp_peer_ring_insert``) that signals, waits and writes every
+rank's new transitions straight into the local replica's ring storage (exchange + insert fused).
 ``allgather()`` launches ONE kernel (``xp_peer_allgather``) that signals, waits and copies every
 rank's block into local rank-major arrays — the job of two NCCL all-gathers, in one launch and
 without NCCL's per-collective latency.  The memory mapping itself comes from
@@ -23,6 +25,10 @@ from . import _native as nv
 
 class XpPeerSeg(C.Structure):
     _fields_ = [("src_off", C.c_int64), ("dst", C.c_void_p), ("bytes", C.c_int64)]
+
+
+class XpPeerRingSeg(C.Structure):
+    _fields_ = [("src_off", C.c_int64), ("dst", C.c_void_p), ("row_bytes", C.c_int64)]
 
 
 def available(group=None) -> bool:
@@ -62,6 +68,7 @@ class PeerExchange:
         self._segs_meta = list(segments)
         self._out = []
         self._segs = (XpPeerSeg * len(self._segs_meta))()
+        self._fn_ring = nv.load().xp_peer_ring_insert
         for i, (off, nbytes, dtype) in enumerate(self._segs_meta):
             o = torch.empty(self.world * nbytes // dtype.itemsize, dtype=dtype, device=device)
             self._out.append(o)
@@ -93,6 +100,23 @@ class PeerExchange:
                           self._segs, len(self._segs_meta), self.err.data_ptr(),
                           nv.raw_stream(self.device.index)), "xp_peer_allgather")
         return self._out
+
+    def ring_insert(self, keys, n_rows: int, cursor: int, ring_rows: int) -> None:
+        """Publish block ``current`` and insert every rank's rows into the local ring in ONE kernel
+        (``xp_peer_ring_insert``).  ``keys``: ``[(offset_in_block, storage [ring_rows, ...])]`` —
+        this rank has written its ``n_rows`` rows of each key at that offset of block ``current``;
+        row ``r * n_rows + i`` of the rank-major concatenation lands in slot
+        ``(cursor + r * n_rows + i) % ring_rows`` of ``storage``."""
+        k = self.epoch & 1
+        self.epoch += 1
+        segs = (XpPeerRingSeg * len(keys))()
+        for i, (off, storage) in enumerate(keys):
+            segs[i].src_off = off
+            segs[i].dst = storage.data_ptr()
+            segs[i].row_bytes = storage[0].numel() * storage.element_size()
+        nv.check(self._fn_ring(self._bases[k], self._flags, self.rank, self.world, self.epoch & 0xFFFFFFFF,
+                               segs, len(keys), n_rows, cursor, ring_rows, self.err.data_ptr(),
+                               nv.raw_stream(self.device.index)), "xp_peer_ring_insert")
 
     def check(self) -> None:
         if int(self.err.item()) != 0:

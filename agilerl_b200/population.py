@@ -93,6 +93,9 @@ class ReplicatedReplay:
         self._px = None      # peer.PeerExchange, created on the first CUDA update
         self._px_n = 0
         self._peer_ok = None
+        self._ix = None      # peer.PeerExchange of the insert path (blocks sized for one add)
+        self._ix_sig = None
+        self._ix_ok = None
 
     def add(self, local_rows) -> None:
         """``local_rows``: the new transitions of this rank's agents, agent-major ``[n]`` (equal
@@ -101,7 +104,48 @@ class ReplicatedReplay:
         dev = self.memory.storage_device if _is_cuda_backend(self.group) else None
         if dev is not None:
             local = local.to(dev)
+        if dev is not None and _group_size(self.group) > 1 and self._ix_ok is not False \
+                and type(self.memory) in _PEER_INSERT_TYPES and self._peer_add(local):
+            return
         self.memory.add(all_gather_batch(local, self.group))
+
+    def _peer_add(self, local) -> bool:
+        """Exchange + insert in ONE kernel over NVLink peer memory (``xp_peer_ring_insert``): each
+        rank stages its rows in its peer-mapped block, every replica pulls all ranks' rows straight
+        into its ring at the rank-major slots.  Returns False when peer memory is unavailable (the
+        NCCL all-gather then serves)."""
+        mem = self.memory
+        data, n = mem._prepare(local)
+        if mem._storage is None:
+            mem._init(data)
+        world = _group_size(self.group)
+        if world * n > mem.max_size:
+            return False
+        pairs = mem._pairs(data, mem._leaves)
+        sig = (n, tuple((tuple(t.shape), t.dtype) for t, _ in pairs))
+        try:
+            if self._ix is None or self._ix_sig != sig:
+                from . import peer
+
+                if len(pairs) > 16 or not peer.available(self.group):
+                    raise RuntimeError("peer insert unavailable")
+                offs, off = [], 0
+                for t, _ in pairs:
+                    offs.append(off)
+                    off += (t.numel() * t.element_size() + 255) // 256 * 256
+                self._ix = peer.PeerExchange(off, [], torch.device(mem.storage_device), self.group)
+                self._ix_sig, self._ix_offs, self._ix_ok = sig, offs, True
+        except Exception:
+            if self._ix_ok:
+                raise
+            self._ix_ok = False
+            return False
+        px, k = self._ix, self._ix.current
+        for (t, _), off in zip(pairs, self._ix_offs):
+            px.view(k, off, t.numel(), t.dtype).copy_(t.reshape(-1))
+        keys = [(off, d) for (_, d), off in zip(pairs, self._ix_offs)]
+        mem._add_rows_with(world * n, lambda cursor: px.ring_insert(keys, n, cursor, mem.max_size))
+        return True
 
     def update_priorities(self, local_idx: torch.Tensor, local_prio: torch.Tensor) -> None:
         """(idx, priority) pairs of this rank's agents -> applied everywhere in rank-major order
@@ -148,6 +192,11 @@ class ReplicatedReplay:
     def sample(self, *args, **kwargs):
         """Sampling and gathering are local to a replica."""
         return self.memory.sample(*args, **kwargs)
+
+
+from .components.replay_buffer import PrioritizedReplayBuffer, ReplayBuffer  # noqa: E402
+
+_PEER_INSERT_TYPES = (ReplayBuffer, PrioritizedReplayBuffer)
 
 
 def _is_cuda_backend(group=None) -> bool:

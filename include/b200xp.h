@@ -244,6 +244,26 @@ xp_status_t xp_peer_allgather(const void *const *peer_base, void *const *peer_fl
                               int world, uint32_t epoch, const xp_peer_seg *segs, int n_segs,
                               int *err_flag_dev, void *stream);
 
+/* Exchange + insert in one kernel: the per-step broadcast of newly collected transitions into the
+ * replicated shared memory (one `memory` object for the whole population,
+ * training/train_off_policy.py:46,343-345; ReplayBuffer.add, components/replay_buffer.py:72-112).
+ * Every rank has written its n_rows new rows of key k at peer_base[r] + segs[k].src_off
+ * (row-major, row_bytes each).  After the same signal/wait handshake as xp_peer_allgather, the
+ * rank-major row q = r * n_rows + i is written to ring slot (cursor + q) % ring_rows of
+ * segs[k].dst — what ReplayBuffer.add does with the concatenated batch (:100-107, wrap
+ * included), without materialising the concatenation.  The caller advances its cursor by
+ * world * n_rows.  Requires world * n_rows <= ring_rows.                                      */
+#define XP_MAX_PEER_RING_SEGS 16
+typedef struct xp_peer_ring_seg {
+  int64_t src_off;   /* byte offset of this key's rows inside every rank's block */
+  void *dst;         /* local ring storage of the key, ring_rows * row_bytes     */
+  int64_t row_bytes;
+} xp_peer_ring_seg;
+xp_status_t xp_peer_ring_insert(const void *const *peer_base, void *const *peer_flags, int rank,
+                                int world, uint32_t epoch, const xp_peer_ring_seg *segs,
+                                int n_segs, int64_t n_rows, int64_t cursor, int64_t ring_rows,
+                                int *err_flag_dev, void *stream);
+
 /* ---- host-side RNG mirror (no GPU needed) -------------------------------------------- */
 /* torch's CPU generator is mt19937; these reproduce the raw 32-bit stream so that the
  * engine consumes "identical uniform draws" (replay_buffer.py:125,377).

@@ -102,3 +102,56 @@ def test_replicated_replay_uses_peer_exchange(tmp_path):
     q1 = torch.load(tmp_path / "q1.pt", weights_only=False)
     assert q0["peer"] is True and q1["peer"] is True
     assert torch.equal(q0["tree"], q1["tree"]) and torch.equal(q0["obs"], q1["obs"])
+
+
+def _rows(step, rank, n):
+    g = torch.Generator().manual_seed(1000 * step + rank)
+    return {"obs": torch.randint(0, 256, (n, 7), generator=g, dtype=torch.uint8),   # 7-byte rows: byte path
+            "vec": torch.randn(n, 3, generator=g),                                  # 12-byte rows: 4-byte path
+            "wide": torch.randn(n, 8, generator=g),                                 # 32-byte rows: 128-bit path
+            "reward": torch.randn(n, generator=g)}
+
+
+def _worker_insert(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from agilerl_b200.components import PrioritizedReplayBuffer, ReplayBuffer, TensorBatch
+    from agilerl_b200.population import ReplicatedReplay
+
+    ok, used = True, []
+    for cls, cap in ((PrioritizedReplayBuffer, 40), (ReplayBuffer, 52)):
+        n = 8
+        mem, exp = cls(cap, device=dev), cls(cap, device=dev)
+        rep = ReplicatedReplay(mem)
+        for step in range(6):  # 6 x 16 rows into 40 / 52 slots: wraps inside a rank's rows and between ranks
+            rep.add(TensorBatch(_rows(step, rank, n), batch_size=[n]))
+            cat = {k: torch.cat([_rows(step, r, n)[k] for r in range(world)]) for k in _rows(0, 0, 1)}
+            exp.add(TensorBatch(cat, batch_size=[world * n]))
+            for path in exp._leaves:
+                ok &= torch.equal(mem._leaves[path], exp._leaves[path])
+            ok &= (mem._cursor, mem._size, mem.counter) == (exp._cursor, exp._size, exp.counter)
+        if cls is PrioritizedReplayBuffer:
+            ok &= torch.equal(mem._trees[2].nodes, exp._trees[2].nodes) and mem.tree_ptr == exp.tree_ptr
+        rep._ix.check()
+        used.append(rep._ix_ok)
+    torch.save({"ok": bool(ok), "used": used}, os.path.join(out_dir, f"i{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_replicated_add_is_one_peer_kernel(tmp_path):
+    """ReplicatedReplay.add through xp_peer_ring_insert == ReplayBuffer.add of the rank-major
+    concatenation (replay_buffer.py:100-107), wrap included, for every row width."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    world = 2
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_worker_insert, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        res = torch.load(tmp_path / f"i{r}.pt", weights_only=False)
+        assert res["used"] == [True, True], "peer insert path was not taken"
+        assert res["ok"]

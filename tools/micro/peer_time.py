@@ -24,4 +24,20 @@ def nccl():
 t_peer = timeit(px.allgather); t_nccl = timeit(nccl)
 px.check()
 if rank == 0: print(f"world {world}: xp_peer_allgather {t_peer:.2f} us   NCCL (2 coalesced all-gathers) {t_nccl:.2f} us")
+# ---- insert path: C2 rows (16 envs x 4 agents per rank, 56 460 B per row) ------------------
+from agilerl_b200.components import ReplayBuffer, TensorBatch
+from agilerl_b200.population import ReplicatedReplay, all_gather_batch
+rows = 64
+batch = TensorBatch({"obs": torch.zeros(rows, 84, 84, 4, dtype=torch.uint8, device=dev),
+                     "next_obs": torch.zeros(rows, 84, 84, 4, dtype=torch.uint8, device=dev),
+                     "action": torch.zeros(rows, device=dev), "reward": torch.zeros(rows, device=dev),
+                     "done": torch.zeros(rows, device=dev)}, batch_size=[rows])
+m1, m2 = ReplayBuffer(65536, device=dev), ReplayBuffer(65536, device=dev)
+rp = ReplicatedReplay(m1)
+t_pi = timeit(lambda: rp.add(batch), 100)
+assert rp._ix_ok, "peer insert not used"
+rp._ix.check()
+t_ni = timeit(lambda: m2.add(all_gather_batch(batch)), 100)
+if rank == 0: print(f"world {world}: replicated add of {rows} C2 rows/rank ({rows * 56460 / 1e6:.1f} MB): peer ring insert "
+                    f"{t_pi:.1f} us   NCCL all-gather per key + xp_ring_insert {t_ni:.1f} us (host-inclusive, stream-timed)")
 dist.destroy_process_group()
