@@ -178,6 +178,149 @@ __device__ __forceinline__ long long descend_wide(const double *sum, long long s
   return idx - cap;
 }
 
+// The same walk again, D levels per memory round trip from ONE aligned group: the 2^D nodes D levels
+// below the current node are contiguous in heap order (D = 3, stride 2: one 128-byte line).  The
+// nodes of the skipped levels are not read but recomputed — every internal node of a tree kept by
+// this library IS `left + right` in fp64 (segment_tree.py:89-95 recomputes every ancestor that
+// way, and so do the batched sets), so `__dadd_rn(left, right)` reproduces the stored value bit for
+// bit, and the comparisons and subtractions below see exactly what the plain walk reads.  Against
+// the plain walk: a third of the dependent round trips, and per sample 128 B of whole lines instead
+// of three 32-byte sectors in three different 64-byte DRAM bursts.
+template <int D>
+__device__ __forceinline__ long long descend_skip(const double *sum, long long stride, long long cap,
+                                                  double ub, double *leaf_val, bool vec256, int stop_rem = 0,
+                                                  double *ub_out = nullptr, int *rem_out = nullptr) {
+  long long idx = 1;
+  int rem = 63 - __clzll(cap);
+  double last = 0.0;
+  if (rem == 0) last = __ldg(&sum[stride]);
+  // levels that do not fill a group are walked one by one at the (cached, shared) top
+  for (int k = rem % D; k > 0; --k, --rem) {
+    const long long left = 2 * idx;
+    const double lv = __ldg(&sum[left * stride]);
+    if (lv > ub) {
+      idx = left;
+      last = lv;
+    } else {
+      ub = __dsub_rn(ub, lv);
+      idx = left + 1;
+      if (rem == 1) last = __ldg(&sum[idx * stride]);
+    }
+  }
+  while (rem > stop_rem) {
+    const long long base = idx << D;
+    double c[1 << D];
+    if (vec256 && stride == 2) {
+      // interleaved (sum, min) nodes: two nodes per 256-bit load, the group is 2^D / 2 of them
+#pragma unroll
+      for (int j = 0; j < (1 << D); j += 2) {
+        double mn0, mn1;
+        asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+                     : "=d"(c[j]), "=d"(mn0), "=d"(c[j + 1]), "=d"(mn1)
+                     : "l"(sum + (base + j) * 2));
+      }
+    } else if (vec256 && stride == 1 && D >= 2) {
+#pragma unroll
+      for (int j = 0; j < (1 << D); j += 4)
+        asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+                     : "=d"(c[j]), "=d"(c[j + 1]), "=d"(c[j + 2]), "=d"(c[j + 3])
+                     : "l"(sum + base + j));
+    } else {
+#pragma unroll
+      for (int j = 0; j < (1 << D); ++j) c[j] = __ldg(&sum[(base + j) * stride]);
+    }
+    // v[k][j]: node j of the level k below idx; v[D] = c, the levels above recomputed pairwise in
+    // the tree's own order (what is not used below is dropped by the compiler)
+    double v[D + 1][1 << D];
+#pragma unroll
+    for (int j = 0; j < (1 << D); ++j) v[D][j] = c[j];
+#pragma unroll
+    for (int k = D - 1; k >= 1; --k)
+#pragma unroll
+      for (int j = 0; j < (1 << k); ++j) v[k][j] = __dadd_rn(v[k + 1][2 * j], v[k + 1][2 * j + 1]);
+    int o = 0;
+#pragma unroll
+    for (int k = 1; k <= D; ++k) {
+      double lv = v[k][0];  // left child of node o of level k-1
+#pragma unroll
+      for (int m = 1; m < (1 << (k - 1)); ++m) lv = (o == m) ? v[k][2 * m] : lv;
+      if (lv > ub) {
+        o = 2 * o;
+      } else {
+        ub = __dsub_rn(ub, lv);
+        o = 2 * o + 1;
+      }
+    }
+    double lastv = c[0];
+#pragma unroll
+    for (int j = 1; j < (1 << D); ++j) lastv = (o == j) ? c[j] : lastv;
+    last = lastv;
+    idx = base + o;
+    rem -= D;
+  }
+  *leaf_val = last;
+  if (stop_rem > 0) {  // partial walk: hand the state to the caller
+    *ub_out = ub;
+    *rem_out = rem;
+    return idx;
+  }
+  return idx - cap;
+}
+
+// Bottom of the walk for large draws, where the lanes of a warp have diverged and every load
+// instruction of the per-thread walk costs the L1 one tag look-up per lane (measured: the 3-level
+// walk is bound by exactly that, 32 look-ups per 256-bit load).  Here the four lanes of a TEAM
+// fetch the four 32-byte quarters of ONE sample's 128-byte group (8 interleaved nodes), so a warp
+// instruction touches 8 lines instead of 32, and the team walks its four samples in turn (their
+// loads are all in flight together).  Lane q holds level+3 nodes 2q, 2q+1; level+2 node q is
+// their sum, level+1 node q/2 the sum of two neighbouring lanes — the tree's own pairwise order —
+// and the three left-child values a step needs come from the owning lane by shuffle.  Every
+// lane of a team sees the same values and takes the same decisions.  Interleaved (stride 2),
+// 32-byte aligned trees only; `rem` is a multiple of 3.
+__device__ __forceinline__ void descend_team3(const double *sum, unsigned &idx, double &ub, int rem,
+                                              double &leaf_val) {
+  const int lane = threadIdx.x & 31, q = lane & 3, tb = lane & 28;
+  double ubs[4];
+  unsigned ids[4];
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    ubs[s] = __shfl_sync(0xffffffffu, ub, tb | s);
+    ids[s] = __shfl_sync(0xffffffffu, idx, tb | s);
+  }
+  double lasts[4] = {0.0, 0.0, 0.0, 0.0};
+  for (; rem > 0; rem -= 3) {
+    double c0[4], c1[4];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      double m0, m1;
+      asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+                   : "=d"(c0[s]), "=d"(m0), "=d"(c1[s]), "=d"(m1)
+                   : "l"(sum + ((((unsigned long long)ids[s]) << 3) + 2 * q) * 2));
+    }
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const double b = __dadd_rn(c0[s], c1[s]);                                  // level+2 node q
+      const double x = __dadd_rn(b, __shfl_xor_sync(0xffffffffu, b, 1));         // level+1 node q/2
+      double lv = __shfl_sync(0xffffffffu, x, tb);                               // level+1 node 0
+      int o = 0;
+      if (lv > ubs[s]) o = 0; else { ubs[s] = __dsub_rn(ubs[s], lv); o = 1; }
+      lv = __shfl_sync(0xffffffffu, b, tb | (2 * o));                            // level+2 node 2o
+      if (lv > ubs[s]) o = 2 * o; else { ubs[s] = __dsub_rn(ubs[s], lv); o = 2 * o + 1; }
+      lv = __shfl_sync(0xffffffffu, c0[s], tb | o);                              // level+3 node 2o
+      const double rv = __shfl_sync(0xffffffffu, c1[s], tb | o);                 // level+3 node 2o+1
+      if (lv > ubs[s]) { o = 2 * o; lasts[s] = lv; } else { ubs[s] = __dsub_rn(ubs[s], lv); o = 2 * o + 1; lasts[s] = rv; }
+      ids[s] = (ids[s] << 3) + o;
+    }
+  }
+#pragma unroll
+  for (int s = 0; s < 4; ++s)
+    if (q == s) {
+      idx = ids[s];
+      ub = ubs[s];
+      leaf_val = lasts[s];
+    }
+}
+
 __global__ void tree_retrieve_kernel(Tree t, const double *ub, long long B, long long *out) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B) out[i] = descend(t.sum, t.stride, t.cap, ub[i]);
@@ -204,20 +347,26 @@ __device__ __forceinline__ float is_weight(const Tree &t, long long leaf, double
 // Thread order is stratum-major / agent-minor: the lanes of a warp draw in the SAME stratum for
 // different agents, so their descents share every node down to where the stratum splits
 // (identical addresses coalesce into one transaction) and then stay inside one small subtree.
-template <bool WIDE>
+// MODE 1: descend_wide<4> (small draws); 3: descend_skip<3> for the shared top of the tree, then
+// descend_team3 for the diverged bottom (large draws)
+// SMALL: latency-bound draw — every thread derives max_w itself instead of waiting at a barrier.
+template <int MODE, bool SMALL>
 __global__ void __launch_bounds__(256) per_sample_kernel(Tree t, const float *u, long long B,
                                                          long long P, long long total_samples,
                                                          double size, double neg_beta,
                                                          long long *idx_out, float *w_out) {
-  constexpr bool wide = WIDE;
   __shared__ double s_max_w;
   const double total = __ldg(&t.sum[t.stride]);  // sum_tree.sum() == tree[1]
-  if (!wide) {
+  if (!SMALL) {
     if (w_out && threadIdx.x == 0) s_max_w = is_max_weight(t, total, size, neg_beta);
     if (w_out) __syncthreads();
   }
-  const long long tt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (tt >= total_samples) return;
+  long long tt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = tt < total_samples;
+  if (!valid) {
+    if (MODE != 3) return;
+    tt = total_samples - 1;  // team walks need whole warps: idle lanes shadow the last sample
+  }
   const long long i = tt / P;                 // stratum
   const long long j = (tt - i * P) * B + i;   // sample slot: agent-major like the reference loop
   const double seg = __ddiv_rn(total, (double)B);
@@ -225,21 +374,34 @@ __global__ void __launch_bounds__(256) per_sample_kernel(Tree t, const float *u,
   const double b = __dmul_rn(seg, (double)(i + 1));
   // torch.rand(1).item() widens fp32 -> fp64 exactly; u*(b-a)+a in three rounded ops (:377)
   const double ub = __dadd_rn(__dmul_rn((double)u[j], __dsub_rn(b, a)), a);
-  if (wide) {
-    // small batch: latency-bound — wide descent, and every thread derives max_w itself (no barrier)
-    const double mn = w_out ? __ldg(&t.mn[t.stride]) : 0.0;
-    double leaf_val;
-    const long long leaf = descend_wide<4>(t.sum, t.stride, t.cap, ub, &leaf_val);
-    idx_out[j] = leaf;
-    if (w_out) {
-      const double max_w = xp::xp_pow(__dmul_rn(__ddiv_rn(mn, total), size), neg_beta);
-      w_out[j] = is_weight_of(leaf_val, total, size, neg_beta, max_w);
+  // 256-bit loads need 32-byte aligned groups: the base of the node array decides
+  const bool vec256 = (reinterpret_cast<uintptr_t>(t.sum) & 31) == 0 && (t.stride == 1 || t.stride == 2);
+  const double mn = (SMALL && w_out) ? __ldg(&t.mn[t.stride]) : 0.0;
+  double leaf_val = 0.0;
+  long long leaf;
+  if (MODE == 1) leaf = descend_wide<4>(t.sum, t.stride, t.cap, ub, &leaf_val);
+  else {
+    constexpr int kTeamLevels = 12;  // the warp's lanes (one stratum, different agents) split about here
+    const int L = 63 - __clzll(t.cap);
+    int team = L < kTeamLevels ? L - L % 3 : kTeamLevels;
+    if (!vec256 || t.stride != 2 || t.cap > (1ll << 27)) team = 0;
+    if (team == 0) {
+      leaf = descend_skip<3>(t.sum, t.stride, t.cap, ub, &leaf_val, vec256);
+    } else {
+      double ub2 = ub;
+      int rem = L;
+      unsigned idx = 1;
+      if (L > team) idx = (unsigned)descend_skip<3>(t.sum, t.stride, t.cap, ub, &leaf_val, vec256, team, &ub2, &rem);
+      descend_team3(t.sum, idx, ub2, rem, leaf_val);
+      leaf = (long long)idx - t.cap;
     }
-    return;
+    if (!valid) return;
   }
-  const long long leaf = descend(t.sum, t.stride, t.cap, ub);
   idx_out[j] = leaf;
-  if (w_out) w_out[j] = is_weight(t, leaf, total, size, neg_beta, s_max_w);
+  if (w_out) {
+    const double max_w = SMALL ? xp::xp_pow(__dmul_rn(__ddiv_rn(mn, total), size), neg_beta) : s_max_w;
+    w_out[j] = is_weight_of(leaf_val, total, size, neg_beta, max_w);
+  }
 }
 
 __global__ void __launch_bounds__(256) per_weights_kernel(Tree t, const long long *idx,
@@ -368,15 +530,17 @@ xp_status_t xp_per_sample(const xp_tree *tree, const float *u_dev, int64_t B, in
   const long long total = B * P;
   if (total == 0) return XP_OK;
   XP_REQUIRE(u_dev && idx_out_dev, XP_ERR_INVALID, "xp_per_sample: null pointer");
-  const int wide = total <= 16384;  // latency-bound: 4 levels per round trip, small CTAs on many SMs
-  const int threads = wide ? 64 : 256;
-  const unsigned grid = (unsigned)((total + threads - 1) / threads);
-  if (wide)
-    per_sample_kernel<true><<<grid, threads, 0, (cudaStream_t)stream>>>(
+  // small draws are latency-bound: small CTAs on many SMs, 4 levels per round trip (descend_wide);
+  // large ones are bound by L1 tag look-ups of diverged lanes: line groups + lane teams
+  if (total <= 16384) {
+    const unsigned grid = (unsigned)((total + 63) / 64);
+    per_sample_kernel<1, true><<<grid, 64, 0, (cudaStream_t)stream>>>(
         t, u_dev, B, P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
-  else
-    per_sample_kernel<false><<<grid, threads, 0, (cudaStream_t)stream>>>(
+  } else {
+    const unsigned grid = (unsigned)((total + 127) / 128);
+    per_sample_kernel<3, false><<<grid, 128, 0, (cudaStream_t)stream>>>(
         t, u_dev, B, P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
+  }
   return xp::check_launch("xp_per_sample");
 }
 

@@ -365,3 +365,43 @@ def reference_gae_f32(rewards, values, dones, next_value, next_done, gamma, gae_
         exec(_cache[key], g)
     adv = g["advantages"]
     return adv.numpy().copy(), (adv + values).numpy().copy()
+
+
+def load_reference_llm_gae():
+    """The UNMODIFIED token- and turn-level GAE of the LLM PPO path, extracted by name:
+    ``PPO._compute_gae_returns_token`` / ``PPO._compute_gae_returns`` (algorithms/ppo_llm.py:758-872)
+    with ``masked_mean / masked_var / masked_whiten / pool_by_turns`` (utils/llm_utils.py:215-312)."""
+    if "llm_gae" in _cache:
+        return _cache["llm_gae"]
+    g = {"torch": torch, "np": np}
+    u = _extract(os.path.join(REF_PKG, "utils", "llm_utils.py"),
+                 ["masked_mean", "masked_var", "masked_whiten", "pool_by_turns"])
+    for name in ("masked_mean", "masked_var", "masked_whiten", "pool_by_turns"):
+        exec("from __future__ import annotations\n" + u[name], g)
+    path = os.path.join(REF_PKG, "algorithms", "ppo_llm.py")
+    cls = next(n.name for n in ast.parse(open(path).read()).body
+               if isinstance(n, ast.ClassDef) and any(isinstance(b, ast.FunctionDef) and b.name == "_compute_gae_returns_token"
+                                                      for b in n.body))
+    m = _extract(path, ["_compute_gae_returns_token", "_compute_gae_returns"], cls=cls)
+    for name in ("_compute_gae_returns_token", "_compute_gae_returns"):
+        exec("from __future__ import annotations\n" + m[name], g)
+    _cache["llm_gae"] = types.SimpleNamespace(token=g["_compute_gae_returns_token"], turn=g["_compute_gae_returns"])
+    return _cache["llm_gae"]
+
+
+def reference_llm_gae(rewards, values, action_mask, gamma, gae_lambda, adv_whitening, turn_ids=None,
+                      turn_value_reduction="final_value"):
+    """Run the reference method on fp32 CPU tensors ``[batch, seq_len]``; ``turn_ids`` None selects the
+    token-level variant.  Returns ``(token_returns, token_advantages)`` as fp32 numpy."""
+    ref = load_reference_llm_gae()
+    me = types.SimpleNamespace(gamma=gamma, gae_lambda=gae_lambda, adv_whitening=adv_whitening,
+                               turn_value_reduction=turn_value_reduction)
+    r = torch.from_numpy(np.ascontiguousarray(rewards, dtype=np.float32))
+    v = torch.from_numpy(np.ascontiguousarray(values, dtype=np.float32))
+    m = torch.from_numpy(np.ascontiguousarray(action_mask))
+    with torch.no_grad():
+        if turn_ids is None:
+            ret, adv = ref.token(me, r, v, m)
+        else:
+            ret, adv = ref.turn(me, r, v, m, torch.from_numpy(np.ascontiguousarray(turn_ids, dtype=np.int64)))
+    return ret.numpy().copy(), adv.numpy().copy()

@@ -358,6 +358,37 @@ def test_per_population_batch_vs_oracle(xp, cuda_device):
         assert np.array_equal(w[p * B:(p + 1) * B], ora.calculate_weights(oi, 0.4))
 
 
+@pytest.mark.parametrize("max_size,B,P", [(1000, 700, 25), (8000, 2048, 9), (50000, 1024, 17), (1 << 20, 4096, 5)])
+def test_per_large_draw_team_descent_vs_oracle(xp, cuda_device, max_size, B, P):
+    """Draws above 16 384 samples take the line-group / lane-team walk (descend_skip + descend_team3):
+    same indices and weights as the reference's level-by-level retrieve (segment_tree.py:147-156),
+    for tree depths 10, 13, 16, 20 (every remainder mod 3) and a ragged last warp."""
+    alpha = 0.6
+    rng = np.random.default_rng(max_size)
+    per = DevPer(xp, cuda_device, max_size, alpha)
+    ora = xo.PerOracle(max_size, alpha)
+    per.add(max_size)
+    ora.size, ora.tree_ptr = max_size, 0
+    for i in range(max_size):
+        ora.sum_tree.tree[ora.sum_tree.capacity + i] = 1.0
+        ora.min_tree.tree[ora.min_tree.capacity + i] = 1.0
+    ora.sum_tree.rebuild_from_leaves()
+    ora.min_tree.rebuild_from_leaves()
+    n_up = min(max_size, 6000)
+    idx = rng.integers(0, max_size, n_up)
+    pr = (np.abs(rng.standard_normal(n_up)) * 3 + 1e-6).astype(np.float32)
+    per.update_priorities(idx, pr)
+    ora.update_priorities(idx, pr)
+    assert P * B > 16384
+    u = rng.random(P * B).astype(np.float32)
+    u[::97] = 0.0  # stratum lower edges
+    got_i, got_w = per.sample(u, 0.4, P)
+    for p in range(P):
+        oi = ora.sample_proportional(B, u[p * B:(p + 1) * B])
+        assert np.array_equal(got_i[p * B:(p + 1) * B], oi), p
+        assert np.array_equal(got_w[p * B:(p + 1) * B], ora.calculate_weights(oi, 0.4)), p
+
+
 def test_pow_is_cpython_pow(xp, cuda_device):
     rng = np.random.default_rng(0)
     x = np.concatenate([np.maximum(np.abs(rng.standard_normal(200000)), 1e-5),
