@@ -68,6 +68,11 @@ _SIGNATURES = {
                                        C.c_int, C.c_int, C.POINTER(C.c_float), c_i64, c_i64, c_i64, c_vp]),
     "xp_gae": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64,
                          C.c_double, C.c_double, c_vp]),
+    "xp_gae_tokens": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, C.c_double, C.c_double, C.c_int, c_vp]),
+    "xp_gae_turns": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, C.c_int, C.c_double,
+                               C.c_double, c_vp]),
+    "xp_gae_turn_broadcast": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_vp]),
+    "xp_masked_whiten": (C.c_int, [c_vp, c_vp, c_vp, c_i64, C.c_int, c_vp, c_vp, c_vp]),
     "xp_gae_f32": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64,
                              C.c_double, C.c_double, c_vp]),
     "xp_mc_returns": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64,

@@ -5,10 +5,17 @@ inside its algorithm classes (no standalone function), so the host mirror is one
 with the argument meaning of the variables the reference loop reads:
 
   * :func:`gae_from_experiences` — ``PPO._deprecated_learn_from_experiences``
-    (algorithms/ppo.py:686-713) and ``IPPO._learn_individual`` (algorithms/ippo.py:703-724).
+    (algorithms/ppo.py:686-713) and ``IPPO._learn_individual`` (algorithms/ippo.py:703-724);
+  * :func:`gae_returns_token` — ``PPO._compute_gae_returns_token`` of the LLM path
+    (algorithms/ppo_llm.py:833-870);
+  * :func:`gae_returns_turn` — ``PPO._compute_gae_returns`` (algorithms/ppo_llm.py:758-831) with
+    ``pool_by_turns`` and ``masked_whiten`` (utils/llm_utils.py:215-312).
 
 Every function launches hand-written kernels from ``libb200xp.so`` and fails loudly without it; the
-results are bit-identical to the reference loop (all-fp32, one rounding per torch op).
+results are bit-identical to the reference loop (all-fp32, one rounding per torch op).  Where the
+reference reduces with ``tensor.sum()`` (turn pooling with ``"mean"``, whitening statistics) torch
+fixes no summation order; those sums are taken in fp64 in a fixed order and rounded once, so the
+results agree with the reference's to a few fp32 ulp (tests: rtol 2e-5) instead of bit for bit.
 """
 
 from __future__ import annotations
@@ -65,3 +72,78 @@ def gae_from_experiences(rewards, values, dones, next_value, next_done, gamma: f
     with nv.on_device(dev):
         xp.gae_f32(r, v, d, nvl, nd, adv, ret, T, N, P, T * N, float(gamma), float(gae_lambda))
     return adv, ret
+
+
+_whiten_scratch: dict = {}
+
+
+def _whiten(x: torch.Tensor, mask: torch.Tensor, times_mask: bool) -> torch.Tensor:
+    """``masked_whiten(x, mask)`` (utils/llm_utils.py:245-254), optionally followed by ``* mask``.
+    Raises the reference's ValueError when fewer than two values are unmasked."""
+    dev = x.device
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    if key not in _whiten_scratch:
+        _whiten_scratch[key] = (torch.zeros(xp.WHITEN_SCRATCH, dtype=torch.float64, device=dev),
+                                torch.zeros(1, dtype=torch.int32, device=dev))
+    scratch, err = _whiten_scratch[key]
+    out = torch.empty_like(x)
+    xp.masked_whiten(x, mask, out, times_mask, scratch, err)
+    if int(err.item()) != 0:  # the reference's `if mask_sum <= 1` is a host read of the same kind
+        err.zero_()
+        raise ValueError("Unbiased masked variance requires at least 2 unmasked values; "
+                         "increase `mini_batch_size` or `gradient_accumulation_steps`.")
+    return out
+
+
+def _llm_inputs(rewards, values, device):
+    dev = nv.require_cuda(device if device is not None else
+                          (values.device if isinstance(values, torch.Tensor) and values.is_cuda else None))
+    r = _dev_f32(rewards, dev)
+    v = _dev_f32(values, dev)
+    if r.dim() != 2 or v.shape != r.shape:
+        raise ValueError(f"rewards {tuple(r.shape)} / values {tuple(v.shape)} must both be [batch, seq_len]")
+    return dev, r, v
+
+
+def gae_returns_token(rewards, values, action_mask, gamma: float, gae_lambda: float,
+                      adv_whitening: bool = True, device=None) -> "tuple[torch.Tensor, torch.Tensor]":
+    """``(token_returns, token_advantages)`` of ``PPO._compute_gae_returns_token``
+    (algorithms/ppo_llm.py:833-870): rewards / values / action_mask ``[batch, seq_len]``; the mask may
+    be bool or float (the reference takes ``action_mask.float()``)."""
+    dev, r, v = _llm_inputs(rewards, values, device)
+    m = _dev_f32(action_mask, dev)
+    if m.shape != r.shape:
+        raise ValueError(f"action_mask {tuple(m.shape)} does not match values {tuple(r.shape)}")
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    with nv.on_device(dev):
+        xp.gae_tokens(r, v, m, adv, ret, not adv_whitening, float(gamma), float(gae_lambda))
+        if adv_whitening:
+            adv = _whiten(adv, m, True)
+    return ret, adv
+
+
+def gae_returns_turn(rewards, values, action_mask, turn_ids, gamma: float, gae_lambda: float,
+                     turn_value_reduction: str = "final_value", adv_whitening: bool = True,
+                     device=None) -> "tuple[torch.Tensor, torch.Tensor]":
+    """``(token_returns, token_advantages)`` of ``PPO._compute_gae_returns`` (algorithms/ppo_llm.py:758-831):
+    each generation turn is one RL action.  ``turn_ids`` int ``[batch, seq_len]``, -1 outside action
+    tokens; ``action_mask`` is accepted for signature parity (the reference does not read it)."""
+    if turn_value_reduction not in ("mean", "final_value"):
+        raise ValueError("turn_value_reduction must be one of ['final_value', 'mean'].")
+    dev, r, v = _llm_inputs(rewards, values, device)
+    tid = torch.as_tensor(turn_ids).to(dev, non_blocking=True).to(torch.int64).contiguous()
+    if tid.shape != r.shape:
+        raise ValueError(f"turn_ids {tuple(tid.shape)} does not match values {tuple(r.shape)}")
+    B, S = r.shape
+    num_turns = int(tid.max().item()) + 1  # `turn_ids.max().item() + 1`, the reference's own host read
+    if num_turns < 1:
+        raise ValueError("turn_ids holds no turn")
+    tv = torch.empty(B, num_turns, dtype=torch.float32, device=dev)
+    tadv, tmask = torch.empty_like(tv), torch.empty_like(tv)
+    ret, adv = torch.empty_like(r), torch.empty_like(r)
+    with nv.on_device(dev):
+        xp.gae_turns(r, v, tid, tv, tadv, tmask, num_turns, turn_value_reduction == "final_value",
+                     float(gamma), float(gae_lambda))
+        tadv_pg = _whiten(tadv, tmask, False) if adv_whitening else tadv
+        xp.gae_turn_broadcast(tid, tv, tadv, tadv_pg, ret, adv, num_turns)
+    return ret, adv

@@ -212,6 +212,47 @@ def gae_f32(rewards, values, dones, next_value, next_done, adv, ret, T: int, N: 
                                _stream(rewards)), "xp_gae_f32")
 
 
+# ---- token- / turn-level GAE of the LLM PPO path ------------------------------------------------
+def gae_tokens(rewards, values, mask, adv, ret, final_mask: bool, gamma: float, gae_lambda: float) -> None:
+    """[B, S] fp32 CUDA tensors (time contiguous); see xp_gae_tokens."""
+    for name, t in (("rewards", rewards), ("values", values), ("mask", mask), ("adv", adv), ("ret", ret)):
+        _need(t, torch.float32, name)
+    B, S = rewards.shape
+    check(nv.load().xp_gae_tokens(rewards.data_ptr(), values.data_ptr(), mask.data_ptr(), adv.data_ptr(),
+                                  ret.data_ptr(), B, S, gamma, gae_lambda, int(final_mask), _stream(rewards)),
+          "xp_gae_tokens")
+
+
+def gae_turns(rewards, values, turn_ids, turn_values, turn_adv, turn_mask, num_turns: int, final_value: bool,
+              gamma: float, gae_lambda: float) -> None:
+    for name, t in (("rewards", rewards), ("values", values), ("turn_values", turn_values),
+                    ("turn_adv", turn_adv), ("turn_mask", turn_mask)):
+        _need(t, torch.float32, name)
+    _need(turn_ids, torch.int64, "turn_ids")
+    B, S = rewards.shape
+    check(nv.load().xp_gae_turns(rewards.data_ptr(), values.data_ptr(), turn_ids.data_ptr(), turn_values.data_ptr(),
+                                 turn_adv.data_ptr(), turn_mask.data_ptr(), B, S, num_turns, int(final_value),
+                                 gamma, gae_lambda, _stream(rewards)), "xp_gae_turns")
+
+
+def gae_turn_broadcast(turn_ids, turn_values, turn_adv, turn_adv_pg, ret, adv, num_turns: int) -> None:
+    B, S = turn_ids.shape
+    check(nv.load().xp_gae_turn_broadcast(turn_ids.data_ptr(), turn_values.data_ptr(), turn_adv.data_ptr(),
+                                          turn_adv_pg.data_ptr(), ret.data_ptr(), adv.data_ptr(), B, S, num_turns,
+                                          _stream(turn_ids)), "xp_gae_turn_broadcast")
+
+
+WHITEN_SCRATCH = 520  # XP_WHITEN_SCRATCH
+
+
+def masked_whiten(x, mask, out, times_mask: bool, scratch, err) -> None:
+    for name, t in (("x", x), ("mask", mask), ("out", out)):
+        _need(t, torch.float32, name)
+    _need(scratch, torch.float64, "scratch")
+    check(nv.load().xp_masked_whiten(x.data_ptr(), mask.data_ptr(), out.data_ptr(), x.numel(), int(times_mask),
+                                     scratch.data_ptr(), err.data_ptr(), _stream(x)), "xp_masked_whiten")
+
+
 # ---- truncated-BPTT sequence preparation ------------------------------------------------------------
 BPTT_TYPES = {"chunked": 0, "maximum": 1, "fifty_percent_overlap": 2}
 

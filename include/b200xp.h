@@ -192,6 +192,41 @@ xp_status_t xp_mc_returns(const float *rewards, const float *values, const uint8
                           float *ret, int64_t T, int64_t N, int64_t P, int64_t agent_stride,
                           double gamma, void *stream);
 
+/* ---- token- and turn-level GAE of the LLM PPO path ------------------- */
+/* All arrays are [B][S] row-major with TIME contiguous (batch, seq_len), fp32; mask is the
+ * reference's action_mask.float().
+ * xp_gae_tokens replaces the loop of PPO._compute_gae_returns_token (algorithms/ppo_llm.py:851-867):
+ *   adv[b][t] = last_gae * mask[b][t],  ret = (adv + values) * mask,  every op rounded in fp32;
+ *   final_mask != 0 also applies the closing `token_advantages * mask` (:870, the no-whitening
+ *   return); with whitening the caller runs xp_masked_whiten(times_mask = 1) on adv instead.   */
+xp_status_t xp_gae_tokens(const float *rewards, const float *values, const float *mask, float *adv,
+                          float *ret, int64_t B, int64_t S, double gamma, double gae_lambda,
+                          int final_mask, void *stream);
+/* xp_gae_turns replaces pool_by_turns (utils/llm_utils.py:256-312: rewards mean-pooled, values
+ * mean-pooled or, final_value != 0, taken at the last token of the turn) and the turn chain of
+ * PPO._compute_gae_returns (ppo_llm.py:786-813).  turn_ids int64 [B][S], -1 = not an action token;
+ * num_turns = max id + 1 (<= XP_MAX_TURNS).  Outputs [B][num_turns] fp32: pooled turn values,
+ * turn advantages, turn mask (1.0 where the sequence has the turn).
+ * xp_gae_turn_broadcast replaces ppo_llm.py:822-829: ret = (turn_adv + turn_values)[turn_id] * valid,
+ * adv = turn_adv_pg[turn_id] * valid (turn_adv_pg = the whitened advantages, or turn_adv).      */
+#define XP_MAX_TURNS 2048
+xp_status_t xp_gae_turns(const float *rewards, const float *values, const int64_t *turn_ids,
+                         float *turn_values, float *turn_adv, float *turn_mask, int64_t B, int64_t S,
+                         int64_t num_turns, int final_value, double gamma, double gae_lambda,
+                         void *stream);
+xp_status_t xp_gae_turn_broadcast(const int64_t *turn_ids, const float *turn_values,
+                                  const float *turn_adv, const float *turn_adv_pg, float *ret,
+                                  float *adv, int64_t B, int64_t S, int64_t num_turns, void *stream);
+/* masked_whiten (utils/llm_utils.py:215-254, shift_mean = True, unbiased variance):
+ *   out = (x - mean) * rsqrt(var + 1e-8) [* mask when times_mask], mean / var over mask-weighted x.
+ * The two sums are accumulated in fp64 in a fixed order and rounded once (torch sums in fp32 in
+ * an unspecified order); everything else is the reference's fp32 op sequence.  scratch_dev:
+ * XP_WHITEN_SCRATCH doubles, zero before the first call (reusable afterwards).  *err_flag_dev is
+ * set when fewer than 2 values are unmasked (the reference raises ValueError).                 */
+#define XP_WHITEN_SCRATCH 520
+xp_status_t xp_masked_whiten(const float *x, const float *mask, float *out, int64_t n,
+                             int times_mask, double *scratch_dev, int *err_flag_dev, void *stream);
+
 /* ---- truncated-BPTT sequence preparation (RolloutBuffer.prepare_sequence_tensors) ------ */
 /* replaces the per-env Python walk of rollout_buffer.py:736-762 + _get_complete_sequences
  * (:677-722) + extract_sequences_from_episode (utils/algo_utils.py:214-265).

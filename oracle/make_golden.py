@@ -57,6 +57,42 @@ def gen_gae32():
              gamma=gamma, gae_lambda=lam, adv=adv, ret=ret)
 
 
+def llm_case(seed, B, S, n_turns):
+    """Synthetic multi-turn completions: per row a prompt, then up to n_turns generation turns separated
+    by observation tokens, then padding; values zero outside the action mask, as ppo_llm.py:484 does."""
+    g = torch.Generator().manual_seed(200 + seed)
+    tid = np.full((B, S), -1, dtype=np.int64)
+    for b in range(B):
+        pos = int(torch.randint(1, max(2, S // 8), (1,), generator=g))
+        k = 0
+        turns = int(torch.randint(1, n_turns + 1, (1,), generator=g))
+        while k < turns and pos < S - 1:
+            ln = int(torch.randint(1, max(2, S // (2 * n_turns)), (1,), generator=g))
+            tid[b, pos:min(S, pos + ln)] = k
+            pos += ln + int(torch.randint(0, 4, (1,), generator=g))
+            k += 1
+    tid[0, :] = -1
+    tid[0, S // 2] = n_turns - 1 if B > 1 else 0   # a row whose only turn is the last id
+    mask = tid >= 0
+    v = torch.randn(B, S, generator=g).numpy() * mask
+    r = (torch.randn(B, S, generator=g).numpy() * 0.05 + (torch.rand(B, S, generator=g) < 0.05).numpy()) * mask
+    return r.astype(np.float32), v.astype(np.float32), mask, tid
+
+
+def gen_llm_gae():
+    for seed, (B, S, K) in [(0, (4, 24, 2)), (1, (33, 260, 5)), (2, (7, 129, 3)), (3, (64, 1024, 6))]:
+        r, v, mask, tid = llm_case(seed, B, S, K)
+        out = {}
+        for w in (False, True):
+            ret, adv = ref_loader.reference_llm_gae(r, v, mask, 0.99, 0.95, w)
+            out[f"tok_ret_w{int(w)}"], out[f"tok_adv_w{int(w)}"] = ret, adv
+            for red in ("final_value", "mean"):
+                ret, adv = ref_loader.reference_llm_gae(r, v, mask, 0.99, 0.95, w, turn_ids=tid,
+                                                        turn_value_reduction=red)
+                out[f"turn_ret_{red}_w{int(w)}"], out[f"turn_adv_{red}_w{int(w)}"] = ret, adv
+        save(f"llm_gae_s{seed}", rewards=r, values=v, mask=mask, turn_ids=tid, gamma=0.99, gae_lambda=0.95, **out)
+
+
 def gen_per():
     ref = ref_loader.load_reference()
     TD = ref.TensorDict
@@ -248,11 +284,15 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["gae32"]:
         gen_gae32()
         sys.exit(0)
+    if sys.argv[1:] == ["llm_gae"]:
+        gen_llm_gae()
+        sys.exit(0)
     if sys.argv[1:] == ["bptt"]:
         gen_bptt()
         sys.exit(0)
     gen_gae()
     gen_gae32()
+    gen_llm_gae()
     gen_per()
     gen_ring_nstep()
     gen_rng()

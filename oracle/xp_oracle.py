@@ -307,6 +307,98 @@ def gae_f32(rewards, values, dones, next_value, next_done, gamma: float, gae_lam
     return adv, adv + values
 
 
+# =================================================================================================
+# token- and turn-level GAE of the LLM PPO path — algorithms/ppo_llm.py:758-872,
+# utils/llm_utils.py:215-312.  [batch, seq_len] fp32; every torch op is one fp32 rounding.
+# Sums (`tensor.sum()`) have no fixed order in torch: taken in fp64 here and rounded once.
+# =================================================================================================
+def masked_whiten(values, mask):
+    """masked_whiten with shift_mean=True, unbiased variance (llm_utils.py:215-254)."""
+    f = np.float32
+    values = np.asarray(values, dtype=f)
+    mask = np.asarray(mask, dtype=f)
+    cnt = f(mask.astype(np.float64).sum())
+    mean = f(f((values * mask).astype(np.float64).sum()) / cnt)               # masked_mean
+    centered = values - mean
+    var = f(f(((centered * centered) * mask).astype(np.float64).sum()) / cnt)   # masked_mean(centered**2)
+    if cnt <= 1:
+        raise ValueError("Unbiased masked variance requires at least 2 unmasked values")
+    var = f(var * f(cnt / f(cnt - f(1.0))))
+    rs = f(f(1.0) / np.sqrt(f(var + f(1e-8))))
+    return (values - mean) * rs
+
+
+def gae_tokens(rewards, values, action_mask, gamma: float, gae_lambda: float, adv_whitening: bool):
+    """PPO._compute_gae_returns_token (ppo_llm.py:833-870) -> (token_returns, token_advantages)."""
+    f = np.float32
+    rewards = np.asarray(rewards, dtype=f)
+    values = np.asarray(values, dtype=f)
+    mask = np.asarray(action_mask).astype(f)
+    B, S = values.shape
+    g32, gl32 = f(gamma), f(gamma * gae_lambda)
+    adv = np.zeros((B, S), dtype=f)
+    last = np.zeros(B, dtype=f)
+    for t in reversed(range(S)):
+        if t == S - 1:
+            nv, nm = np.zeros(B, dtype=f), np.zeros(B, dtype=f)
+        else:
+            nv, nm = values[:, t + 1], mask[:, t + 1]
+        delta = (rewards[:, t] + (g32 * nv) * nm) - values[:, t]
+        last = delta + (gl32 * last) * nm
+        adv[:, t] = last * mask[:, t]
+    ret = (adv + values) * mask
+    if adv_whitening:
+        adv = masked_whiten(adv, mask)
+    return ret, adv * mask
+
+
+def pool_by_turns(token_values, turn_ids, num_turns: int, reduction: str = "mean"):
+    """llm_utils.py:256-312 ("mean" and "final_value")."""
+    f = np.float32
+    token_values = np.asarray(token_values, dtype=f)
+    B, S = token_values.shape
+    out = np.zeros((B, num_turns), dtype=f)
+    for t in range(num_turns):
+        mask_t = (turn_ids == t)
+        if reduction == "mean":
+            summed = (token_values * mask_t.astype(f)).astype(np.float64).sum(axis=1).astype(f)
+            count = np.maximum(mask_t.sum(axis=1).astype(f), f(1.0))
+            out[:, t] = summed / count
+        else:
+            pos = np.where(mask_t, np.arange(S)[None, :], -1).max(axis=1)
+            out[:, t] = np.where(pos >= 0, token_values[np.arange(B), np.maximum(pos, 0)], f(0.0))
+    return out
+
+
+def gae_turns(rewards, values, turn_ids, gamma: float, gae_lambda: float, adv_whitening: bool,
+              turn_value_reduction: str = "final_value"):
+    """PPO._compute_gae_returns (ppo_llm.py:758-831) -> (token_returns, token_advantages)."""
+    f = np.float32
+    turn_ids = np.asarray(turn_ids).astype(np.int64)
+    B, S = turn_ids.shape
+    K = int(turn_ids.max()) + 1
+    tv = pool_by_turns(values, turn_ids, K, turn_value_reduction)
+    tr = pool_by_turns(rewards, turn_ids, K)
+    g32, gl32 = f(gamma), f(gamma * gae_lambda)
+    tadv = np.zeros((B, K), dtype=f)
+    last = np.zeros(B, dtype=f)
+    nb = turn_ids.max(axis=1) + 1
+    for t in reversed(range(K)):
+        is_last = t >= nb - 1
+        nv = np.zeros(B, dtype=f) if t == K - 1 else tv[:, t + 1]
+        nv = np.where(is_last, f(0.0), nv).astype(f)
+        delta = (tr[:, t] + g32 * nv) - tv[:, t]
+        has = (nb > t).astype(f)
+        last = (delta + gl32 * last) * has
+        tadv[:, t] = last
+    turn_mask = (turn_ids[:, :, None] == np.arange(K)[None, None, :]).any(axis=1).astype(f)
+    tadv_pg = masked_whiten(tadv, turn_mask) if adv_whitening else tadv
+    valid = (turn_ids >= 0).astype(f)
+    safe = np.maximum(turn_ids, 0)
+    rows = np.arange(B)[:, None]
+    return (tadv + tv)[rows, safe] * valid, tadv_pg[rows, safe] * valid
+
+
 def pow_cpython(x: float, y: float) -> float:
     """float ** float in CPython = libm pow (replay_buffer.py:322,401,406)."""
     return math.pow(x, y)

@@ -266,3 +266,22 @@ def test_marb_oracle_matches_reference_golden(seed):
                         assert np.array_equal(t, z[f"s{k}|{name}"], equal_nan=True), (k, name)
                     k += 1
     assert k == int(z["n_samples"]) and len(buf) == int(z["final_len"]) and buf.counter == int(z["counter"])
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_llm_gae_oracle_matches_reference_methods(seed):
+    """oracle gae_tokens / gae_turns vs PPO._compute_gae_returns_token / _compute_gae_returns
+    (algorithms/ppo_llm.py:758-872) run unmodified: the token chain bit for bit; whatever sits behind
+    a torch `.sum()` (whitening, mean pooling) within rtol 2e-5."""
+    g = load_golden(f"llm_gae_s{seed}")
+    gamma, lam = float(g["gamma"]), float(g["gae_lambda"])
+    ret, adv = xo.gae_tokens(g["rewards"], g["values"], g["mask"], gamma, lam, False)
+    assert np.array_equal(ret, g["tok_ret_w0"]) and np.array_equal(adv, g["tok_adv_w0"])
+    ret, adv = xo.gae_tokens(g["rewards"], g["values"], g["mask"], gamma, lam, True)
+    assert np.array_equal(ret, g["tok_ret_w1"])
+    np.testing.assert_allclose(adv, g["tok_adv_w1"], rtol=2e-5, atol=1e-6)
+    for red in ("final_value", "mean"):
+        for w in (0, 1):
+            ret, adv = xo.gae_turns(g["rewards"], g["values"], g["turn_ids"], gamma, lam, bool(w), red)
+            np.testing.assert_allclose(ret, g[f"turn_ret_{red}_w{w}"], rtol=2e-5, atol=1e-6)
+            np.testing.assert_allclose(adv, g[f"turn_adv_{red}_w{w}"], rtol=2e-5, atol=1e-6)

@@ -93,3 +93,24 @@ def test_per_trees_sampling_weights_live(seed):
     oi = orc.sample_proportional(B, u.numpy())
     assert np.array_equal(idx.numpy().reshape(-1), oi)
     assert np.array_equal(w.numpy().reshape(-1), orc.calculate_weights(oi, 0.5))
+
+
+@pytest.mark.parametrize("seed", [11, 12, 13])
+def test_llm_gae_live(seed):
+    """Fresh random cases through the reference's own token- / turn-level GAE methods."""
+    rng = np.random.default_rng(seed)
+    B, S, K = int(rng.integers(1, 40)), int(rng.integers(2, 300)), int(rng.integers(1, 6))
+    tid = rng.integers(-1, K, (B, S))
+    tid[rng.random((B, S)) < 0.4] = -1
+    tid[0, 0] = K - 1
+    mask = tid >= 0
+    r = (rng.standard_normal((B, S)) * mask).astype(np.float32)
+    v = (rng.standard_normal((B, S)) * mask).astype(np.float32)
+    want = ref_loader.reference_llm_gae(r, v, mask, 0.99, 0.95, False)
+    got = xo.gae_tokens(r, v, mask, 0.99, 0.95, False)
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    for red in ("final_value", "mean"):
+        want = ref_loader.reference_llm_gae(r, v, mask, 0.99, 0.95, True, turn_ids=tid, turn_value_reduction=red)
+        got = xo.gae_turns(r, v, tid, 0.99, 0.95, True, red)
+        np.testing.assert_allclose(got[0], want[0], rtol=2e-5, atol=1e-6)
+        np.testing.assert_allclose(got[1], want[1], rtol=2e-5, atol=1e-6)
