@@ -14,6 +14,11 @@ namespace {
 constexpr int kSortThreads = 1024;
 constexpr int kIdxBits = 14;  // B <= 16384
 
+// x % m for a 32-bit draw: one 32-bit remainder when m fits 32 bits, x itself otherwise
+__device__ __forceinline__ unsigned long long draw_mod(unsigned x, unsigned long long m) {
+  return m > 0xffffffffull ? (unsigned long long)x : (unsigned long long)(x % (unsigned)m);
+}
+
 __global__ void __launch_bounds__(kSortThreads) randperm_prefix_kernel(
     const unsigned *raw, long long B, long long n, long long *out, int npow2) {
   extern __shared__ unsigned long long keys[];  // (j << kIdxBits) | i, sorted ascending
@@ -22,7 +27,7 @@ __global__ void __launch_bounds__(kSortThreads) randperm_prefix_kernel(
   for (int i = threadIdx.x; i < npow2; i += blockDim.x) {
     unsigned long long key = ~0ull;
     if (i < B) {
-      const unsigned long long j = (unsigned long long)i + (unsigned long long)x[i] % (unsigned long long)(n - i);
+      const unsigned long long j = (unsigned long long)i + draw_mod(x[i], (unsigned long long)(n - i));
       key = (j << kIdxBits) | (unsigned long long)i;
     }
     keys[i] = key;
@@ -45,7 +50,7 @@ __global__ void __launch_bounds__(kSortThreads) randperm_prefix_kernel(
     }
   }
   for (int i = threadIdx.x; i < B; i += blockDim.x) {
-    unsigned long long q = (unsigned long long)i + (unsigned long long)x[i] % (unsigned long long)(n - i);
+    unsigned long long q = (unsigned long long)i + draw_mod(x[i], (unsigned long long)(n - i));
     unsigned long long bound = (unsigned long long)i;
     while (true) {
       // largest key strictly below (q << bits | bound)
@@ -61,6 +66,45 @@ __global__ void __launch_bounds__(kSortThreads) randperm_prefix_kernel(
       const unsigned long long k = cand & ((1ull << kIdxBits) - 1);
       q = k;       // content of position k just before step k
       bound = k;
+    }
+    o[i] = (long long)q;
+  }
+}
+
+// Sparse draws (n >= 16 B): steps that share a target are rare, so the (target, step) pairs go into
+// an open-addressing table in shared memory instead of being sorted — "largest k < bound with
+// j_k == q" scans q's probe cluster (every entry of a target lies between its home slot and the
+// next empty slot; nothing is ever deleted).  Same chains, same result, three barriers.
+__global__ void __launch_bounds__(kSortThreads) randperm_prefix_hash_kernel(
+    const unsigned *raw, long long B, long long n, long long *out, int log_slots) {
+  extern __shared__ unsigned long long tab[];
+  const unsigned *x = raw + (long long)blockIdx.x * B;
+  long long *o = out + (long long)blockIdx.x * B;
+  const unsigned mask = (1u << log_slots) - 1u;
+  auto home = [&](unsigned long long j) { return (unsigned)((j * 0x9E3779B97F4A7C15ull) >> (64 - log_slots)); };
+  for (int i = threadIdx.x; i <= (int)mask; i += blockDim.x) tab[i] = ~0ull;
+  __syncthreads();
+  for (int i = threadIdx.x; i < B; i += blockDim.x) {
+    const unsigned long long j = (unsigned long long)i + draw_mod(x[i], (unsigned long long)(n - i));
+    const unsigned long long key = (j << kIdxBits) | (unsigned long long)i;
+    unsigned h = home(j);
+    while (atomicCAS(&tab[h], ~0ull, key) != ~0ull) h = (h + 1) & mask;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < B; i += blockDim.x) {
+    unsigned long long q = (unsigned long long)i + draw_mod(x[i], (unsigned long long)(n - i));
+    long long bound = i;
+    while (true) {
+      long long best = -1;
+      for (unsigned h = home(q);; h = (h + 1) & mask) {
+        const unsigned long long e = tab[h];
+        if (e == ~0ull) break;
+        const long long k = (long long)(e & ((1ull << kIdxBits) - 1));
+        if ((e >> kIdxBits) == q && k < bound && k > best) best = k;
+      }
+      if (best < 0) break;
+      q = (unsigned long long)best;  // content of position k just before step k
+      bound = best;
     }
     o[i] = (long long)q;
   }
@@ -109,6 +153,25 @@ xp_status_t xp_randperm_prefix(const uint32_t *raw_dev, int64_t B, int64_t P, in
   XP_REQUIRE(raw_dev && idx_out_dev, XP_ERR_INVALID, "xp_randperm_prefix: null pointer");
   int npow2 = 1;
   while (npow2 < B) npow2 <<= 1;
+  if (n >= 16 * B && B <= 4096) {  // sparse: hash table of 4 slots per draw (<= 128 KB)
+    int log_slots = 2;
+    while ((1 << log_slots) < 4 * npow2) ++log_slots;
+    const size_t hsmem = (size_t)8 << log_slots;
+    static bool hattr = false;
+    if (hsmem > 48 * 1024 && !hattr) {
+      cudaError_t e = cudaFuncSetAttribute(randperm_prefix_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           128 * 1024);
+      if (e != cudaSuccess) {
+        xp::set_error("xp_randperm_prefix: %s", cudaGetErrorString(e));
+        return XP_ERR_CUDA;
+      }
+      hattr = true;
+    }
+    const int hthreads = npow2 < kSortThreads ? (npow2 < 32 ? 32 : npow2) : kSortThreads;
+    randperm_prefix_hash_kernel<<<(unsigned)P, hthreads, hsmem, (cudaStream_t)stream>>>(
+        raw_dev, B, n, (long long *)idx_out_dev, log_slots);
+    return xp::check_launch("xp_randperm_prefix");
+  }
   const size_t smem = (size_t)npow2 * sizeof(unsigned long long);
   static bool attr_set = false;
   if (smem > 48 * 1024 && !attr_set) {

@@ -508,6 +508,56 @@ def bench_per_tree(dev, reps=10):
             "l2": "tree 805 MB > L2; top levels L2-resident by design"}
 
 
+def bench_uniform(dev, reps=10):
+    """C5: TD3 uniform replay, 10 M Humanoid-shape rows (30.8 GB), 32 agents x 1024 per launch:
+    xp_randperm_prefix (torch.randperm(size)[:B] from the raw mt19937 words, replay_buffer.py:125)
+    + xp_gather of every key (:126-131)."""
+    import torch
+
+    from agilerl_b200 import xp
+
+    c = C5
+    cap, B, P = c["cap"], c["B"], c["P"]
+    n = P * B
+    shapes = [("obs", (c["obs"],)), ("action", (c["act"],)), ("reward", (1,)), ("next_obs", (c["obs"],)),
+              ("done", (1,))]
+    gd = torch.Generator(device=dev).manual_seed(5)
+    store = [torch.empty(cap, *sh, dtype=torch.float32, device=dev) for _, sh in shapes]
+    for t in store:  # touch every page once; values are irrelevant to the timing
+        t.view(-1)[::1024].fill_(1.0)
+    R = 4
+    outs = [[torch.empty(n, *sh, dtype=torch.float32, device=dev) for _, sh in shapes] for _ in range(R)]
+    raw = [torch.randint(-2**31, 2**31 - 1, (n,), device=dev, generator=gd, dtype=torch.int64).to(torch.int32)
+           for _ in range(R)]
+    idx = [torch.empty(n, dtype=torch.int64, device=dev) for _ in range(R)]
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def draw(i):
+        return lambda: xp.randperm_prefix(raw[i], B, P, cap, idx[i])
+
+    def gather(i):
+        return lambda: xp.gather(list(zip(store, outs[i])), idx[i], cap, err)
+
+    for i in range(R):
+        draw(i)()
+    us_d = graph_time_us([draw(i) for i in range(R)], reps)
+    us_g = graph_time_us([gather(i) for i in range(R)], reps)
+    seq = []
+    for i in range(R):
+        seq += [draw(i), gather(i)]
+    us_b = 2 * graph_time_us(seq, reps)
+    assert int(err.item()) == 0
+    for i in range(R):  # every agent's indices are distinct and in range (a randperm prefix)
+        a = idx[i].view(P, B)
+        assert int(a.min()) >= 0 and int(a.max()) < cap
+        assert all(int(torch.unique(a[p]).numel()) == B for p in (0, P - 1))
+    alg = n * (2 * R_C5 + 8)
+    return {"workload": c["name"], "metric": "uniform_sampled_transitions_per_s", "value": n / (us_b * 1e-6),
+            "unit": UNIT, "us_randperm_prefix": us_d, "us_gather": us_g, "us_sample": us_b, "row_bytes": R_C5,
+            "algorithmic_bytes": alg, "gather_roofline": roofline(alg, us_g),
+            "l2": "random rows of a 30.8 GB storage; 4 rotating output sets of 101 MB"}
+
+
 def ncu_traffic(kernel_substr: str):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of a kernel, from the newest
     committed ``profiles/r*_ncu_*.txt`` summary that contains it (tools/ncu_summary.py output of an
@@ -650,7 +700,10 @@ def b200_arm(args):
         g16["roofline"] = roofline(g16["algorithmic_bytes"], g16["us_per_launch"])
         p = bench_per_tree(dev)
         p["roofline"] = roofline(p["algorithmic_bytes"], p["us_sample_plus_update"])
-        also = [g, g16, p]
+        torch.cuda.empty_cache()
+        c5 = bench_uniform(dev)
+        c5["roofline"] = roofline(c5["algorithmic_bytes"], c5["us_sample"])
+        also = [g, g16, p, c5]
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = reference_c2(seconds=args.cpu_seconds, workers=1)
 

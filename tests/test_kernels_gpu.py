@@ -489,7 +489,8 @@ def test_randperm_prefix_golden(xp, cuda_device):
 
 def test_randperm_prefix_population_and_dense(xp, cuda_device):
     rng = np.random.default_rng(0)
-    for n, B, P in [(4096, 4096, 3), (5000, 4096, 2), (10_000_000, 1024, 32), (16384, 16384, 1)]:
+    for n, B, P in [(4096, 4096, 3), (5000, 4096, 2), (10_000_000, 1024, 32), (16384, 16384, 1),
+                    (65536, 4096, 2), (1000, 50, 3), (20000, 1024, 4), (800, 50, 2), (799, 50, 2)]:  # hash path from n >= 16 B
         raw = rng.integers(0, 2**32, P * B, dtype=np.uint64).astype(np.uint32)
         got = xp.randperm_prefix(dev(raw.view(np.int32), cuda_device), B, P, n).cpu().numpy()
         for p in (0, P - 1):
