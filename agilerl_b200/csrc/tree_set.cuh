@@ -82,8 +82,12 @@ __device__ __forceinline__ double src_value(const SetSrc &s, long long pos) {
 __device__ __forceinline__ void fold_max_priority(const SetSrc &s, double p) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) p = fmax(p, __shfl_xor_sync(0xffffffffu, p, o));
-  if ((threadIdx.x & 31) == 0 && p > 0.0)
-    atomicMax(s.max_priority_bits, (unsigned long long)__double_as_longlong(p));
+  // the maximum only grows: a warp whose best is not above the value it reads (however stale) has
+  // nothing to contribute, which in steady state is every warp — no same-address atomic traffic
+  if ((threadIdx.x & 31) == 0 && p > 0.0) {
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(p);
+    if (bits > __ldcg(s.max_priority_bits)) atomicMax(s.max_priority_bits, bits);
+  }
 }
 
 
@@ -417,9 +421,7 @@ __global__ void __launch_bounds__(256) set_hist_kernel(Tree t, SetSrc s, long lo
   if (s.kind == kSrcPrio) fold_max_priority(s, p);
 }
 
-// exclusive scan of counts[nb] -> offsets[nb+1], cursors[nb] by one CTA of 32 warps:
-// coalesced 32-wide rows scanned with shuffles (row-local exclusive values parked in shared
-// memory), a block scan of the <= 1024 row totals, then one coalesced write pass.
+// exclusive scan of counts[nb] -> offsets[nb+1], cursors[nb] by one CTA of 32 warps
 __device__ __forceinline__ int warp_inclusive(int v, int lane) {
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -429,33 +431,29 @@ __device__ __forceinline__ int warp_inclusive(int v, int lane) {
   return v;
 }
 __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
-  extern __shared__ int s_excl[];   // [nb] exclusive prefix inside each 32-row
-  __shared__ int s_row[1024];       // row totals -> exclusive row offsets
+  // One CTA.  Counters come in and prefixes go out coalesced through shared memory (one pad word
+  // per 32 keeps both the row-wise copies and the per-thread runs bank-conflict free); in between
+  // thread t owns E = nb / 1024 CONSECUTIVE counters (nb is a power of two <= 32768): a serial sum,
+  // one warp scan + one block scan of the 1024 thread totals, and the running prefix written back.
+  extern __shared__ int s_cnt[];  // [nb + nb / 32]
   __shared__ int s_warp[32];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nb = bk.nb;
-  const int rows = (nb + 31) >> 5;
-  constexpr int kRowsPerWarp = 32;  // nb <= 32768
-  int vals[kRowsPerWarp];
+  const int nb = bk.nb, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < nb; i += 1024) s_cnt[i + (i >> 5)] = __ldcg(&bk.counts[i]);
+  __syncthreads();
+  const int E = nb >= 1024 ? nb >> 10 : 1;
+  const int base = tid * E;
+  int v[32];
+  int sum = 0;
 #pragma unroll
-  for (int k = 0; k < kRowsPerWarp; ++k) {  // every load of this warp in flight at once
-    const int i = (warp + 32 * k) * 32 + lane;
-    vals[k] = (warp + 32 * k < rows && i < nb) ? __ldcg(&bk.counts[i]) : 0;
-  }
-#pragma unroll
-  for (int k = 0; k < kRowsPerWarp; ++k) {
-    const int r = warp + 32 * k;
-    if (r < rows) {
-      const int i = r * 32 + lane;
-      const int inc = warp_inclusive(vals[k], lane);
-      if (i < nb) s_excl[i] = inc - vals[k];
-      if (lane == 31) s_row[r] = inc;
+  for (int k = 0; k < 32; ++k) {
+    if (k < E) {
+      const int i = base + k;
+      v[k] = i < nb ? s_cnt[i + (i >> 5)] : 0;
+      sum += v[k];
     }
   }
-  __syncthreads();
-  const int rv = threadIdx.x < rows ? s_row[threadIdx.x] : 0;
-  const int rinc = warp_inclusive(rv, lane);
-  if (lane == 31) s_warp[warp] = rinc;
+  const int inc = warp_inclusive(sum, lane);
+  if (lane == 31) s_warp[warp] = inc;
   __syncthreads();
   if (warp == 0) {
     const int w = s_warp[lane];
@@ -464,15 +462,20 @@ __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
     if (lane == 31) bk.offsets[nb] = winc;
   }
   __syncthreads();
-  if (threadIdx.x < rows) s_row[threadIdx.x] = s_warp[warp] + rinc - rv;
-  __syncthreads();
-  for (int r = warp; r < rows; r += 32) {
-    const int i = r * 32 + lane;
-    if (i < nb) {
-      const int off = s_row[r] + s_excl[i];
-      bk.offsets[i] = off;
-      bk.cursors[i] = off;
+  int run = s_warp[warp] + inc - sum;  // exclusive prefix of this thread's first counter
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {
+    if (k < E) {
+      const int i = base + k;
+      if (i < nb) s_cnt[i + (i >> 5)] = run;
+      run += v[k];
     }
+  }
+  __syncthreads();
+  for (int i = tid; i < nb; i += 1024) {
+    const int off = s_cnt[i + (i >> 5)];
+    bk.offsets[i] = off;
+    bk.cursors[i] = off;
   }
 }
 
@@ -698,10 +701,10 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     set_hist_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
     static bool scan_attr = false;
     {
-      xp_status_t rc = set_attr_once((const void *)set_scan_kernel, (size_t)32768 * 4, scan_attr);
+      xp_status_t rc = set_attr_once((const void *)set_scan_kernel, (size_t)(32768 + 1024) * 4, scan_attr);
       if (rc != XP_OK) return rc;
     }
-    set_scan_kernel<<<1, 1024, (size_t)nb * 4, st>>>(bk);
+    set_scan_kernel<<<1, 1024, (size_t)(nb + nb / 32 + 1) * 4, st>>>(bk);
     set_scatter_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
     const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps) / kBucketWarps);
     if (paired)

@@ -389,6 +389,59 @@ def test_per_large_draw_team_descent_vs_oracle(xp, cuda_device, max_size, B, P):
         assert np.array_equal(got_w[p * B:(p + 1) * B], ora.calculate_weights(oi, 0.4)), p
 
 
+def test_per_full_size_properties(xp, cuda_device):
+    """C4 size (cap 2^24, 64 agents x 4096 strata): properties that hold exactly at any size.
+    * after batched updates every internal node IS op(left, right) (segment_tree.py:89-95) and
+      max_priority is the running maximum (:329);
+    * the large-draw walk (line groups + lane teams) returns exactly the leaves of the plain
+      level-by-level retrieve on the same upper bounds, and the fused IS weights equal xp_per_weights;
+    * repeating an update with the same (idx, priority) leaves the tree unchanged (idempotence), and
+      duplicate indices resolve to the LAST priority (sequential semantics, :423-428)."""
+    cap, B, P, alpha, beta = 1 << 24, 4096, 64, 0.6, 0.4
+    per = DevPer(xp, cuda_device, cap, alpha)
+    per.add(cap)
+    g = torch.Generator(device=cuda_device).manual_seed(0)
+    n = P * B
+    for _ in range(2):
+        idx = torch.randint(0, cap, (n,), device=cuda_device, generator=g)
+        pr = torch.randn(n, device=cuda_device, generator=g).abs() * 2 + 1e-6
+        xp.per_update(per.tree.t, per.state, idx, pr, cap, alpha, per.tree.err)
+    nodes = per.tree.nodes
+    kids = nodes[2:].view(cap - 1, 2, 2)  # node i (1 <= i < cap): children 2i, 2i+1
+    assert torch.equal(nodes[1:cap, 0], kids[:, 0, 0] + kids[:, 1, 0])
+    assert torch.equal(nodes[1:cap, 1], torch.minimum(kids[:, 0, 1], kids[:, 1, 1]))
+    assert float(per.state.item()) == max(1.0, float(pr.double().max().item()), float(per.state.item()))
+    # last writer wins: the leaf of a duplicated index holds its last priority
+    last = {}
+    ci, cp = idx[-4096:].cpu().numpy(), pr[-4096:].cpu().numpy()
+    for i, p_ in zip(ci, cp):
+        last[int(i)] = float(p_)
+    seen_later = set(idx[-4096:].cpu().numpy().tolist())
+    some = list(last.items())[:512]
+    leaves = nodes[cap + torch.tensor([k for k, _ in some], device=cuda_device), 0].cpu().numpy()
+    want = np.array([math.pow(max(v, 1e-5), alpha) for _, v in some])
+    assert np.array_equal(leaves, want) and seen_later
+    # descent: team walk == plain walk, fused weights == xp_per_weights
+    u = torch.rand(n, device=cuda_device, generator=g)
+    got_i = torch.empty(n, dtype=torch.int64, device=cuda_device)
+    got_w = torch.empty(n, dtype=torch.float32, device=cuda_device)
+    xp.per_sample(per.tree.t, u, B, P, cap, beta, got_i, got_w)
+    total = nodes[1, 0]
+    seg = total / B
+    i = torch.arange(B, device=cuda_device, dtype=torch.float64).repeat(P)
+    a, b = seg * i, seg * (i + 1)
+    ub = u.double() * (b - a) + a
+    assert torch.equal(got_i, xp.tree_retrieve(per.tree.t, ub))
+    w2 = torch.empty_like(got_w)
+    xp.per_weights(per.tree.t, got_i, cap, beta, w2)
+    assert torch.equal(got_w, w2)
+    assert int(got_i.min()) >= 0 and int(got_i.max()) < cap
+    # idempotence of the batched set
+    before = nodes.clone()
+    xp.per_update(per.tree.t, per.state, idx, pr, cap, alpha, per.tree.err)
+    assert torch.equal(nodes, before) and int(per.tree.err.item()) == 0
+
+
 def test_pow_is_cpython_pow(xp, cuda_device):
     rng = np.random.default_rng(0)
     x = np.concatenate([np.maximum(np.abs(rng.standard_normal(200000)), 1e-5),
