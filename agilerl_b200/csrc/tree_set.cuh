@@ -379,8 +379,9 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
 }
 
 // ---- schedule L (large B): histogram+scan -> scatter -> one warp per bucket -> dense top --------
-// aux scratch layout (ints): [0] done counter, [16, 16+NB) counts, then offsets[NB+1], cursors[NB],
-// then (8-byte aligned) items u64[B].
+// aux scratch layout (ints): [0] done counter, [1] dense ticket, [16, 16+MB) counts (MB =
+// max_buckets(cap); zero between calls), then offsets[NB+1],
+// cursors[NB], then (8-byte aligned) items u64[B] and the leaf values f64[B].
 struct Buckets {
   int nb;          // number of bucket subtrees (power of two)
   int shift;       // leaves per bucket = 1 << shift
@@ -390,15 +391,30 @@ struct Buckets {
   double *vals;    // kSrcPrio only: leaf value per batch position (else NULL)
 };
 
+// Largest bucket count any batch can ask for on this tree: the counters that must be ZERO between
+// calls live in a region sized by it, so that calls with different batch sizes —
+// hence different nb — never find another call's offsets or items where they expect zeros.
+__host__ __device__ inline long long max_buckets(long long cap) {
+  long long nb = 1;
+  while (nb < 32768 && nb * 4 <= cap) nb <<= 1;  // the bound of run_set's bucket count
+  return nb;
+}
+
+__host__ __device__ inline long long bucket_scratch_ints(long long cap, long long nb, long long B, bool want_vals) {
+  const long long mb = max_buckets(cap);
+  return 16 + mb + 2 * nb + 2 + (want_vals ? 4 : 2) * B;
+}
+
 __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift, long long B, bool want_vals) {
   Buckets b;
+  const long long mb = max_buckets(t.cap);
   b.nb = nb;
   b.shift = shift;
   b.top = shift;
-  b.counts = t.aux + 16;
-  b.offsets = b.counts + nb;
+  b.counts = t.aux + 16;      // [mb] zero between calls (the bucket kernel clears what it used)
+  b.offsets = b.counts + mb;  // everything from here on is rewritten by every call
   b.cursors = b.offsets + nb + 1;
-  long long off = 16 + 3ll * nb + 1;
+  long long off = 16 + mb + 2ll * nb + 1;
   off = (off + 1) & ~1ll;
   b.items = reinterpret_cast<u64 *>(t.aux + off);
   b.vals = want_vals ? reinterpret_cast<double *>(t.aux + off + 2 * B) : nullptr;
@@ -687,7 +703,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   const int use_half = 1;
   while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;  // ~16 items per bucket
   const bool want_vals = s.kind == kSrcPrio;
-  const long long need = 16 + 3 * nb + 2 + (want_vals ? 4 : 2) * B;
+  const long long need = bucket_scratch_ints(t.cap, nb, B, want_vals);
   if (need <= t.cap) {  // schedule L
     const int shift = L - ilog2(nb);
     Buckets bk = make_buckets(t, (int)nb, shift, B, want_vals);

@@ -269,6 +269,31 @@ def test_tree_set_batch_adversarial_patterns(xp, cuda_device, pattern, cap, B):
     assert int(t.aux[cap:].abs().sum()) == 0
 
 
+def test_tree_set_batch_sizes_may_change_between_calls(xp, cuda_device):
+    """The bucket scratch of a large batch is laid out by the batch size; a later call with another
+    size (other bucket count, one-launch path in between) must still find its counters zero."""
+    cap = 1 << 18
+    rng = np.random.default_rng(5)
+    tree = DevTree(xp, cuda_device, cap)
+    ref_s = np.zeros(2 * cap)
+    ref_m = np.full(2 * cap, np.inf)
+    for B in (20000, 200000, 3000, 70000, 20000, 262144):
+        idx = rng.integers(0, cap, B)
+        val = rng.random(B) + 0.01
+        tree.set(idx, val)
+        # sequential last-writer-wins leaves, then the bottom-up rebuild the invariant implies
+        ref_s[cap + idx] = 0  # placeholder write so that fancy assignment below is last-wins
+        for arr in (ref_s, ref_m):
+            arr[cap + idx] = val  # numpy fancy assignment keeps the LAST value of duplicate indices
+        for lvl in range(17, -1, -1):
+            lo, hi = 1 << lvl, 2 << lvl
+            ref_s[lo:hi] = ref_s[2 * lo:2 * hi:2] + ref_s[2 * lo + 1:2 * hi:2]
+            ref_m[lo:hi] = np.minimum(ref_m[2 * lo:2 * hi:2], ref_m[2 * lo + 1:2 * hi:2])
+        s_, m_ = tree.arrays()
+        assert np.array_equal(s_[1:], ref_s[1:]) and np.array_equal(m_[1:], ref_m[1:]), B
+        assert int(tree.err.item()) == 0
+
+
 def test_tree_set_out_of_range_flags(xp, cuda_device):
     t = DevTree(xp, cuda_device, 8)
     t.set([1, 8, -1], [1.0, 2.0, 3.0])
