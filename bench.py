@@ -558,16 +558,17 @@ def bench_uniform(dev, reps=10):
             "l2": "random rows of a 30.8 GB storage; 4 rotating output sets of 101 MB"}
 
 
-def ncu_traffic(kernel_substr: str):
+def ncu_traffic(kernel_substr: str, capture: str = "ncu_*.txt"):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of a kernel, from the newest
     committed ``profiles/r*_ncu_*.txt`` summary that contains it (tools/ncu_summary.py output of an
-    ``ncu --set full`` capture); None when no capture is on disk."""
+    ``ncu --set full`` capture); ``capture`` narrows the file name (the same kernel is captured on
+    more than one workload); None when no capture is on disk."""
     import glob
     import re
 
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     root = os.path.dirname(os.path.abspath(__file__))
-    for path in sorted(glob.glob(os.path.join(root, "profiles", "r*_ncu_*.txt")), reverse=True):
+    for path in sorted(glob.glob(os.path.join(root, "profiles", "r*_" + capture)), reverse=True):
         cur, rd, wr = None, None, None
         for ln in open(path, errors="replace"):
             if ln.startswith("Kernel Name"):
@@ -724,11 +725,11 @@ def b200_arm(args):
             "gpu_launches": int(l1 - l0),
             "clocks": clocks.summary(),
             "roofline": dict(roofline(C2["P"] * C2["B"] * (2 * R_C2 + 8), gather_us,
-                                      (ncu_traffic("move_kernel<0>") or {}).get("bytes")),
+                                      (ncu_traffic("move_kernel<0>", "ncu_gather.txt") or {}).get("bytes")),
                              kernel="move_kernel<gather>", us_per_launch=round(gather_us, 2),
                              algorithmic_bytes_per_launch=C2["P"] * C2["B"] * (2 * R_C2 + 8),
                              launches_timed=2 * K,
-                             traffic_source=(ncu_traffic("move_kernel<0>") or {}).get("source")),
+                             traffic_source=(ncu_traffic("move_kernel<0>", "ncu_gather.txt") or {}).get("source")),
             "step_breakdown": breakdown,
             "cpu_baseline": cpu,
             "also": also,
