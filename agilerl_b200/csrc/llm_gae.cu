@@ -265,9 +265,12 @@ __device__ __forceinline__ double block_sum(double x, double *sh) {
 }
 
 // PASS 0: sum(x*m), sum(m) -> mean, count.  PASS 1: sum(((x-mean)^2)*m) -> rsqrt(var*bessel + 1e-8).
+// standardize != 0 (mask may be NULL = all ones): the global advantage normalisation of PPO's flat
+// learn step, (x - x.mean()) / (x.std() + 1e-8) (algorithms/ppo.py:829-833) — torch.std accumulates
+// in fp64 and divides by n-1, so PASS 1 does the same and stores the DENOMINATOR std + 1e-8.
 template <int PASS>
 __global__ void __launch_bounds__(kWhitenThreads) whiten_stats_kernel(const float *x, const float *mask, long long n,
-                                                                      double *stats, int *err) {
+                                                                      double *stats, int *err, int standardize) {
   __shared__ double sh[kWhitenThreads / 32];
   __shared__ int s_last;
   const float mean = PASS == 1 ? (float)stats[0] : 0.0f;
@@ -276,10 +279,13 @@ __global__ void __launch_bounds__(kWhitenThreads) whiten_stats_kernel(const floa
   const long long per = (n + gridDim.x - 1) / gridDim.x;
   const long long lo = per * blockIdx.x, hi = lo + per < n ? lo + per : n;
   for (long long i = lo + threadIdx.x; i < hi; i += kWhitenThreads) {
-    const float xi = __ldg(x + i), mi = __ldg(mask + i);
+    const float xi = __ldg(x + i), mi = mask ? __ldg(mask + i) : 1.0f;
     if (PASS == 0) {
       a += (double)__fmul_rn(xi, mi);
       c += (double)mi;
+    } else if (standardize) {
+      const double d = (double)xi - (double)mean;
+      a += d * d * (double)mi;
     } else {
       const float d = __fsub_rn(xi, mean);
       a += (double)__fmul_rn(__fmul_rn(d, d), mi);
@@ -307,6 +313,9 @@ __global__ void __launch_bounds__(kWhitenThreads) whiten_stats_kernel(const floa
     stats[0] = (double)__fdiv_rn((float)A, (float)C);  // (values*mask).sum() / mask.sum()
     stats[1] = C;
     if (C <= 1.0 && err) *err = 1;  // "Unbiased masked variance requires at least 2 unmasked values"
+  } else if (standardize) {
+    const float sd = (float)sqrt(A / (stats[1] - 1.0));   // unbiased, fp64 accumulation like torch.std
+    stats[2] = (double)__fadd_rn(sd, 1e-8f);
   } else {
     const float cnt = (float)stats[1];
     float var = __fdiv_rn((float)A, cnt);
@@ -316,11 +325,12 @@ __global__ void __launch_bounds__(kWhitenThreads) whiten_stats_kernel(const floa
 }
 
 __global__ void __launch_bounds__(256) whiten_apply_kernel(const float *x, const float *mask, float *out, long long n,
-                                                           const double *stats, int times_mask) {
+                                                           const double *stats, int times_mask, int standardize) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float mean = (float)stats[0], rs = (float)stats[2];
-  float w = __fmul_rn(__fsub_rn(__ldg(x + i), mean), rs);
+  const float d = __fsub_rn(__ldg(x + i), mean);
+  float w = standardize ? __fdiv_rn(d, rs) : __fmul_rn(d, rs);
   if (times_mask) w = __fmul_rn(w, __ldg(mask + i));
   out[i] = w;
 }
@@ -391,10 +401,23 @@ xp_status_t xp_masked_whiten(const float *x, const float *mask, float *out, int6
   long long ctas = (n + 4 * kWhitenThreads - 1) / (4 * kWhitenThreads);
   if (ctas > kWhitenCtas) ctas = kWhitenCtas;
   cudaStream_t s = (cudaStream_t)stream;
-  whiten_stats_kernel<0><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, mask, n, scratch_dev, err_flag_dev);
-  whiten_stats_kernel<1><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, mask, n, scratch_dev, nullptr);
-  whiten_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, mask, out, n, scratch_dev, times_mask);
+  whiten_stats_kernel<0><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, mask, n, scratch_dev, err_flag_dev, 0);
+  whiten_stats_kernel<1><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, mask, n, scratch_dev, nullptr, 0);
+  whiten_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, mask, out, n, scratch_dev, times_mask, 0);
   return xp::check_launch("xp_masked_whiten", 3);
+}
+
+xp_status_t xp_standardize(const float *x, float *out, int64_t n, double *scratch_dev, void *stream) {
+  XP_REQUIRE(n >= 0, XP_ERR_INVALID, "xp_standardize: n < 0");
+  if (n == 0) return XP_OK;
+  XP_REQUIRE(x && out && scratch_dev, XP_ERR_INVALID, "xp_standardize: null pointer");
+  long long ctas = (n + 4 * kWhitenThreads - 1) / (4 * kWhitenThreads);
+  if (ctas > kWhitenCtas) ctas = kWhitenCtas;
+  cudaStream_t s = (cudaStream_t)stream;
+  whiten_stats_kernel<0><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, nullptr, n, scratch_dev, nullptr, 1);
+  whiten_stats_kernel<1><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, nullptr, n, scratch_dev, nullptr, 1);
+  whiten_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, nullptr, out, n, scratch_dev, 0, 1);
+  return xp::check_launch("xp_standardize", 3);
 }
 
 }  // extern "C"

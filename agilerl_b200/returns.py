@@ -6,6 +6,8 @@ with the argument meaning of the variables the reference loop reads:
 
   * :func:`gae_from_experiences` — ``PPO._deprecated_learn_from_experiences``
     (algorithms/ppo.py:686-713) and ``IPPO._learn_individual`` (algorithms/ippo.py:703-724);
+  * :func:`normalize_advantages` — the global advantage normalisation of
+    ``PPO._learn_from_rollout_buffer_flat`` (algorithms/ppo.py:829-833);
   * :func:`gae_returns_token` — ``PPO._compute_gae_returns_token`` of the LLM path
     (algorithms/ppo_llm.py:833-870);
   * :func:`gae_returns_turn` — ``PPO._compute_gae_returns`` (algorithms/ppo_llm.py:758-831) with
@@ -92,6 +94,27 @@ def _whiten(x: torch.Tensor, mask: torch.Tensor, times_mask: bool) -> torch.Tens
         err.zero_()
         raise ValueError("Unbiased masked variance requires at least 2 unmasked values; "
                          "increase `mini_batch_size` or `gradient_accumulation_steps`.")
+    return out
+
+
+def normalize_advantages(advantages, out=None, device=None) -> torch.Tensor:
+    """``(adv - adv.mean()) / (adv.std() + 1e-8)`` over the whole rollout — the global advantage
+    normalisation at the top of ``PPO._learn_from_rollout_buffer_flat`` (algorithms/ppo.py:829-833) —
+    on the device, so a device-resident ``get_tensor_batch()`` never leaves HBM.  ``out`` may be the
+    input itself (in place, what ``buffer_td["advantages"] = ...`` amounts to)."""
+    dev = nv.require_cuda(device if device is not None else
+                          (advantages.device if isinstance(advantages, torch.Tensor) and advantages.is_cuda else None))
+    x = _dev_f32(advantages, dev)
+    if out is None:
+        out = torch.empty_like(x)
+    elif out.dtype != torch.float32 or not out.is_cuda or not out.is_contiguous() or out.shape != x.shape:
+        raise ValueError("out must be a contiguous fp32 CUDA tensor shaped like advantages")
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    if key not in _whiten_scratch:
+        _whiten_scratch[key] = (torch.zeros(xp.WHITEN_SCRATCH, dtype=torch.float64, device=dev),
+                                torch.zeros(1, dtype=torch.int32, device=dev))
+    with nv.on_device(dev):
+        xp.standardize(x, out, _whiten_scratch[key][0])
     return out
 
 

@@ -253,6 +253,15 @@ def masked_whiten(x, mask, out, times_mask: bool, scratch, err) -> None:
                                      scratch.data_ptr(), err.data_ptr(), _stream(x)), "xp_masked_whiten")
 
 
+def standardize(x, out, scratch) -> None:
+    """out = (x - x.mean()) / (x.std() + 1e-8) over all elements (fp32 CUDA, contiguous; out may be x)."""
+    _need(x, torch.float32, "x")
+    _need(out, torch.float32, "out")
+    _need(scratch, torch.float64, "scratch")
+    check(nv.load().xp_standardize(x.data_ptr(), out.data_ptr(), x.numel(), scratch.data_ptr(), _stream(x)),
+          "xp_standardize")
+
+
 # ---- truncated-BPTT sequence preparation ------------------------------------------------------------
 BPTT_TYPES = {"chunked": 0, "maximum": 1, "fifty_percent_overlap": 2}
 

@@ -227,6 +227,11 @@ xp_status_t xp_gae_turn_broadcast(const int64_t *turn_ids, const float *turn_val
 xp_status_t xp_masked_whiten(const float *x, const float *mask, float *out, int64_t n,
                              int times_mask, double *scratch_dev, int *err_flag_dev, void *stream);
 
+/* Global advantage normalisation of PPO's flat learn step (algorithms/ppo.py:829-833, SURVEY.md 8f
+ * row 2): out = (x - x.mean()) / (x.std() + 1e-8), std unbiased with fp64 accumulation as
+ * torch.std; out may alias x.  n == 1 gives NaN like torch.  scratch_dev as for xp_masked_whiten. */
+xp_status_t xp_standardize(const float *x, float *out, int64_t n, double *scratch_dev, void *stream);
+
 /* ---- truncated-BPTT sequence preparation (RolloutBuffer.prepare_sequence_tensors) ------ */
 /* replaces the per-env Python walk of rollout_buffer.py:736-762 + _get_complete_sequences
  * (:677-722) + extract_sequences_from_episode (utils/algo_utils.py:214-265).

@@ -93,6 +93,13 @@ def gen_llm_gae():
         save(f"llm_gae_s{seed}", rewards=r, values=v, mask=mask, turn_ids=tid, gamma=0.99, gae_lambda=0.95, **out)
 
 
+def gen_advnorm():
+    for seed, shape in [(0, (7,)), (1, (128, 64)), (2, (131072,)), (3, (2,))]:
+        g = torch.Generator().manual_seed(300 + seed)
+        a = (torch.randn(*shape, generator=g) * 3 + 0.7).numpy()
+        save(f"advnorm_s{seed}", advantages=a, normalized=ref_loader.reference_normalize_advantages(a))
+
+
 def gen_per():
     ref = ref_loader.load_reference()
     TD = ref.TensorDict
@@ -284,6 +291,9 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["gae32"]:
         gen_gae32()
         sys.exit(0)
+    if sys.argv[1:] == ["advnorm"]:
+        gen_advnorm()
+        sys.exit(0)
     if sys.argv[1:] == ["llm_gae"]:
         gen_llm_gae()
         sys.exit(0)
@@ -293,6 +303,7 @@ if __name__ == "__main__":
     gen_gae()
     gen_gae32()
     gen_llm_gae()
+    gen_advnorm()
     gen_per()
     gen_ring_nstep()
     gen_rng()

@@ -405,3 +405,21 @@ def reference_llm_gae(rewards, values, action_mask, gamma, gae_lambda, adv_white
         else:
             ret, adv = ref.turn(me, r, v, m, torch.from_numpy(np.ascontiguousarray(turn_ids, dtype=np.int64)))
     return ret.numpy().copy(), adv.numpy().copy()
+
+
+def reference_normalize_advantages(advantages):
+    """The reference's own statement ``normalized_advantages = (valid_advantages - valid_advantages.mean())
+    / (valid_advantages.std() + 1e-8)`` (PPO._learn_from_rollout_buffer_flat, algorithms/ppo.py:829-833),
+    extracted unmodified and run on an fp32 CPU tensor."""
+    if "advnorm" not in _cache:
+        path = os.path.join(REF_PKG, "algorithms", "ppo.py")
+        src = open(path).read()
+        tree = ast.parse(src)
+        klass = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "PPO")
+        fn = next(n for n in klass.body if isinstance(n, ast.FunctionDef) and n.name == "_learn_from_rollout_buffer_flat")
+        stmt = next(n for n in ast.walk(fn) if isinstance(n, ast.Assign) and isinstance(n.targets[0], ast.Name)
+                    and n.targets[0].id == "normalized_advantages")
+        _cache["advnorm"] = textwrap.dedent(" " * stmt.col_offset + ast.get_source_segment(src, stmt))
+    g = {"torch": torch, "valid_advantages": torch.from_numpy(np.ascontiguousarray(advantages, dtype=np.float32))}
+    exec(_cache["advnorm"], g)
+    return g["normalized_advantages"].numpy().copy()

@@ -399,6 +399,16 @@ def gae_turns(rewards, values, turn_ids, gamma: float, gae_lambda: float, adv_wh
     return (tadv + tv)[rows, safe] * valid, tadv_pg[rows, safe] * valid
 
 
+def normalize_advantages(advantages):
+    """(adv - adv.mean()) / (adv.std() + 1e-8), std unbiased (algorithms/ppo.py:829-833); fp32 result,
+    statistics in fp64 rounded once (torch fixes no summation order)."""
+    f = np.float32
+    a = np.asarray(advantages, dtype=f)
+    mean = f(a.astype(np.float64).mean())
+    sd = f(np.sqrt(((a.astype(np.float64) - np.float64(mean)) ** 2).sum() / (a.size - 1))) if a.size > 1 else f(np.nan)
+    return (a - mean) / f(sd + f(1e-8))
+
+
 def pow_cpython(x: float, y: float) -> float:
     """float ** float in CPython = libm pow (replay_buffer.py:322,401,406)."""
     return math.pow(x, y)

@@ -111,3 +111,25 @@ def test_llm_gae_errors(returns, cuda_device):
                                  device=cuda_device)
     with pytest.raises(ValueError):
         returns.gae_returns_token(r, r[:, :4], m, 0.99, 0.95, device=cuda_device)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_normalize_advantages_golden(returns, cuda_device, seed):
+    """(adv - adv.mean()) / (adv.std() + 1e-8) of PPO's flat learn step (algorithms/ppo.py:829-833) against the
+    reference's own statement run on the CPU; mean / std sit behind torch reductions -> rtol 2e-5."""
+    g = load_golden(f"advnorm_s{seed}")
+    out = returns.normalize_advantages(g["advantages"], device=cuda_device)
+    assert out.shape == g["advantages"].shape and out.dtype == torch.float32
+    np.testing.assert_allclose(out.cpu().numpy(), g["normalized"], **TOL)
+    np.testing.assert_allclose(out.cpu().numpy(), xo.normalize_advantages(g["advantages"]), **TOL)
+    # in place on a device-resident buffer, and deterministic run to run
+    x = torch.from_numpy(g["advantages"]).to(cuda_device)
+    y = returns.normalize_advantages(x, out=x)
+    assert y.data_ptr() == x.data_ptr() and torch.equal(y, out)
+
+
+def test_normalize_advantages_c3_size_and_single_value(returns, cuda_device):
+    x = torch.randn(128 * 1024, device=cuda_device) * 2 + 1  # one C3 agent's rollout
+    y = returns.normalize_advantages(x)
+    assert abs(float(y.mean())) < 1e-5 and abs(float(y.std()) - 1.0) < 1e-5
+    assert torch.isnan(returns.normalize_advantages(torch.ones(1, device=cuda_device))).all()  # torch: std of 1 value

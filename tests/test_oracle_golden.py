@@ -285,3 +285,9 @@ def test_llm_gae_oracle_matches_reference_methods(seed):
             ret, adv = xo.gae_turns(g["rewards"], g["values"], g["turn_ids"], gamma, lam, bool(w), red)
             np.testing.assert_allclose(ret, g[f"turn_ret_{red}_w{w}"], rtol=2e-5, atol=1e-6)
             np.testing.assert_allclose(adv, g[f"turn_adv_{red}_w{w}"], rtol=2e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_normalize_advantages_oracle_matches_reference_statement(seed):
+    g = load_golden(f"advnorm_s{seed}")
+    np.testing.assert_allclose(xo.normalize_advantages(g["advantages"]), g["normalized"], rtol=2e-5, atol=1e-6)
