@@ -39,6 +39,37 @@ inline xp_status_t check_launch(const char *what, int n_kernels = 1) {
     }                               \
   } while (0)
 
+// ---- programmatic dependent launch ------------------------------------------------------
+// The path is a chain of short kernels on one stream (sample -> gather -> gather -> update; hist ->
+// scan -> scatter -> climb -> dense top); each pays 2-3 us of launch latency and CTA ramp after the
+// previous grid has drained.  Launched with programmatic stream serialization, a kernel's CTAs
+// become resident as soon as every CTA of its predecessor has executed pdl_enter() (or exited),
+// and then block in hardware at `griddepcontrol.wait` until the predecessor has completed and
+// flushed its memory — the successor starts on the next clock instead of after a launch.  Every
+// kernel launched through xp::launch() calls pdl_enter() first thing; nothing before the wait reads
+// or writes global memory, so ordering is exactly stream order.  XP_NO_PDL=1 turns it off.
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline void launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);  // errors surface through check_launch()
+}
+
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---- device helpers -------------------------------------------------------------------
 // L2-coherent loads (bypass the non-coherent L1) for data other CTAs write in this launch.
 __device__ __forceinline__ double ld_cg_f64(const double *p) { return __ldcg(p); }

@@ -1,6 +1,7 @@
 // core.cu — library plumbing: version, thread-local error text, device facts.
 #include <stdarg.h>
 #include <atomic>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -18,6 +19,14 @@ void set_error(const char *fmt, ...) {
 
 static std::atomic<unsigned long long> g_launches{0};
 void note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char *e = getenv("XP_NO_PDL");
+    return !(e && e[0] && e[0] != '0');
+  }();
+  return on;
+}
 
 int sm_count() {
   static int cached[64] = {0};

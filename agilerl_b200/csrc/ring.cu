@@ -190,6 +190,7 @@ __device__ __forceinline__ void fold_reward(const MoveParams &p, const KeyDesc &
 
 template <int OP>
 __global__ void __launch_bounds__(kThreads) move_kernel(const __grid_constant__ MoveParams p) {
+  xp::pdl_enter();
   // flat grid: key k owns CTAs [cta0_k, cta0_k + ctas_k)
   int key = 0;
   while (key + 1 < p.n_keys && (long long)blockIdx.x >= p.k[key + 1].cta0) ++key;
@@ -276,7 +277,7 @@ xp_status_t xp_ring_insert(const xp_key *keys, int n_keys, int64_t n_rows, int64
   p.cursor = cursor;
   p.max_size = max_size;
   dim3 grid((unsigned)ctas);
-  move_kernel<kOpInsert><<<grid, kThreads, 0, (cudaStream_t)stream>>>(p);
+  xp::launch(move_kernel<kOpInsert>, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, p);
   return xp::check_launch("xp_ring_insert");
 }
 
@@ -293,7 +294,7 @@ xp_status_t xp_gather(const xp_key *keys, int n_keys, const int64_t *idx_dev, in
   p.n_src_rows = n_src_rows;
   p.err = err_flag_dev;
   dim3 grid((unsigned)ctas);
-  move_kernel<kOpGather><<<grid, kThreads, 0, (cudaStream_t)stream>>>(p);
+  xp::launch(move_kernel<kOpGather>, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, p);
   return xp::check_launch("xp_gather");
 }
 
@@ -320,7 +321,7 @@ xp_status_t xp_nstep_fold_insert(const xp_key *keys, const int *roles, int n_key
   p.done_elem_bytes = done_elem_bytes;
   for (int i = 0; i < n_step; ++i) p.gpow[i] = gpow[i];
   dim3 grid((unsigned)ctas);
-  move_kernel<kOpNstep><<<grid, kThreads, 0, (cudaStream_t)stream>>>(p);
+  xp::launch(move_kernel<kOpNstep>, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, p);
   return xp::check_launch("xp_nstep_fold_insert");
 }
 

@@ -21,6 +21,7 @@ __device__ __forceinline__ unsigned long long draw_mod(unsigned x, unsigned long
 
 __global__ void __launch_bounds__(kSortThreads) randperm_prefix_kernel(
     const unsigned *raw, long long B, long long n, long long *out, int npow2) {
+  xp::pdl_enter();
   extern __shared__ unsigned long long keys[];  // (j << kIdxBits) | i, sorted ascending
   const unsigned *x = raw + (long long)blockIdx.x * B;
   long long *o = out + (long long)blockIdx.x * B;
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(kSortThreads) randperm_prefix_kernel(
 // next empty slot; nothing is ever deleted).  Same chains, same result, three barriers.
 __global__ void __launch_bounds__(kSortThreads) randperm_prefix_hash_kernel(
     const unsigned *raw, long long B, long long n, long long *out, int log_slots) {
+  xp::pdl_enter();
   extern __shared__ unsigned long long tab[];
   const unsigned *x = raw + (long long)blockIdx.x * B;
   long long *o = out + (long long)blockIdx.x * B;
@@ -168,8 +170,8 @@ xp_status_t xp_randperm_prefix(const uint32_t *raw_dev, int64_t B, int64_t P, in
       hattr = true;
     }
     const int hthreads = npow2 < kSortThreads ? (npow2 < 32 ? 32 : npow2) : kSortThreads;
-    randperm_prefix_hash_kernel<<<(unsigned)P, hthreads, hsmem, (cudaStream_t)stream>>>(
-        raw_dev, B, n, (long long *)idx_out_dev, log_slots);
+    xp::launch(randperm_prefix_hash_kernel, dim3((unsigned)P), dim3(hthreads), hsmem, (cudaStream_t)stream,
+               (const unsigned *)raw_dev, (long long)B, (long long)n, (long long *)idx_out_dev, log_slots);
     return xp::check_launch("xp_randperm_prefix");
   }
   const size_t smem = (size_t)npow2 * sizeof(unsigned long long);
@@ -183,8 +185,8 @@ xp_status_t xp_randperm_prefix(const uint32_t *raw_dev, int64_t B, int64_t P, in
     attr_set = true;
   }
   const int threads = npow2 < kSortThreads ? (npow2 < 32 ? 32 : npow2) : kSortThreads;
-  randperm_prefix_kernel<<<(unsigned)P, threads, smem, (cudaStream_t)stream>>>(
-      raw_dev, B, n, (long long *)idx_out_dev, npow2);
+  xp::launch(randperm_prefix_kernel, dim3((unsigned)P), dim3(threads), smem, (cudaStream_t)stream,
+             (const unsigned *)raw_dev, (long long)B, (long long)n, (long long *)idx_out_dev, npow2);
   return xp::check_launch("xp_randperm_prefix");
 }
 

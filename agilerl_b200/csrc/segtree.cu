@@ -355,6 +355,7 @@ __global__ void __launch_bounds__(256) per_sample_kernel(Tree t, const float *u,
                                                          long long P, long long total_samples,
                                                          double size, double neg_beta,
                                                          long long *idx_out, float *w_out) {
+  xp::pdl_enter();
   __shared__ double s_max_w;
   const double total = __ldg(&t.sum[t.stride]);  // sum_tree.sum() == tree[1]
   if (!SMALL) {
@@ -534,12 +535,12 @@ xp_status_t xp_per_sample(const xp_tree *tree, const float *u_dev, int64_t B, in
   // large ones are bound by L1 tag look-ups of diverged lanes: line groups + lane teams
   if (total <= 16384) {
     const unsigned grid = (unsigned)((total + 63) / 64);
-    per_sample_kernel<1, true><<<grid, 64, 0, (cudaStream_t)stream>>>(
-        t, u_dev, B, P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
+    xp::launch(per_sample_kernel<1, true>, dim3(grid), dim3(64), 0, (cudaStream_t)stream, t, u_dev, (long long)B,
+               (long long)P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
   } else {
     const unsigned grid = (unsigned)((total + 127) / 128);
-    per_sample_kernel<3, false><<<grid, 128, 0, (cudaStream_t)stream>>>(
-        t, u_dev, B, P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
+    xp::launch(per_sample_kernel<3, false>, dim3(grid), dim3(128), 0, (cudaStream_t)stream, t, u_dev, (long long)B,
+               (long long)P, total, (double)size, -beta, (long long *)idx_out_dev, w_out_dev);
   }
   return xp::check_launch("xp_per_sample");
 }

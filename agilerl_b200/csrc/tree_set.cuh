@@ -286,6 +286,7 @@ constexpr int kMidListCap = 1024;   // compact list capacity per CTA (keys)
 constexpr int kMidCompactFrom = 1024;
 template <bool PAIRED>
 __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc s, int B, int nb, int shift) {
+  xp::pdl_enter();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ u64 s_list[kMidWarps][32];
   __shared__ int s_last, s_cnt;
@@ -423,6 +424,7 @@ __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift
 
 // per-bucket item counts (duplicates included); the last CTA to finish turns them into offsets
 __global__ void __launch_bounds__(256) set_hist_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
+  xp::pdl_enter();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   double p = 0.0;
   if (i < B) {
@@ -447,6 +449,7 @@ __device__ __forceinline__ int warp_inclusive(int v, int lane) {
   return v;
 }
 __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
+  xp::pdl_enter();
   // One CTA.  Counters come in and prefixes go out coalesced through shared memory (one pad word
   // per 32 keeps both the row-wise copies and the per-thread runs bank-conflict free); in between
   // thread t owns E = nb / 1024 CONSECUTIVE counters (nb is a power of two <= 32768): a serial sum,
@@ -498,6 +501,7 @@ __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
 // every valid item goes into its bucket's slice; the leaf value (pow) is computed HERE, with all
 // lanes busy, and parked by batch position for the bucket warp that will need it
 __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
+  xp::pdl_enter();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B) return;
   long long leaf;
@@ -513,6 +517,7 @@ __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long
 constexpr int kBucketWarps = 8;
 template <bool PAIRED>
 __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk, int use_half) {
+  xp::pdl_enter();
   const int lane = threadIdx.x & 31;
   const int b0 = 2 * (blockIdx.x * kBucketWarps + (threadIdx.x >> 5));
   if (b0 >= bk.nb) return;
@@ -582,6 +587,7 @@ __global__ void __launch_bounds__(256) set_leafwrite_kernel(Tree t, SetSrc s, lo
 constexpr int kDenseThreads = 512;
 constexpr int kDenseLogC = 12;
 __global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0, int logC, int finish) {
+  xp::pdl_enter();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_last;
   const int C = 1 << logC;
@@ -661,7 +667,7 @@ inline xp_status_t launch_dense(const Tree &t, int h0, long long width, int max_
     const int logC = lw < max_logc ? lw : max_logc;
     const long long grid = width >> logC;
     const int finish = grid <= (1ll << logC) ? 1 : 0;  // the chunk roots fit one CTA's heap
-    set_dense_kernel<<<(unsigned)grid, kDenseThreads, (size_t)4 * (1 << logC) * 8, st>>>(t, h0, logC, finish);
+    xp::launch(set_dense_kernel, dim3((unsigned)grid), dim3(kDenseThreads), (size_t)4 * (1 << logC) * 8, st, t, h0, logC, finish);
     ++launches;
     if (finish) break;
     h0 += logC;
@@ -693,9 +699,9 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
                                    (size_t)65536, mid_attr[paired ? 1 : 0]);
     if (rc != XP_OK) return rc;
     if (paired)
-      set_mid_kernel<true><<<grid, warps * 32, smem, st>>>(t, s, (int)B, (int)nb, shift);
+      xp::launch(set_mid_kernel<true>, dim3(grid), dim3(warps * 32), smem, st, t, s, (int)B, (int)nb, shift);
     else
-      set_mid_kernel<false><<<grid, warps * 32, smem, st>>>(t, s, (int)B, (int)nb, shift);
+      xp::launch(set_mid_kernel<false>, dim3(grid), dim3(warps * 32), smem, st, t, s, (int)B, (int)nb, shift);
     return xp::check_launch("tree set (M)", 1);
   }
   const unsigned grid = (unsigned)((B + 255) / 256);
@@ -714,19 +720,19 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     if (top < 1) top = 1;
     if (top > shift) top = shift;
     bk.top = top;
-    set_hist_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
+    xp::launch(set_hist_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bk);
     static bool scan_attr = false;
     {
       xp_status_t rc = set_attr_once((const void *)set_scan_kernel, (size_t)(32768 + 1024) * 4, scan_attr);
       if (rc != XP_OK) return rc;
     }
-    set_scan_kernel<<<1, 1024, (size_t)(nb + nb / 32 + 1) * 4, st>>>(bk);
-    set_scatter_kernel<<<grid, 256, 0, st>>>(t, s, B, bk);
+    xp::launch(set_scan_kernel, dim3(1), dim3(1024), (size_t)(nb + nb / 32 + 1) * 4, st, bk);
+    xp::launch(set_scatter_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bk);
     const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps) / kBucketWarps);
     if (paired)
-      set_wbucket_kernel<true><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk, use_half);
+      xp::launch(set_wbucket_kernel<true>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
     else
-      set_wbucket_kernel<false><<<bgrid, kBucketWarps * 32, 0, st>>>(t, s, bk, use_half);
+      xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
     launches = 4;
     xp_status_t rc = launch_dense(t, bk.top, t.cap >> bk.top, bk.top == shift ? 8 : 10, st, launches);
     if (rc != XP_OK) return rc;
