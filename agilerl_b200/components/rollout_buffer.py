@@ -470,9 +470,31 @@ class RolloutBuffer:
         return state
 
     def __setstate__(self, state: dict[str, Any]) -> None:
+        """Unpickling with the reference's integrity checks (:940-970): a missing / invalid buffer is
+        re-initialised with a warning (or left alone, with a second warning, when the spaces are
+        missing too); a buffer whose leading shape is not ``[capacity, num_envs]`` is re-initialised."""
         self.__dict__.update(state)
         self._sdev = nv.require_cuda(state.get("_sdev"))
-        self._leaves = OrderedDict((p, t.to(self._sdev)) for p, t in state["_leaves"].items())
+        leaves = state.get("_leaves")
+        given = state.get("buffer", "missing")
+        valid = (isinstance(leaves, dict) and len(leaves) > 0 and all(isinstance(t, torch.Tensor) for t in leaves.values())
+                 and (given is None or isinstance(given, TensorBatch)))
+        if not valid:
+            warnings.warn("TensorDict buffer not found or invalid during unpickling. Re-initializing.", stacklevel=2)
+            if not hasattr(self, "observation_space") or not hasattr(self, "action_space"):
+                warnings.warn("Observation or action space missing during RolloutBuffer unpickling. "
+                              "Buffer might be invalid.", stacklevel=2)
+                return
+            self._initialize_buffers()
+            return
+        expected = (self.capacity, self.num_envs)
+        if any(tuple(t.shape[:2]) != expected for t in leaves.values()):
+            got = tuple(next(iter(leaves.values())).shape[:2])
+            warnings.warn(f"Loaded TensorDict has batch_size {torch.Size(got)}, expected {torch.Size(expected)}. "
+                          "Re-initializing.", stacklevel=2)
+            self._initialize_buffers()
+            return
+        self._leaves = OrderedDict((p, t.to(self._sdev)) for p, t in leaves.items())
         self.buffer = _nest(self._leaves, [self.capacity, self.num_envs])
 
 

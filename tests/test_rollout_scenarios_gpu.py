@@ -1,0 +1,122 @@
+"""Scenarios of the reference's own tests/test_components/test_rollout_buffer.py, restated against the
+B200 RolloutBuffer (same constructor arguments, same calls, same assertions; storage on the GPU)."""
+
+import numpy as np
+import pytest
+import torch
+
+from agilerl_b200.components import RolloutBuffer, spaces
+
+pytestmark = pytest.mark.gpu
+
+
+def test_dict_observations_add_get(cuda_device):  # reference tests/test_components/test_rollout_buffer.pytest_rollout_buffer.py:53-75,278-324,842-884
+    sp = spaces.Dict({"vector": spaces.Box(low=-1, high=1, shape=(2,), dtype=np.float32), "discrete": spaces.Discrete(3)})
+    b = RolloutBuffer(capacity=5, observation_space=sp, action_space=spaces.Discrete(2), num_envs=2, device="cuda")
+    assert b.buffer["observations"]["vector"].shape == (5, 2, 2) and b.buffer["observations"]["discrete"].shape == (5, 2, 1)
+    obs = {"vector": np.array([[1.0, 2.0], [3.0, 4.0]]), "discrete": np.array([[0], [2]])}
+    b.add(obs=obs, action=np.array([0, 1]), reward=np.array([1.0, -1.0]), done=np.array([False, True]),
+          value=np.array([0.5, -0.5]), log_prob=np.array([0.1, 0.2]))
+    assert b.pos == 1
+    assert torch.allclose(b.buffer["observations"]["vector"][0].cpu(), torch.tensor(obs["vector"], dtype=torch.float32))
+    assert torch.allclose(b.buffer["observations"]["discrete"][0].cpu(), torch.tensor(obs["discrete"], dtype=torch.float32))
+    b.compute_returns_and_advantages(np.zeros(2), np.zeros(2))
+    d = b.get()
+    assert isinstance(d["observations"], dict) and d["observations"]["vector"].shape == (2, 2)
+    tb = b.get_tensor_batch()
+    assert tb["observations"]["vector"].shape == (2, 2)
+
+def test_recurrent_hidden_states_through_bptt(cuda_device):  # reference tests/test_components/test_rollout_buffer.py:77-121,417-456,990-1147
+    arch = {"h_actor": (1, 2, 4)}
+    b = RolloutBuffer(capacity=5, observation_space=spaces.Box(low=-1, high=1, shape=(2,), dtype=np.float32),
+                      action_space=spaces.Discrete(2), num_envs=2, device="cuda", recurrent=True, hidden_state_architecture=arch)
+    assert b.buffer.get("hidden_states") is not None
+    for t in range(5):
+        b.add(obs=np.ones((2, 2)) * t, action=np.array([0, 1]), reward=np.array([1.0, -1.0]), done=np.array([False, t == 2]),
+              value=np.array([0.5, -0.5]), log_prob=np.array([0.1, 0.2]), hidden_state={"h_actor": torch.randn(1, 2, 4)})
+    assert "h_actor" in b.buffer["hidden_states"] and b.full
+    b.compute_returns_and_advantages(np.zeros(2), np.zeros(2))
+    b.prepare_sequence_tensors()
+    mbs = list(b.get_minibatch_sequences(batch_size=2))
+    assert len(mbs) >= 1
+    padded, unpadded = mbs[0]  # rollout_buffer.py:922 yields (padded, unpadded)
+    for k in ("observations", "actions", "pad_mask"):
+        assert k in padded
+    for k in ("log_probs", "advantages", "values", "returns"):
+        assert k in unpadded
+    assert "h_actor" in padded.get_non_tensor("initial_hidden_states")
+
+def test_recurrent_without_architecture_raises(cuda_device):  # reference tests/test_components/test_rollout_buffer.py:123-139
+    with pytest.raises(ValueError):
+        RolloutBuffer(capacity=5, observation_space=spaces.Box(low=-1, high=1, shape=(2,), dtype=np.float32),
+                      action_space=spaces.Discrete(2), num_envs=2, device="cuda", recurrent=True)
+
+def test_action_space_shapes(cuda_device):  # reference tests/test_components/test_rollout_buffer.py:208-276,2031-2071
+    for asp, act, shape in ((spaces.MultiDiscrete([3, 2]), np.array([[1, 0], [2, 1]]), (5, 2, 2)),
+                            (spaces.Box(low=-1, high=1, shape=(3,), dtype=np.float32), np.ones((2, 3)), (5, 2, 3)),
+                            (spaces.Discrete(4), np.array([1, 3]), (5, 2, 1))):
+        b = RolloutBuffer(capacity=5, observation_space=spaces.Box(low=-1, high=1, shape=(2,), dtype=np.float32),
+                          action_space=asp, num_envs=2, device="cuda")
+        b.add(obs=np.ones((2, 2)), action=act, reward=np.ones(2), done=np.zeros(2, bool), value=np.ones(2), log_prob=np.ones(2))
+        assert tuple(b.buffer["actions"].shape) == shape, (asp, b.buffer["actions"].shape)
+
+def test_empty_oversize_batch_and_reset(cuda_device):  # reference tests/test_components/test_rollout_buffer.py:652-734,886-922,1770-1862
+    b = RolloutBuffer(capacity=5, observation_space=spaces.Box(low=-1, high=1, shape=(2,), dtype=np.float32),
+                      action_space=spaces.Discrete(2), num_envs=2, device="cuda")
+    assert b.get() == {} and b.get_tensor_batch().is_empty()
+    for t in range(3):
+        b.add(obs=np.ones((2, 2)), action=np.array([0, 1]), reward=np.ones(2), done=np.zeros(2, bool), value=np.ones(2), log_prob=np.ones(2))
+    import warnings
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        d = b.get(batch_size=100)
+        assert d["rewards"].shape[0] == 6
+    d = b.get(batch_size=4)
+    assert d["rewards"].shape[0] == 4
+    b.reset(); assert b.pos == 0 and not b.full and b.size() == 0
+
+def test_setstate_reinitialises_invalid_buffer(cuda_device):  # reference tests/test_components/test_rollout_buffer.py:1908-2029
+    import warnings
+
+    def fresh():
+        return RolloutBuffer(capacity=5, observation_space=spaces.Box(low=-1, high=1, shape=(2,), dtype=np.float32),
+                             action_space=spaces.Discrete(2), num_envs=2, device="cuda")
+
+    b = fresh()
+    b.add(obs=np.ones((2, 2)), action=np.array([0, 1]), reward=np.ones(2), done=np.zeros(2, bool), value=np.ones(2),
+          log_prob=np.ones(2))
+    # a sound state round-trips with its contents
+    nb = RolloutBuffer.__new__(RolloutBuffer)
+    nb.__setstate__(b.__getstate__())
+    assert nb.pos == 1 and torch.equal(nb.buffer["rewards"], b.buffer["rewards"])
+    # missing / invalid buffer -> warning + fresh buffers (:1908-1953)
+    for mutate in (lambda s: s.pop("buffer"), lambda s: s.__setitem__("buffer", "invalid"), lambda s: s.pop("_leaves")):
+        st = b.__getstate__()
+        mutate(st)
+        nb = RolloutBuffer.__new__(RolloutBuffer)
+        with pytest.warns(UserWarning, match="Re-initializing"):
+            nb.__setstate__(st)
+        assert nb.buffer["rewards"].shape == (5, 2) and float(nb.buffer["rewards"].abs().sum()) == 0.0
+    # spaces missing as well -> second warning, early return, buffer left as found (:1955-1979)
+    st = b.__getstate__()
+    st["buffer"] = "invalid"
+    del st["observation_space"]
+    nb = RolloutBuffer.__new__(RolloutBuffer)
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        nb.__setstate__(st)
+    assert any("Observation" in str(m.message) for m in w) and nb.buffer == "invalid"
+    # leading shape mismatch -> warning + re-initialisation at the expected shape (:1981-2029)
+    st = b.__getstate__()
+    st["num_envs"] = 3
+    nb = RolloutBuffer.__new__(RolloutBuffer)
+    with pytest.warns(UserWarning, match="expected"):
+        nb.__setstate__(st)
+    assert nb.buffer["rewards"].shape == (5, 3)
+
+
+def test_single_env_and_next_obs(cuda_device):  # reference tests/test_components/test_rollout_buffer.py:326-359,2073-2110
+    b = RolloutBuffer(capacity=4, observation_space=spaces.Box(low=-1, high=1, shape=(3,), dtype=np.float32),
+                      action_space=spaces.Discrete(2), num_envs=1, device="cuda")
+    b.add(obs=np.ones(3), action=np.array(1), reward=np.array(1.0), done=np.array(False), value=np.array(0.3), log_prob=np.array(-0.2), next_obs=np.ones(3) * 2)
+    assert b.buffer["next_observations"][0].cpu().flatten().tolist() == [2.0, 2.0, 2.0]
