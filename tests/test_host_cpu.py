@@ -113,3 +113,28 @@ def test_shard_plan_partitions_population():
                 assert plan.owner(a) == r
         assert seen == list(range(P))
     assert list(ShardPlan(64, 8, 3).local_agents) == list(range(24, 32))
+
+
+# ---- reference tests/test_components/test_replay_data.py:80-170, restated (host-only formatters) -----
+def test_transition_and_formatters_like_reference_data_tests():
+    from agilerl_b200.components.data import Transition, to_tensordict, to_torch_tensor
+
+    t = Transition(obs=(np.array([1.0, 2.0]), 3.0), action=1, reward=1.0, next_obs=(np.array([4.0, 5.0]), 6.0), done=False)
+    assert "tuple_obs_0" in t.obs.keys() and "tuple_obs_1" in t.obs.keys()
+    with pytest.raises(AssertionError, match="Expected all elements of the tuple"):
+        Transition(obs=(np.array([1.0]), object()), action=0, reward=0.0, next_obs=np.array([2.0]), done=False)
+    t = Transition(obs={"vec": np.array([1.0, 2.0])}, action=0, reward=1.0, next_obs={"vec": np.array([3.0, 4.0])}, done=False)
+    assert "vec" in t.obs.keys() and "vec" in t.next_obs.keys()
+    t = Transition(obs=np.array([1.0]), action=0, reward=1.0, next_obs=np.array([2.0]), done=False)
+    assert t.reward.ndim >= 1 and t.done.ndim >= 1
+    td = to_tensordict((np.array([1.0, 2.0]), 3.0))
+    assert "tuple_obs_0" in td.keys() and td["tuple_obs_1"].dtype == torch.float32
+    td = to_tensordict({"a": np.array([1.0]), "b": torch.tensor([2.0])})
+    assert "a" in td.keys() and "b" in td.keys() and all(v.dtype == torch.float32 for v in td.values())
+    with pytest.raises(AssertionError, match="Expected all values of the dict"):
+        to_tensordict({"a": np.array([1.0]), "b": "invalid"})
+    assert to_torch_tensor(np.array([1.0, 2.0])).dtype == torch.float32
+    assert to_torch_tensor(42).item() == 42
+    assert to_torch_tensor(True).dtype == torch.float32
+    assert to_torch_tensor(torch.tensor([1.0], dtype=torch.float64)).dtype == torch.float32
+    assert to_torch_tensor([1, 2, 3]).shape == (3,)

@@ -120,3 +120,29 @@ def test_single_env_and_next_obs(cuda_device):  # reference tests/test_component
                       action_space=spaces.Discrete(2), num_envs=1, device="cuda")
     b.add(obs=np.ones(3), action=np.array(1), reward=np.array(1.0), done=np.array(False), value=np.array(0.3), log_prob=np.array(-0.2), next_obs=np.ones(3) * 2)
     assert b.buffer["next_observations"][0].cpu().flatten().tolist() == [2.0, 2.0, 2.0]
+
+
+# ---- replay buffers: reference tests/test_components/test_replay_buffer.py scenarios not covered elsewhere ----
+def test_replay_dict_observations_size_setter_storage(cuda_device):  # :302-340, :398-430, :826-864
+    from agilerl_b200.components import PrioritizedReplayBuffer, ReplayBuffer, TensorBatch
+
+    for cls, kw in ((ReplayBuffer, {}), (PrioritizedReplayBuffer, {"alpha": 0.6})):
+        buf = cls(max_size=100, device="cuda", **kw)
+        for i in range(10):
+            obs = TensorBatch({"image": torch.ones((1, 3, 84, 84)) * i, "vector": torch.tensor([[i, i + 1, i + 2]])},
+                              batch_size=[1])
+            buf.add(TensorBatch({"state": obs, "action": torch.tensor([[i % 3]]), "reward": torch.tensor([[float(i)]])},
+                                batch_size=[1]))
+        assert len(buf) == 10 and buf.storage is not None and buf.storage.batch_size[0] == 100
+        s = buf.sample(5) if cls is ReplayBuffer else buf.sample(5, beta=0.4)
+        assert tuple(s.batch_size) == (5,)
+        assert s["state"]["image"].shape == (5, 3, 84, 84) and s["state"]["vector"].shape == (5, 3)
+        assert s["action"].shape == (5, 1) and s["reward"].shape == (5, 1)
+        # every sampled row is one of the stored transitions, image and vector from the SAME step
+        img = s["state"]["image"][:, 0, 0, 0].cpu()
+        assert torch.equal(img.to(s["state"]["vector"].dtype), s["state"]["vector"][:, 0].cpu())
+        assert torch.equal(img, s["reward"][:, 0].cpu())
+        if cls is PrioritizedReplayBuffer:
+            assert s["weights"].shape == (5, 1) and s["idxs"].shape == (5, 1)
+        buf.size = 5
+        assert buf._size == 5 and len(buf) == 5
