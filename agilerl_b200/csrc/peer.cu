@@ -112,6 +112,7 @@ __device__ __forceinline__ void pull(const char *src, char *dst, long long bytes
 }
 
 __global__ void __launch_bounds__(256) peer_allgather_kernel(const __grid_constant__ PeerParams p) {
+  xp::pdl_enter();  // the block being published was written by earlier kernels of this stream
   const int r = blockIdx.x;  // the peer this CTA serves
   __shared__ int s_ok;
   if (threadIdx.x == 0) s_ok = peer_sync(p, r, true) ? 1 : 0;
@@ -141,6 +142,7 @@ struct PeerRingParams {
 };
 
 __global__ void __launch_bounds__(256) peer_ring_insert_kernel(const __grid_constant__ PeerRingParams p) {
+  xp::pdl_enter();
   const int r = blockIdx.y, c = blockIdx.x, parts = gridDim.x;
   __shared__ int s_ok;
   if (threadIdx.x == 0) s_ok = peer_sync(p, r, c == 0) ? 1 : 0;
@@ -187,7 +189,7 @@ xp_status_t xp_peer_allgather(const void *const *peer_base, void *const *peer_fl
   p.epoch = epoch;
   p.err = err_flag_dev;
   p.timeout_cycles = 4000000000ll;  // ~2 s at 2 GHz: report, do not hang
-  peer_allgather_kernel<<<world, 256, 0, (cudaStream_t)stream>>>(p);
+  xp::launch(peer_allgather_kernel, dim3(world), dim3(256), 0, (cudaStream_t)stream, p);
   return xp::check_launch("xp_peer_allgather");
 }
 
@@ -232,7 +234,7 @@ xp_status_t xp_peer_ring_insert(const void *const *peer_base, void *const *peer_
   const long long cap = 128 / world;
   if (parts > cap) parts = cap;
   if (parts < 1) parts = 1;
-  peer_ring_insert_kernel<<<dim3((unsigned)parts, (unsigned)world), 256, 0, (cudaStream_t)stream>>>(p);
+  xp::launch(peer_ring_insert_kernel, dim3((unsigned)parts, (unsigned)world), dim3(256), 0, (cudaStream_t)stream, p);
   return xp::check_launch("xp_peer_ring_insert");
 }
 
