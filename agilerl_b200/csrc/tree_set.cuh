@@ -514,7 +514,7 @@ __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long
 
 // one warp per PAIR of buckets: both <= 16 items -> the two half-warps climb them side by side;
 // otherwise one after the other with the whole warp.
-constexpr int kBucketWarps = 8;
+constexpr int kBucketWarps = 4;  // 56 registers: 9 CTAs of 4 warps fit an SM where 4 CTAs of 8 do (36 vs 32 warps)
 template <bool PAIRED>
 __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk, int use_half) {
   xp::pdl_enter();
