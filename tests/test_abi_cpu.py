@@ -110,3 +110,43 @@ def test_torch_cpu_stream_mirror_and_writeback():
     torch.manual_seed(2)
     want = torch.randperm(100000)[:64].numpy()
     assert np.array_equal(xo.randperm_prefix(raw, 64, 100000), want) and torch.equal(nxt, torch.rand(3))
+
+
+def test_ctypes_signatures_match_the_header_argument_by_argument():
+    """Binding drift check: for every prototype in include/b200xp.h the ctypes table has the same number
+    of parameters and the same kind for each (pointer / 64-bit integer / 32-bit integer / double)."""
+    text = open(os.path.join(ROOT, "include", "b200xp.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    protos = re.findall(r"\b[a-z_0-9]+(?:\s*\*)?\s+(xp_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", text, flags=re.S)
+    assert len(protos) >= 30
+
+    def kind_of_c(param: str) -> str:
+        param = " ".join(param.split())
+        if "*" in param:
+            return "ptr"
+        base = param.rsplit(" ", 1)[0] if " " in param else param
+        if base in ("int64_t", "uint64_t"):
+            return "i64"
+        if base in ("int", "uint32_t", "xp_status_t"):
+            return "i32"
+        if base == "double":
+            return "f64"
+        raise AssertionError(f"unclassified parameter {param!r}")
+
+    def kind_of_ctypes(t) -> str:
+        if t is C.c_void_p or t is C.c_char_p or (isinstance(t, type) and issubclass(t, C._Pointer)):
+            return "ptr"
+        if t in (C.c_int64, C.c_uint64, C.c_longlong, C.c_ulonglong):
+            return "i64"
+        if t in (C.c_int, C.c_uint32, C.c_uint):
+            return "i32"
+        if t is C.c_double:
+            return "f64"
+        raise AssertionError(f"unclassified ctypes type {t}")
+
+    for name, params in protos:
+        params = params.strip()
+        want = [] if params in ("", "void") else [kind_of_c(q) for q in params.split(",")]
+        _, argtypes = nv._SIGNATURES[name]
+        got = [kind_of_ctypes(t) for t in argtypes]
+        assert got == want, f"{name}: header {want} vs _native.py {got}"
