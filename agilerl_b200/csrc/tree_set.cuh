@@ -390,6 +390,10 @@ struct Buckets {
   int *counts, *offsets, *cursors;
   u64 *items;
   double *vals;    // kSrcPrio only: leaf value per batch position (else NULL)
+  int slots;       // 0: compact slices (offsets / cursors).  > 0 (schedule S): bucket b owns the fixed
+                   // slice items[b*slots, (b+1)*slots); what does not fit goes to `ovf`
+  u64 *ovf;        // overflow items of all buckets, *ovn of them (aux[5], zero between calls)
+  int *ovn;
 };
 
 // Largest bucket count any batch can ask for on this tree: the counters that must be ZERO between
@@ -419,6 +423,34 @@ __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift
   off = (off + 1) & ~1ll;
   b.items = reinterpret_cast<u64 *>(t.aux + off);
   b.vals = want_vals ? reinterpret_cast<double *>(t.aux + off + 2 * B) : nullptr;
+  b.slots = 0;
+  b.ovf = nullptr;
+  b.ovn = nullptr;
+  return b;
+}
+
+// schedule S: one pass instead of histogram + scan + scatter.  A bucket expects ~16 items; its fixed
+// slice holds 32, the rest (hot ranges: freshly inserted transitions carry the maximum priority and
+// are sampled together) spill to one shared overflow list that only the overflowing buckets scan.
+constexpr int kSlots = 32;
+__host__ __device__ inline long long slotted_scratch_ints(long long cap, long long nb, long long B, bool want_vals) {
+  return 16 + max_buckets(cap) + 2 + 2 * nb * kSlots + 2 * B + (want_vals ? 2 * B : 0);
+}
+__host__ __device__ inline Buckets make_slotted(const Tree &t, int nb, int shift, long long B, bool want_vals) {
+  Buckets b;
+  b.nb = nb;
+  b.shift = shift;
+  b.top = shift;
+  b.counts = t.aux + 16;
+  b.offsets = nullptr;
+  b.cursors = nullptr;
+  long long off = 16 + max_buckets(t.cap);
+  off = (off + 1) & ~1ll;
+  b.items = reinterpret_cast<u64 *>(t.aux + off);
+  b.ovf = b.items + (long long)nb * kSlots;
+  b.vals = want_vals ? reinterpret_cast<double *>(b.ovf + B) : nullptr;
+  b.slots = kSlots;
+  b.ovn = t.aux + 5;
   return b;
 }
 
@@ -512,6 +544,29 @@ __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long
   if (bk.vals) bk.vals[i] = pow_call(clamp_prio(s.prio[i]), s.alpha);
 }
 
+__global__ void __launch_bounds__(256) set_slot_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
+  xp::pdl_enter();
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  double p = 0.0;
+  if (i < B) {
+    long long leaf;
+    const u64 key = item_key(s, i, leaf);
+    if (key == kPad) {
+      if (s.err) *s.err = 1;
+    } else {
+      const int b = (int)(leaf >> bk.shift);
+      const int slot = atomicAdd(&bk.counts[b], 1);
+      if (slot < bk.slots) bk.items[(long long)b * bk.slots + slot] = key;
+      else bk.ovf[atomicAdd(bk.ovn, 1)] = key;
+    }
+    if (s.kind == kSrcPrio) {
+      p = clamp_prio(s.prio[i]);
+      if (bk.vals) bk.vals[i] = pow_call(p, s.alpha);
+    }
+  }
+  if (s.kind == kSrcPrio) fold_max_priority(s, p);
+}
+
 // one warp per PAIR of buckets: both <= 16 items -> the two half-warps climb them side by side;
 // otherwise one after the other with the whole warp.
 constexpr int kBucketWarps = 4;  // 56 registers: 9 CTAs of 4 warps fit an SM where 4 CTAs of 8 do (36 vs 32 warps)
@@ -523,8 +578,18 @@ __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, 
   if (b0 >= bk.nb) return;
   s.pre = bk.vals;
   const int has1 = (b0 + 1 < bk.nb);
-  const int beg0 = bk.offsets[b0], n0 = bk.cursors[b0] - beg0;
-  const int beg1 = has1 ? bk.offsets[b0 + 1] : 0, n1 = has1 ? bk.cursors[b0 + 1] - beg1 : 0;
+  int beg0, n0, beg1, n1;
+  if (bk.slots) {
+    beg0 = b0 * bk.slots;
+    n0 = __ldcg(&bk.counts[b0]);
+    beg1 = beg0 + bk.slots;
+    n1 = has1 ? __ldcg(&bk.counts[b0 + 1]) : 0;
+  } else {
+    beg0 = bk.offsets[b0];
+    n0 = bk.cursors[b0] - beg0;
+    beg1 = has1 ? bk.offsets[b0 + 1] : 0;
+    n1 = has1 ? bk.cursors[b0 + 1] - beg1 : 0;
+  }
   if (n0 == 0 && n1 == 0) return;
   if (lane == 0) {  // scratch back to zero for the next call
     bk.counts[b0] = 0;
@@ -543,6 +608,15 @@ __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, 
     const u64 *items = bk.items + beg;
     if (n <= 32) {
       warp_climb<PAIRED, 32>(t, s, lane < n ? __ldcg(&items[lane]) : kPad, bk.top);
+    } else if (bk.slots) {
+      // the slice is full: the rest of this bucket's items are somewhere in the shared overflow list
+      const int b = b0 + h, ov = __ldcg(bk.ovn);
+      auto fetch = [&](long long i) -> u64 {
+        if (i < bk.slots) return __ldcg(&items[i]);
+        const u64 k = __ldcg(&bk.ovf[i - bk.slots]);
+        return ((int)(k >> 32) >> bk.shift) == b ? k : kPad;
+      };
+      warp_climb_large<PAIRED>(t, s, fetch, (long long)bk.slots + ov, bk.top);
     } else {
       auto fetch = [&](long long i) -> u64 { return __ldcg(&items[i]); };
       warp_climb_large<PAIRED>(t, s, fetch, n, bk.top);
@@ -590,6 +664,7 @@ __global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0
   xp::pdl_enter();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_last;
+  if (blockIdx.x == 0 && threadIdx.x == 0) t.aux[5] = 0;  // schedule S's overflow count: its readers are done
   const int C = 1 << logC;
   double *S = reinterpret_cast<double *>(smem_raw);
   double *M = S + 2 * C;
@@ -709,6 +784,24 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   const int use_half = 1;
   while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;  // ~16 items per bucket
   const bool want_vals = s.kind == kSrcPrio;
+  if (slotted_scratch_ints(t.cap, nb, B, want_vals) <= t.cap && !getenv("XP_NO_S")) {  // schedule S
+    const int shift = L - ilog2(nb);
+    Buckets bk = make_slotted(t, (int)nb, shift, B, want_vals);
+    int top = L - ilog2(B) - 1;  // as in schedule L below
+    if (top < 1) top = 1;
+    if (top > shift) top = shift;
+    bk.top = top;
+    xp::launch(set_slot_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bk);
+    const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps) / kBucketWarps);
+    if (paired)
+      xp::launch(set_wbucket_kernel<true>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
+    else
+      xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
+    launches = 2;
+    xp_status_t rc = launch_dense(t, bk.top, t.cap >> bk.top, bk.top == shift ? 8 : 10, st, launches);
+    if (rc != XP_OK) return rc;
+    return xp::check_launch("tree set (S)", launches);
+  }
   const long long need = bucket_scratch_ints(t.cap, nb, B, want_vals);
   if (need <= t.cap) {  // schedule L
     const int shift = L - ilog2(nb);
