@@ -394,7 +394,16 @@ struct Buckets {
                    // slice items[b*slots, (b+1)*slots); what does not fit goes to `ovf`
   u64 *ovf;        // overflow items of all buckets, *ovn of them (aux[5], zero between calls)
   int *ovn;
+  int guard;       // schedule S with its exact fallback: +1 = this launch is the slotted climb and runs only
+                   // while the overflow stays small, -1 = it belongs to the fallback (scan / scatter /
+                   // compact climb over the SAME counters) and runs only when it did not, 0 = always
 };
+constexpr int kOvfLimit = 1024;  // overflow entries an overflowing bucket may have to scan
+__device__ __forceinline__ bool guarded_out(const Buckets &bk) {
+  if (bk.guard == 0) return false;
+  const bool big = __ldcg(bk.ovn) > kOvfLimit;
+  return bk.guard > 0 ? big : !big;
+}
 
 // Largest bucket count any batch can ask for on this tree: the counters that must be ZERO between
 // calls live in a region sized by it, so that calls with different batch sizes —
@@ -425,7 +434,8 @@ __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift
   b.vals = want_vals ? reinterpret_cast<double *>(t.aux + off + 2 * B) : nullptr;
   b.slots = 0;
   b.ovf = nullptr;
-  b.ovn = nullptr;
+  b.ovn = t.aux + 5;
+  b.guard = 0;
   return b;
 }
 
@@ -433,24 +443,19 @@ __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift
 // slice holds 32, the rest (hot ranges: freshly inserted transitions carry the maximum priority and
 // are sampled together) spill to one shared overflow list that only the overflowing buckets scan.
 constexpr int kSlots = 32;
+// (the slices and the overflow list sit BEHIND schedule L's scratch: when too much overflows, L's scan /
+// scatter / climb finish the job from the same counters)
 __host__ __device__ inline long long slotted_scratch_ints(long long cap, long long nb, long long B, bool want_vals) {
-  return 16 + max_buckets(cap) + 2 + 2 * nb * kSlots + 2 * B + (want_vals ? 2 * B : 0);
+  return bucket_scratch_ints(cap, nb, B, want_vals) + 2 + 2 * nb * kSlots + 2 * B;
 }
 __host__ __device__ inline Buckets make_slotted(const Tree &t, int nb, int shift, long long B, bool want_vals) {
-  Buckets b;
-  b.nb = nb;
-  b.shift = shift;
-  b.top = shift;
-  b.counts = t.aux + 16;
-  b.offsets = nullptr;
-  b.cursors = nullptr;
-  long long off = 16 + max_buckets(t.cap);
+  Buckets b = make_buckets(t, nb, shift, B, want_vals);  // same counters, same vals
+  long long off = bucket_scratch_ints(t.cap, nb, B, want_vals);
   off = (off + 1) & ~1ll;
   b.items = reinterpret_cast<u64 *>(t.aux + off);
   b.ovf = b.items + (long long)nb * kSlots;
-  b.vals = want_vals ? reinterpret_cast<double *>(b.ovf + B) : nullptr;
   b.slots = kSlots;
-  b.ovn = t.aux + 5;
+  b.guard = 1;
   return b;
 }
 
@@ -482,6 +487,7 @@ __device__ __forceinline__ int warp_inclusive(int v, int lane) {
 }
 __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
   xp::pdl_enter();
+  if (guarded_out(bk)) return;
   // One CTA.  Counters come in and prefixes go out coalesced through shared memory (one pad word
   // per 32 keeps both the row-wise copies and the per-thread runs bank-conflict free); in between
   // thread t owns E = nb / 1024 CONSECUTIVE counters (nb is a power of two <= 32768): a serial sum,
@@ -534,14 +540,16 @@ __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
 // lanes busy, and parked by batch position for the bucket warp that will need it
 __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
   xp::pdl_enter();
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B) return;
-  long long leaf;
-  const u64 key = item_key(s, i, leaf);
-  if (key == kPad) return;
-  const int slot = atomicAdd(&bk.cursors[leaf >> bk.shift], 1);
-  bk.items[slot] = key;
-  if (bk.vals) bk.vals[i] = pow_call(clamp_prio(s.prio[i]), s.alpha);
+  if (guarded_out(bk)) return;
+  // grid-stride: as schedule S's fallback this is launched with a small grid (it usually returns above)
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < B; i += (long long)gridDim.x * blockDim.x) {
+    long long leaf;
+    const u64 key = item_key(s, i, leaf);
+    if (key == kPad) continue;
+    const int slot = atomicAdd(&bk.cursors[leaf >> bk.shift], 1);
+    bk.items[slot] = key;
+    if (bk.vals) bk.vals[i] = pow_call(clamp_prio(s.prio[i]), s.alpha);
+  }
 }
 
 __global__ void __launch_bounds__(256) set_slot_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
@@ -571,12 +579,9 @@ __global__ void __launch_bounds__(256) set_slot_kernel(Tree t, SetSrc s, long lo
 // otherwise one after the other with the whole warp.
 constexpr int kBucketWarps = 4;  // 56 registers: 9 CTAs of 4 warps fit an SM where 4 CTAs of 8 do (36 vs 32 warps)
 template <bool PAIRED>
-__global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk, int use_half) {
-  xp::pdl_enter();
+__device__ __forceinline__ void climb_bucket_pair(const Tree &t, const SetSrc &s, const Buckets &bk, int use_half,
+                                                  int b0) {
   const int lane = threadIdx.x & 31;
-  const int b0 = 2 * (blockIdx.x * kBucketWarps + (threadIdx.x >> 5));
-  if (b0 >= bk.nb) return;
-  s.pre = bk.vals;
   const int has1 = (b0 + 1 < bk.nb);
   int beg0, n0, beg1, n1;
   if (bk.slots) {
@@ -622,6 +627,16 @@ __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, 
       warp_climb_large<PAIRED>(t, s, fetch, n, bk.top);
     }
   }
+}
+
+template <bool PAIRED>
+__global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk, int use_half) {
+  xp::pdl_enter();
+  if (guarded_out(bk)) return;
+  s.pre = bk.vals;
+  // warp-uniform grid-stride over bucket pairs (one trip, except as schedule S's small-grid fallback)
+  for (int w = blockIdx.x * kBucketWarps + (threadIdx.x >> 5); 2 * w < bk.nb; w += gridDim.x * kBucketWarps)
+    climb_bucket_pair<PAIRED>(t, s, bk, use_half, 2 * w);
 }
 
 // ---- schedule D helpers ----------------------------------------------------------------------------
@@ -784,21 +799,38 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   const int use_half = 1;
   while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;  // ~16 items per bucket
   const bool want_vals = s.kind == kSrcPrio;
-  if (slotted_scratch_ints(t.cap, nb, B, want_vals) <= t.cap && !getenv("XP_NO_S")) {  // schedule S
+  if (slotted_scratch_ints(t.cap, nb, B, want_vals) <= t.cap && s.kind != kSrcRange && !getenv("XP_NO_S")) {
+    // schedule S, and behind it — same counters, launches that return at once unless the overflow list
+    // grew past kOvfLimit (skewed batches) — the scan / scatter / compact climb of schedule L
     const int shift = L - ilog2(nb);
-    Buckets bk = make_slotted(t, (int)nb, shift, B, want_vals);
+    Buckets bs = make_slotted(t, (int)nb, shift, B, want_vals);
+    Buckets bl = make_buckets(t, (int)nb, shift, B, want_vals);
+    bl.guard = -1;
     int top = L - ilog2(B) - 1;  // as in schedule L below
     if (top < 1) top = 1;
     if (top > shift) top = shift;
-    bk.top = top;
-    xp::launch(set_slot_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bk);
+    bs.top = bl.top = top;
+    static bool scan_attr2 = false;
+    {
+      xp_status_t rc = set_attr_once((const void *)set_scan_kernel, (size_t)(32768 + 1024) * 4, scan_attr2);
+      if (rc != XP_OK) return rc;
+    }
     const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps) / kBucketWarps);
+    xp::launch(set_slot_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bs);
     if (paired)
-      xp::launch(set_wbucket_kernel<true>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
+      xp::launch(set_wbucket_kernel<true>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bs, use_half);
     else
-      xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
-    launches = 2;
-    xp_status_t rc = launch_dense(t, bk.top, t.cap >> bk.top, bk.top == shift ? 8 : 10, st, launches);
+      xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bs, use_half);
+    xp::launch(set_scan_kernel, dim3(1), dim3(1024), (size_t)(nb + nb / 32 + 1) * 4, st, bl);
+    const unsigned fgrid = (unsigned)(2 * xp::sm_count());  // the fallback's launches: small grids, grid-stride
+    xp::launch(set_scatter_kernel, dim3(grid < fgrid ? grid : fgrid), dim3(256), 0, st, t, s, B, bl);
+    const unsigned fb = bgrid < 4 * fgrid ? bgrid : 4 * fgrid;
+    if (paired)
+      xp::launch(set_wbucket_kernel<true>, dim3(fb), dim3(kBucketWarps * 32), 0, st, t, s, bl, use_half);
+    else
+      xp::launch(set_wbucket_kernel<false>, dim3(fb), dim3(kBucketWarps * 32), 0, st, t, s, bl, use_half);
+    launches = 5;
+    xp_status_t rc = launch_dense(t, top, t.cap >> top, top == shift ? 8 : 10, st, launches);
     if (rc != XP_OK) return rc;
     return xp::check_launch("tree set (S)", launches);
   }
