@@ -639,6 +639,88 @@ __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, 
     climb_bucket_pair<PAIRED>(t, s, bk, use_half, 2 * w);
 }
 
+// ---- schedule S's fallback in ONE launch ----------------------------------------------------------
+// scan | scatter | compact climb over the counters schedule S has already filled, as phases of one small
+// grid (<= 2 CTAs per SM, all resident) separated by grid barriers.  In the common case — the
+// overflow list stayed under kOvfLimit — every CTA returns at its first instruction, so the
+// robustness against skewed batches costs one empty launch instead of three.
+__device__ __forceinline__ bool grid_barrier(int *ctr, int target) {
+  __shared__ int s_ok;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(ctr, 1);
+    const long long t0 = clock64();
+    int v, ok = 1;
+    do {
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+      if (v < target) {
+        if (clock64() - t0 > 4000000000ll) {  // ~2 s: a CTA of this grid never became resident
+          ok = 0;
+          break;
+        }
+        __nanosleep(32);
+      }
+    } while (v < target);
+    s_ok = ok;
+  }
+  __syncthreads();
+  return s_ok != 0;
+}
+
+template <bool PAIRED>
+__global__ void __launch_bounds__(256) set_fallback_kernel(Tree t, SetSrc s, long long B, Buckets bk, int use_half) {
+  xp::pdl_enter();
+  if (guarded_out(bk)) return;
+  __shared__ int s_part[8];
+  int *bar = t.aux + 6;  // arrivals; zeroed by the dense kernel that follows
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // phase 1: exclusive scan of the counters by CTA 0 (thread-serial runs + one block scan)
+  if (blockIdx.x == 0) {
+    const int nb = bk.nb;
+    const int E = (nb + 255) >> 8;
+    const int base = tid * E;
+    int sum = 0;
+    for (int k = 0; k < E; ++k)
+      if (base + k < nb) sum += __ldcg(&bk.counts[base + k]);
+    const int inc = warp_inclusive(sum, lane);
+    if (lane == 31) s_part[warp] = inc;
+    __syncthreads();
+    int before = 0;
+    for (int w = 0; w < warp; ++w) before += s_part[w];
+    int run = before + inc - sum;
+    for (int k = 0; k < E; ++k) {
+      if (base + k < nb) {
+        const int c = __ldcg(&bk.counts[base + k]);
+        bk.offsets[base + k] = run;
+        bk.cursors[base + k] = run;
+        run += c;
+      }
+    }
+    if (tid == 255) bk.offsets[nb] = run;
+  }
+  if (!grid_barrier(bar, (int)gridDim.x)) {
+    if (s.err) *s.err = 1;
+    return;
+  }
+  // phase 2: scatter into the compact slices
+  for (long long i = (long long)blockIdx.x * blockDim.x + tid; i < B; i += (long long)gridDim.x * blockDim.x) {
+    long long leaf;
+    const u64 key = item_key(s, i, leaf);
+    if (key == kPad) continue;
+    const int slot = atomicAdd(&bk.cursors[leaf >> bk.shift], 1);
+    bk.items[slot] = key;
+  }
+  if (!grid_barrier(bar, 2 * (int)gridDim.x)) {
+    if (s.err) *s.err = 1;
+    return;
+  }
+  // phase 3: the compact climb (leaf values were parked by the slot kernel)
+  s.pre = bk.vals;
+  for (int w = blockIdx.x * 8 + warp; 2 * w < bk.nb; w += gridDim.x * 8)
+    climb_bucket_pair<PAIRED>(t, s, bk, use_half, 2 * w);
+}
+
 // ---- schedule D helpers ----------------------------------------------------------------------------
 // tickets: aux[cap + leaf] = max(pos + 1) = the last writer of the leaf
 __global__ void __launch_bounds__(256) set_ticket_kernel(Tree t, SetSrc s, long long B) {
@@ -679,7 +761,10 @@ __global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0
   xp::pdl_enter();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_last;
-  if (blockIdx.x == 0 && threadIdx.x == 0) t.aux[5] = 0;  // schedule S's overflow count: its readers are done
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // schedule S's overflow count and its fallback's barrier: readers are done
+    t.aux[5] = 0;
+    t.aux[6] = 0;
+  }
   const int C = 1 << logC;
   double *S = reinterpret_cast<double *>(smem_raw);
   double *M = S + 2 * C;
@@ -800,8 +885,8 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;  // ~16 items per bucket
   const bool want_vals = s.kind == kSrcPrio;
   if (slotted_scratch_ints(t.cap, nb, B, want_vals) <= t.cap && s.kind != kSrcRange && !getenv("XP_NO_S")) {
-    // schedule S, and behind it — same counters, launches that return at once unless the overflow list
-    // grew past kOvfLimit (skewed batches) — the scan / scatter / compact climb of schedule L
+    // schedule S, and behind it — same counters, ONE launch that returns at once unless the overflow list
+    // grew past kOvfLimit (skewed batches) — the scan | scatter | compact climb of schedule L
     const int shift = L - ilog2(nb);
     Buckets bs = make_slotted(t, (int)nb, shift, B, want_vals);
     Buckets bl = make_buckets(t, (int)nb, shift, B, want_vals);
@@ -810,26 +895,18 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     if (top < 1) top = 1;
     if (top > shift) top = shift;
     bs.top = bl.top = top;
-    static bool scan_attr2 = false;
-    {
-      xp_status_t rc = set_attr_once((const void *)set_scan_kernel, (size_t)(32768 + 1024) * 4, scan_attr2);
-      if (rc != XP_OK) return rc;
-    }
     const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps) / kBucketWarps);
     xp::launch(set_slot_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bs);
     if (paired)
       xp::launch(set_wbucket_kernel<true>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bs, use_half);
     else
       xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bs, use_half);
-    xp::launch(set_scan_kernel, dim3(1), dim3(1024), (size_t)(nb + nb / 32 + 1) * 4, st, bl);
-    const unsigned fgrid = (unsigned)(2 * xp::sm_count());  // the fallback's launches: small grids, grid-stride
-    xp::launch(set_scatter_kernel, dim3(grid < fgrid ? grid : fgrid), dim3(256), 0, st, t, s, B, bl);
-    const unsigned fb = bgrid < 4 * fgrid ? bgrid : 4 * fgrid;
+    const unsigned fgrid = (unsigned)(2 * xp::sm_count());  // all resident: the phases meet at grid barriers
     if (paired)
-      xp::launch(set_wbucket_kernel<true>, dim3(fb), dim3(kBucketWarps * 32), 0, st, t, s, bl, use_half);
+      xp::launch(set_fallback_kernel<true>, dim3(fgrid), dim3(256), 0, st, t, s, B, bl, use_half);
     else
-      xp::launch(set_wbucket_kernel<false>, dim3(fb), dim3(kBucketWarps * 32), 0, st, t, s, bl, use_half);
-    launches = 5;
+      xp::launch(set_fallback_kernel<false>, dim3(fgrid), dim3(256), 0, st, t, s, B, bl, use_half);
+    launches = 3;
     xp_status_t rc = launch_dense(t, top, t.cap >> top, top == shift ? 8 : 10, st, launches);
     if (rc != XP_OK) return rc;
     return xp::check_launch("tree set (S)", launches);
