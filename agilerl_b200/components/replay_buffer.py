@@ -29,6 +29,8 @@ from .tensor_batch import TensorBatch, as_batch
 
 DataType = Any
 
+_TORCH_RAND = torch.rand  # the builtin: a patched ``torch.rand`` (the reference's tests mock it, test_replay_buffer.py:956-1000) is honoured call by call
+
 
 def _flatten(batch: TensorBatch, prefix=()) -> list[tuple[tuple, torch.Tensor]]:
     out = []
@@ -60,13 +62,16 @@ class ReplayBuffer:
         lives on this device when it is a CUDA device, else on the current CUDA device.
     :param dtype: kept for signature compatibility (the reference ignores it too)
     :param rng: "torch" (reference's CPU mt19937 stream) or "device" (Philox on the GPU)
-    :param exact_rng_advance: also skip the ``size-1-batch`` draws torch.randperm would have
-        consumed, so that *subsequent* calls stay aligned with the reference (O(size) host work).
+    :param exact_rng_advance: (default) also skip the ``size-1-batch`` words torch.randperm would
+        have consumed, so that a whole seeded RUN — later ``sample`` calls and every other consumer
+        of torch's global generator — stays aligned with the reference, not just the first call.
+        O(size) host work at ~0.4 ns per word (0.4 ms at 1 M rows; the reference's own randperm is
+        ~60 ms there).  ``False`` trades that alignment for throughput.
     """
 
     def __init__(self, max_size: int, device: str | torch.device = "cpu",
                  dtype: torch.dtype = torch.float32, *, rng: str = "torch",
-                 exact_rng_advance: bool = False, seed: int = 0) -> None:
+                 exact_rng_advance: bool = True, seed: int = 0) -> None:
         self.max_size = max_size
         self.device = device
         self.dtype = dtype
@@ -117,14 +122,17 @@ class ReplayBuffer:
             self._sdev = nv.require_cuda(self.device)
         return self._sdev
 
-    def _out(self, batch: TensorBatch) -> TensorBatch:
-        """Move a sampled batch to ``self.device`` (no-op when that is the storage device)."""
+    def _out_is_storage(self) -> bool:
         same = getattr(self, "_out_same", None)
         if same is None:
             dev = torch.device(self.device)
             same = dev.type == "cuda" and (dev.index is None or dev == self.storage_device)
             self._out_same = same
-        return batch if same else batch.to(torch.device(self.device))
+        return same
+
+    def _out(self, batch: TensorBatch) -> TensorBatch:
+        """Move a sampled batch to ``self.device`` (no-op when that is the storage device)."""
+        return batch if self._out_is_storage() else batch.to(torch.device(self.device))
 
     # -- add (reference :60-112) ---------------------------------------------------------------
     def _init(self, data: TensorBatch) -> None:
@@ -207,6 +215,10 @@ class ReplayBuffer:
                 raw = xp.philox_u32(self._philox_seed, self._philox_offset, b, dev)
             self._philox_offset += (b + 3) // 4
         with nv.on_device(dev):
+            if b > 16384:  # beyond the kernel's shared-memory table: the chunked prefix
+                from .rollout_buffer import chunked_randperm_prefix
+
+                return chunked_randperm_prefix(raw, b, n)
             return xp.randperm_prefix(raw, b, 1, n)
 
     def _gather_plan(self):
@@ -318,15 +330,15 @@ class MultiStepReplayBuffer(ReplayBuffer):
         self.reward_key = "reward"
         self.done_key = None
         self.ns_key = "next_obs"
-        self._stage: dict[tuple, torch.Tensor] = {}
-        self._stage_n = 0
-        self._stage_count = 0
+        self._nstage: dict[tuple, torch.Tensor] = {}
+        self._nstage_n = 0
+        self._nstage_count = 0
 
     def _init_stage(self, data: TensorBatch, n: int) -> None:
-        self._stage = {p: torch.zeros((self.n_step * n, *t.shape[1:]), dtype=t.dtype,
+        self._nstage = {p: torch.zeros((self.n_step * n, *t.shape[1:]), dtype=t.dtype,
                                       device=self.storage_device)
                        for p, t in _flatten(data)}
-        self._stage_n = n
+        self._nstage_n = n
 
     def _detect_keys(self) -> None:
         first = self.n_step_buffer[0]
@@ -347,7 +359,7 @@ class MultiStepReplayBuffer(ReplayBuffer):
     def _fold_into(self, dst: dict[tuple, torch.Tensor], cursor: int, dst_rows: int) -> None:
         if not self.initialized or self.done_key is None:
             self._detect_keys()
-        paths = list(self._stage.keys())
+        paths = list(self._nstage.keys())
         roles = []
         for p in paths:
             if p[0] == self.reward_key:
@@ -357,33 +369,33 @@ class MultiStepReplayBuffer(ReplayBuffer):
             else:
                 roles.append(nv.XP_ROLE_FIRST)
         done_path = (self.done_key,)
-        done_t = self._stage[done_path]
+        done_t = self._nstage[done_path]
         if done_t.dtype in (torch.bool, torch.uint8, torch.int8):
             done_bytes = 1
         elif done_t.dtype in (torch.float32, torch.int32):
             done_bytes = 4
         else:
             raise TypeError(f"unsupported done dtype {done_t.dtype}")
-        if self._stage[(self.reward_key,)].dtype != torch.float32:
+        if self._nstage[(self.reward_key,)].dtype != torch.float32:
             raise TypeError("n-step reward must be float32 (Transition casts it, data.py:85-87)")
         gpow = [float(np.float32(self.gamma**i)) for i in range(self.n_step)]
-        slot0 = self._stage_count % self.n_step  # oldest step (the ring is full here)
+        slot0 = self._nstage_count % self.n_step  # oldest step (the ring is full here)
         with nv.on_device(self.storage_device):
-            xp.nstep_fold_insert([(self._stage[p], dst[p]) for p in paths], roles,
+            xp.nstep_fold_insert([(self._nstage[p], dst[p]) for p in paths], roles,
                                  paths.index(done_path), done_bytes, self.n_step, slot0, gpow,
-                                 self._stage_n, cursor, dst_rows)
+                                 self._nstage_n, cursor, dst_rows)
 
     def add(self, data: DataType) -> TensorBatch | None:
         data, n = self._prepare(data)
-        if not self._stage:
+        if not self._nstage:
             self._init_stage(data, n)
-        if n != self._stage_n:
-            raise ValueError(f"n-step buffer was initialised with {self._stage_n} envs, got {n}")
-        slot = self._stage_count % self.n_step
+        if n != self._nstage_n:
+            raise ValueError(f"n-step buffer was initialised with {self._nstage_n} envs, got {n}")
+        slot = self._nstage_count % self.n_step
         with nv.on_device(self.storage_device):
-            xp.ring_insert(self._pairs(data, self._stage), n, slot * n, self.n_step * n)
-        self._stage_count += 1
-        view = _unflatten({p: t[slot * n:(slot + 1) * n] for p, t in self._stage.items()}, [n])
+            xp.ring_insert(self._pairs(data, self._nstage), n, slot * n, self.n_step * n)
+        self._nstage_count += 1
+        view = _unflatten({p: t[slot * n:(slot + 1) * n] for p, t in self._nstage.items()}, [n])
         self.n_step_buffer.append(view)
 
         if len(self.n_step_buffer) < self.n_step:
@@ -404,12 +416,29 @@ class MultiStepReplayBuffer(ReplayBuffer):
         return self._out(self._gather(idxs, tuple(idxs.shape) if idxs.ndim > 1 else None))
 
     def _get_n_step_info(self) -> TensorBatch:
-        """The folded n-step transition for the current window (reference :206-258)."""
-        n = self._stage_n
-        tmp = {p: torch.empty((n, *t.shape[1:]), dtype=t.dtype, device=t.device)
-               for p, t in self._stage.items()}
-        self._fold_into(tmp, 0, n)
-        return _unflatten(tmp, [n])
+        """The folded n-step transition of the transitions currently in ``n_step_buffer``, oldest
+        first (reference :206-258) — whatever put them there: ``add`` (device views of the stage
+        ring) or a direct ``n_step_buffer.append`` as the reference's tests do.  Not the hot path:
+        ``add`` folds straight out of the stage ring into the storage."""
+        entries = [as_batch(e) for e in self.n_step_buffer]
+        assert entries, "n_step_buffer is empty"
+        if not self.initialized or self.done_key is None:
+            self._detect_keys()
+        dev = self.storage_device
+        n = entries[0].shape[0] if len(entries[0].shape) else 1
+        m = len(entries)
+        flat = [dict(_flatten(e.to(dev))) for e in entries]
+        paths = list(flat[0].keys())
+        stage = {p: torch.cat([f[p].reshape(n, -1) for f in flat], 0).contiguous() for p in paths}
+        tmp = {p: torch.empty_like(stage[p][:n]) for p in paths}
+        saved = self._nstage, self._nstage_n, self._nstage_count, self.n_step
+        try:
+            self._nstage, self._nstage_n, self._nstage_count, self.n_step = stage, n, 0, m
+            self._fold_into(tmp, 0, n)
+        finally:
+            self._nstage, self._nstage_n, self._nstage_count, self.n_step = saved
+        out = {p: tmp[p].reshape(flat[0][p].shape) for p in paths}
+        return self._out(_unflatten(out, list(entries[0].batch_size)))
 
     def clear(self) -> None:
         super().clear()
@@ -507,7 +536,11 @@ class PrioritizedReplayBuffer(ReplayBuffer):
             with nv.on_device(dev):
                 ring = self._stage()
                 slot, host, dv = ring.views(batch_size, torch.float32)
-                torch.rand(batch_size, out=host)
+                if torch.rand is _TORCH_RAND:
+                    torch.rand(batch_size, out=host)
+                else:  # someone replaced torch.rand: make the reference's calls, one per stratum (:377)
+                    for i in range(batch_size):
+                        host[i] = float(torch.rand(1).item())
                 return ring.push(slot, host, dv)
         with nv.on_device(dev):
             raw = xp.philox_u32(self._philox_seed, self._philox_offset, batch_size, dev)
@@ -522,7 +555,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         idx = torch.empty(batch_size, dtype=torch.int64, device=self.storage_device)
         with nv.on_device(self.storage_device):
             xp.per_sample(h, u, batch_size, 1, self.size, 0.0, idx, None)
-        return idx
+        return idx.cpu()  # the reference builds these indices on the CPU whatever `device` is (:365)
 
     def _calculate_weights(self, indices: torch.Tensor, beta: float) -> torch.Tensor:
         _, _, st, h = self._ensure_trees()
@@ -530,7 +563,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         w = torch.empty(idx.numel(), dtype=torch.float32, device=self.storage_device)
         with nv.on_device(self.storage_device):
             xp.per_weights(h, idx, self.size, float(beta), w)
-        return w
+        return w if self._out_is_storage() else w.to(torch.device(self.device))
 
     def sample(self, batch_size: int, beta: float = 0.4, u: torch.Tensor | None = None) -> TensorBatch:
         """``u`` (optional): the fp32 uniforms to use instead of drawing them."""
@@ -540,7 +573,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         dev = self.storage_device
         fp = self._fast_per()
         if fp is not None and torch._C._cuda_getDevice() == dev.index:
-            if u is None and self.rng != "torch":
+            if u is None and (self.rng != "torch" or torch.rand is not _TORCH_RAND):
                 u = self._draw_uniforms(batch_size)
             if u is None or (u.is_cuda and u.device == dev and u.dtype == torch.float32
                              and u.is_contiguous() and u.numel() == batch_size):

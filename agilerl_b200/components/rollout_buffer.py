@@ -119,6 +119,9 @@ class RolloutBuffer:
         self.max_seq_len = max_seq_len
         self.bptt_sequence_type = bptt_sequence_type
 
+        # keep torch's CPU generator where the reference leaves it after get_tensor_batch(batch_size)
+        # (torch.randperm consumes total-1 words, :570); class-level default, an instance may set False
+        self.exact_rng_advance = True
         self.pos = 0
         self.full = False
         self.num_sequences = None
@@ -264,6 +267,8 @@ class RolloutBuffer:
         raw = torch.zeros(batch_size, dtype=torch.int32)
         if draws:
             raw[:draws] = stream.draw_u32(draws)
+        if getattr(self, "exact_rng_advance", True) and total - 1 > draws:
+            stream.skip(total - 1 - draws)  # torch.randperm consumes total-1 words: stay aligned for the run
         stream.commit()
         with nv.on_device(self._sdev):
             return chunked_randperm_prefix(raw.to(self._sdev), batch_size, total)

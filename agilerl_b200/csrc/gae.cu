@@ -21,6 +21,8 @@
 //                    adv[t] = f32(carry);  ret[t] = adv[t] +f32 v[t]
 //   MC   (:468-477)  G = last_value*(1-last_done);  G = f64(r[t]) + (gamma*G)*(1-done[t])
 //                    ret[t] = f32(G);  adv[t] = ret[t] -f32 v[t]
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "gae_tma.cuh"
 
@@ -28,6 +30,7 @@ namespace {
 
 constexpr int kModeGae = 0;
 constexpr int kModeMc = 1;
+constexpr bool kDefaultLanes = false;  // which kernel xp_gae launches by default
 
 struct ScanParams {
   const float *rewards;
@@ -294,6 +297,175 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
   if (lane == 0) tma_wait_read<0>();
 }
 
+// ---- "lanes" kernel: every warp loads and prepares one 32-step box, warp 0 only runs the chain -----
+// CTA = 4 warps on a strip of 32 envs; the strip is walked in chunks of 128 steps, newest first; warp w
+// owns rows [32w, 32w+32) of a chunk (row j <-> t = t_hi - j).  Lane = env.
+//   1. every thread requests its 32 (r, v, done) triples with plain coalesced loads — one 128-byte row per
+//      warp instruction, ~100 requests per thread in flight, all 14 warps of an SM at once (the TMA kernel
+//      has one thread per CTA issuing; what bounds C3 is bytes in flight, not bandwidth);
+//   2. it computes the carry-independent part A_t of its rows in fp64 (three of the four fp32<->fp64
+//      conversions of a step — the scarce unit, 16 lanes/clk/SM — now run on four warps instead of one)
+//      and parks A_t (fp64) + the carry-factor flag in shared memory; v_t stays in its registers;
+//   3. warp 0 walks the boxes in order: per step one 8-byte + one 1-byte shared load, DMUL -> DADD, one
+//      conversion, one 4-byte shared store (the value goes over A_t's slot);
+//   4. the box's own warp picks the chain's fp32 values up, finishes (ret = adv + v / adv = ret - v in
+//      fp32) and stores both outputs coalesced.
+// Hand-offs are named barriers between warp 0 and one box warp (64 threads), no CTA-wide barrier inside a
+// chunk.  Same operations in the same order as the TMA kernel => bit-identical results.
+namespace gaelanes {
+constexpr int kWarps = 4;
+constexpr int kRows = 32;             // rows per warp
+constexpr int kHalf = 16;             // rows requested together
+constexpr int kChunk = kWarps * kRows;
+// named barriers 1..3: "box w is parked" (warp w arrives, warp 0 waits); 4..6: "box w is chained" (the reverse)
+template <int ID>
+__device__ __forceinline__ void bar_sync() { asm volatile("bar.sync %0, 64;" ::"n"(ID) : "memory"); }
+template <int ID>
+__device__ __forceinline__ void bar_arrive() { asm volatile("bar.arrive %0, 64;" ::"n"(ID) : "memory"); }
+__device__ __forceinline__ void bar_sync_id(int id) {
+  if (id == 1) bar_sync<1>(); else if (id == 2) bar_sync<2>(); else if (id == 3) bar_sync<3>();
+  else if (id == 4) bar_sync<4>(); else if (id == 5) bar_sync<5>(); else bar_sync<6>();
+}
+__device__ __forceinline__ void bar_arrive_id(int id) {
+  if (id == 1) bar_arrive<1>(); else if (id == 2) bar_arrive<2>(); else if (id == 3) bar_arrive<3>();
+  else if (id == 4) bar_arrive<4>(); else if (id == 5) bar_arrive<5>(); else bar_arrive<6>();
+}
+}  // namespace gaelanes
+
+template <int MODE>
+__global__ void __launch_bounds__(gaelanes::kWarps * 32, 4) gae_lanes_kernel(const ScanParams p) {
+  using namespace gaelanes;
+  __shared__ __align__(16) double s_a[kChunk][32];   // A_t, later (low word) the chain's fp32 value
+  __shared__ uint8_t s_f[kChunk][32];                // GAE: done[t+1]; MC: done[t]
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const long long tiles_per_agent = (p.N + 31) / 32;
+  const long long agent = blockIdx.x / tiles_per_agent;
+  const long long env0 = (blockIdx.x - agent * tiles_per_agent) * 32;
+  const bool env_ok = env0 + lane < p.N;
+  const long long base = agent * p.agent_stride + env0 + lane;
+  const float *rw = p.rewards + base;
+  const float *vl = p.values + base;
+  const uint8_t *dn = p.dones + base;
+  float *adv = p.adv + base;
+  float *ret = p.ret + base;
+  double lv = 0.0, ld = 0.0;
+  if (env_ok) {
+    lv = p.last_value[agent * p.N + env0 + lane];
+    ld = p.last_done[agent * p.N + env0 + lane];
+  }
+  double carry = (MODE == kModeMc) ? __dmul_rn(lv, __dsub_rn(1.0, ld)) : 0.0;  // warp 0 only
+  const double k1 = __dmul_rn(p.gl, 1.0), k0 = __dmul_rn(p.gl, 0.0);
+  const double k_last = __dmul_rn(p.gl, __dsub_rn(1.0, ld));                   // t = T-1 (:463-466)
+
+  for (long long t_hi = p.T - 1; t_hi >= 0; t_hi -= kChunk) {
+    const int rows = (int)((t_hi + 1) < kChunk ? (t_hi + 1) : kChunk);
+    const int j0 = w * kRows;                                  // first (newest) row of this warp
+    const int mine = rows - j0 < 0 ? 0 : (rows - j0 < kRows ? rows - j0 : kRows);
+    // ---- 1 + 2. loads, A_t and the flag: two halves of 16 rows (48 requests per thread in flight) ------
+    float v[kRows];                                            // stays in registers for step 4
+    const long long t_first = t_hi - j0;
+    const bool boot = (t_first == p.T - 1);                    // bootstraps from last_value / last_done
+    float v_up = 0.f;                                          // the step after the half's newest row
+    uint8_t d_up = 0;
+    if (MODE == kModeGae && env_ok && mine > 0 && !boot) {     // the previous box's / chunk's oldest row
+      v_up = __ldg(vl + (t_first + 1) * p.N);
+      d_up = __ldg(dn + (t_first + 1) * p.N);
+    }
+#pragma unroll
+    for (int h = 0; h < kRows; h += kHalf) {
+      float r[kHalf];
+      uint8_t d[kHalf];
+#pragma unroll
+      for (int u = 0; u < kHalf; ++u) {
+        const long long t = t_first - h - u;
+        const bool ok = env_ok && h + u < mine;
+        r[u] = ok ? __ldcs(rw + t * p.N) : 0.f;
+        v[h + u] = ok ? __ldcs(vl + t * p.N) : 0.f;
+        d[u] = ok ? __ldcs(dn + t * p.N) : (uint8_t)0;
+      }
+#pragma unroll
+      for (int u = 0; u < kHalf; ++u) {
+        if (h + u < mine) {
+          double a;
+          uint8_t f;
+          if (MODE == kModeGae) {
+            const float vn = u == 0 ? v_up : v[h + u - 1];
+            f = u == 0 ? d_up : d[u - 1];
+            if (h + u == 0 && boot) {
+              const double nnt = __dsub_rn(1.0, ld);
+              a = __dsub_rn(__dadd_rn((double)r[0], __dmul_rn(__dmul_rn(p.gamma, lv), nnt)), (double)v[0]);
+            } else {
+              const double g_nv = (double)__fmul_rn(p.gamma32, vn);
+              a = __dsub_rn(__dadd_rn((double)r[u], __dmul_rn(g_nv, f ? 0.0 : 1.0)), (double)v[h + u]);
+            }
+          } else {
+            a = (double)r[u];
+            f = d[u];
+          }
+          s_a[j0 + h + u][lane] = a;
+          s_f[j0 + h + u][lane] = f;
+        }
+      }
+      v_up = v[h + kHalf - 1];
+      d_up = d[kHalf - 1];
+    }
+    // ---- 3. the chain (warp 0), box by box ---------------------------------------------------------
+    if (w == 0) {
+      for (int b = 0; b * kRows < rows; ++b) {
+        if (b > 0) bar_sync_id(b);         // box b's warp has parked its A_t
+        else __syncwarp();
+        const int jb = b * kRows;
+        const int nb = rows - jb < kRows ? rows - jb : kRows;
+        for (int g0 = 0; g0 < nb; g0 += 8) {
+          double a8[8];
+          uint8_t f8[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int j = jb + (g0 + u < nb ? g0 + u : nb - 1);
+            a8[u] = s_a[j][lane];
+            f8[u] = s_f[j][lane];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            if (g0 + u < nb) {
+              const int j = jb + g0 + u;
+              if (MODE == kModeGae) {
+                double k = f8[u] ? k0 : k1;
+                if (t_hi - j == p.T - 1) k = k_last;
+                carry = __dadd_rn(a8[u], __dmul_rn(k, carry));
+              } else {
+                carry = __dadd_rn(a8[u], __dmul_rn(__dmul_rn(p.gamma, carry), f8[u] ? 0.0 : 1.0));
+              }
+              *reinterpret_cast<float *>(&s_a[j][lane]) = __double2float_rn(carry);
+            }
+          }
+        }
+        if (b > 0) bar_arrive_id(kWarps - 1 + b);  // box b's values are ready for its warp
+        else __syncwarp();
+      }
+    } else if (mine > 0) {
+      bar_arrive_id(w);
+      bar_sync_id(kWarps - 1 + w);
+    }
+    // ---- 4. finish and store this warp's rows ------------------------------------------------------
+#pragma unroll
+    for (int u = 0; u < kRows; ++u) {
+      if (env_ok && u < mine) {
+        const long long t = t_hi - j0 - u;
+        const float x = *reinterpret_cast<const float *>(&s_a[j0 + u][lane]);
+        if (MODE == kModeGae) {
+          __stcs(adv + t * p.N, x);
+          __stcs(ret + t * p.N, __fadd_rn(x, v[u]));
+        } else {
+          __stcs(ret + t * p.N, x);
+          __stcs(adv + t * p.N, __fsub_rn(x, v[u]));
+        }
+      }
+    }
+    if (t_hi - kChunk >= 0) __syncthreads();  // shared memory is reused by the next chunk
+  }
+}
+
 // cuTensorMapEncodeTiled through the runtime (no -lcuda): rank-3 maps {env, t, agent}.
 typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                              const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
@@ -417,7 +589,17 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   const bool tma_ok = (p.N % 16 == 0) && (astride % 16 == 0) && al16(p.rewards) && al16(p.values) &&
                       al16(p.dones) && al16(p.adv) && al16(p.ret) && p.T < (1ll << 30) &&
                       p.N < (1ll << 31) && p.P < (1ll << 31);
-  if (tma_ok) {
+  static const int which = [] {
+    const char *e = getenv("XP_GAE_KERNEL");  // developer knob: "tma" | "lanes" | "tile"
+    if (!e || !e[0]) return 0;
+    return e[0] == 'l' ? 1 : e[0] == 't' && e[1] == 'i' ? 2 : e[0] == 't' ? 3 : 0;
+  }();
+  const bool lanes_ok = p.T < (1ll << 30);
+  if (lanes_ok && (which == 1 || (which == 0 && kDefaultLanes))) {
+    gae_lanes_kernel<MODE><<<(unsigned)grid, gaelanes::kWarps * 32, 0, s>>>(p);
+    return xp::check_launch("xp_gae (lanes)");
+  }
+  if (tma_ok && which != 2) {
     gaetma::Maps maps;
     if (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
         encode_map(&maps.d, p.dones, 1, p) && encode_map(&maps.adv, p.adv, 4, p) &&

@@ -1,9 +1,11 @@
 // peer.cu — exchange step of the replicated prioritized replay over NVLink peer memory.
 //
-// Reference: the distributed off-policy loop broadcasts the sampled indices and gathers the new
-// priorities so that every replica of the shared buffer applies the same updates
-// (agilerl/training/train_off_policy.py:363-381).  With one process per GPU every rank keeps its
-// block (indices, priorities) in peer-mapped memory; ONE kernel per rank then
+// The reference's buffers take part in NO collective: one `memory` object serves the whole population
+// inside one process (agilerl/training/train_off_policy.py:46,343-345,363-376).  The exchange below is
+// this build's own (BASELINE.json north_star: "the shared replay memory is replicated, with each step's
+// newly inserted transitions broadcast over NVLink"): with one process per GPU every replica must see
+// every rank's (indices, priorities) and new rows, in one canonical order, to stay bit-identical.
+// Every rank keeps its block in peer-mapped memory; ONE kernel per rank then
 //   1. tells every peer "my block of this epoch is complete" (a release store of the epoch number
 //      into the peer's flag array, over NVLink),
 //   2. waits until each peer has said the same (acquire loads of its own flag array),
@@ -19,11 +21,13 @@
 namespace {
 
 struct PeerParams {
-  const char *base[XP_MAX_PEERS];     // peer r's block memory (peer-mapped address)
+  const char *base[2][XP_MAX_PEERS];  // block k of peer r (peer-mapped address); host-epoch calls use k = 0
   unsigned *flags[XP_MAX_PEERS];      // peer r's flag array, unsigned[world]
   xp_peer_seg seg[XP_MAX_PEER_SEGS];
   int n_segs, rank, world;
-  unsigned epoch;
+  unsigned epoch;                     // epoch_dev == NULL: the epoch of this call
+  unsigned *epoch_dev;                // else [0] = exchanges completed so far, [1] = CTA arrivals of this launch:
+                                      // the launch parameters never change, so the call can sit in a CUDA graph
   int *err;
   long long timeout_cycles;
 };
@@ -40,15 +44,15 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
 // Signal "rank p.rank reached `epoch`" to peer r (when `signal`), then wait for peer r's epoch.
 // Called by one thread of the CTA; returns false after a bounded wait (the error flag is set).
 template <class P>
-__device__ __forceinline__ bool peer_sync(const P &p, int r, bool signal) {
+__device__ __forceinline__ bool peer_sync(const P &p, int r, bool signal, unsigned epoch) {
   if (r == p.rank) return true;
   if (signal) {
     __threadfence_system();                          // this rank's block is visible system-wide
-    st_release_sys(p.flags[r] + p.rank, p.epoch);    // "rank p.rank reached epoch" in r's array
+    st_release_sys(p.flags[r] + p.rank, epoch);      // "rank p.rank reached epoch" in r's array
   }
   const long long t0 = clock64();
   // epochs only grow; the signed difference survives wrap-around
-  while ((int)(ld_acquire_sys(p.flags[p.rank] + r) - p.epoch) < 0) {
+  while ((int)(ld_acquire_sys(p.flags[p.rank] + r) - epoch) < 0) {
     if (clock64() - t0 > p.timeout_cycles) {
       if (p.err) *p.err = 1;
       return false;
@@ -111,16 +115,37 @@ __device__ __forceinline__ void pull(const char *src, char *dst, long long bytes
   else pull_vec<1>(src, dst, v0, v1);
 }
 
+// grid = (parts, world): CTA (c, r) moves the c-th share of peer r's block; CTA (0, r) sends this rank's
+// signal to peer r, every CTA of row r waits for peer r's.
 __global__ void __launch_bounds__(256) peer_allgather_kernel(const __grid_constant__ PeerParams p) {
   xp::pdl_enter();  // the block being published was written by earlier kernels of this stream
-  const int r = blockIdx.x;  // the peer this CTA serves
+  const int r = blockIdx.y, c = blockIdx.x, parts = gridDim.x;  // r: the peer this CTA serves
   __shared__ int s_ok;
-  if (threadIdx.x == 0) s_ok = peer_sync(p, r, true) ? 1 : 0;
+  __shared__ unsigned s_epoch;
+  if (threadIdx.x == 0) {
+    unsigned e = p.epoch;
+    if (p.epoch_dev) e = *reinterpret_cast<volatile unsigned *>(p.epoch_dev) + 1u;
+    s_epoch = e;
+    s_ok = peer_sync(p, r, c == 0, e) ? 1 : 0;
+  }
   __syncthreads();
-  if (!s_ok) return;
-  for (int k = 0; k < p.n_segs; ++k) {
-    const xp_peer_seg &sg = p.seg[k];
-    pull(p.base[r] + sg.src_off, static_cast<char *>(sg.dst) + (long long)r * sg.bytes, sg.bytes, 0, 1);
+  const int k = p.epoch_dev ? (int)((s_epoch - 1u) & 1u) : 0;  // blocks alternate: epoch 1 publishes block 0
+  if (s_ok) {
+    for (int q = 0; q < p.n_segs; ++q) {
+      const xp_peer_seg &sg = p.seg[q];
+      pull(p.base[k][r] + sg.src_off, static_cast<char *>(sg.dst) + (long long)r * sg.bytes, sg.bytes, c, parts);
+    }
+  }
+  if (p.epoch_dev) {  // the last CTA of the launch publishes the new epoch for the next launch to read
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      const unsigned n = gridDim.x * gridDim.y;
+      if (atomicAdd(p.epoch_dev + 1, 1u) == n - 1u) {
+        p.epoch_dev[1] = 0u;
+        *reinterpret_cast<volatile unsigned *>(p.epoch_dev) = s_epoch;
+      }
+    }
   }
 }
 
@@ -145,7 +170,7 @@ __global__ void __launch_bounds__(256) peer_ring_insert_kernel(const __grid_cons
   xp::pdl_enter();
   const int r = blockIdx.y, c = blockIdx.x, parts = gridDim.x;
   __shared__ int s_ok;
-  if (threadIdx.x == 0) s_ok = peer_sync(p, r, c == 0) ? 1 : 0;
+  if (threadIdx.x == 0) s_ok = peer_sync(p, r, c == 0, p.epoch) ? 1 : 0;
   __syncthreads();
   if (!s_ok) return;
   const long long start = (p.cursor + (long long)r * p.n_rows) % p.ring_rows;
@@ -163,34 +188,66 @@ __global__ void __launch_bounds__(256) peer_ring_insert_kernel(const __grid_cons
 
 extern "C" {
 
-xp_status_t xp_peer_allgather(const void *const *peer_base, void *const *peer_flags, int rank, int world,
-                              uint32_t epoch, const xp_peer_seg *segs, int n_segs, int *err_flag_dev,
-                              void *stream) {
-  XP_REQUIRE(world >= 1 && world <= XP_MAX_PEERS, XP_ERR_INVALID, "xp_peer_allgather: world %d not in [1,%d]", world,
+static long long g_peer_timeout_cycles = 60000000000ll;  // ~30 s at 2 GHz: report, do not hang
+
+void xp_peer_set_timeout_cycles(int64_t cycles) {
+  if (cycles > 0) g_peer_timeout_cycles = cycles;
+}
+
+static xp_status_t peer_allgather_common(const void *const *base0, const void *const *base1,
+                                         void *const *peer_flags, int rank, int world, uint32_t epoch,
+                                         uint32_t *epoch_state_dev, const xp_peer_seg *segs, int n_segs,
+                                         int *err_flag_dev, void *stream, const char *what) {
+  XP_REQUIRE(world >= 1 && world <= XP_MAX_PEERS, XP_ERR_INVALID, "%s: world %d not in [1,%d]", what, world,
              XP_MAX_PEERS);
-  XP_REQUIRE(rank >= 0 && rank < world, XP_ERR_INVALID, "xp_peer_allgather: bad rank");
-  XP_REQUIRE(n_segs >= 1 && n_segs <= XP_MAX_PEER_SEGS, XP_ERR_INVALID, "xp_peer_allgather: n_segs %d not in [1,%d]",
+  XP_REQUIRE(rank >= 0 && rank < world, XP_ERR_INVALID, "%s: bad rank", what);
+  XP_REQUIRE(n_segs >= 1 && n_segs <= XP_MAX_PEER_SEGS, XP_ERR_INVALID, "%s: n_segs %d not in [1,%d]", what,
              n_segs, XP_MAX_PEER_SEGS);
-  XP_REQUIRE(peer_base && peer_flags && segs, XP_ERR_INVALID, "xp_peer_allgather: null pointer");
+  XP_REQUIRE(base0 && base1 && peer_flags && segs, XP_ERR_INVALID, "%s: null pointer", what);
   PeerParams p{};
   for (int r = 0; r < world; ++r) {
-    XP_REQUIRE(peer_base[r] && peer_flags[r], XP_ERR_INVALID, "xp_peer_allgather: null peer pointer");
-    p.base[r] = static_cast<const char *>(peer_base[r]);
+    XP_REQUIRE(base0[r] && base1[r] && peer_flags[r], XP_ERR_INVALID, "%s: null peer pointer", what);
+    p.base[0][r] = static_cast<const char *>(base0[r]);
+    p.base[1][r] = static_cast<const char *>(base1[r]);
     p.flags[r] = static_cast<unsigned *>(peer_flags[r]);
   }
+  long long bytes = 0;
   for (int k = 0; k < n_segs; ++k) {
     XP_REQUIRE(segs[k].bytes >= 0 && segs[k].src_off >= 0 && (segs[k].bytes == 0 || segs[k].dst), XP_ERR_INVALID,
-               "xp_peer_allgather: bad segment %d", k);
+               "%s: bad segment %d", what, k);
     p.seg[k] = segs[k];
+    bytes += segs[k].bytes;
   }
   p.n_segs = n_segs;
   p.rank = rank;
   p.world = world;
   p.epoch = epoch;
+  p.epoch_dev = epoch_state_dev;
   p.err = err_flag_dev;
-  p.timeout_cycles = 4000000000ll;  // ~2 s at 2 GHz: report, do not hang
-  xp::launch(peer_allgather_kernel, dim3(world), dim3(256), 0, (cudaStream_t)stream, p);
-  return xp::check_launch("xp_peer_allgather");
+  p.timeout_cycles = g_peer_timeout_cycles;
+  // one CTA per 32 KB of a peer's block, never more CTAs than stay resident together (the signalling
+  // CTAs must not queue behind waiting ones)
+  long long parts = (bytes + 32767) / 32768;
+  const long long cap = 128 / world;
+  if (parts > cap) parts = cap;
+  if (parts < 1) parts = 1;
+  xp::launch(peer_allgather_kernel, dim3((unsigned)parts, (unsigned)world), dim3(256), 0, (cudaStream_t)stream, p);
+  return xp::check_launch(what);
+}
+
+xp_status_t xp_peer_allgather(const void *const *peer_base, void *const *peer_flags, int rank, int world,
+                              uint32_t epoch, const xp_peer_seg *segs, int n_segs, int *err_flag_dev,
+                              void *stream) {
+  return peer_allgather_common(peer_base, peer_base, peer_flags, rank, world, epoch, nullptr, segs, n_segs,
+                               err_flag_dev, stream, "xp_peer_allgather");
+}
+
+xp_status_t xp_peer_allgather_graph(const void *const *peer_base0, const void *const *peer_base1,
+                                    void *const *peer_flags, int rank, int world, uint32_t *epoch_state_dev,
+                                    const xp_peer_seg *segs, int n_segs, int *err_flag_dev, void *stream) {
+  XP_REQUIRE(epoch_state_dev, XP_ERR_INVALID, "xp_peer_allgather_graph: null epoch state");
+  return peer_allgather_common(peer_base0, peer_base1, peer_flags, rank, world, 0, epoch_state_dev, segs, n_segs,
+                               err_flag_dev, stream, "xp_peer_allgather_graph");
 }
 
 xp_status_t xp_peer_ring_insert(const void *const *peer_base, void *const *peer_flags, int rank, int world,
@@ -224,7 +281,7 @@ xp_status_t xp_peer_ring_insert(const void *const *peer_base, void *const *peer_
   p.world = world;
   p.epoch = epoch;
   p.err = err_flag_dev;
-  p.timeout_cycles = 4000000000ll;
+  p.timeout_cycles = g_peer_timeout_cycles;
   p.n_rows = n_rows;
   p.cursor = cursor;
   p.ring_rows = ring_rows;

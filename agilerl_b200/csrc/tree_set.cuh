@@ -11,11 +11,18 @@
 // Three schedules, chosen by batch size:
 //   M  B <= 8192    one launch: every warp filters the whole (L2-resident) batch for its bucket,
 //                   climbs it; the last CTA to finish rebuilds the top.
-//   L  larger B     histogram(+scan) -> scatter into per-bucket slices -> one warp per bucket ->
-//                   dense top (256-node chunks).
+//   S  larger B     ONE bucketing pass into fixed 32-slot slices -> one warp per bucket -> dense top.
+//   L  (trees too small for the slices) histogram(+scan) -> scatter into compact slices -> one warp
+//                   per bucket -> dense top.
 //   D  B ~ cap      tickets -> winners write leaves -> dense coalesced bottom-up rebuild.
+// Hot buckets (more than 32 items: skewed batches — fresh transitions carry the maximum priority and
+// are drawn together) are not climbed at all under S / L: their items leave last-writer tickets on
+// the leaves (the items beyond a slice do so in the bucketing pass itself), the bucket is flagged,
+// and the dense kernel, which rebuilds everything above height `top` anyway, first rebuilds the
+// flagged buckets' subtrees from their leaves — leaf-parallel, no list scan, any skew costs what
+// its leaves cost.
 // `aux` (int32[2*cap]): [cap, 2cap) last-writer tickets (zero between calls; schedule D and
-// oversize buckets); [0, cap) scratch (done counter, bucket counters/offsets/cursors, items).
+// hot buckets); [0, cap) scratch (done counter, bucket counters/offsets/cursors, items).
 #pragma once
 #include "common.cuh"
 #include "pow.cuh"
@@ -252,24 +259,76 @@ __device__ __forceinline__ u64 item_key(const SetSrc &s, long long i, long long 
   return ((u64)leaf << 32) | (u64)i;
 }
 
-// dense rebuild of the top of the tree by ONE CTA: `width` (power of two) nodes at height h0 are
-// loaded into a shared-memory heap and reduced; recomputing an untouched node from unchanged
-// children gives the value it already has (every node is op(children) by construction).
+// ---- dense fold of one level's nodes by a CTA (used by schedule M's top and by the dense kernel) ----------
 template <bool PAIRED>
-__device__ void cta_dense_top(const Tree &t, int h0, int width, double2 *heap) {
-  for (int i = threadIdx.x; i < width; i += blockDim.x)
-    heap[width + i] = ld_node<PAIRED>(t, (int)(t.cap >> h0) + i);
-  __syncthreads();
-  int h = h0;
-  for (int w = width >> 1; w >= 1; w >>= 1) {
-    ++h;
-    for (int q = threadIdx.x; q < w; q += blockDim.x) {
-      const double2 l = heap[2 * (w + q)], r = heap[2 * (w + q) + 1];
-      const double2 v = make_double2(__dadd_rn(l.x, r.x), py_min(l.y, r.y));
-      heap[w + q] = v;
-      st_node<PAIRED>(t, (int)(t.cap >> h) + q, v);
+__device__ __forceinline__ double2 node_op(double2 l, double2 r) {
+  return make_double2(__dadd_rn(l.x, r.x), py_min(l.y, r.y));
+}
+__device__ __forceinline__ double2 shfl_down2(double2 v, int d) {
+  return make_double2(__shfl_down_sync(0xffffffffu, v.x, d), __shfl_down_sync(0xffffffffu, v.y, d));
+}
+
+// Reduce the n (power of two, <= blockDim.x * E) nodes first .. first+n-1 (heap ids, one level) to their
+// common ancestor, storing every node on the way.  All threads of the CTA call it; blockDim.x is a
+// multiple of 32 and at most 1024.  s_v: 32 entries of shared scratch.
+template <bool PAIRED, int E>
+__device__ __forceinline__ void cta_reduce(const Tree &t, int first, int n, double2 *s_v) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double2 v[E];
+  int m = 0;                    // valid nodes of this thread (a power of two, or 0)
+  int b = first + tid * E;      // heap id of this thread's first node
+  if (tid * E < n) m = n < E ? n : E;
+#pragma unroll
+  for (int e = 0; e < E; ++e) v[e] = (e < m) ? ld_node<PAIRED>(t, b + e) : make_double2(0.0, 0.0);
+  // levels held in registers (a thread that holds fewer than E nodes — n < E — joins at its own width)
+#pragma unroll
+  for (int w = E; w > 1; w >>= 1) {
+    if (m == w) {
+#pragma unroll
+      for (int j = 0; j < w / 2; ++j) {
+        v[j] = node_op<PAIRED>(v[2 * j], v[2 * j + 1]);
+        st_node<PAIRED>(t, (b >> 1) + j, v[j]);
+      }
+      m >>= 1;
+      b >>= 1;
     }
+  }
+  int nt = n / E;               // threads holding one node each (power of two), at least 1
+  if (nt < 1) nt = 1;
+  double2 cur = v[0];
+  // levels folded inside a warp
+  const int wl = nt < 32 ? nt : 32;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    if (d < wl) {  // CTA-uniform
+      const double2 o = shfl_down2(cur, d);
+      if ((lane & (2 * d - 1)) == 0 && tid < nt) {
+        cur = node_op<PAIRED>(cur, o);
+        b >>= 1;
+        st_node<PAIRED>(t, b, cur);
+      }
+    }
+  }
+  const int nw = nt >> 5;       // warps holding one node each (power of two) when > 1
+  if (nw > 1) {
+    if (lane == 0 && warp < nw) s_v[warp] = cur;
     __syncthreads();
+    if (warp == 0) {
+      cur = lane < nw ? s_v[lane] : make_double2(0.0, 0.0);
+      b = (first >> (31 - __clz(n / nw))) + lane;  // heap id of warp `lane`'s root
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        if (d < nw) {
+          const double2 o = shfl_down2(cur, d);
+          if ((lane & (2 * d - 1)) == 0 && lane < nw) {
+            cur = node_op<PAIRED>(cur, o);
+            b >>= 1;
+            st_node<PAIRED>(t, b, cur);
+          }
+        }
+      }
+    }
+    __syncthreads();            // s_v may be reused by the caller
   }
 }
 
@@ -289,6 +348,7 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
   xp::pdl_enter();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ u64 s_list[kMidWarps][32];
+  __shared__ double2 s_top[32];
   __shared__ int s_last, s_cnt;
   const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -376,7 +436,8 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  cta_dense_top<PAIRED>(t, shift, nb, reinterpret_cast<double2 *>(smem_raw));
+  // dense rebuild of the nb-leaf top by this CTA (nb <= 2048 <= 8 nodes per thread)
+  cta_reduce<PAIRED, 8>(t, (int)(t.cap >> shift), nb, s_top);
 }
 
 // ---- schedule L (large B): histogram+scan -> scatter -> one warp per bucket -> dense top --------
@@ -391,19 +452,11 @@ struct Buckets {
   u64 *items;
   double *vals;    // kSrcPrio only: leaf value per batch position (else NULL)
   int slots;       // 0: compact slices (offsets / cursors).  > 0 (schedule S): bucket b owns the fixed
-                   // slice items[b*slots, (b+1)*slots); what does not fit goes to `ovf`
-  u64 *ovf;        // overflow items of all buckets, *ovn of them (aux[5], zero between calls)
-  int *ovn;
-  int guard;       // schedule S with its exact fallback: +1 = this launch is the slotted climb and runs only
-                   // while the overflow stays small, -1 = it belongs to the fallback (scan / scatter /
-                   // compact climb over the SAME counters) and runs only when it did not, 0 = always
+                   // slice items[b*slots, (b+1)*slots); items beyond it only leave their ticket
+  int *hotlist;    // ids of the hot buckets of this call, *nhot of them (aux[5], zero between calls);
+  int *nhot;       // a hot bucket's counter stays at -1 until the dense kernel has rebuilt it
 };
-constexpr int kOvfLimit = 1024;  // overflow entries an overflowing bucket may have to scan
-__device__ __forceinline__ bool guarded_out(const Buckets &bk) {
-  if (bk.guard == 0) return false;
-  const bool big = __ldcg(bk.ovn) > kOvfLimit;
-  return bk.guard > 0 ? big : !big;
-}
+constexpr int kHotOver = 32;  // a bucket with more items than a warp has lanes is "hot"
 
 // Largest bucket count any batch can ask for on this tree: the counters that must be ZERO between
 // calls live in a region sized by it, so that calls with different batch sizes —
@@ -416,7 +469,7 @@ __host__ __device__ inline long long max_buckets(long long cap) {
 
 __host__ __device__ inline long long bucket_scratch_ints(long long cap, long long nb, long long B, bool want_vals) {
   const long long mb = max_buckets(cap);
-  return 16 + mb + 2 * nb + 2 + (want_vals ? 4 : 2) * B;
+  return 16 + mb + 2 * nb + 2 + (want_vals ? 4 : 2) * B + nb;
 }
 
 __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift, long long B, bool want_vals) {
@@ -433,29 +486,24 @@ __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift
   b.items = reinterpret_cast<u64 *>(t.aux + off);
   b.vals = want_vals ? reinterpret_cast<double *>(t.aux + off + 2 * B) : nullptr;
   b.slots = 0;
-  b.ovf = nullptr;
-  b.ovn = t.aux + 5;
-  b.guard = 0;
+  b.hotlist = t.aux + off + (want_vals ? 4 : 2) * B;
+  b.nhot = t.aux + 5;
   return b;
 }
 
 // schedule S: one pass instead of histogram + scan + scatter.  A bucket expects ~16 items; its fixed
-// slice holds 32, the rest (hot ranges: freshly inserted transitions carry the maximum priority and
-// are sampled together) spill to one shared overflow list that only the overflowing buckets scan.
+// slice holds 32.  An item that finds the slice full belongs to a hot bucket: it leaves its last-writer
+// ticket on the leaf right away and is not stored anywhere (the dense kernel finds it by the ticket).
 constexpr int kSlots = 32;
-// (the slices and the overflow list sit BEHIND schedule L's scratch: when too much overflows, L's scan /
-// scatter / climb finish the job from the same counters)
 __host__ __device__ inline long long slotted_scratch_ints(long long cap, long long nb, long long B, bool want_vals) {
-  return bucket_scratch_ints(cap, nb, B, want_vals) + 2 + 2 * nb * kSlots + 2 * B;
+  return bucket_scratch_ints(cap, nb, B, want_vals) + 2 + 2 * nb * kSlots;
 }
 __host__ __device__ inline Buckets make_slotted(const Tree &t, int nb, int shift, long long B, bool want_vals) {
-  Buckets b = make_buckets(t, nb, shift, B, want_vals);  // same counters, same vals
+  Buckets b = make_buckets(t, nb, shift, B, want_vals);  // same counters, same vals, same hot list
   long long off = bucket_scratch_ints(t.cap, nb, B, want_vals);
   off = (off + 1) & ~1ll;
   b.items = reinterpret_cast<u64 *>(t.aux + off);
-  b.ovf = b.items + (long long)nb * kSlots;
   b.slots = kSlots;
-  b.guard = 1;
   return b;
 }
 
@@ -487,7 +535,6 @@ __device__ __forceinline__ int warp_inclusive(int v, int lane) {
 }
 __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
   xp::pdl_enter();
-  if (guarded_out(bk)) return;
   // One CTA.  Counters come in and prefixes go out coalesced through shared memory (one pad word
   // per 32 keeps both the row-wise copies and the per-thread runs bank-conflict free); in between
   // thread t owns E = nb / 1024 CONSECUTIVE counters (nb is a power of two <= 32768): a serial sum,
@@ -540,8 +587,6 @@ __global__ void __launch_bounds__(1024) set_scan_kernel(Buckets bk) {
 // lanes busy, and parked by batch position for the bucket warp that will need it
 __global__ void __launch_bounds__(256) set_scatter_kernel(Tree t, SetSrc s, long long B, Buckets bk) {
   xp::pdl_enter();
-  if (guarded_out(bk)) return;
-  // grid-stride: as schedule S's fallback this is launched with a small grid (it usually returns above)
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < B; i += (long long)gridDim.x * blockDim.x) {
     long long leaf;
     const u64 key = item_key(s, i, leaf);
@@ -565,7 +610,7 @@ __global__ void __launch_bounds__(256) set_slot_kernel(Tree t, SetSrc s, long lo
       const int b = (int)(leaf >> bk.shift);
       const int slot = atomicAdd(&bk.counts[b], 1);
       if (slot < bk.slots) bk.items[(long long)b * bk.slots + slot] = key;
-      else bk.ovf[atomicAdd(bk.ovn, 1)] = key;
+      else atomicMax(&t.aux[t.cap + leaf], (int)i + 1);  // hot bucket: the ticket is all that is needed
     }
     if (s.kind == kSrcPrio) {
       p = clamp_prio(s.prio[i]);
@@ -576,7 +621,9 @@ __global__ void __launch_bounds__(256) set_slot_kernel(Tree t, SetSrc s, long lo
 }
 
 // one warp per PAIR of buckets: both <= 16 items -> the two half-warps climb them side by side;
-// otherwise one after the other with the whole warp.
+// otherwise one after the other with the whole warp.  A bucket with more than 32 items is HOT: nothing
+// is climbed — its (stored) items leave their tickets on the leaves, the bucket's counter stays at -1 and
+// its id goes to the hot list; the dense kernel rebuilds its subtree from the leaves.
 constexpr int kBucketWarps = 4;  // 56 registers: 9 CTAs of 4 warps fit an SM where 4 CTAs of 8 do (36 vs 32 warps)
 template <bool PAIRED>
 __device__ __forceinline__ void climb_bucket_pair(const Tree &t, const SetSrc &s, const Buckets &bk, int use_half,
@@ -596,9 +643,15 @@ __device__ __forceinline__ void climb_bucket_pair(const Tree &t, const SetSrc &s
     n1 = has1 ? bk.cursors[b0 + 1] - beg1 : 0;
   }
   if (n0 == 0 && n1 == 0) return;
-  if (lane == 0) {  // scratch back to zero for the next call
-    bk.counts[b0] = 0;
-    if (has1) bk.counts[b0 + 1] = 0;
+  if (lane == 0) {  // scratch back to zero for the next call (hot buckets: by the dense kernel)
+    bk.counts[b0] = n0 > kHotOver ? -1 : 0;
+    if (has1) bk.counts[b0 + 1] = n1 > kHotOver ? -1 : 0;
+    const int nh = (n0 > kHotOver) + (n1 > kHotOver);
+    if (nh) {
+      int at = atomicAdd(bk.nhot, nh);
+      if (n0 > kHotOver) bk.hotlist[at++] = b0;
+      if (n1 > kHotOver) bk.hotlist[at] = b0 + 1;
+    }
   }
   if (use_half && n0 <= 16 && n1 <= 16) {
     const int half = lane >> 4, l = lane & 15;
@@ -611,20 +664,14 @@ __device__ __forceinline__ void climb_bucket_pair(const Tree &t, const SetSrc &s
     const int beg = h ? beg1 : beg0, n = h ? n1 : n0;
     if (n == 0) continue;
     const u64 *items = bk.items + beg;
-    if (n <= 32) {
+    if (n <= kHotOver) {
       warp_climb<PAIRED, 32>(t, s, lane < n ? __ldcg(&items[lane]) : kPad, bk.top);
-    } else if (bk.slots) {
-      // the slice is full: the rest of this bucket's items are somewhere in the shared overflow list
-      const int b = b0 + h, ov = __ldcg(bk.ovn);
-      auto fetch = [&](long long i) -> u64 {
-        if (i < bk.slots) return __ldcg(&items[i]);
-        const u64 k = __ldcg(&bk.ovf[i - bk.slots]);
-        return ((int)(k >> 32) >> bk.shift) == b ? k : kPad;
-      };
-      warp_climb_large<PAIRED>(t, s, fetch, (long long)bk.slots + ov, bk.top);
     } else {
-      auto fetch = [&](long long i) -> u64 { return __ldcg(&items[i]); };
-      warp_climb_large<PAIRED>(t, s, fetch, n, bk.top);
+      const int stored = bk.slots ? bk.slots : n;  // schedule S: the rest ticketed themselves already
+      for (int i = lane; i < stored; i += 32) {
+        const u64 key = __ldcg(&items[i]);
+        atomicMax(&t.aux[t.cap + (long long)(key >> 32)], (int)(key & 0xffffffffull) + 1);
+      }
     }
   }
 }
@@ -632,93 +679,9 @@ __device__ __forceinline__ void climb_bucket_pair(const Tree &t, const SetSrc &s
 template <bool PAIRED>
 __global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk, int use_half) {
   xp::pdl_enter();
-  if (guarded_out(bk)) return;
   s.pre = bk.vals;
-  // warp-uniform grid-stride over bucket pairs (one trip, except as schedule S's small-grid fallback)
-  for (int w = blockIdx.x * kBucketWarps + (threadIdx.x >> 5); 2 * w < bk.nb; w += gridDim.x * kBucketWarps)
-    climb_bucket_pair<PAIRED>(t, s, bk, use_half, 2 * w);
-}
-
-// ---- schedule S's fallback in ONE launch ----------------------------------------------------------
-// scan | scatter | compact climb over the counters schedule S has already filled, as phases of one small
-// grid (<= 2 CTAs per SM, all resident) separated by grid barriers.  In the common case — the
-// overflow list stayed under kOvfLimit — every CTA returns at its first instruction, so the
-// robustness against skewed batches costs one empty launch instead of three.
-__device__ __forceinline__ bool grid_barrier(int *ctr, int target) {
-  __shared__ int s_ok;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(ctr, 1);
-    const long long t0 = clock64();
-    int v, ok = 1;
-    do {
-      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
-      if (v < target) {
-        if (clock64() - t0 > 4000000000ll) {  // ~2 s: a CTA of this grid never became resident
-          ok = 0;
-          break;
-        }
-        __nanosleep(32);
-      }
-    } while (v < target);
-    s_ok = ok;
-  }
-  __syncthreads();
-  return s_ok != 0;
-}
-
-template <bool PAIRED>
-__global__ void __launch_bounds__(256) set_fallback_kernel(Tree t, SetSrc s, long long B, Buckets bk, int use_half) {
-  xp::pdl_enter();
-  if (guarded_out(bk)) return;
-  __shared__ int s_part[8];
-  int *bar = t.aux + 6;  // arrivals; zeroed by the dense kernel that follows
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  // phase 1: exclusive scan of the counters by CTA 0 (thread-serial runs + one block scan)
-  if (blockIdx.x == 0) {
-    const int nb = bk.nb;
-    const int E = (nb + 255) >> 8;
-    const int base = tid * E;
-    int sum = 0;
-    for (int k = 0; k < E; ++k)
-      if (base + k < nb) sum += __ldcg(&bk.counts[base + k]);
-    const int inc = warp_inclusive(sum, lane);
-    if (lane == 31) s_part[warp] = inc;
-    __syncthreads();
-    int before = 0;
-    for (int w = 0; w < warp; ++w) before += s_part[w];
-    int run = before + inc - sum;
-    for (int k = 0; k < E; ++k) {
-      if (base + k < nb) {
-        const int c = __ldcg(&bk.counts[base + k]);
-        bk.offsets[base + k] = run;
-        bk.cursors[base + k] = run;
-        run += c;
-      }
-    }
-    if (tid == 255) bk.offsets[nb] = run;
-  }
-  if (!grid_barrier(bar, (int)gridDim.x)) {
-    if (s.err) *s.err = 1;
-    return;
-  }
-  // phase 2: scatter into the compact slices
-  for (long long i = (long long)blockIdx.x * blockDim.x + tid; i < B; i += (long long)gridDim.x * blockDim.x) {
-    long long leaf;
-    const u64 key = item_key(s, i, leaf);
-    if (key == kPad) continue;
-    const int slot = atomicAdd(&bk.cursors[leaf >> bk.shift], 1);
-    bk.items[slot] = key;
-  }
-  if (!grid_barrier(bar, 2 * (int)gridDim.x)) {
-    if (s.err) *s.err = 1;
-    return;
-  }
-  // phase 3: the compact climb (leaf values were parked by the slot kernel)
-  s.pre = bk.vals;
-  for (int w = blockIdx.x * 8 + warp; 2 * w < bk.nb; w += gridDim.x * 8)
-    climb_bucket_pair<PAIRED>(t, s, bk, use_half, 2 * w);
+  const int w = blockIdx.x * kBucketWarps + (threadIdx.x >> 5);
+  if (2 * w < bk.nb) climb_bucket_pair<PAIRED>(t, s, bk, use_half, 2 * w);
 }
 
 // ---- schedule D helpers ----------------------------------------------------------------------------
@@ -752,65 +715,94 @@ __global__ void __launch_bounds__(256) set_leafwrite_kernel(Tree t, SetSrc s, lo
   if (t.mn) __stcg(&t.mn[node * t.stride], v);
 }
 
-// Each CTA takes C = 2^logC consecutive nodes at height h0 and recomputes the logC levels above
-// them (a heap in shared memory).  Recomputing an untouched node from unchanged children gives
-// the value it already has (every node is op(children) by construction), so dense == sparse.
-constexpr int kDenseThreads = 512;
-constexpr int kDenseLogC = 12;
-__global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0, int logC, int finish) {
+// Dense rebuild.  Each CTA takes C = kDenseThreads * E consecutive nodes at height h0 and recomputes the
+// log2(C) levels above them WITHOUT block barriers in the level loop: a thread holds E consecutive nodes
+// (log2 E levels in registers), a warp folds its 32 thread roots with shuffles (5 levels), warp 0 folds the
+// warp roots (one barrier).  Recomputing an untouched node from unchanged children gives the value it
+// already has (every node is op(children) by construction), so dense == sparse.  Operand order is
+// (left, right) = (lower node id, higher node id) everywhere, as segment_tree.py:89-95 has it.
+constexpr int kDenseThreads = 256;
+
+// What the first dense launch of schedules S / L needs to rebuild the hot buckets below h0 (= top).
+struct HotCtx {
+  SetSrc s;       // s.pre = leaf values parked by batch position (kSrcPrio), else the source itself
+  int *flags;     // per-bucket counters: -1 = hot (leaves carry tickets, nothing was climbed)
+  int shift;      // leaves per bucket = 1 << shift
+  int *hotlist;   // hot bucket ids, *nhot of them
+  int *nhot;
+  int mode;       // bit 0: rebuild the flagged buckets below h0 first; bit 1: the finishing CTA clears the flags
+};
+
+template <bool PAIRED, int E>
+__global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0, int finish, HotCtx hc) {
   xp::pdl_enter();
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ int s_last;
-  if (blockIdx.x == 0 && threadIdx.x == 0) {  // schedule S's overflow count and its fallback's barrier: readers are done
-    t.aux[5] = 0;
-    t.aux[6] = 0;
+  constexpr int C = kDenseThreads * E;
+  __shared__ double2 s_v[32];
+  __shared__ int s_hot[C];
+  __shared__ int s_nhot, s_last;
+  const int tid = threadIdx.x;
+  const long long width = t.cap >> h0;            // nodes at height h0
+  const int n = width < C ? (int)width : C;       // nodes of this CTA
+  const long long x0 = (long long)blockIdx.x * C; // index of its first node inside the level
+
+  if (hc.mode & 1) {
+    // hot buckets: every node of height h0 under a flagged bucket is rebuilt from its 2^h0 leaves, whose
+    // winners are named by the tickets (ticket = batch position + 1 of the LAST item of the leaf)
+    if (tid == 0) s_nhot = 0;
+    __syncthreads();
+    const int per = hc.shift - h0;                // log2(nodes of height h0 per bucket), >= 0
+    for (int i = tid; i < n; i += kDenseThreads)
+      if (__ldcg(&hc.flags[(x0 + i) >> per]) < 0) s_hot[atomicAdd(&s_nhot, 1)] = i;
+    __syncthreads();
+    const int nh = s_nhot;
+    if (nh) {
+      for (int h = 0; h <= h0; ++h) {
+        const int sh = h0 - h;                    // log2(nodes of height h under one node of height h0)
+        const long long total = (long long)nh << sh;
+        for (long long q = tid; q < total; q += kDenseThreads) {
+          const long long g = x0 + s_hot[(int)(q >> sh)];
+          const long long id = (t.cap >> h) + (g << sh) + (q & ((1ll << sh) - 1));
+          if (h == 0) {
+            int *tk = &t.aux[id];                 // aux[cap + leaf]
+            const int w = __ldcg(tk);
+            if (w > 0) {
+              const double val = src_value(hc.s, (long long)w - 1);
+              st_node<PAIRED>(t, (int)id, make_double2(val, val));
+              __stcg(tk, 0);
+            }
+          } else {
+            st_node<PAIRED>(t, (int)id,
+                            node_op<PAIRED>(ld_node<PAIRED>(t, (int)(2 * id)), ld_node<PAIRED>(t, (int)(2 * id + 1))));
+          }
+        }
+        __syncthreads();                          // level h is complete (and visible) inside this CTA
+      }
+    }
   }
-  const int C = 1 << logC;
-  double *S = reinterpret_cast<double *>(smem_raw);
-  double *M = S + 2 * C;
-  const bool hs = t.sum != nullptr, hm = t.mn != nullptr;
-  // reduce `n` (power of two <= C) nodes at height h starting at node id `base`; level r above
-  // them starts at node id lvl0(r)
-  auto reduce = [&](long long base, int n, int h, long long chunk) {
-    for (int i = threadIdx.x; i < n; i += kDenseThreads) {
-      if (hs) S[n + i] = __ldcg(&t.sum[(base + i) * t.stride]);
-      if (hm) M[n + i] = __ldcg(&t.mn[(base + i) * t.stride]);
+
+  cta_reduce<PAIRED, E>(t, (int)(width + x0), n, s_v);
+
+  bool last = gridDim.x == 1;
+  if (finish && gridDim.x > 1) {
+    // the last CTA to finish reduces the gridDim.x chunk roots (a power of two <= C) to the root
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+      s_last = (atomicAdd(&t.aux[1], 1) == (int)gridDim.x - 1);
+      if (s_last) t.aux[1] = 0;
     }
     __syncthreads();
-    int r = 0;
-    for (int w = n >> 1; w >= 1; w >>= 1) {
-      ++r;
-      const long long lvl = (t.cap >> (h + r)) + chunk * w;
-      for (int q = threadIdx.x; q < w; q += kDenseThreads) {
-        const int m = w + q;
-        if (hs) {
-          const double v = __dadd_rn(S[2 * m], S[2 * m + 1]);
-          S[m] = v;
-          __stcg(&t.sum[(lvl + q) * t.stride], v);
-        }
-        if (hm) {
-          const double v = py_min(M[2 * m], M[2 * m + 1]);
-          M[m] = v;
-          __stcg(&t.mn[(lvl + q) * t.stride], v);
-        }
-      }
-      __syncthreads();
-    }
-  };
-  const long long chunk = blockIdx.x;
-  reduce((t.cap >> h0) + chunk * C, C, h0, chunk);
-  if (!finish || gridDim.x == 1) return;
-  // the last CTA to finish reduces the gridDim.x chunk roots (a power of two <= C) to the root
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    s_last = (atomicAdd(&t.aux[1], 1) == (int)gridDim.x - 1);
-    if (s_last) t.aux[1] = 0;
+    if (!s_last) return;
+    __threadfence();
+    cta_reduce<PAIRED, E>(t, (int)(width / C), (int)gridDim.x, s_v);
+    last = true;
   }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  reduce(t.cap >> (h0 + logC), (int)gridDim.x, h0 + logC, 0);
+  if (last && (hc.mode & 2)) {  // every reader of the hot flags is done: back to zero for the next call
+    const int nh = __ldcg(hc.nhot);
+    for (int i = tid; i < nh; i += kDenseThreads) hc.flags[__ldcg(&hc.hotlist[i])] = 0;
+    __syncthreads();
+    if (tid == 0) *hc.nhot = 0;
+  }
 }
 
 // ---- host: pick a schedule -------------------------------------------------------------------------
@@ -832,23 +824,57 @@ inline xp_status_t set_attr_once(const void *fn, size_t bytes, bool &done) {
 }
 
 
-inline xp_status_t launch_dense(const Tree &t, int h0, long long width, int max_logc, cudaStream_t st,
-                                int &launches) {
-  static bool attr = false;
-  xp_status_t rc = set_attr_once((const void *)set_dense_kernel, (size_t)4 * (1 << kDenseLogC) * 8, attr);
-  if (rc != XP_OK) return rc;
+// Dense rebuild of everything above height h0 (`width` nodes there).  `hot` (schedules S / L): the first
+// launch rebuilds the flagged buckets below h0 first, the last one clears the flags.
+inline int env_int(const char *name, int dflt) {
+  const char *e = getenv(name);
+  return (e && e[0]) ? atoi(e) : dflt;
+}
+
+template <bool PAIRED, int E>
+inline void launch_dense_one(const Tree &t, int h0, long long width, int finish, const HotCtx &hc, cudaStream_t st) {
+  const long long C = (long long)kDenseThreads * E;
+  const long long grid = width > C ? width / C : 1;
+  xp::launch(set_dense_kernel<PAIRED, E>, dim3((unsigned)grid), dim3(kDenseThreads), 0, st, t, h0, finish, hc);
+}
+
+inline xp_status_t launch_dense(const Tree &t, int h0, long long width, bool paired, const HotCtx *hot,
+                                cudaStream_t st, int &launches) {
+  HotCtx none{};
+  bool first = true;
   while (width > 1) {
-    const int lw = ilog2(width);
-    const int logC = lw < max_logc ? lw : max_logc;
-    const long long grid = width >> logC;
-    const int finish = grid <= (1ll << logC) ? 1 : 0;  // the chunk roots fit one CTA's heap
-    xp::launch(set_dense_kernel, dim3((unsigned)grid), dim3(kDenseThreads), (size_t)4 * (1 << logC) * 8, st, t, h0, logC, finish);
+    // 8 nodes per thread (2 048 per CTA) once that still fills the GPU, else 2 (512 per CTA)
+    const int E = width >= (1ll << 17) ? 8 : 2;
+    const long long C = (long long)kDenseThreads * E;
+    const long long grid = width > C ? width / C : 1;
+    const int finish = grid <= C ? 1 : 0;  // the chunk roots fit one CTA
+    HotCtx hc = hot ? *hot : none;
+    hc.mode = hot ? ((first ? 1 : 0) | (finish ? 2 : 0)) : 0;
+    if (paired) {
+      if (E == 8) launch_dense_one<true, 8>(t, h0, width, finish, hc, st);
+      else launch_dense_one<true, 2>(t, h0, width, finish, hc, st);
+    } else {
+      if (E == 8) launch_dense_one<false, 8>(t, h0, width, finish, hc, st);
+      else launch_dense_one<false, 2>(t, h0, width, finish, hc, st);
+    }
     ++launches;
     if (finish) break;
-    h0 += logC;
-    width >>= logC;
+    first = false;
+    h0 += ilog2(C);
+    width /= C;
   }
   return XP_OK;
+}
+
+inline HotCtx make_hot(const SetSrc &s, const Buckets &bk) {
+  HotCtx hc{};
+  hc.s = s;
+  hc.s.pre = bk.vals;
+  hc.flags = bk.counts;
+  hc.shift = bk.shift;
+  hc.hotlist = bk.hotlist;
+  hc.nhot = bk.nhot;
+  return hc;
 }
 
 inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStream_t st) {
@@ -866,8 +892,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     int warps = B > 4096 ? 16 : B > 2048 ? 8 : 4;
     if (warps > nb) warps = (int)nb;
     const unsigned grid = (unsigned)(nb / warps);
-    const size_t heap = nb > 1 ? (size_t)2 * nb * sizeof(double2) : 0;
-    size_t smem = heap > (size_t)B * 4 ? heap : (size_t)B * 4;
+    size_t smem = (size_t)B * 4;
     if (B > kMidCompactFrom && smem < (size_t)kMidListCap * 8) smem = (size_t)kMidListCap * 8;
     static bool mid_attr[2] = {false, false};
     xp_status_t rc = set_attr_once(paired ? (const void *)set_mid_kernel<true> : (const void *)set_mid_kernel<false>,
@@ -884,43 +909,34 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   const int use_half = 1;
   while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;  // ~16 items per bucket
   const bool want_vals = s.kind == kSrcPrio;
-  if (slotted_scratch_ints(t.cap, nb, B, want_vals) <= t.cap && s.kind != kSrcRange && !getenv("XP_NO_S")) {
-    // schedule S, and behind it — same counters, ONE launch that returns at once unless the overflow list
-    // grew past kOvfLimit (skewed batches) — the scan | scatter | compact climb of schedule L
-    const int shift = L - ilog2(nb);
-    Buckets bs = make_slotted(t, (int)nb, shift, B, want_vals);
-    Buckets bl = make_buckets(t, (int)nb, shift, B, want_vals);
-    bl.guard = -1;
-    int top = L - ilog2(B) - 1;  // as in schedule L below
-    if (top < 1) top = 1;
-    if (top > shift) top = shift;
-    bs.top = bl.top = top;
-    const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps) / kBucketWarps);
-    xp::launch(set_slot_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bs);
+  const int shift = L - ilog2(nb);
+  // The sparse climb costs ~2 scattered sector requests per item per level; a dense coalesced
+  // rebuild of everything above height `top` costs 32 B per node of that level.  Measured at
+  // cap 2^24, B 2^18: the two meet where the level holds ~2 B nodes (update 88 -> 83 us).
+  static const int top_delta = env_int("XP_TOP_DELTA", 0);  // developer knob (tools/micro)
+  static const int no_s = env_int("XP_NO_S", 0);
+  int top = L - ilog2(B) - 1 + top_delta;
+  if (top < 1) top = 1;
+  if (top > shift) top = shift;
+  const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps - 1) / kBucketWarps) + (nb < 2 ? 1u : 0u);
+  if (slotted_scratch_ints(t.cap, nb, B, want_vals) <= t.cap && s.kind != kSrcRange && !no_s) {
+    // schedule S: bucketing in one pass | one warp per bucket pair | dense top (hot buckets included)
+    Buckets bk = make_slotted(t, (int)nb, shift, B, want_vals);
+    bk.top = top;
+    xp::launch(set_slot_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bk);
     if (paired)
-      xp::launch(set_wbucket_kernel<true>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bs, use_half);
+      xp::launch(set_wbucket_kernel<true>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
     else
-      xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bs, use_half);
-    const unsigned fgrid = (unsigned)(2 * xp::sm_count());  // all resident: the phases meet at grid barriers
-    if (paired)
-      xp::launch(set_fallback_kernel<true>, dim3(fgrid), dim3(256), 0, st, t, s, B, bl, use_half);
-    else
-      xp::launch(set_fallback_kernel<false>, dim3(fgrid), dim3(256), 0, st, t, s, B, bl, use_half);
-    launches = 3;
-    xp_status_t rc = launch_dense(t, top, t.cap >> top, top == shift ? 8 : 10, st, launches);
+      xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
+    launches = 2;
+    const HotCtx hc = make_hot(s, bk);
+    xp_status_t rc = launch_dense(t, top, t.cap >> top, paired, &hc, st, launches);
     if (rc != XP_OK) return rc;
     return xp::check_launch("tree set (S)", launches);
   }
   const long long need = bucket_scratch_ints(t.cap, nb, B, want_vals);
   if (need <= t.cap) {  // schedule L
-    const int shift = L - ilog2(nb);
     Buckets bk = make_buckets(t, (int)nb, shift, B, want_vals);
-    // The sparse climb costs ~2 scattered sector requests per item per level; a dense coalesced
-    // rebuild of everything above height `top` costs 32 B per node of that level.  Measured at
-    // cap 2^24, B 2^18: the two meet where the level holds ~2 B nodes (update 88 -> 83 us).
-    int top = L - ilog2(B) - 1;
-    if (top < 1) top = 1;
-    if (top > shift) top = shift;
     bk.top = top;
     xp::launch(set_hist_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bk);
     static bool scan_attr = false;
@@ -930,13 +946,13 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     }
     xp::launch(set_scan_kernel, dim3(1), dim3(1024), (size_t)(nb + nb / 32 + 1) * 4, st, bk);
     xp::launch(set_scatter_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bk);
-    const unsigned bgrid = (unsigned)((nb / 2 + kBucketWarps) / kBucketWarps);
     if (paired)
       xp::launch(set_wbucket_kernel<true>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
     else
       xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
     launches = 4;
-    xp_status_t rc = launch_dense(t, bk.top, t.cap >> bk.top, bk.top == shift ? 8 : 10, st, launches);
+    const HotCtx hc = make_hot(s, bk);
+    xp_status_t rc = launch_dense(t, top, t.cap >> top, paired, &hc, st, launches);
     if (rc != XP_OK) return rc;
     return xp::check_launch("tree set (L)", launches);
   }
@@ -944,7 +960,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   set_ticket_kernel<<<grid, 256, 0, st>>>(t, s, B);
   set_leafwrite_kernel<<<grid, 256, 0, st>>>(t, s, B);
   launches = 2;
-  xp_status_t rc = launch_dense(t, 0, t.cap, kDenseLogC, st, launches);
+  xp_status_t rc = launch_dense(t, 0, t.cap, paired, nullptr, st, launches);
   if (rc != XP_OK) return rc;
   return xp::check_launch("tree set (D)", launches);
 }

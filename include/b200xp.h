@@ -263,16 +263,20 @@ xp_status_t xp_bptt_indices(const int32_t *seq_t0_dev, const int32_t *seq_env_de
                             int64_t *unp_idx_dev, int64_t *first_idx_dev, void *stream);
 
 /* ---- replicated-replay exchange over NVLink peer memory ---------------------------------- */
-/* replaces the broadcast of sampled indices + gather of new priorities of the distributed
- * off-policy loop (training/train_off_policy.py:363-381) when every rank is one GPU of an NVLink
- * domain.  Rank r keeps its block in peer-mapped memory at peer_base[r]; peer_flags[r] is a
+/* The reference's buffers take part in no collective (one `memory` object serves the whole population
+ * in one process: training/train_off_policy.py:46,343-345,363-376).  This exchange is the build's own
+ * (BASELINE.json north_star: replicated shared replay, one process per GPU): every replica applies every
+ * rank's update_priorities (components/replay_buffer.py:411-428) in rank-major order, which needs every
+ * rank's (indices, priorities).  Rank r keeps its block in peer-mapped memory at peer_base[r];
+ * peer_flags[r] is a
  * uint32[world] array in r's peer-mapped memory (zero before the first call).  The kernel signals
  * `epoch` to every peer, waits for every peer's `epoch`, and copies segment k of every rank's
  * block (peer_base[r] + src_off, `bytes` long) to segs[k].dst + r*bytes (local memory): a
  * rank-major all-gather.  Call with epoch = 1, 2, 3, ... on every rank, and alternate between two
  * source blocks so that a block is not rewritten while a slower peer may still read it.
- * peer_base / peer_flags / segs are HOST arrays.  A peer that does not arrive within ~2 s sets
- * *err_flag_dev instead of hanging.                                                          */
+ * peer_base / peer_flags / segs are HOST arrays.  A peer that does not arrive within the time-out
+ * (xp_peer_set_timeout_cycles, default ~30 s) sets *err_flag_dev instead of hanging; the data of that
+ * call is then NOT valid and the caller must treat the replica as lost.                          */
 #define XP_MAX_PEERS 16
 #define XP_MAX_PEER_SEGS 4
 typedef struct xp_peer_seg {
@@ -283,6 +287,18 @@ typedef struct xp_peer_seg {
 xp_status_t xp_peer_allgather(const void *const *peer_base, void *const *peer_flags, int rank,
                               int world, uint32_t epoch, const xp_peer_seg *segs, int n_segs,
                               int *err_flag_dev, void *stream);
+/* The same exchange with the epoch kept on the device, so that the call's parameters never change and
+ * it can be captured in a CUDA graph together with the sample / gather / update launches of a step:
+ * epoch_state_dev is uint32[2], zero before the first call ([0] = exchanges completed, [1] = scratch);
+ * exchange number e = 1, 2, 3, ... publishes block (e - 1) & 1 (peer_base0 / peer_base1 of every rank)
+ * and the last CTA of the launch stores e for the next launch to read.  Every rank must issue the same
+ * sequence of calls on one stream.                                                               */
+xp_status_t xp_peer_allgather_graph(const void *const *peer_base0, const void *const *peer_base1,
+                                    void *const *peer_flags, int rank, int world,
+                                    uint32_t *epoch_state_dev, const xp_peer_seg *segs, int n_segs,
+                                    int *err_flag_dev, void *stream);
+/* Bounded wait of the handshake, in SM clock cycles (default 6e10, ~30 s).                       */
+void xp_peer_set_timeout_cycles(int64_t cycles);
 
 /* Exchange + insert in one kernel: the per-step broadcast of newly collected transitions into the
  * replicated shared memory (one `memory` object for the whole population,
