@@ -294,6 +294,56 @@ def test_tree_set_batch_sizes_may_change_between_calls(xp, cuda_device):
         assert int(tree.err.item()) == 0
 
 
+def _rebuild(leaves_s, leaves_m, cap):
+    """Bottom-up rebuild in the tree's own pairwise order (what segment_tree.py:89-95 leaves behind)."""
+    s = np.zeros(2 * cap)
+    m = np.full(2 * cap, np.inf)
+    s[cap:], m[cap:] = leaves_s, leaves_m
+    lvl = cap >> 1
+    while lvl >= 1:
+        s[lvl:2 * lvl] = s[2 * lvl:4 * lvl:2] + s[2 * lvl + 1:4 * lvl:2]
+        m[lvl:2 * lvl] = np.minimum(m[2 * lvl:4 * lvl:2], m[2 * lvl + 1:4 * lvl:2])
+        lvl >>= 1
+    return s, m
+
+
+@pytest.mark.parametrize("cap,B,share,hot", [(1 << 20, 100000, 0.3, 4096), (1 << 20, 100000, 0.1, 64),
+                                             (1 << 22, 262144, 0.3, 4096), (1 << 22, 262144, 0.9, 1 << 16),
+                                             (1 << 20, 40000, 1.0, 8), (1 << 22, 262144, 0.5, 33 * 400)])
+def test_tree_set_skewed_large_batches(xp, cuda_device, cap, B, share, hot):
+    """Schedule S / L with HOT buckets: a share of a large batch falls into a few leaves (fresh
+    transitions carry max_priority and are drawn together, replay_buffer.py:306-309).  Hot buckets are
+    not climbed: their items leave last-writer tickets and the dense kernel rebuilds them.  Both entry
+    points (values / priorities), twice in a row (scratch back to zero), every node compared."""
+    rng = np.random.default_rng(cap + B + hot)
+    t = DevTree(xp, cuda_device, cap)
+    ls, lm = np.zeros(cap), np.full(cap, np.inf)
+    state = torch.ones(1, dtype=torch.float64, device=cuda_device)
+    for rnd in range(3):
+        k = int(B * share)
+        idx = rng.integers(0, cap, B)
+        lo = cap - hot if rnd != 1 else cap // 2      # another hot range in the second round
+        idx[:k] = lo + rng.integers(0, hot, k)
+        idx = idx[rng.permutation(B)]
+        if rnd < 2:
+            val = rng.random(B) * 5.0 + 1e-3
+            t.set(idx, val)
+        else:                                          # the PER entry point: leaf = max(p, 1e-5) ** alpha
+            pr = (rng.random(B) * 3.0 + 1e-3).astype(np.float32)
+            xp.per_update(t.t, state, dev(idx, cuda_device, torch.int64), dev(pr, cuda_device, torch.float32),
+                          cap, 0.6, t.err)
+            val = np.array([max(float(p), 1e-5) ** 0.6 for p in pr])  # CPython pow, as the reference (:322,425)
+        ls[idx] = val   # numpy fancy assignment: the LAST duplicate wins, as the sequential loop
+        lm[idx] = val
+        ws, wm = _rebuild(ls, lm, cap)
+        ds, dm = t.arrays()
+        assert np.array_equal(ds[1:], ws[1:]) and np.array_equal(dm[1:], wm[1:]), rnd
+        assert int(t.err.item()) == 0
+        assert int(t.aux[cap:].abs().sum()) == 0       # tickets consumed
+        mb = min(32768, cap // 4)                      # tree_set.cuh max_buckets(): counters / hot flags, zero between calls
+        assert int(t.aux[:16].abs().sum()) == 0 and int(t.aux[16:16 + mb].abs().sum()) == 0
+
+
 def test_tree_set_out_of_range_flags(xp, cuda_device):
     t = DevTree(xp, cuda_device, 8)
     t.set([1, 8, -1], [1.0, 2.0, 3.0])
