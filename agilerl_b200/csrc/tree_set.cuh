@@ -16,11 +16,10 @@
 //                   per bucket -> dense top.
 //   D  B ~ cap      tickets -> winners write leaves -> dense coalesced bottom-up rebuild.
 // Hot buckets (more than 32 items: skewed batches — fresh transitions carry the maximum priority and
-// are drawn together) are not climbed at all under S / L: their items leave last-writer tickets on
-// the leaves (the items beyond a slice do so in the bucketing pass itself), the bucket is flagged,
-// and the dense kernel, which rebuilds everything above height `top` anyway, first rebuilds the
-// flagged buckets' subtrees from their leaves — leaf-parallel, no list scan, any skew costs what
-// its leaves cost.
+// are drawn together) are not climbed item by item under S / L: their items leave last-writer tickets
+// on the leaves (the items beyond a slice do so in the bucketing pass itself) and the bucket's warp
+// rebuilds the whole bucket subtree from its leaves — leaf-parallel, no list scan, one warp per hot
+// bucket: any skew costs what its leaves cost.
 // `aux` (int32[2*cap]): [cap, 2cap) last-writer tickets (zero between calls; schedule D and
 // hot buckets); [0, cap) scratch (done counter, bucket counters/offsets/cursors, items).
 #pragma once
@@ -453,8 +452,6 @@ struct Buckets {
   double *vals;    // kSrcPrio only: leaf value per batch position (else NULL)
   int slots;       // 0: compact slices (offsets / cursors).  > 0 (schedule S): bucket b owns the fixed
                    // slice items[b*slots, (b+1)*slots); items beyond it only leave their ticket
-  int *hotlist;    // ids of the hot buckets of this call, *nhot of them (aux[5], zero between calls);
-  int *nhot;       // a hot bucket's counter stays at -1 until the dense kernel has rebuilt it
 };
 constexpr int kHotOver = 32;  // a bucket with more items than a warp has lanes is "hot"
 
@@ -469,7 +466,7 @@ __host__ __device__ inline long long max_buckets(long long cap) {
 
 __host__ __device__ inline long long bucket_scratch_ints(long long cap, long long nb, long long B, bool want_vals) {
   const long long mb = max_buckets(cap);
-  return 16 + mb + 2 * nb + 2 + (want_vals ? 4 : 2) * B + nb;
+  return 16 + mb + 2 * nb + 2 + (want_vals ? 4 : 2) * B;
 }
 
 __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift, long long B, bool want_vals) {
@@ -486,8 +483,6 @@ __host__ __device__ inline Buckets make_buckets(const Tree &t, int nb, int shift
   b.items = reinterpret_cast<u64 *>(t.aux + off);
   b.vals = want_vals ? reinterpret_cast<double *>(t.aux + off + 2 * B) : nullptr;
   b.slots = 0;
-  b.hotlist = t.aux + off + (want_vals ? 4 : 2) * B;
-  b.nhot = t.aux + 5;
   return b;
 }
 
@@ -499,7 +494,7 @@ __host__ __device__ inline long long slotted_scratch_ints(long long cap, long lo
   return bucket_scratch_ints(cap, nb, B, want_vals) + 2 + 2 * nb * kSlots;
 }
 __host__ __device__ inline Buckets make_slotted(const Tree &t, int nb, int shift, long long B, bool want_vals) {
-  Buckets b = make_buckets(t, nb, shift, B, want_vals);  // same counters, same vals, same hot list
+  Buckets b = make_buckets(t, nb, shift, B, want_vals);  // same counters, same vals
   long long off = bucket_scratch_ints(t.cap, nb, B, want_vals);
   off = (off + 1) & ~1ll;
   b.items = reinterpret_cast<u64 *>(t.aux + off);
@@ -620,11 +615,71 @@ __global__ void __launch_bounds__(256) set_slot_kernel(Tree t, SetSrc s, long lo
   if (s.kind == kSrcPrio) fold_max_priority(s, p);
 }
 
+// A HOT bucket (more than 32 items) is rebuilt from its leaves by its warp: every item of the bucket has
+// left its last-writer ticket on its leaf (ticket = batch position + 1; the items beyond a schedule-S
+// slice did so in the bucketing pass, the stored ones do it here), so the winner of a leaf is named by
+// the leaf itself — no list is scanned.  Leaves first (4 independent ticket -> value chains per lane in
+// flight), then the levels 1..top of the bucket, each from the stored level below.
+template <bool PAIRED>
+__device__ __forceinline__ void rebuild_hot_bucket(const Tree &t, const SetSrc &s, const u64 *items, int stored,
+                                                   int b, int shift, int top) {
+  const int lane = threadIdx.x & 31;
+  for (int i = lane; i < stored; i += 32) {
+    const u64 key = __ldcg(&items[i]);
+    atomicMax(&t.aux[t.cap + (long long)(key >> 32)], (int)(key & 0xffffffffull) + 1);
+  }
+  __threadfence();  // the tickets above are in L2 before any lane reads them back
+  __syncwarp();
+  const long long leaf0 = (long long)b << shift;
+  const int nleaves = 1 << shift;
+  int *tickets = t.aux + t.cap + leaf0;
+  constexpr int U = 4;
+  for (int i0 = 0; i0 < nleaves; i0 += 32 * U) {
+    int tk[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * 32 + lane;
+      tk[u] = i < nleaves ? __ldcg(&tickets[i]) : 0;
+    }
+    double val[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) val[u] = tk[u] > 0 ? src_value(s, (long long)tk[u] - 1) : 0.0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (tk[u] > 0) {
+        const int i = i0 + u * 32 + lane;
+        st_node<PAIRED>(t, (int)(t.cap + leaf0 + i), make_double2(val[u], val[u]));
+        __stcg(&tickets[i], 0);  // consumed
+      }
+    }
+  }
+  __syncwarp();  // orders this warp's stores before its loads of the next level
+  for (int h = 1; h <= top; ++h) {
+    const int cnt = nleaves >> h;
+    const int first = (int)((t.cap >> h) + (leaf0 >> h));
+    for (int j0 = 0; j0 < cnt; j0 += 32 * 2) {
+      double2 l[2], r[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int j = j0 + u * 32 + lane;
+        if (j < cnt) {
+          l[u] = ld_node<PAIRED>(t, 2 * (first + j));
+          r[u] = ld_node<PAIRED>(t, 2 * (first + j) + 1);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int j = j0 + u * 32 + lane;
+        if (j < cnt) st_node<PAIRED>(t, first + j, node_op<PAIRED>(l[u], r[u]));
+      }
+    }
+    __syncwarp();
+  }
+}
+
 // one warp per PAIR of buckets: both <= 16 items -> the two half-warps climb them side by side;
-// otherwise one after the other with the whole warp.  A bucket with more than 32 items is HOT: nothing
-// is climbed — its (stored) items leave their tickets on the leaves, the bucket's counter stays at -1 and
-// its id goes to the hot list; the dense kernel rebuilds its subtree from the leaves.
-constexpr int kBucketWarps = 4;  // 56 registers: 9 CTAs of 4 warps fit an SM where 4 CTAs of 8 do (36 vs 32 warps)
+// otherwise one after the other with the whole warp; more than 32 items: rebuild_hot_bucket.
+constexpr int kBucketWarps = 4;  // 64 registers: 8 CTAs of 4 warps per SM
 template <bool PAIRED>
 __device__ __forceinline__ void climb_bucket_pair(const Tree &t, const SetSrc &s, const Buckets &bk, int use_half,
                                                   int b0) {
@@ -643,15 +698,9 @@ __device__ __forceinline__ void climb_bucket_pair(const Tree &t, const SetSrc &s
     n1 = has1 ? bk.cursors[b0 + 1] - beg1 : 0;
   }
   if (n0 == 0 && n1 == 0) return;
-  if (lane == 0) {  // scratch back to zero for the next call (hot buckets: by the dense kernel)
-    bk.counts[b0] = n0 > kHotOver ? -1 : 0;
-    if (has1) bk.counts[b0 + 1] = n1 > kHotOver ? -1 : 0;
-    const int nh = (n0 > kHotOver) + (n1 > kHotOver);
-    if (nh) {
-      int at = atomicAdd(bk.nhot, nh);
-      if (n0 > kHotOver) bk.hotlist[at++] = b0;
-      if (n1 > kHotOver) bk.hotlist[at] = b0 + 1;
-    }
+  if (lane == 0) {  // scratch back to zero for the next call
+    bk.counts[b0] = 0;
+    if (has1) bk.counts[b0 + 1] = 0;
   }
   if (use_half && n0 <= 16 && n1 <= 16) {
     const int half = lane >> 4, l = lane & 15;
@@ -667,17 +716,14 @@ __device__ __forceinline__ void climb_bucket_pair(const Tree &t, const SetSrc &s
     if (n <= kHotOver) {
       warp_climb<PAIRED, 32>(t, s, lane < n ? __ldcg(&items[lane]) : kPad, bk.top);
     } else {
-      const int stored = bk.slots ? bk.slots : n;  // schedule S: the rest ticketed themselves already
-      for (int i = lane; i < stored; i += 32) {
-        const u64 key = __ldcg(&items[i]);
-        atomicMax(&t.aux[t.cap + (long long)(key >> 32)], (int)(key & 0xffffffffull) + 1);
-      }
+      // schedule S stores only the first `slots` items of a bucket; the rest ticketed themselves already
+      rebuild_hot_bucket<PAIRED>(t, s, items, bk.slots ? bk.slots : n, b0 + h, bk.shift, bk.top);
     }
   }
 }
 
 template <bool PAIRED>
-__global__ void __launch_bounds__(kBucketWarps * 32) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk, int use_half) {
+__global__ void __launch_bounds__(kBucketWarps * 32, 8) set_wbucket_kernel(Tree t, SetSrc s, Buckets bk, int use_half) {
   xp::pdl_enter();
   s.pre = bk.vals;
   const int w = blockIdx.x * kBucketWarps + (threadIdx.x >> 5);
@@ -723,86 +769,28 @@ __global__ void __launch_bounds__(256) set_leafwrite_kernel(Tree t, SetSrc s, lo
 // (left, right) = (lower node id, higher node id) everywhere, as segment_tree.py:89-95 has it.
 constexpr int kDenseThreads = 256;
 
-// What the first dense launch of schedules S / L needs to rebuild the hot buckets below h0 (= top).
-struct HotCtx {
-  SetSrc s;       // s.pre = leaf values parked by batch position (kSrcPrio), else the source itself
-  int *flags;     // per-bucket counters: -1 = hot (leaves carry tickets, nothing was climbed)
-  int shift;      // leaves per bucket = 1 << shift
-  int *hotlist;   // hot bucket ids, *nhot of them
-  int *nhot;
-  int mode;       // bit 0: rebuild the flagged buckets below h0 first; bit 1: the finishing CTA clears the flags
-};
-
 template <bool PAIRED, int E>
-__global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0, int finish, HotCtx hc) {
+__global__ void __launch_bounds__(kDenseThreads) set_dense_kernel(Tree t, int h0, int finish) {
   xp::pdl_enter();
   constexpr int C = kDenseThreads * E;
   __shared__ double2 s_v[32];
-  __shared__ int s_hot[C];
-  __shared__ int s_nhot, s_last;
-  const int tid = threadIdx.x;
+  __shared__ int s_last;
   const long long width = t.cap >> h0;            // nodes at height h0
   const int n = width < C ? (int)width : C;       // nodes of this CTA
   const long long x0 = (long long)blockIdx.x * C; // index of its first node inside the level
-
-  if (hc.mode & 1) {
-    // hot buckets: every node of height h0 under a flagged bucket is rebuilt from its 2^h0 leaves, whose
-    // winners are named by the tickets (ticket = batch position + 1 of the LAST item of the leaf)
-    if (tid == 0) s_nhot = 0;
-    __syncthreads();
-    const int per = hc.shift - h0;                // log2(nodes of height h0 per bucket), >= 0
-    for (int i = tid; i < n; i += kDenseThreads)
-      if (__ldcg(&hc.flags[(x0 + i) >> per]) < 0) s_hot[atomicAdd(&s_nhot, 1)] = i;
-    __syncthreads();
-    const int nh = s_nhot;
-    if (nh) {
-      for (int h = 0; h <= h0; ++h) {
-        const int sh = h0 - h;                    // log2(nodes of height h under one node of height h0)
-        const long long total = (long long)nh << sh;
-        for (long long q = tid; q < total; q += kDenseThreads) {
-          const long long g = x0 + s_hot[(int)(q >> sh)];
-          const long long id = (t.cap >> h) + (g << sh) + (q & ((1ll << sh) - 1));
-          if (h == 0) {
-            int *tk = &t.aux[id];                 // aux[cap + leaf]
-            const int w = __ldcg(tk);
-            if (w > 0) {
-              const double val = src_value(hc.s, (long long)w - 1);
-              st_node<PAIRED>(t, (int)id, make_double2(val, val));
-              __stcg(tk, 0);
-            }
-          } else {
-            st_node<PAIRED>(t, (int)id,
-                            node_op<PAIRED>(ld_node<PAIRED>(t, (int)(2 * id)), ld_node<PAIRED>(t, (int)(2 * id + 1))));
-          }
-        }
-        __syncthreads();                          // level h is complete (and visible) inside this CTA
-      }
-    }
-  }
-
   cta_reduce<PAIRED, E>(t, (int)(width + x0), n, s_v);
-
-  bool last = gridDim.x == 1;
-  if (finish && gridDim.x > 1) {
-    // the last CTA to finish reduces the gridDim.x chunk roots (a power of two <= C) to the root
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-      s_last = (atomicAdd(&t.aux[1], 1) == (int)gridDim.x - 1);
-      if (s_last) t.aux[1] = 0;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    cta_reduce<PAIRED, E>(t, (int)(width / C), (int)gridDim.x, s_v);
-    last = true;
+  if (!finish || gridDim.x == 1) return;
+  // the last CTA to finish reduces the gridDim.x chunk roots (a power of two <= C) to the root
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    s_last = (atomicAdd(&t.aux[1], 1) == (int)gridDim.x - 1);
+    if (s_last) t.aux[1] = 0;
   }
-  if (last && (hc.mode & 2)) {  // every reader of the hot flags is done: back to zero for the next call
-    const int nh = __ldcg(hc.nhot);
-    for (int i = tid; i < nh; i += kDenseThreads) hc.flags[__ldcg(&hc.hotlist[i])] = 0;
-    __syncthreads();
-    if (tid == 0) *hc.nhot = 0;
-  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  cta_reduce<PAIRED, E>(t, (int)(width / C), (int)gridDim.x, s_v);
 }
 
 // ---- host: pick a schedule -------------------------------------------------------------------------
@@ -824,57 +812,44 @@ inline xp_status_t set_attr_once(const void *fn, size_t bytes, bool &done) {
 }
 
 
-// Dense rebuild of everything above height h0 (`width` nodes there).  `hot` (schedules S / L): the first
-// launch rebuilds the flagged buckets below h0 first, the last one clears the flags.
+// Dense rebuild of everything above height h0 (`width` nodes there).
 inline int env_int(const char *name, int dflt) {
   const char *e = getenv(name);
   return (e && e[0]) ? atoi(e) : dflt;
 }
 
 template <bool PAIRED, int E>
-inline void launch_dense_one(const Tree &t, int h0, long long width, int finish, const HotCtx &hc, cudaStream_t st) {
+inline void launch_dense_one(const Tree &t, int h0, long long width, int finish, cudaStream_t st) {
   const long long C = (long long)kDenseThreads * E;
   const long long grid = width > C ? width / C : 1;
-  xp::launch(set_dense_kernel<PAIRED, E>, dim3((unsigned)grid), dim3(kDenseThreads), 0, st, t, h0, finish, hc);
+  xp::launch(set_dense_kernel<PAIRED, E>, dim3((unsigned)grid), dim3(kDenseThreads), 0, st, t, h0, finish);
 }
 
-inline xp_status_t launch_dense(const Tree &t, int h0, long long width, bool paired, const HotCtx *hot,
-                                cudaStream_t st, int &launches) {
-  HotCtx none{};
-  bool first = true;
+inline xp_status_t launch_dense(const Tree &t, int h0, long long width, bool paired, cudaStream_t st, int &launches) {
   while (width > 1) {
-    // 8 nodes per thread (2 048 per CTA) once that still fills the GPU, else 2 (512 per CTA)
-    const int E = width >= (1ll << 17) ? 8 : 2;
+    // 2 nodes per thread (512 per CTA) measured best behind the bucket kernel (programmatic launch: the
+    // early-resident CTAs of a fat 8-per-thread variant slowed the climb, C4 update 74 vs 65 us);
+    // 8 per thread only where the level is so wide that the chunk roots would not fit one CTA
+    static const int force_e = env_int("XP_DENSE_E", 0);  // developer knob
+    const int E = force_e ? force_e : (width > (1ll << 20) ? 8 : 2);
     const long long C = (long long)kDenseThreads * E;
     const long long grid = width > C ? width / C : 1;
     const int finish = grid <= C ? 1 : 0;  // the chunk roots fit one CTA
-    HotCtx hc = hot ? *hot : none;
-    hc.mode = hot ? ((first ? 1 : 0) | (finish ? 2 : 0)) : 0;
     if (paired) {
-      if (E == 8) launch_dense_one<true, 8>(t, h0, width, finish, hc, st);
-      else launch_dense_one<true, 2>(t, h0, width, finish, hc, st);
+      if (E == 8) launch_dense_one<true, 8>(t, h0, width, finish, st);
+      else if (E == 4) launch_dense_one<true, 4>(t, h0, width, finish, st);
+      else launch_dense_one<true, 2>(t, h0, width, finish, st);
     } else {
-      if (E == 8) launch_dense_one<false, 8>(t, h0, width, finish, hc, st);
-      else launch_dense_one<false, 2>(t, h0, width, finish, hc, st);
+      if (E == 8) launch_dense_one<false, 8>(t, h0, width, finish, st);
+      else if (E == 4) launch_dense_one<false, 4>(t, h0, width, finish, st);
+      else launch_dense_one<false, 2>(t, h0, width, finish, st);
     }
     ++launches;
     if (finish) break;
-    first = false;
     h0 += ilog2(C);
     width /= C;
   }
   return XP_OK;
-}
-
-inline HotCtx make_hot(const SetSrc &s, const Buckets &bk) {
-  HotCtx hc{};
-  hc.s = s;
-  hc.s.pre = bk.vals;
-  hc.flags = bk.counts;
-  hc.shift = bk.shift;
-  hc.hotlist = bk.hotlist;
-  hc.nhot = bk.nhot;
-  return hc;
 }
 
 inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStream_t st) {
@@ -929,8 +904,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     else
       xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
     launches = 2;
-    const HotCtx hc = make_hot(s, bk);
-    xp_status_t rc = launch_dense(t, top, t.cap >> top, paired, &hc, st, launches);
+    xp_status_t rc = launch_dense(t, top, t.cap >> top, paired, st, launches);
     if (rc != XP_OK) return rc;
     return xp::check_launch("tree set (S)", launches);
   }
@@ -951,8 +925,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     else
       xp::launch(set_wbucket_kernel<false>, dim3(bgrid), dim3(kBucketWarps * 32), 0, st, t, s, bk, use_half);
     launches = 4;
-    const HotCtx hc = make_hot(s, bk);
-    xp_status_t rc = launch_dense(t, top, t.cap >> top, paired, &hc, st, launches);
+    xp_status_t rc = launch_dense(t, top, t.cap >> top, paired, st, launches);
     if (rc != XP_OK) return rc;
     return xp::check_launch("tree set (L)", launches);
   }
@@ -960,7 +933,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   set_ticket_kernel<<<grid, 256, 0, st>>>(t, s, B);
   set_leafwrite_kernel<<<grid, 256, 0, st>>>(t, s, B);
   launches = 2;
-  xp_status_t rc = launch_dense(t, 0, t.cap, paired, nullptr, st, launches);
+  xp_status_t rc = launch_dense(t, 0, t.cap, paired, st, launches);
   if (rc != XP_OK) return rc;
   return xp::check_launch("tree set (D)", launches);
 }
