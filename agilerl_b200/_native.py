@@ -75,6 +75,7 @@ _SIGNATURES = {
                                C.c_double, c_vp]),
     "xp_gae_turn_broadcast": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_vp]),
     "xp_standardize": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
+    "xp_standardize_static": (C.c_int, [c_vp, c_vp, c_i64, c_vp]),
     "xp_masked_whiten": (C.c_int, [c_vp, c_vp, c_vp, c_i64, C.c_int, c_vp, c_vp, c_vp]),
     "xp_gae_f32": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_i64,
                              C.c_double, C.c_double, c_vp]),

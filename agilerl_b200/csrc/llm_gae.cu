@@ -10,6 +10,8 @@
 // scalars (gamma and gamma*lambda enter as fp32): reproduced op for op, bit-exact.  The reductions
 // (turn pooling, whitening statistics) are fp32 sums of unspecified order in torch; here they are
 // accumulated in fp64 in a fixed order and rounded once — within a few ulp of any fp32 order.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -337,6 +339,40 @@ __global__ void __launch_bounds__(256) whiten_apply_kernel(const float *x, const
 
 }  // namespace
 
+// ---- xp_standardize_static: the same three launches with the scratch inside the library ----------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+// The array lives in every GPU context that loads the library, until exit (4 160 bytes).  In HOST code
+// its name is only a stand-in, not a device address: the address is looked up once per device with that
+// device current (cudaGetSymbolAddress) and it is that pointer the kernels receive.
+static __device__ __align__(256) double g_standardize_scratch[XP_WHITEN_SCRATCH];
+
+namespace {
+constexpr int kMaxDevices = 64;
+double *g_scratch_ptr[kMaxDevices] = {nullptr};
+std::mutex g_scratch_mu;
+
+// Device address of g_standardize_scratch on the CURRENT device (cached per device), or NULL + error text.
+double *static_scratch() {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    xp::set_error("xp_standardize_static: cudaGetDevice: %s", e != cudaSuccess ? cudaGetErrorString(e) : "device index");
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
+  if (!g_scratch_ptr[dev]) {
+    void *p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_standardize_scratch);
+    if (e != cudaSuccess || !p) {
+      xp::set_error("xp_standardize_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return nullptr;
+    }
+    g_scratch_ptr[dev] = static_cast<double *>(p);
+  }
+  return g_scratch_ptr[dev];
+}
+}  // namespace
+
 extern "C" {
 
 xp_status_t xp_gae_tokens(const float *rewards, const float *values, const float *mask, float *adv, float *ret,
@@ -418,6 +454,31 @@ xp_status_t xp_standardize(const float *x, float *out, int64_t n, double *scratc
   whiten_stats_kernel<1><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, nullptr, n, scratch_dev, nullptr, 1);
   whiten_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, nullptr, out, n, scratch_dev, 0, 1);
   return xp::check_launch("xp_standardize", 3);
+}
+
+xp_status_t xp_standardize_static(const float *x, float *out, int64_t n, void *stream) {
+  XP_REQUIRE(n >= 0, XP_ERR_INVALID, "xp_standardize_static: n < 0");
+  XP_REQUIRE(n <= XP_STANDARDIZE_STATIC_MAX_N, XP_ERR_INVALID,
+             "xp_standardize_static: n = %lld exceeds the maximum of %lld elements of the no-allocation variant "
+             "(use xp_standardize with caller-owned scratch)", (long long)n, (long long)XP_STANDARDIZE_STATIC_MAX_N);
+  if (n == 0) return XP_OK;
+  XP_REQUIRE(x && out, XP_ERR_INVALID, "xp_standardize_static: null pointer");
+  double *scratch = static_scratch();
+  if (!scratch) return XP_ERR_CUDA;
+  cudaStream_t s = (cudaStream_t)stream;
+  // the array keeps the previous call's contents: the one word that must start at zero is the ticket the
+  // CTAs count themselves with (everything else is written before it is read)
+  cudaError_t e = cudaMemsetAsync(scratch + 3, 0, sizeof(double), s);
+  if (e != cudaSuccess) {
+    xp::set_error("xp_standardize_static: cudaMemsetAsync: %s", cudaGetErrorString(e));
+    return XP_ERR_CUDA;
+  }
+  long long ctas = (n + 4 * kWhitenThreads - 1) / (4 * kWhitenThreads);
+  if (ctas > kWhitenCtas) ctas = kWhitenCtas;
+  whiten_stats_kernel<0><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, nullptr, n, scratch, nullptr, 1);
+  whiten_stats_kernel<1><<<(unsigned)ctas, kWhitenThreads, 0, s>>>(x, nullptr, n, scratch, nullptr, 1);
+  whiten_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, nullptr, out, n, scratch, 0, 1);
+  return xp::check_launch("xp_standardize_static", 3);
 }
 
 }  // extern "C"

@@ -231,6 +231,19 @@ xp_status_t xp_masked_whiten(const float *x, const float *mask, float *out, int6
  * row 2): out = (x - x.mean()) / (x.std() + 1e-8), std unbiased with fp64 accumulation as
  * torch.std; out may alias x.  n == 1 gives NaN like torch.  scratch_dev as for xp_masked_whiten. */
 xp_status_t xp_standardize(const float *x, float *out, int64_t n, double *scratch_dev, void *stream);
+/* xp_standardize without caller-owned scratch.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  Same kernels, same fixed summation order, hence the same
+ * bits as xp_standardize.  The XP_WHITEN_SCRATCH doubles of scratch (4 160 bytes) live in a file-scope
+ * `static __device__` array inside the library — every GPU that loads the library holds it until exit —
+ * whose device address is looked up once per device (cudaGetSymbolAddress, with that device current) on
+ * the first call made on it.  The call allocates nothing: no cudaMalloc / cudaFree, no allocating
+ * library routine; it clears the one scratch word that must start at zero with a stream-ordered
+ * cudaMemsetAsync.  n > XP_STANDARDIZE_STATIC_MAX_N is refused with XP_ERR_INVALID.  ALL calls on a
+ * device share the one array: calls that overlap on the GPU (different streams, or different host
+ * threads / processes sharing a context) race — serialise them on one stream, or use xp_standardize.  */
+#define XP_STANDARDIZE_STATIC_MAX_N (1ll << 26) /* elements (256 MiB of fp32) */
+xp_status_t xp_standardize_static(const float *x, float *out, int64_t n, void *stream);
 
 /* ---- truncated-BPTT sequence preparation (RolloutBuffer.prepare_sequence_tensors) ------ */
 /* replaces the per-env Python walk of rollout_buffer.py:736-762 + _get_complete_sequences
