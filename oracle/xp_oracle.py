@@ -546,3 +546,65 @@ class MarbOracle:
                     per[a] = f32(ts)
             out.append(per)
         return tuple(out)
+
+
+# ---- array-based restatements for sizes the list trees cannot reach in seconds (C4: cap 2^24) --------
+# Same arithmetic as SegTree / PerOracle above, on numpy fp64 arrays in heap order.  fp64 add / subtract /
+# compare are single IEEE operations in numpy exactly as in CPython, so these are bit-identical to the
+# list-based walk; tests/test_oracle_golden.py pins them against SegTree.retrieve and PerOracle at 2^16
+# (and tests/test_oracle_vs_reference_cpu.py against the unmodified reference classes).
+def np_trees_from_leaves(leaves: np.ndarray, cap: int):
+    """(sum, min) heap arrays [2*cap] whose internal nodes are op(left, right) of their children — the
+    tree the reference's sequential root walks leave behind (segment_tree.py:89-95).
+    ``leaves`` [n <= cap] fp64; unfilled leaves are 0.0 / +inf (segment_tree.py:122,170)."""
+    s = np.zeros(2 * cap, dtype=np.float64)
+    m = np.full(2 * cap, np.inf, dtype=np.float64)
+    s[cap:cap + len(leaves)] = leaves
+    m[cap:cap + len(leaves)] = leaves
+    lvl = cap >> 1
+    while lvl >= 1:
+        s[lvl:2 * lvl] = s[2 * lvl:4 * lvl:2] + s[2 * lvl + 1:4 * lvl:2]
+        # builtin min(a, b) returns a on ties and b only when b < a (segment_tree.py:170)
+        a, b = m[2 * lvl:4 * lvl:2], m[2 * lvl + 1:4 * lvl:2]
+        m[lvl:2 * lvl] = np.where(b < a, b, a)
+        lvl >>= 1
+    return s, m
+
+
+def np_retrieve(sum_tree: np.ndarray, cap: int, upperbound: np.ndarray) -> np.ndarray:
+    """SumSegmentTree.retrieve (segment_tree.py:136-156) for a vector of upper bounds: strict '>' and one
+    rounded subtraction per level, every element walking its own path."""
+    ub = np.array(upperbound, dtype=np.float64, copy=True)
+    assert np.all(ub >= 0) and np.all(ub <= sum_tree[1] + 1e-5)
+    idx = np.ones(len(ub), dtype=np.int64)
+    while idx[0] < cap:  # all paths have the same length
+        left = 2 * idx
+        lv = sum_tree[left]
+        go_left = lv > ub
+        ub = np.where(go_left, ub, ub - lv)
+        idx = np.where(go_left, left, left + 1)
+    return idx - cap
+
+
+def np_sample_proportional(sum_tree: np.ndarray, cap: int, batch_size: int, u: np.ndarray) -> np.ndarray:
+    """_sample_proportional (replay_buffer.py:357-381): u[i] = the fp32 torch.rand(1).item() of stratum i."""
+    total = sum_tree[1]
+    segment = total / batch_size
+    i = np.arange(batch_size, dtype=np.float64)
+    a = segment * i
+    b = segment * (i + 1.0)
+    ub = np.asarray(u, dtype=np.float32).astype(np.float64) * (b - a) + a  # four separately rounded fp64 ops
+    return np_retrieve(sum_tree, cap, ub)
+
+
+def np_calculate_weights(sum_tree: np.ndarray, min_tree: np.ndarray, cap: int, indices, size: int,
+                         beta: float) -> np.ndarray:
+    """_calculate_weights (replay_buffer.py:383-409); the two ``**`` stay CPython float pows (libm)."""
+    total = float(sum_tree[1])
+    p_min = float(min_tree[1]) / total
+    max_weight = (p_min * size) ** -beta
+    leaves = sum_tree[cap + np.asarray(indices, dtype=np.int64)]
+    out = np.empty(len(leaves), dtype=np.float32)
+    for k, lv in enumerate(leaves.tolist()):
+        out[k] = ((lv / total) * size) ** -beta / max_weight
+    return out

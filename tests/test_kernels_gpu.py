@@ -517,6 +517,43 @@ def test_per_full_size_properties(xp, cuda_device):
     assert torch.equal(nodes, before) and int(per.tree.err.item()) == 0
 
 
+def test_per_c4_size_indices_and_weights_vs_array_oracle(xp, cuda_device):
+    """BASELINE.json config 4 (cap 2^24, 64 agents x 4 096 strata, L = 24) against an oracle OUTSIDE the
+    library: oracle.xp_oracle.np_* (numpy restatement of segment_tree.py:136-156 / replay_buffer.py:357-409,
+    pinned to the list oracle at 2^16 and to the unmodified reference at 2^14 on the CPU).  Every node of
+    both device trees, every sampled index and every IS weight — bit-exact.  Leaves go in through the
+    library's own update path (priority ** alpha on the device); the host computes them with CPython's pow."""
+    cap, B, P, alpha, beta = 1 << 24, 4096, 64, 0.6, 0.4
+    rng = np.random.default_rng(24)
+    per = DevPer(xp, cuda_device, cap, alpha)
+    per.add(cap)
+    pri = (np.abs(rng.standard_normal(cap)) + 1e-3).astype(np.float32)
+    idx_all = torch.arange(cap, device=cuda_device)
+    xp.per_update(per.tree.t, per.state, idx_all, dev(pri, cuda_device, torch.float32), cap, alpha, per.tree.err)
+    # a second, sparse, duplicate-laden update of the C4 batch size on top (schedule S)
+    n = P * B
+    up_i = rng.integers(0, cap, n)
+    up_i[n // 2:] = up_i[: n - n // 2]
+    up_p = (np.abs(rng.standard_normal(n)) + 1e-6).astype(np.float32)
+    xp.per_update(per.tree.t, per.state, dev(up_i, cuda_device, torch.int64), dev(up_p, cuda_device, torch.float32),
+                  cap, alpha, per.tree.err)
+    pri[up_i] = up_p  # numpy keeps the LAST duplicate: sequential last-writer-wins (replay_buffer.py:423-428)
+    leaves = np.fromiter((max(float(p), 1e-5) ** alpha for p in pri.tolist()), dtype=np.float64, count=cap)
+    s, m = xo.np_trees_from_leaves(leaves, cap)
+    ds, dm = per.tree.arrays()
+    assert np.array_equal(ds[1:], s[1:]) and np.array_equal(dm[1:], m[1:])
+    assert int(per.tree.err.item()) == 0
+    u = rng.random(n).astype(np.float32)
+    u[::4099] = 0.0
+    got_i, got_w = per.sample(u, beta, P)
+    for p in range(P):
+        want = xo.np_sample_proportional(s, cap, B, u[p * B:(p + 1) * B])
+        assert np.array_equal(got_i[p * B:(p + 1) * B], want), p
+    for p in (0, 31, 63):  # weights: CPython pow per element on the host, three agents
+        sl = slice(p * B, (p + 1) * B)
+        assert np.array_equal(got_w[sl], xo.np_calculate_weights(s, m, cap, got_i[sl], cap, beta)), p
+
+
 def test_pow_is_cpython_pow(xp, cuda_device):
     rng = np.random.default_rng(0)
     x = np.concatenate([np.maximum(np.abs(rng.standard_normal(200000)), 1e-5),

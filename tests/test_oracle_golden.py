@@ -145,6 +145,50 @@ def test_per_oracle_matches_reference(seed):
     assert np.array_equal(w, g["weights"])
 
 
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_array_oracle_matches_reference_golden(seed):
+    """The numpy restatements used at C4 size (np_trees_from_leaves / np_sample_proportional /
+    np_calculate_weights) against the fixtures written by the unmodified reference."""
+    g = load_golden(f"per_s{seed}")
+    cap = len(g["sum_tree_after_update"]) // 2
+    s_leaves, m_leaves = g["sum_tree_after_update"][cap:], g["min_tree_after_update"][cap:]
+    filled = ~np.isinf(m_leaves)  # leaves the reference never set: 0.0 in the sum tree, +inf in the min tree
+    n = int(filled.sum())
+    assert filled[:n].all() and not filled[n:].any(), "filled leaves are a prefix in the golden scenarios"
+    s, m = xo.np_trees_from_leaves(s_leaves[:n], cap)
+    assert np.array_equal(s[1:], g["sum_tree_after_update"][1:])
+    assert np.array_equal(m[1:], g["min_tree_after_update"][1:])
+    idx = xo.np_sample_proportional(s, cap, len(g["u"]), g["u"])
+    assert np.array_equal(idx, g["sample_idx"])
+    w = xo.np_calculate_weights(s, m, cap, idx, int(g["size"]), float(g["beta"]))
+    assert np.array_equal(w, g["weights"])
+
+
+def test_array_oracle_matches_list_oracle_at_2p16():
+    """Pin of the vectorised walk: every index and weight equal to SegTree.retrieve / PerOracle on a
+    65 536-leaf tree, including the stratum edges u = 0 and u -> 1."""
+    cap, B = 1 << 16, 4096
+    rng = np.random.default_rng(3)
+    leaves = (np.abs(rng.standard_normal(cap)) + 1e-3) ** 0.6
+    per = xo.PerOracle(cap, 0.6)
+    per.size = cap
+    per.sum_tree.tree[cap:] = leaves.tolist()
+    per.min_tree.tree[cap:] = leaves.tolist()
+    per.sum_tree.rebuild_from_leaves()
+    per.min_tree.rebuild_from_leaves()
+    s, m = xo.np_trees_from_leaves(leaves, cap)
+    assert np.array_equal(s[1:], np.array(per.sum_tree.tree)[1:]) and np.array_equal(m[1:], np.array(per.min_tree.tree)[1:])
+    u = rng.random(B).astype(np.float32)
+    u[::64] = 0.0
+    u[1::64] = np.float32(1.0) - np.float32(2.0**-24)
+    want = per.sample_proportional(B, u)
+    got = xo.np_sample_proportional(s, cap, B, u)
+    assert np.array_equal(got, want)
+    assert np.array_equal(xo.np_calculate_weights(s, m, cap, got, cap, 0.4), per.calculate_weights(want, 0.4))
+    ub = np.concatenate([rng.random(2000) * s[1], [0.0, s[1]]])
+    assert np.array_equal(xo.np_retrieve(s, cap, ub), np.array([per.sum_tree.retrieve(float(x)) for x in ub]))
+
+
 def test_bulk_rebuild_equals_sequential_sets():
     rng = np.random.default_rng(0)
     a, b = xo.SegTree(64, "sum"), xo.SegTree(64, "sum")

@@ -63,6 +63,29 @@ def test_bptt_live(seed, seq_type):
     assert np.array_equal(r["pad_mask"], mask) and np.array_equal(r["padded"]["x"], padded)
 
 
+def test_array_oracle_vs_unmodified_reference_live():
+    """The numpy restatement that serves as the C4-size oracle (tests/test_kernels_gpu.py) against the
+    UNMODIFIED reference classes on a 2^14-leaf tree filled through the reference's own
+    _update_priority calls: tree arrays, sampled indices (same torch seed) and IS weights."""
+    ref = ref_loader.load_reference()
+    cap, B = 1 << 14, 512
+    rng = np.random.default_rng(17)
+    buf = ref.PrioritizedReplayBuffer(max_size=cap, alpha=0.6)
+    buf._size = cap
+    pri = (np.abs(rng.standard_normal(cap)) + 1e-3).astype(np.float32)
+    for i, p in enumerate(pri):
+        buf._update_priority(i, float(p))
+    s, m = xo.np_trees_from_leaves(np.array([float(p) ** 0.6 for p in pri]), cap)
+    assert np.array_equal(s[1:], np.array(buf.sum_tree.tree)[1:]) and np.array_equal(m[1:], np.array(buf.min_tree.tree)[1:])
+    torch.manual_seed(5)
+    u = torch.rand(B).numpy()
+    torch.manual_seed(5)
+    idx = buf._sample_proportional(B)
+    got = xo.np_sample_proportional(s, cap, B, u)
+    assert np.array_equal(got, idx.numpy())
+    assert np.array_equal(xo.np_calculate_weights(s, m, cap, got, cap, 0.4), buf._calculate_weights(idx, 0.4).numpy())
+
+
 @pytest.mark.parametrize("seed", range(3))
 def test_per_trees_sampling_weights_live(seed):
     ref = ref_loader.load_reference()
