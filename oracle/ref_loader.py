@@ -1,9 +1,10 @@
 """TEST INFRASTRUCTURE — loads the UNMODIFIED reference (AgileRL) hot-path modules by file path.
 
-Only usable where /root/reference exists (this build container); it is used by
-``oracle/make_golden.py`` to generate the committed fixtures under ``tests/golden/`` and by
-``tests/test_oracle_vs_reference.py`` (skipped when the reference tree is absent, e.g. on the GPU
-box).  Nothing in the product package imports this file.
+Reads /root/reference where it exists (the build container) and otherwise the unmodified copy that
+``oracle/stage_reference.py`` staged under git-ignored ``oracle/_ref`` (sha256-checked), which travels
+to the GPU box.  Used by ``oracle/make_golden.py`` to generate the committed fixtures under
+``tests/golden/``, by ``tests/test_oracle_vs_reference_cpu.py``, and by ``bench.py``'s reference arm /
+``cpu_baseline`` legs.  Nothing in the product package imports this file.
 
 ``import agilerl`` itself fails here (tensordict / gymnasium / accelerate are not installed), so:
   * agilerl/components/segment_tree.py is stdlib-only        -> loaded as is;
@@ -24,7 +25,20 @@ import types
 import numpy as np
 import torch
 
-REF_ROOT = os.environ.get("AGILERL_REFERENCE", "/root/reference")
+def _resolve_root() -> tuple[str, str]:
+    """The reference tree itself where it exists (build container), else the byte-for-byte staged copy
+    under oracle/_ref (oracle/stage_reference.py; sha256-checked) — e.g. on the GPU box."""
+    live = os.environ.get("AGILERL_REFERENCE", "/root/reference")
+    if os.path.isfile(os.path.join(live, "agilerl", "components", "replay_buffer.py")):
+        return live, "live"
+    from . import stage_reference as sr
+
+    if sr.verify():
+        return sr.STAGE_ROOT, "staged"
+    return live, "absent"
+
+
+REF_ROOT, REF_SOURCE = _resolve_root()
 REF_PKG = os.path.join(REF_ROOT, "agilerl")
 
 
