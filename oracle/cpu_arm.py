@@ -110,3 +110,270 @@ def atari_transition(td_cls, n: int, g: torch.Generator):
         "reward": torch.randn(n, generator=g),
         "next_obs": torch.randint(0, 256, (n, *ATARI), dtype=torch.uint8, generator=g),
         "done": (torch.rand(n, generator=g) < 0.01).float()}, batch_size=[n])
+
+
+# ---- C2: Rainbow PER + 3-step replay (BASELINE.json configs[1]) -----------------------------------------
+class C2Reference:
+    """The reference's ``PrioritizedReplayBuffer`` + ``MultiStepReplayBuffer`` pair at the config's
+    capacity, driven as training/train_off_policy.py:363-376 drives it: per agent
+    ``memory.sample(B, beta)`` -> ``n_step_memory.sample_from_indices(experiences["idxs"])`` ->
+    ``memory.update_priorities(idxs, priorities)`` with ``idxs`` the (B,1) tensor of the batch and
+    ``priorities`` an fp32 ndarray (algorithms/dqn_rainbow.py:487-488)."""
+
+    def __init__(self, cap=1_000_000, B=256, n_step=3, gamma=0.99, alpha=0.6, beta=0.4, num_envs=16,
+                 fill_seconds=30.0, ram_fraction=0.45, seed=0):
+        self.cap, self.B, self.beta = cap, B, beta
+        self.kind = kind()
+        rng = np.random.default_rng(seed)
+        leaves = (np.abs(rng.standard_normal(cap)) + 1e-3) ** alpha
+        self.prio = (np.abs(rng.standard_normal(B)) + 1e-6).astype(np.float32)
+        g = torch.Generator().manual_seed(seed)
+        t0 = time.perf_counter()
+        if self.kind == "reference":
+            ref = ref_loader.load_reference()
+            self.per = ref.PrioritizedReplayBuffer(max_size=cap, alpha=alpha)
+            self.nstep = ref.MultiStepReplayBuffer(max_size=cap, n_step=n_step, gamma=gamma)
+            # real env steps through n-step -> PER (train_off_policy.py:341-345): the reference's own
+            # _init allocates both storages (zeros_like of the expanded first row, replay_buffer.py:60-70)
+            for _ in range(n_step + 2):
+                one = self.nstep.add(atari_transition(ref.TensorDict, num_envs, g))
+                if one is not None:
+                    self.per.add(one)
+            big = [buf.storage[k] for buf in (self.per, self.nstep) for k in ("obs", "next_obs")]
+            self.filled = fill_rows(big, fill_seconds, ram_fraction * mem_available_bytes(), seed)
+            for buf in (self.per, self.nstep):
+                buf._size, buf._cursor = cap, 0
+                for k in ("action", "reward", "done"):
+                    buf.storage[k][:] = torch.randn(buf.storage[k].shape, generator=g)
+            self.per.tree_ptr = 0
+            fill_tree_pair(self.per.sum_tree, self.per.min_tree, leaves)
+            self.storage_rows = cap
+        else:  # oracle port (no copy of the reference on this machine)
+            self.per = xo.PerOracle(cap, alpha)
+            self.per.size = cap
+            cap2 = self.per.sum_tree.capacity
+            self.per.sum_tree.tree[cap2:cap2 + cap] = leaves.tolist()
+            self.per.min_tree.tree[cap2:cap2 + cap] = leaves.tolist()
+            self.per.sum_tree.rebuild_from_leaves()
+            self.per.min_tree.rebuild_from_leaves()
+            rows = 4096
+            self.storage_rows = self.filled = rows
+            self.tables = [{"obs": rng.integers(0, 256, (rows, *ATARI), dtype=np.uint8),
+                            "action": rng.standard_normal((rows, 1)).astype(np.float32),
+                            "reward": rng.standard_normal((rows, 1)).astype(np.float32),
+                            "next_obs": rng.integers(0, 256, (rows, *ATARI), dtype=np.uint8),
+                            "done": rng.standard_normal((rows, 1)).astype(np.float32)} for _ in range(2)]
+            self.gen = torch.Generator().manual_seed(seed)
+        self.setup_s = time.perf_counter() - t0
+
+    def agent_step(self):
+        """One agent's learn-step buffer traffic; returns the number of sampled transitions."""
+        if self.kind == "reference":
+            experiences = self.per.sample(self.B, self.beta)
+            n_step_experiences = self.nstep.sample_from_indices(experiences["idxs"])  # noqa: F841
+            self.per.update_priorities(experiences["idxs"], self.prio)
+        else:
+            u = torch.rand(self.B, generator=self.gen).numpy()
+            idx = self.per.sample_proportional(self.B, u)
+            xo.gather(self.tables[0], idx % self.storage_rows)
+            self.per.calculate_weights(idx, self.beta)
+            xo.gather(self.tables[1], idx % self.storage_rows)
+            self.per.update_priorities(idx, self.prio)
+        return self.B
+
+    def describe(self) -> str:
+        if self.kind == "reference":
+            return (f"unmodified reference classes ({ref_loader.REF_SOURCE} copy), 1 process, agents sequential on ONE "
+                    f"shared memory; tree capacity 2^{int(np.log2(self.per.sum_tree.capacity))} filled by direct leaf "
+                    f"assignment; storage {self.cap} rows per buffer allocated by the reference's own _init, rows "
+                    f"[0,{self.filled}) filled with random bytes (rest untouched zero pages); setup {self.setup_s:.0f} s untimed")
+        return (f"ORACLE PORT (no reference copy on this machine): list trees at full capacity, numpy row storage "
+                f"bounded to {self.storage_rows} rows (idx mod rows)")
+
+
+def time_c2(seconds: float, max_agent_steps: int = 1 << 30, warmup_agent_steps: int = 2, **kw) -> dict:
+    """sampled transitions / s of the C2 learn-step traffic on this host, one process."""
+    w = C2Reference(**kw)
+    torch.manual_seed(1234)
+    for _ in range(warmup_agent_steps):
+        w.agent_step()
+    t0 = time.perf_counter()
+    n = 0
+    while n < max_agent_steps:
+        w.agent_step()
+        n += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    wall = time.perf_counter() - t0
+    return {"value": n * w.B / wall, "unit": "transitions/s", "cores": 1, "kind": w.kind,
+            "sample": f"{n} agent-steps of {w.B} samples (sample + n-step sample_from_indices + update_priorities) "
+                      f"in {wall:.1f} s; " + w.describe(),
+            "agent_steps": n, "wall_s": round(wall, 2), **host_info()}
+
+
+def _c2_worker(args):
+    seconds, max_steps, seed, kw = args
+    torch.set_num_threads(1)
+    r = time_c2(seconds, max_steps, seed=seed, **kw)
+    return r["agent_steps"], r["wall_s"], r["kind"]
+
+
+def time_c2_population_parallel(seconds: float, workers: int, **kw) -> dict:
+    """Upper bound the reference does NOT implement: ``workers`` independent processes, one agent and one
+    PRIVATE memory each (the reference shares one memory and runs the agents one after the other).
+    Reported beside the one-process headline, never as it."""
+    import multiprocessing as mp
+
+    kw = dict(kw)
+    kw.setdefault("fill_seconds", 6.0)
+    kw.setdefault("ram_fraction", 0.3 / workers)
+    with mp.get_context("fork").Pool(workers) as pool:
+        res = pool.map(_c2_worker, [(seconds, 1 << 30, s, kw) for s in range(workers)])
+    steps, wall = sum(r[0] for r in res), max(r[1] for r in res)
+    return {"value": steps * kw.get("B", 256) / wall, "unit": "transitions/s", "cores": workers, "kind": res[0][2],
+            "sample": f"{workers} independent single-thread processes x 1 agent with a private memory each, "
+                      f"{steps} agent-steps in {wall:.1f} s (not the reference's execution model: an upper bound)"}
+
+
+# ---- C3: PPO RolloutBuffer GAE, 1024 envs x 128 steps x population 16 --------------------------------------
+def time_c3(seconds: float, T=128, N=1024, P=16, gamma=0.99, lam=0.95) -> dict:
+    """(t, env, agent) elements / s of RolloutBuffer.compute_returns_and_advantages (rollout_buffer.py:413-481,
+    the method's own source, AST-extracted), called per agent as rollouts/on_policy.py:198-201 does."""
+    rng = np.random.default_rng(3)
+    data = [(rng.standard_normal((T, N)).astype(np.float32), rng.standard_normal((T, N)).astype(np.float32),
+             rng.random((T, N)) < 0.02, rng.standard_normal(N).astype(np.float32), rng.random(N) < 0.02)
+            for _ in range(P)]
+    is_ref = ref_loader.available()
+    fn = (lambda r, v, d, lv, ld: ref_loader.reference_gae(r, v, d, lv, ld, gamma, lam)) if is_ref else \
+         (lambda r, v, d, lv, ld: xo.gae(r, v, d, lv, ld, gamma, lam))
+    fn(*data[0])
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        fn(*data[n % P])
+        n += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    wall = time.perf_counter() - t0
+    return {"value": n * T * N / wall, "unit": "steps/s", "cores": 1, "kind": "reference" if is_ref else "port",
+            "sample": f"{n} per-agent calls of compute_returns_and_advantages ([{T},{N}]) in {wall:.1f} s, agents "
+                      f"sequential, numpy single thread ({1e3 * wall / n:.1f} ms per agent)"}
+
+
+# ---- C4: PER sum-tree at capacity 2^24, batch 4096 per agent -------------------------------------------------
+def time_c4(seconds: float, cap=1 << 24, B=4096, alpha=0.6, beta=0.4) -> dict:
+    """sampled transitions / s of the TREE operations of one agent's learn step on the unmodified
+    PrioritizedReplayBuffer: _sample_proportional + _calculate_weights + update_priorities (no storage)."""
+    rng = np.random.default_rng(4)
+    leaves = (np.abs(rng.standard_normal(cap)) + 1e-3) ** alpha
+    prio = (np.abs(rng.standard_normal(B)) + 1e-6).astype(np.float32)
+    t0 = time.perf_counter()
+    is_ref = ref_loader.available()
+    if is_ref:
+        per = ref_loader.load_reference().PrioritizedReplayBuffer(max_size=cap, alpha=alpha)
+        per._size = cap
+        fill_tree_pair(per.sum_tree, per.min_tree, leaves)
+
+        def step():
+            idx = per._sample_proportional(B)
+            per._calculate_weights(idx, beta)
+            per.update_priorities(idx, prio)
+    else:
+        per = xo.PerOracle(cap, alpha)
+        per.size = cap
+        s, m = xo.np_trees_from_leaves(leaves, cap)
+        per.sum_tree.tree[:] = s.tolist()
+        per.min_tree.tree[:] = m.tolist()
+        g = torch.Generator().manual_seed(4)
+
+        def step():
+            idx = per.sample_proportional(B, torch.rand(B, generator=g).numpy())
+            per.calculate_weights(idx, beta)
+            per.update_priorities(idx, prio)
+    setup = time.perf_counter() - t0
+    torch.manual_seed(4)
+    step()
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        step()
+        n += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    wall = time.perf_counter() - t0
+    return {"value": n * B / wall, "unit": "transitions/s", "cores": 1, "kind": "reference" if is_ref else "port",
+            "sample": f"{n} agent-steps of {B} (tree ops only: _sample_proportional + _calculate_weights + "
+                      f"update_priorities) in {wall:.1f} s on 2^{int(np.log2(cap))}-leaf Python-list trees filled by direct leaf "
+                      f"assignment (setup {setup:.0f} s untimed); 1 process"}
+
+
+# ---- uniform replay: C5 (TD3, 10 M Humanoid rows, batch 1024) and C1 (DQN CartPole, 100 k rows, batch 64) ------
+def _uniform_buffer(cap, row, num_envs, fill_seconds, ram_fraction, seed):
+    """The reference's ReplayBuffer at ``cap`` rows; ``row(n, g)`` makes n transitions.  A few real adds let
+    the reference's own _init allocate the storage; the rest is bulk-filled (untimed)."""
+    g = torch.Generator().manual_seed(seed)
+    ref = ref_loader.load_reference()
+    buf = ref.ReplayBuffer(max_size=cap)
+    for _ in range(3):
+        buf.add(ref.TensorDict(row(num_envs, g), batch_size=[num_envs]))
+    keys = list(buf.storage.keys())
+    filled = fill_rows([buf.storage[k] for k in keys], fill_seconds, ram_fraction * mem_available_bytes(), seed)
+    buf._size, buf._cursor = cap, 0
+    return buf, filled
+
+
+def time_uniform(seconds: float, cap: int, B: int, row, label: str, num_envs=16, fill_seconds=15.0,
+                 ram_fraction=0.4, seed=5) -> dict:
+    """sampled transitions / s of ReplayBuffer.sample(B) (replay_buffer.py:114-131: an O(size)
+    torch.randperm per call + storage[indices]), one agent after the other in one process."""
+    t0 = time.perf_counter()
+    is_ref = ref_loader.available()
+    if is_ref:
+        buf, filled = _uniform_buffer(cap, row, num_envs, fill_seconds, ram_fraction, seed)
+
+        def step():
+            buf.sample(B)
+    else:
+        g = torch.Generator().manual_seed(seed)
+        rows = min(cap, 65536)
+        table = {k: v.numpy() for k, v in row(rows, g).items()}
+        filled = rows
+
+        def step():
+            idx = torch.randperm(cap)[:B].numpy()
+            xo.gather(table, idx % rows)
+    setup = time.perf_counter() - t0
+    torch.manual_seed(seed)
+    step()
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        step()
+        n += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    wall = time.perf_counter() - t0
+    return {"value": n * B / wall, "unit": "transitions/s", "cores": 1, "kind": "reference" if is_ref else "port",
+            "sample": f"{label}: {n} calls of ReplayBuffer.sample({B}) in {wall:.1f} s ({1e3 * wall / n:.2f} ms per call, "
+                      f"torch.randperm({cap}) inside every call); {cap} rows, [0,{filled}) filled with random bytes; "
+                      f"1 process, torch threads {torch.get_num_threads()}; setup {setup:.0f} s untimed"}
+
+
+def humanoid_row(n, g):
+    return {"obs": torch.randn(n, 376, generator=g), "action": torch.rand(n, 17, generator=g) * 0.8 - 0.4,
+            "reward": torch.randn(n, generator=g), "next_obs": torch.randn(n, 376, generator=g),
+            "done": (torch.rand(n, generator=g) < 0.01).float()}
+
+
+def cartpole_row(n, g):
+    return {"obs": torch.randn(n, 4, generator=g), "action": torch.randint(0, 2, (n,), generator=g).float(),
+            "reward": torch.ones(n), "next_obs": torch.randn(n, 4, generator=g),
+            "done": (torch.rand(n, generator=g) < 0.02).float()}
+
+
+def time_c5(seconds: float, cap=10_000_000, B=1024) -> dict:
+    return time_uniform(seconds, cap, B, humanoid_row, "C5 TD3 uniform replay")
+
+
+def time_c1(seconds: float, cap=100_000, B=64) -> dict:
+    return time_uniform(seconds, cap, B, cartpole_row, "C1 DQN CartPole uniform replay", fill_seconds=5.0)
