@@ -18,11 +18,13 @@ transition.  The metric is sampled transitions per second.
           priorities arrive as host arrays (dqn_rainbow.py:487), H2D inside the timed region,
           indices + IS weights read back D2H every step.
   roofline     : the dominant kernel (the row gather), algorithmic bytes / CUDA-event duration.
-  cpu_baseline : the oracle port of the reference's CPU path, timed on this host (N=1 only).
+  cpu_baseline : the unmodified reference classes, timed on this host (N=1 only; oracle/cpu_arm.py).
   also         : device-timed numbers + rooflines for C3 (GAE) and C4 (PER tree 2^24), N=1 only.
 
-`--impl reference` times the reference's CPU implementation (oracle port — the reference is pure
-Python and cannot be installed on this image) on the host cores, same metric/config.
+`--impl reference` times the reference's own CPU implementation — the UNMODIFIED reference classes,
+loaded by path (oracle/ref_loader.py) from /root/reference or from the byte-identical copy build()
+staged under oracle/_ref — on the host, one process with the agents sequential on one shared memory
+(the reference's execution model), same metric/config.
 
 Multi-GPU (torchrun, one rank per GPU): weak scaling — every rank owns `population` agents; the
 shared replay is replicated, so the (idx, priority) pairs of every rank are all-gathered (NCCL)
@@ -461,6 +463,42 @@ def bench_gae(dev, sets=8, P=None, reps=40):
             "l2": f"rotating {sets} buffer sets ({sets * steps * 17 / 1e6:.0f} MB)"}
 
 
+def bench_gae_per_agent(dev, sets=8, reps=20):
+    """C3 as the DROP-IN issues it: rollouts/on_policy.py:198-201 calls compute_returns_and_advantages per
+    agent, i.e. 16 launches with P = 1 (32 CTAs each) — timed back to back over the agents of a slab, and one
+    such launch alone (rotating 64 single-agent buffer sets, > L2 in total)."""
+    import torch
+
+    from agilerl_b200 import xp
+
+    c = C3
+    P, T, N = c["P"], c["T"], c["N"]
+    gd = torch.Generator(device=dev).manual_seed(6)
+
+    def mk_set(p_):
+        r = torch.randn(p_, T, N, device=dev, generator=gd)
+        v = torch.randn(p_, T, N, device=dev, generator=gd)
+        d = torch.rand(p_, T, N, device=dev, generator=gd) < 0.02
+        lv = torch.randn(p_, N, device=dev, generator=gd).double()
+        ld = (torch.rand(p_, N, device=dev, generator=gd) < 0.02).double()
+        return r, v, d, lv, ld, torch.empty_like(r), torch.empty_like(r)
+
+    def one(b, p_):
+        r, v, d, lv, ld, a, g = b
+        return lambda: xp.gae(r[p_], v[p_], d[p_], lv[p_], ld[p_], a[p_], g[p_], T, N, 1, T * N, c["gamma"], c["lam"])
+
+    slabs = [mk_set(P) for _ in range(sets)]
+    us16 = graph_time_us([one(b, p_) for b in slabs for p_ in range(P)], reps) * P
+    singles = [mk_set(1) for _ in range(64)]
+    us1 = graph_time_us([one(b, 0) for b in singles], reps)
+    steps = P * T * N
+    return {"workload": c["name"] + "_per_agent_launches", "metric": "gae_steps_per_s",
+            "value": steps / (us16 * 1e-6), "unit": "steps/s", "us_16_launches_of_P1": us16, "us_one_P1_launch": us1,
+            "algorithmic_bytes": steps * 17, "roofline": roofline(steps * 17, us16),
+            "roofline_one_P1_launch": roofline(T * N * 17, us1),
+            "l2": f"rotating {sets} slabs of 16 agents / 64 single-agent sets (> L2 in total)"}
+
+
 def bench_per_tree(dev, reps=10):
     """C4: PER tree cap 2^24, 64 agents x 4096 samples per launch; sample(+weights) and update."""
     import torch
@@ -500,10 +538,24 @@ def bench_per_tree(dev, reps=10):
         seq += [sample(i), update(i)]
     us_b = 2 * graph_time_us(seq, reps)
     assert int(err.item()) == 0
+    # skewed batches: fresh transitions carry max_priority and are drawn together
+    # (replay_buffer.py:306-309) — a share of the batch falls into the most recently written leaves
+    skew = {}
+    for share, hot in ((0.1, 4096), (0.3, 4096), (0.3, 65536)):
+        sk = []
+        for i in range(R):
+            k = int(n * share)
+            ix = torch.randint(0, cap, (n,), device=dev, generator=gd)
+            ix[:k] = cap - hot + torch.randint(0, hot, (k,), device=dev, generator=gd)
+            sk.append(ix[torch.randperm(n, device=dev, generator=gd)])
+        us = graph_time_us([(lambda i=i: xp.per_update(t, state, sk[i], pr[i], cap, c["alpha"], err)) for i in range(R)], reps)
+        skew[f"{int(share * 100)}pct_in_last_{hot}_leaves"] = round(us, 2)
+    assert int(err.item()) == 0
     bps = per_bytes_per_sample(c["L"])
     tot = sum(bps.values())
     return {"workload": c["name"], "metric": METRIC, "value": n / (us_b * 1e-6), "unit": UNIT,
             "us_sample": us_s, "us_update": us_u, "us_sample_plus_update": us_b,
+            "us_update_skewed": skew, "skew_worst_over_uniform": round(max(skew.values()) / us_u, 2),
             "algorithmic_bytes_per_sample": tot, "algorithmic_bytes": n * tot,
             "l2": "tree 805 MB > L2; top levels L2-resident by design"}
 
@@ -558,6 +610,138 @@ def bench_uniform(dev, reps=10):
             "l2": "random rows of a 30.8 GB storage; 4 rotating output sets of 101 MB"}
 
 
+def bench_insert(dev, reps=10):
+    """Insert side (SURVEY.md 8d metric 3; train_off_policy.py:339-345): (a) the per-step path through the
+    classes — for each of 8 agents MultiStepReplayBuffer.add(16 env rows) -> PrioritizedReplayBuffer.add —
+    rows/s with device-resident transitions (host-driven: ~10 small launches per agent); (b) the ring-insert
+    kernel on a bulk batch (offline ingestion, train_offline.py:190: ReplayBuffer.add of 16 384 Atari rows),
+    roofline 2R bytes per row."""
+    import torch
+
+    from agilerl_b200 import xp
+    from agilerl_b200.components import MultiStepReplayBuffer, PrioritizedReplayBuffer, TensorBatch
+
+    c = C2
+    cap, E, P = 65536, c["num_envs"], c["P"]
+    per = PrioritizedReplayBuffer(cap, alpha=c["alpha"], device=dev)
+    nst = MultiStepReplayBuffer(cap, n_step=c["n_step"], gamma=c["gamma"], device=dev)
+    gd = torch.Generator(device=dev).manual_seed(8)
+
+    def rows(n):
+        return {"obs": torch.randint(0, 256, (n, *ATARI), dtype=torch.uint8, device=dev, generator=gd),
+                "action": torch.randint(0, 18, (n,), device=dev, generator=gd).float(),
+                "reward": torch.randn(n, device=dev, generator=gd),
+                "next_obs": torch.randint(0, 256, (n, *ATARI), dtype=torch.uint8, device=dev, generator=gd),
+                "done": (torch.rand(n, device=dev, generator=gd) < 0.01).float()}
+
+    trs = [rows(E) for _ in range(8)]
+
+    def step(i):
+        for a in range(P):
+            one = nst.add(TensorBatch(dict(trs[(i + a) % 8]), batch_size=[E]))
+            if one is not None:
+                per.add(one)
+
+    for i in range(5):
+        step(i)
+    torch.cuda.synchronize()
+    K = 50
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    a.record()
+    for i in range(K):
+        step(i)
+    b.record()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    api_ms = max(a.elapsed_time(b), wall * 1e3) / K
+    # (b) bulk ring insert, kernel-timed, rotating two source batches and a moving cursor
+    nb = 16384
+    big = torch.empty(4 * nb, *ATARI, dtype=torch.uint8, device=dev)
+    small = torch.empty(4 * nb, 1, dtype=torch.float32, device=dev)
+    src = [rows(nb) for _ in range(2)]
+
+    def ins(i):
+        pairs = [(src[i % 2]["obs"], big), (src[i % 2]["reward"].view(nb, 1), small)]
+        return lambda: xp.ring_insert(pairs, nb, (i * nb + 1234) % (4 * nb), 4 * nb)
+
+    us = graph_time_us([ins(i) for i in range(4)], reps)
+    alg = nb * 2 * (84 * 84 * 4 + 4)
+    return {"workload": "c2_insert_nstep3_to_per_16envs_x_8agents", "metric": "inserted_rows_per_s",
+            "value": P * E / (api_ms * 1e-3), "unit": "rows/s", "ms_per_population_step": api_ms,
+            "api": "per agent: MultiStepReplayBuffer.add -> PrioritizedReplayBuffer.add (device-resident rows)",
+            "bulk_ring_insert": {"rows": nb, "us_per_launch": us, "algorithmic_bytes": alg,
+                                 "rows_per_s": nb / (us * 1e-6), "roofline": roofline(alg, us)},
+            "l2": "bulk: 2 x 462 MB source batches into a 1.8 GB ring (> L2)"}
+
+
+def bench_c1(dev):
+    """C1 (BASELINE.json configs[0], the reference's CPU-runnable case): DQN CartPole uniform replay,
+    capacity 100 000, batch 64, population 4 — through the public API, one ReplayBuffer.sample per agent
+    (exact torch.randperm stream, replay_buffer.py:125), batch read back to the host every step."""
+    import torch
+
+    from agilerl_b200.components import ReplayBuffer, TensorBatch
+
+    cap, B, P = 100_000, 64, 4
+    buf = ReplayBuffer(cap, device=dev)
+    g = torch.Generator().manual_seed(1)
+    n = 10_000
+    for _ in range(cap // n):
+        buf.add(TensorBatch({"obs": torch.randn(n, 4, generator=g), "action": torch.randint(0, 2, (n,), generator=g).float(),
+                             "reward": torch.ones(n), "next_obs": torch.randn(n, 4, generator=g),
+                             "done": (torch.rand(n, generator=g) < 0.02).float()}, batch_size=[n]))
+    torch.manual_seed(0)
+    for _ in range(10):
+        buf.sample(B)
+    torch.cuda.synchronize()
+    K = 300
+    t0 = time.perf_counter()
+    for _ in range(K):
+        for _a in range(P):
+            s_ = buf.sample(B)
+        s_["reward"].cpu()
+    wall = time.perf_counter() - t0
+    return {"workload": "c1_dqn_cartpole_uniform_cap100k_b64_pop4", "metric": "uniform_sampled_transitions_per_s",
+            "value": K * P * B / wall, "unit": UNIT, "ms_per_population_step": 1e3 * wall / K,
+            "api": "ReplayBuffer.sample(64) per agent, host-timed incl. D2H of the last batch's rewards; "
+                   "exact torch generator advance (size-1 words per call)",
+            "note": "latency-bound: 4 x 64 rows of 44 B; the CPU-reference config, GPU number for completeness"}
+
+
+def also_single_gpu(dev, with_cpu=True):
+    """C3 / C4 / C5 (+ C1, insert side) device-timed with rooflines, each beside the reference's CPU number."""
+    import torch
+
+    def cpu(entry, fn, seconds):
+        if with_cpu:
+            entry["cpu_baseline"] = cpu_leg(fn, seconds)
+        return entry
+
+    g = bench_gae(dev)
+    g["roofline"] = roofline(g["algorithmic_bytes"], g["us_per_launch"], kernel="gae_", capture="ncu_gae.txt")
+    cpu(g, "time_c3", 4.0)
+    ga = bench_gae_per_agent(dev)
+    g16 = bench_gae(dev, sets=2, P=C3["P"] * 16, reps=20)
+    g16["roofline"] = roofline(g16["algorithmic_bytes"], g16["us_per_launch"])
+    p = bench_per_tree(dev)
+    p["roofline"] = roofline(p["algorithmic_bytes"], p["us_sample_plus_update"])
+    p["roofline_sample"] = roofline(C4["P"] * C4["B"] * (8 * C4["L"] + 24), p["us_sample"],
+                                    kernel="per_sample_kernel", capture="ncu_sample.txt")
+    p["roofline_update"] = roofline(C4["P"] * C4["B"] * per_bytes_per_sample(C4["L"])["update"], p["us_update"],
+                                    kernel="set_wbucket_kernel", capture="ncu_update.txt")
+    cpu(p, "time_c4", 6.0)
+    torch.cuda.empty_cache()
+    c5 = bench_uniform(dev)
+    c5["roofline"] = roofline(c5["algorithmic_bytes"], c5["us_sample"], kernel="move_kernel", capture="ncu_gather_c5.txt")
+    cpu(c5, "time_c5", 6.0)
+    torch.cuda.empty_cache()
+    ins = bench_insert(dev)
+    torch.cuda.empty_cache()
+    c1 = cpu(bench_c1(dev), "time_c1", 3.0)
+    return [g, ga, g16, p, c5, ins, c1]
+
+
 def ncu_traffic(kernel_substr: str, capture: str = "ncu_*.txt"):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of a kernel, from the newest
     committed ``profiles/r*_ncu_*.txt`` summary that contains it (tools/ncu_summary.py output of an
@@ -588,11 +772,34 @@ def ncu_traffic(kernel_substr: str, capture: str = "ncu_*.txt"):
     return None
 
 
-def roofline(alg_bytes: float, us: float, traffic=None) -> dict:
+NOMINAL_HBM_GBS = 8000.0  # north_star's "~8 TB/s peak"; SURVEY.md 8(d) asks for both denominators
+
+
+def roofline(alg_bytes: float, us: float, traffic=None, kernel: str | None = None, capture: str | None = None) -> dict:
+    """achieved = algorithmic bytes / event-timed duration; frac of the MEASURED copy bandwidth
+    (MEASURED_PEAKS.json) and, beside it, of the nominal 8 TB/s.  ``kernel`` / ``capture``: read `traffic`
+    (dram read + write bytes of one launch) from the committed ncu summary under profiles/."""
     peak, how = hbm_peak()
     ach = alg_bytes / (us * 1e-6) / 1e9
+    src = None
+    if traffic is None and kernel:
+        t = ncu_traffic(kernel, capture or "ncu_*.txt")
+        if t:
+            traffic, src = t["bytes"], t["source"]
     return {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(ach / peak, 4), "traffic": traffic, "peak_source": how}
+            "frac": round(ach / peak, 4), "traffic": traffic, "peak_source": how,
+            "frac_of_nominal_8tbs": round(ach / NOMINAL_HBM_GBS, 4), "traffic_source": src}
+
+
+def cpu_leg(fn, seconds: float):
+    """A bounded CPU-baseline leg (oracle/cpu_arm.py: the unmodified reference on this host); a failure
+    there (say, too little host RAM) must not take the GPU numbers down with it."""
+    try:
+        from oracle import cpu_arm
+
+        return getattr(cpu_arm, fn)(seconds)
+    except Exception as e:  # pragma: no cover - depends on the host
+        return {"value": None, "kind": "unavailable", "sample": f"{type(e).__name__}: {e}"}
 
 
 def b200_arm(args):
@@ -700,18 +907,9 @@ def b200_arm(args):
     if rank == 0 and world == 1 and not args.no_also:
         del wl
         torch.cuda.empty_cache()
-        g = bench_gae(dev)
-        g["roofline"] = roofline(g["algorithmic_bytes"], g["us_per_launch"])
-        g16 = bench_gae(dev, sets=2, P=C3["P"] * 16, reps=20)
-        g16["roofline"] = roofline(g16["algorithmic_bytes"], g16["us_per_launch"])
-        p = bench_per_tree(dev)
-        p["roofline"] = roofline(p["algorithmic_bytes"], p["us_sample_plus_update"])
-        torch.cuda.empty_cache()
-        c5 = bench_uniform(dev)
-        c5["roofline"] = roofline(c5["algorithmic_bytes"], c5["us_sample"])
-        also = [g, g16, p, c5]
+        also = also_single_gpu(dev, with_cpu=not args.no_cpu)
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = reference_c2(seconds=args.cpu_seconds, workers=1)
+        cpu = reference_c2(seconds=args.cpu_seconds, fill_seconds=20.0)
 
     if rank == 0:
         line = {
@@ -745,99 +943,17 @@ def b200_arm(args):
 
 
 # =================================================================================================
-# reference arm / cpu_baseline: the oracle port of the reference's CPU path
+# reference arm / cpu_baseline: the UNMODIFIED reference classes on the host (oracle/cpu_arm.py)
 # =================================================================================================
-_REF_STATE = {}
-
-
-def _ref_build(rows: int, seed: int):
-    """PerOracle (Python-list trees, replay_buffer.py:261-428) at the config's tree capacity and
-    a BOUNDED slice of the row storage (numpy, struct-of-arrays like the TensorDict storage)."""
-    import numpy as np
-
-    from oracle import xp_oracle as xo
+def reference_c2(seconds: float, max_agent_steps: int = 1 << 30, fill_seconds: float = 30.0) -> dict:
+    """One process, agents sequential on one shared memory — the reference's own execution model
+    (train_off_policy.py:46,249).  kind == "reference" wherever a copy of the reference is present
+    (/root/reference here, the staged oracle/_ref on the GPU box), else the oracle port."""
+    from oracle import cpu_arm
 
     c = C2
-    rng = np.random.default_rng(seed)
-    per = xo.PerOracle(c["cap"], c["alpha"])
-    per.size = c["cap"]
-    cap2 = per.sum_tree.capacity
-    leaves = (np.abs(rng.standard_normal(c["cap"])) + 1e-3) ** c["alpha"]
-    # direct leaf fill + one bottom-up pass (1M sequential _update_priority calls take minutes);
-    # produces exactly the tree the sequential walks produce (SURVEY.md A.1)
-    per.sum_tree.tree[cap2:cap2 + c["cap"]] = leaves.tolist()
-    per.min_tree.tree[cap2:cap2 + c["cap"]] = leaves.tolist()
-    per.sum_tree.rebuild_from_leaves()
-    per.min_tree.rebuild_from_leaves()
-
-    def storage():
-        return {"obs": rng.integers(0, 256, (rows, *ATARI), dtype=np.uint8),
-                "action": rng.integers(0, 18, (rows, 1)).astype(np.float32),
-                "reward": rng.standard_normal((rows, 1)).astype(np.float32),
-                "next_obs": rng.integers(0, 256, (rows, *ATARI), dtype=np.uint8),
-                "done": (rng.random((rows, 1)) < 0.01).astype(np.float32)}
-
-    return per, storage(), storage()
-
-
-def _ref_agent_step(per, st_per, st_n, rows, B, beta, rng_t, prio):
-    """One agent's sample + n-step gather + update, as train_off_policy.py:363-412 drives it."""
-    import numpy as np
-    import torch
-
-    from oracle import xp_oracle as xo
-
-    u = torch.rand(B, generator=rng_t).numpy()       # B x torch.rand(1).item() (:377)
-    idx = per.sample_proportional(B, u)
-    batch = xo.gather(st_per, idx % rows)             # storage[idx].clone()
-    w = per.calculate_weights(idx, beta)
-    nb = xo.gather(st_n, idx % rows)                  # sample_from_indices
-    per.update_priorities(idx, prio)
-    return batch, nb, w
-
-
-def _ref_worker(args):
-    seconds, max_agent_steps, seed, rows = args
-    import numpy as np
-    import torch
-
-    torch.set_num_threads(1)
-    c = C2
-    per, st_per, st_n = _ref_build(rows, seed)
-    rng_t = torch.Generator().manual_seed(seed)
-    prio = (np.abs(np.random.default_rng(seed).standard_normal(c["B"])) + 1e-6).astype(np.float32)
-    _ref_agent_step(per, st_per, st_n, rows, c["B"], c["beta"], rng_t, prio)  # warm-up
-    t0 = time.perf_counter()
-    n = 0
-    while n < max_agent_steps:
-        _ref_agent_step(per, st_per, st_n, rows, c["B"], c["beta"], rng_t, prio)
-        n += 1
-        if time.perf_counter() - t0 > seconds:
-            break
-    return n, time.perf_counter() - t0
-
-
-def reference_c2(seconds: float, workers: int, max_agent_steps: int = 1 << 30, rows: int = 4096):
-    """Time the oracle port on the host.  workers == 1: the reference's own execution model
-    (agents sequential in one Python process, train_off_policy.py:249).  workers > 1: that many
-    independent processes, one agent each — the population-parallel upper bound."""
-    c = C2
-    if workers == 1:
-        res = [_ref_worker((seconds, max_agent_steps, 0, rows))]
-    else:
-        import multiprocessing as mp
-
-        ctx = mp.get_context("fork")
-        with ctx.Pool(workers) as pool:
-            res = pool.map(_ref_worker, [(seconds, max_agent_steps, s, rows) for s in range(workers)])
-    agent_steps = sum(r[0] for r in res)
-    wall = max(r[1] for r in res)
-    value = agent_steps * c["B"] / wall
-    return {"value": value, "unit": UNIT, "cores": workers, "kind": "port",
-            "host_cores": os.cpu_count(),
-            "sample": f"{agent_steps} agent-steps of {c['B']} samples in {wall:.1f} s; Python-list "
-                      f"sum/min trees at the full 2^20 capacity, row storage bounded to {rows} rows "
-                      f"(idx mod {rows}); sample_proportional + gather x2 + weights + update_priorities"}
+    return cpu_arm.time_c2(seconds, max_agent_steps, cap=c["cap"], B=c["B"], n_step=c["n_step"], gamma=c["gamma"],
+                           alpha=c["alpha"], beta=c["beta"], num_envs=c["num_envs"], fill_seconds=fill_seconds)
 
 
 def reference_arm(args):
@@ -846,28 +962,32 @@ def reference_arm(args):
         return
     if args.workload != "c2":
         raise SystemExit("only --workload c2 is a bench line")
+    from oracle import cpu_arm
+
     K, W = args.steps, args.warmup
     c = C2
-    workers = max(1, min(c["P"], os.cpu_count() or 1))
-    # each "step" = one bounded sample: every worker runs ONE agent's sample+update (256 samples);
-    # the budget keeps the whole run within a few minutes whatever K is
-    budget = 60.0
     t0 = time.perf_counter()
-    cpu = reference_c2(seconds=budget, workers=workers, max_agent_steps=max(K + W, 1))
+    # a "step" = one population step: P agents x (sample + n-step sample_from_indices + update_priorities);
+    # K + W of them, bounded to ~60 s of timed work so that the run ends within a few minutes whatever K is
+    cpu = reference_c2(seconds=60.0, max_agent_steps=max((K + W) * c["P"], c["P"]))
+    upper = None
+    if not args.no_also:
+        workers = max(1, min(c["P"], os.cpu_count() or 1))
+        upper = cpu_arm.time_c2_population_parallel(12.0, workers, cap=c["cap"], B=c["B"])
     wall = time.perf_counter() - t0
-    agent_steps = int(cpu["sample"].split()[0])
     line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT,
             "n_gpus": args.gpus, "steps": K, "warmup": W,
-            "ms_per_step": 1e3 * c["B"] * workers / cpu["value"],
+            "ms_per_step": 1e3 * c["B"] * c["P"] / cpu["value"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64 tree / u8 rows", "data": "synthetic",
             "config": {"workload": c["name"], "rows": c["cap"], "batch": c["B"],
                        "population_per_gpu": c["P"], "population": c["P"], "row_bytes": R_C2,
-                       "tree_levels": c["L"], "parallelism": f"{workers} host processes"},
+                       "tree_levels": c["L"], "parallelism": "1 host process, agents sequential (the reference's model)"},
             "cpu_baseline": cpu,
+            "population_parallel_upper_bound": upper,
             "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0},
-            "gpu_launches": 0, "wall_s": round(wall, 1), "agent_steps": agent_steps}
+            "gpu_launches": 0, "wall_s": round(wall, 1), "agent_steps": cpu["agent_steps"]}
     print(json.dumps(line), flush=True)
 
 

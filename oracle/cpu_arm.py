@@ -120,10 +120,18 @@ class C2Reference:
     ``memory.update_priorities(idxs, priorities)`` with ``idxs`` the (B,1) tensor of the batch and
     ``priorities`` an fp32 ndarray (algorithms/dqn_rainbow.py:487-488)."""
 
+    ROW_BYTES = 2 * 84 * 84 * 4 + 12
+
     def __init__(self, cap=1_000_000, B=256, n_step=3, gamma=0.99, alpha=0.6, beta=0.4, num_envs=16,
-                 fill_seconds=30.0, ram_fraction=0.45, seed=0):
-        self.cap, self.B, self.beta = cap, B, beta
+                 fill_seconds=30.0, ram_fraction=0.6, seed=0):
         self.kind = kind()
+        self.cap_config = cap
+        if self.kind == "reference":
+            # the reference's _init ZERO-FILLS max_size rows of every key (torch.zeros_like, :68): the whole
+            # storage is resident, so the capacity this host can hold bounds max_size (stated in `sample`)
+            fit = int(ram_fraction * mem_available_bytes() // (2 * self.ROW_BYTES))
+            cap = max(4096, min(cap, fit))
+        self.cap, self.B, self.beta = cap, B, beta
         rng = np.random.default_rng(seed)
         leaves = (np.abs(rng.standard_normal(cap)) + 1e-3) ** alpha
         self.prio = (np.abs(rng.standard_normal(B)) + 1e-6).astype(np.float32)
@@ -140,7 +148,7 @@ class C2Reference:
                 if one is not None:
                     self.per.add(one)
             big = [buf.storage[k] for buf in (self.per, self.nstep) for k in ("obs", "next_obs")]
-            self.filled = fill_rows(big, fill_seconds, ram_fraction * mem_available_bytes(), seed)
+            self.filled = fill_rows(big, fill_seconds, float("inf"), seed)
             for buf in (self.per, self.nstep):
                 buf._size, buf._cursor = cap, 0
                 for k in ("action", "reward", "done"):
@@ -185,8 +193,11 @@ class C2Reference:
         if self.kind == "reference":
             return (f"unmodified reference classes ({ref_loader.REF_SOURCE} copy), 1 process, agents sequential on ONE "
                     f"shared memory; tree capacity 2^{int(np.log2(self.per.sum_tree.capacity))} filled by direct leaf "
-                    f"assignment; storage {self.cap} rows per buffer allocated by the reference's own _init, rows "
-                    f"[0,{self.filled}) filled with random bytes (rest untouched zero pages); setup {self.setup_s:.0f} s untimed")
+                    f"assignment; max_size {self.cap} rows per buffer"
+                    + ("" if self.cap == self.cap_config else f" (config: {self.cap_config}; bounded by host RAM — the "
+                       f"reference zero-fills the whole storage, 2 x {self.cap * self.ROW_BYTES / 2**30:.0f} GiB here)")
+                    + f", allocated by the reference's own _init, rows [0,{self.filled}) overwritten with random bytes "
+                    f"(rest zeros); setup {self.setup_s:.0f} s untimed")
         return (f"ORACLE PORT (no reference copy on this machine): list trees at full capacity, numpy row storage "
                 f"bounded to {self.storage_rows} rows (idx mod rows)")
 
@@ -226,7 +237,7 @@ def time_c2_population_parallel(seconds: float, workers: int, **kw) -> dict:
 
     kw = dict(kw)
     kw.setdefault("fill_seconds", 6.0)
-    kw.setdefault("ram_fraction", 0.3 / workers)
+    kw.setdefault("ram_fraction", 0.5 / workers)
     with mp.get_context("fork").Pool(workers) as pool:
         res = pool.map(_c2_worker, [(seconds, 1 << 30, s, kw) for s in range(workers)])
     steps, wall = sum(r[0] for r in res), max(r[1] for r in res)
@@ -313,13 +324,16 @@ def _uniform_buffer(cap, row, num_envs, fill_seconds, ram_fraction, seed):
     the reference's own _init allocate the storage; the rest is bulk-filled (untimed)."""
     g = torch.Generator().manual_seed(seed)
     ref = ref_loader.load_reference()
+    probe = row(1, g)
+    row_bytes = sum(max(v[0].numel(), 1) * v.element_size() for v in probe.values())
+    cap = max(1024, min(cap, int(ram_fraction * mem_available_bytes() // row_bytes)))  # _init zero-fills it all
     buf = ref.ReplayBuffer(max_size=cap)
     for _ in range(3):
         buf.add(ref.TensorDict(row(num_envs, g), batch_size=[num_envs]))
     keys = list(buf.storage.keys())
-    filled = fill_rows([buf.storage[k] for k in keys], fill_seconds, ram_fraction * mem_available_bytes(), seed)
+    filled = fill_rows([buf.storage[k] for k in keys], fill_seconds, float("inf"), seed)
     buf._size, buf._cursor = cap, 0
-    return buf, filled
+    return buf, filled, cap
 
 
 def time_uniform(seconds: float, cap: int, B: int, row, label: str, num_envs=16, fill_seconds=15.0,
@@ -329,7 +343,8 @@ def time_uniform(seconds: float, cap: int, B: int, row, label: str, num_envs=16,
     t0 = time.perf_counter()
     is_ref = ref_loader.available()
     if is_ref:
-        buf, filled = _uniform_buffer(cap, row, num_envs, fill_seconds, ram_fraction, seed)
+        cap_config = cap
+        buf, filled, cap = _uniform_buffer(cap, row, num_envs, fill_seconds, ram_fraction, seed)
 
         def step():
             buf.sample(B)
@@ -355,7 +370,9 @@ def time_uniform(seconds: float, cap: int, B: int, row, label: str, num_envs=16,
     wall = time.perf_counter() - t0
     return {"value": n * B / wall, "unit": "transitions/s", "cores": 1, "kind": "reference" if is_ref else "port",
             "sample": f"{label}: {n} calls of ReplayBuffer.sample({B}) in {wall:.1f} s ({1e3 * wall / n:.2f} ms per call, "
-                      f"torch.randperm({cap}) inside every call); {cap} rows, [0,{filled}) filled with random bytes; "
+                      f"torch.randperm({cap}) inside every call); max_size {cap} rows"
+                      + (f" (config: {cap_config}; bounded by host RAM)" if is_ref and cap != cap_config else "")
+                      + f", [0,{filled}) overwritten with random bytes; "
                       f"1 process, torch threads {torch.get_num_threads()}; setup {setup:.0f} s untimed"}
 
 
