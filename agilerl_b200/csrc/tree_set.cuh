@@ -859,7 +859,11 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   const int L = ilog2(t.cap);
   const bool paired = is_paired(t);
   int launches = 0;
-  if (B <= 16384) {  // schedule M: one launch
+  // schedule M (one launch) up to 8 192 items; beyond that every CTA of M would re-read a batch that no longer
+  // pays for saving two launches (cap 2^20, 16 384 items: M 21.7 us, S below; 32 768 items: S 16 us)
+  static const int m_max = env_int("XP_SET_M_MAX", 8192);  // developer knob
+  const bool fits_s = slotted_scratch_ints(t.cap, [&] { long long nb = 1; while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1; return nb; }(), B, s.kind == kSrcPrio) <= t.cap && s.kind != kSrcRange;
+  if (B <= m_max || (B <= 16384 && !fits_s)) {  // schedule M: one launch
     long long nb = 1;
     while (nb * 8 < B && nb < 2048 && nb * 2 <= t.cap) nb <<= 1;
     const int shift = L - ilog2(nb);

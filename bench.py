@@ -259,7 +259,9 @@ class C2Workload:
             if one is not None:
                 self.per.add(one)
         # bulk fill of the remaining rows straight into HBM (setup, untimed): random bytes
-        gd = torch.Generator(device=dev).manual_seed(1 + self.rank)
+        # the shared memory is REPLICATED: storage and priorities are seeded identically on every rank;
+        # only the agents' own uniform draws / new priorities (below) differ per rank
+        gd = torch.Generator(device=dev).manual_seed(1)
         block = torch.randint(0, 256, (1 << 28,), dtype=torch.uint8, device=dev, generator=gd)
         for buf in (self.per, self.nstep):
             for path, t in buf._leaves.items():
@@ -286,8 +288,10 @@ class C2Workload:
         # resident inputs of the timed steps (rotated)
         n = self.P * self.B
         self.R = 4
-        self.u = [torch.rand(n, generator=torch.Generator().manual_seed(10 + i)).to(dev) for i in range(self.R)]
-        self.pr = [(torch.randn(n, device=dev, generator=gd).abs() + 1e-6) for _ in range(self.R)]
+        self.u = [torch.rand(n, generator=torch.Generator().manual_seed(10 + i + 1000 * self.rank)).to(dev)
+                  for i in range(self.R)]
+        gr = torch.Generator(device=dev).manual_seed(77 + self.rank)
+        self.pr = [(torch.randn(n, device=dev, generator=gr).abs() + 1e-6) for _ in range(self.R)]
         self.idx = torch.empty(n, dtype=torch.int64, device=dev)
         self.w = torch.empty(n, dtype=torch.float32, device=dev)
         self.err = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -375,6 +379,42 @@ class C2Workload:
         if ev is not None and len(ev) > 3:
             ev[3].record()
 
+    def capture_steps(self):
+        """R consecutive steps (every rotating input set once; an even number of exchanges, so the two
+        peer-mapped blocks alternate consistently) as ONE CUDA graph: at N > 1 no host work sits between the
+        rendez-vous of consecutive steps (xp_peer_allgather_graph keeps the exchange epoch on the device)."""
+        torch = self.torch
+        side = torch.cuda.Stream(self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        if self.px is not None:
+            assert self.px.epoch % 2 == 0, "capture on an even exchange count"
+        g = torch.cuda.CUDAGraph()
+        n0 = self.lib.xp_launch_count()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                for i in range(self.R):
+                    self.step(i)
+        self.launches_per_graph = int(self.lib.xp_launch_count() - n0)  # kernel nodes of one replay
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        if self.px is not None:
+            self.px.epoch -= self.R  # nothing ran during capture
+        return g
+
+    def replay(self, g):
+        g.replay()
+        if self.px is not None:
+            self.px.advance(self.R)
+
+    def replica_checksum(self):
+        """Two 64-bit checksums of everything the replicas must agree on after the timed steps: every
+        (sum, min) node of the tree pair, max_priority, and the ring / tree cursors."""
+        torch = self.torch
+        _, _, st, _ = self.per._ensure_trees()
+        bits = st.nodes.view(-1).view(torch.int64)[2:]  # node 0 is unused
+        w = torch.arange(1, bits.numel() + 1, device=bits.device, dtype=torch.int64) * 2654435761 + 1
+        host = torch.tensor([self.per._cursor, self.per.tree_ptr, self.per._size], dtype=torch.int64, device=bits.device)
+        return torch.stack([bits.sum(), (bits * w).sum(), self.per._state.view(torch.int64)[0], host.sum()])
+
     def verify(self):
         """size-independent property at full size: the gathered rows equal torch indexing of the
         storage, indices are within [0, size), the tree root equals the sum of the leaves'
@@ -404,7 +444,13 @@ class C2Workload:
         self.res_idx_host = torch.empty(self.P * n, 1, dtype=torch.int64).pin_memory()
         self.res_w_host = torch.empty(self.P * n, 1, dtype=torch.float32).pin_memory()
         self.res_ev = torch.cuda.Event()
-        torch.manual_seed(1234)
+        self.rep = None
+        if self.world > 1:
+            # the SAME algorithm as `value`: every agent's update is exchanged and applied on every replica
+            from agilerl_b200.population import ReplicatedReplay
+
+            self.rep = ReplicatedReplay(self.per)
+        torch.manual_seed(1234 + self.rank)
 
     def e2e_step(self, i):
         torch = self.torch
@@ -415,7 +461,11 @@ class C2Workload:
             nb = self.nstep.sample_from_indices(batch["idxs"])    # noqa: F841 (n-step batch)
             idxs.append(batch["idxs"])
             ws.append(batch["weights"])
-            self.per.update_priorities(batch["idxs"], self.prio_host[(i * self.P + a) % len(self.prio_host)])
+            prio = self.prio_host[(i * self.P + a) % len(self.prio_host)]
+            if self.rep is not None:
+                self.rep.update_priorities(batch["idxs"], prio)  # exchange (NVLink peer kernel) + replicated update
+            else:
+                self.per.update_priorities(batch["idxs"], prio)
         # D2H: the step's result (sampled indices + IS weights of all agents) into pinned memory
         n = self.P * self.B
         torch.cat(idxs, out=self.res_idx_dev)
@@ -560,7 +610,7 @@ def bench_per_tree(dev, reps=10):
             "l2": "tree 805 MB > L2; top levels L2-resident by design"}
 
 
-def bench_uniform(dev, reps=10):
+def bench_uniform(dev, reps=10, P=None):
     """C5: TD3 uniform replay, 10 M Humanoid-shape rows (30.8 GB), 32 agents x 1024 per launch:
     xp_randperm_prefix (torch.randperm(size)[:B] from the raw mt19937 words, replay_buffer.py:125)
     + xp_gather of every key (:126-131)."""
@@ -569,7 +619,7 @@ def bench_uniform(dev, reps=10):
     from agilerl_b200 import xp
 
     c = C5
-    cap, B, P = c["cap"], c["B"], c["P"]
+    cap, B, P = c["cap"], c["B"], P or c["P"]
     n = P * B
     shapes = [("obs", (c["obs"],)), ("action", (c["act"],)), ("reward", (1,)), ("next_obs", (c["obs"],)),
               ("done", (1,))]
@@ -709,6 +759,103 @@ def bench_c1(dev):
             "note": "latency-bound: 4 x 64 rows of 44 B; the CPU-reference config, GPU number for completeness"}
 
 
+def bench_per_tree_replicated(dev, rank, world, reps=10):
+    """C4 strong scaling (BASELINE.json configs[3]: population 64 sharded over the GPUs): every rank samples for
+    its 64/world agents from ITS replica of the 2^24-leaf tree, the (index, priority) pairs of all ranks are
+    exchanged over NVLink peer memory (xp_peer_allgather_graph) and EVERY replica applies all 262 144 updates in
+    rank-major order — the price of keeping the shared memory bit-identical.  One CUDA graph of 4 steps."""
+    import torch
+    import torch.distributed as dist
+
+    from agilerl_b200 import peer, xp
+
+    c = C4
+    cap, B, P = c["cap"], c["B"], c["P"] // world
+    n = P * B
+    nodes = torch.empty(2 * cap, 2, dtype=torch.float64, device=dev)
+    aux = torch.zeros(2 * cap, dtype=torch.int32, device=dev)
+    t = xp.make_tree(nodes[:, 0], nodes[:, 1], 2, cap, aux)
+    xp.tree_init(t, torch.cuda.current_stream().cuda_stream)
+    state = torch.ones(1, dtype=torch.float64, device=dev)
+    gd = torch.Generator(device=dev).manual_seed(4)  # the replicated tree: same seed on every rank
+    xp.per_add(t, state, 0, cap, cap, c["alpha"])
+    pr0 = torch.randn(cap, device=dev, generator=gd).abs() + 1e-3
+    xp.per_update(t, state, torch.arange(cap, device=dev), pr0, cap, c["alpha"])
+    del pr0
+    gr = torch.Generator(device=dev).manual_seed(400 + rank)  # this rank's agents
+    R = 4
+    u = [torch.rand(n, device=dev, generator=gr) for _ in range(R)]
+    px = peer.PeerExchange(12 * n, [(0, 8 * n, torch.int64), (8 * n, 4 * n, torch.float32)], dev)
+    for k in (0, 1):
+        px.view(k, 8 * n, n, torch.float32).copy_(torch.randn(n, device=dev, generator=gr).abs() + 1e-6)
+    idx_blk = [px.view(k, 0, n, torch.int64) for k in (0, 1)]
+    w = torch.empty(n, dtype=torch.float32, device=dev)
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def step(i):
+        def run():
+            xp.per_sample(t, u[i], B, P, cap, c["beta"], idx_blk[i & 1], w)
+            all_idx, all_pr = px.allgather()
+            xp.per_update(t, state, all_idx, all_pr, cap, c["alpha"], err)
+        return run
+
+    torch.cuda.synchronize()
+    dist.barrier()
+    us = graph_time_us([step(i) for i in range(R)], reps)
+    px.epoch = int(px._epoch_dev[0].item())  # the graph replays advanced the device epoch on their own
+    px.check()
+    assert int(err.item()) == 0
+    tt = torch.tensor([us], device=dev, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    us = float(tt.item())
+    bits = nodes.view(-1).view(torch.int64)[2:]
+    ck = torch.stack([bits.sum(), (bits * (torch.arange(bits.numel(), device=dev) * 2654435761 + 1)).sum(),
+                      state.view(torch.int64)[0]])
+    allck = [torch.empty_like(ck) for _ in range(world)]
+    dist.all_gather(allck, ck)
+    total = c["P"] * B
+    tot_bytes = total * sum(per_bytes_per_sample(c["L"]).values())
+    return {"workload": c["name"] + f"_sharded_x{world}", "metric": METRIC, "value": total / (us * 1e-6), "unit": UNIT,
+            "scaling": "strong", "agents_per_gpu": P, "us_sample_exchange_update": us,
+            "updates_applied_per_replica": total, "replicas_identical": all(bool(torch.equal(allck[0], x)) for x in allck[1:]),
+            "algorithmic_bytes_all_replicas": tot_bytes,
+            "note": "per replica: 1/N of the descents, ALL of the updates (replicated tree) + the NVLink exchange"}
+
+
+def also_multi_gpu(dev, rank, world):
+    """The configs BASELINE.json names for 1/2/4/8 GPUs, per N: C3 and C5 shard by population with no
+    exchange (each rank's agents own their rollout buffers / sample their replica); C4 is strong scaling with a
+    replicated tree.  Every number is the max over ranks of a device-timed graph replay."""
+    import torch
+    import torch.distributed as dist
+
+    def max_over_ranks(x):
+        tt = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    out = []
+    pl = max(1, C3["P"] // world)
+    dist.barrier()
+    g = bench_gae(dev, sets=8 * world, P=pl)
+    us = max_over_ranks(g["us_per_launch"])
+    steps = pl * world * C3["T"] * C3["N"]
+    out.append({"workload": C3["name"] + f"_sharded_x{world}", "metric": "gae_steps_per_s", "value": steps / (us * 1e-6),
+                "unit": "steps/s", "scaling": "strong", "agents_per_gpu": pl, "us_per_launch": us,
+                "roofline_per_gpu": roofline(pl * C3["T"] * C3["N"] * 17, us), "exchange": "none"})
+    torch.cuda.empty_cache()
+    out.append(bench_per_tree_replicated(dev, rank, world))
+    torch.cuda.empty_cache()
+    pl = max(1, C5["P"] // world)
+    dist.barrier()
+    c5 = bench_uniform(dev, P=pl)
+    us = max_over_ranks(c5["us_sample"])
+    out.append({"workload": C5["name"] + f"_sharded_x{world}", "metric": "uniform_sampled_transitions_per_s",
+                "value": pl * world * C5["B"] / (us * 1e-6), "unit": UNIT, "scaling": "strong", "agents_per_gpu": pl,
+                "us_sample": us, "roofline_per_gpu": roofline(pl * C5["B"] * (2 * R_C5 + 8), us), "exchange": "none"})
+    return out
+
+
 def also_single_gpu(dev, with_cpu=True):
     """C3 / C4 / C5 (+ C1, insert side) device-timed with rooflines, each beside the reference's CPU number."""
     import torch
@@ -831,33 +978,61 @@ def b200_arm(args):
     wl.setup()
     wl.verify()
     K, W = args.steps, max(args.warmup, 3)
+    use_graph = world > 1 and os.environ.get("XP_BENCH_NOGRAPH") != "1"
     for i in range(W):
         wl.step(i)
     sync()
     clocks = ClockSampler(local)
-    # the gather pair is event-timed on every 4th step of the timed region: an event record between two
-    # kernels ends the programmatic-launch chain there, so timing every step would tax the step itself
-    EV = 4
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) if i % EV == 0 else None
-           for i in range(K)]
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    clocks.start()
-    l0 = lib.xp_launch_count()
-    a.record()
-    for i in range(K):
-        wl.step(W + i, evs[i])
-    b.record()
-    sync()
-    l1 = lib.xp_launch_count()
+    if use_graph:
+        # N > 1: R consecutive steps captured once and replayed — every kernel of the step is host-sync-free, so
+        # the ranks meet only inside xp_peer_allgather.  One untimed replay after the host barrier aligns the
+        # ranks ON THE DEVICE (its exchanges are rendez-vous) before event `a` is recorded.
+        if wl.px is not None and wl.px.epoch % 2:
+            wl.step(W)  # even exchange count before capture
+        graph = wl.capture_steps()
+        sync()
+        wl.replay(graph)
+        clocks.start()
+        l0 = lib.xp_launch_count()
+        a.record()
+        for _ in range(K // wl.R):
+            wl.replay(graph)
+        for i in range(K % wl.R):
+            wl.step(i)
+        b.record()
+        sync()
+        # replays launch kernels without passing through the library's host entry points: count them from the capture
+        l1 = lib.xp_launch_count() + (K // wl.R) * wl.launches_per_graph
+        timed = []
+    else:
+        # the gather pair is event-timed on every 4th step of the timed region: an event record between two
+        # kernels ends the programmatic-launch chain there, so timing every step would tax the step itself
+        EV = 4
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) if i % EV == 0 else None
+               for i in range(K)]
+        clocks.start()
+        l0 = lib.xp_launch_count()
+        a.record()
+        for i in range(K):
+            wl.step(W + i, evs[i])
+        b.record()
+        sync()
+        l1 = lib.xp_launch_count()
+        timed = [e for e in evs if e is not None]
     ms = a.elapsed_time(b)
-    # the two gather launches (PER table, n-step table; same indices) sit between one event pair
-    timed = [e for e in evs if e is not None]
-    gather_us = sum(x.elapsed_time(y) for x, y in timed) * 1e3 / len(timed) / 2
     if world > 1:
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = wl.units_per_step * world * K / (ms * 1e-3)
+    # replicas must still be bit-identical after the timed steps (untimed check; fails the run otherwise)
+    replicas_identical = None
+    if world > 1:
+        ck = wl.replica_checksum()
+        allck = [torch.empty_like(ck) for _ in range(world)]
+        dist.all_gather(allck, ck)
+        replicas_identical = all(bool(torch.equal(allck[0], x)) for x in allck[1:])
 
     # per-kernel breakdown of the step (separate untimed pass; events between every launch)
     Kb = min(K, 50)
@@ -869,6 +1044,12 @@ def b200_arm(args):
     breakdown = {n: round(sum(e[x].elapsed_time(e[y]) for e in bev) * 1e3 / Kb, 2)
                  for n, x, y in (("per_sample_us", 4, 0), ("gather_per_table_us", 0, 2),
                                  ("gather_nstep_table_us", 2, 1), ("per_update_us", 1, 3))}
+    if timed:  # the two gather launches (PER table, n-step table; same indices) sit between one event pair
+        gather_us = sum(x.elapsed_time(y) for x, y in timed) * 1e3 / len(timed) / 2
+        gather_how = f"event-timed inside the timed region on every {EV}th step"
+    else:      # graph replays hold no event nodes: the same launches event-timed in the pass right after
+        gather_us = (breakdown["gather_per_table_us"] + breakdown["gather_nstep_table_us"]) / 2
+        gather_how = f"event-timed in the {Kb}-step per-kernel pass that follows the (graph-replayed) timed region"
 
     # -- e2e through the public per-agent API ---------------------------------------------------
     e2e = None
@@ -904,6 +1085,10 @@ def b200_arm(args):
     exchange = "peer" if wl.px is not None else "nccl"
     if wl.px is not None:
         wl.px.check()
+    if world > 1 and not args.no_also:  # collective: every rank takes part
+        del wl
+        torch.cuda.empty_cache()
+        also = also_multi_gpu(dev, rank, world)
     if rank == 0 and world == 1 and not args.no_also:
         del wl
         torch.cuda.empty_cache()
@@ -937,9 +1122,17 @@ def b200_arm(args):
             "cpu_baseline": cpu,
             "also": also,
         }
+        line["roofline"]["timed_how"] = gather_how
+        if world > 1:
+            line["replicas_identical"] = replicas_identical
+            line["timed_region"] = ("CUDA-graph replays of 4 consecutive steps (sample, gather x2, NVLink exchange, "
+                                    "replicated update); ranks aligned on the device by one untimed replay"
+                                    if use_graph else "host-launched steps")
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+        if replicas_identical is False:
+            raise SystemExit("bench.py: the replicas diverged during the timed steps")
 
 
 # =================================================================================================
