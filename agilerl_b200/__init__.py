@@ -28,3 +28,12 @@ def install() -> None:
         mod = importlib.import_module(name)
         for s in symbols:
             setattr(mod, s, getattr(c, s))
+
+
+def link_n_step(memory, n_step_memory) -> None:
+    """Optional one-liner for the off-policy loop (training/train_off_policy.py:46-60 creates ``memory`` and
+    ``n_step_memory`` side by side): ``agilerl_b200.link_n_step(memory, n_step_memory)`` lets
+    ``memory.sample(batch_size, beta)`` gather the rows of both buffers in one launch, so that the
+    reference's next call ``n_step_sampler.sample(experiences["idxs"])`` costs no second launch.  Same
+    results with or without it (``PrioritizedReplayBuffer.link_n_step``)."""
+    memory.link_n_step(n_step_memory)

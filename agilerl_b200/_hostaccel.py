@@ -42,6 +42,7 @@ def load():
 
         mod.bind(addr(lib.xp_gather), addr(lib.xp_per_sample), addr(lib.xp_per_update),
                  addr(lib.xp_copy_to_device), nv.check)
+        mod.bind_peer(addr(lib.xp_peer_allgather_graph))
         _MOD = mod
     except Exception as e:  # pragma: no cover - depends on the local toolchain
         warnings.warn(f"agilerl_b200: native host fast path unavailable ({e}); using the Python host")

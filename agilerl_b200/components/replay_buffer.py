@@ -333,6 +333,7 @@ class MultiStepReplayBuffer(ReplayBuffer):
         self._nstage: dict[tuple, torch.Tensor] = {}
         self._nstage_n = 0
         self._nstage_count = 0
+        self._prefetched = None  # (idxs tensor, its version, self.counter, {key: rows}) from a linked PER sample
 
     def _init_stage(self, data: TensorBatch, n: int) -> None:
         self._nstage = {p: torch.zeros((self.n_step * n, *t.shape[1:]), dtype=t.dtype,
@@ -410,6 +411,17 @@ class MultiStepReplayBuffer(ReplayBuffer):
         return self.n_step_buffer[0]
 
     def sample_from_indices(self, idxs: torch.Tensor) -> TensorBatch:
+        pf = self._prefetched
+        if pf is not None:
+            # rows for exactly THESE indices were gathered together with the linked PER buffer's batch
+            # (link_n_step): valid while it is the same, unmodified index tensor and nothing was added since
+            self._prefetched = None
+            if pf[0] is idxs and idxs._version == pf[1] and self.counter == pf[2]:
+                tb = TensorBatch.__new__(TensorBatch)
+                tb._d = pf[3]
+                tb._non_tensor = {}
+                tb.batch_size = idxs.shape
+                return self._out(tb)
         if not isinstance(idxs, torch.Tensor):
             idxs = torch.as_tensor(idxs)
         # storage[idxs] with (B,1) indices gives [B,1,...] in the reference
@@ -459,6 +471,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         self._tree_capacity = tree_capacity
         self._trees = None
         self._pending_max_priority = 1.0
+        self._sibling = None  # linked n-step buffer (link_n_step)
         self._pending_err = None
         self._err_pin = None
         self._err_ev = None
@@ -577,8 +590,13 @@ class PrioritizedReplayBuffer(ReplayBuffer):
                 u = self._draw_uniforms(batch_size)
             if u is None or (u.is_cuda and u.device == dev and u.dtype == torch.float32
                              and u.is_contiguous() and u.numel() == batch_size):
+                d = fp.sample(batch_size, float(beta), self._size, u)
+                sib_rows = d.pop("__sibling__", None)
+                if sib_rows is not None:
+                    ix = d["idxs"]
+                    self._sibling._prefetched = (ix, ix._version, self._sibling.counter, sib_rows)
                 tb = TensorBatch.__new__(TensorBatch)
-                tb._d = fp.sample(batch_size, float(beta), self._size, u)
+                tb._d = d
                 tb._non_tensor = {}
                 tb.batch_size = torch.Size((batch_size,))
                 return self._out(tb)
@@ -603,15 +621,31 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         if tab is None:
             return None
         fp = getattr(self, "_fper", None)
-        if fp is None or fp[0] is not tab or fp[1] is not self._trees:
+        sib = self._sibling
+        stab = None
+        if sib is not None and sib._leaves and sib.max_size == self.max_size and sib.storage_device == self.storage_device \
+                and len(sib._leaves) + len(self._leaves) <= 24:
+            stab = sib._fast_table()
+        if fp is None or fp[0] is not tab or fp[1] is not self._trees or fp[3] is not stab:
             import ctypes as _C
 
             _, _, st, h = self._ensure_trees()
             obj = _hostaccel.load().FastPer(tab, _C.addressof(h), st.nodes, st.aux, self._state, st.err,
                                             self.max_size, float(self.alpha))
-            fp = (tab, self._trees, obj)
+            obj.set_sibling(stab)
+            fp = (tab, self._trees, obj, stab)
             self._fper = fp
+            self._xchg = None  # a replicated-update exchange bound to the previous object is gone with it
         return fp[2]
+
+    def link_n_step(self, n_step_memory: "MultiStepReplayBuffer | None") -> None:
+        """Optional: tell this buffer which ``MultiStepReplayBuffer`` is filled in lock-step with it
+        (train_off_policy.py:341-343 adds one row batch to both per env step, so row i of the two is the
+        same transition).  ``sample(batch_size, beta)`` then moves the rows of BOTH tables in one gather
+        launch and the following ``n_step_memory.sample_from_indices(batch["idxs"])`` — the reference's own
+        call, unchanged — is served from it.  Results are identical with or without the link; any other
+        use of either buffer falls back to its own gather."""
+        self._sibling = n_step_memory
 
     def _raise_deferred(self) -> None:
         """Out-of-range indices that arrived as DEVICE tensors are detected by the kernel (a sticky

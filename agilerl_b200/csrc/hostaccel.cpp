@@ -27,17 +27,24 @@ using sample_fn = xp_status_t (*)(const xp_tree *, const float *, int64_t, int64
 using update_fn = xp_status_t (*)(const xp_tree *, xp_per_state *, const int64_t *, const float *,
                                   int64_t, int64_t, double, int *, void *);
 using copy_fn = xp_status_t (*)(void *, const void *, int64_t, void *);
+using peer_fn = xp_status_t (*)(const void *const *, const void *const *, void *const *, int, int, uint32_t *,
+                                const xp_peer_seg *, int, int *, void *);
 
 struct Fns {
   gather_fn gather = nullptr;
   sample_fn per_sample = nullptr;
   update_fn per_update = nullptr;
   copy_fn copy_to_device = nullptr;
+  peer_fn peer_allgather_graph = nullptr;
   // agilerl_b200._native.check(status, what): raises the mapped exception.  A borrowed handle whose
   // reference is deliberately never released: this struct is destroyed by the C runtime's exit
   // handlers, after the interpreter has been finalised, where a Py_DECREF would touch freed memory.
   py::handle check;
 } g;
+
+void bind_peer(uint64_t peer_allgather_graph) {
+  g.peer_allgather_graph = reinterpret_cast<peer_fn>(peer_allgather_graph);
+}
 
 void bind(uint64_t gather, uint64_t per_sample, uint64_t per_update, uint64_t copy_to_device,
           py::object check) {
@@ -91,6 +98,11 @@ class Ring {
     last_ = st.stream();
     have_last_ = true;
     ok(g.copy_to_device(s.dp, s.hp, nbytes, st.stream()), "xp_copy_to_device");
+    advance(st);
+  }
+
+  // the slot just acquired has been consumed by a copy the caller enqueued on `st` itself
+  void advance(c10::cuda::CUDAStream st) {
     const int i = next_;
     next_ = (i + 1) % (int)slots_.size();
     if ((i + 1) % half_ == 0) {
@@ -165,6 +177,25 @@ class FastGather {
   }
 
   c10::DeviceIndex index() const { return index_; }
+  int64_t max_size() const { return max_size_; }
+  size_t n_keys() const { return keys_.size(); }
+
+  // Allocate this table's fresh outputs into `out` and append its keys (dst filled in) to `keys`: lets a
+  // caller move the rows of TWO tables (PER + n-step, same indices) with ONE xp_gather launch.
+  void stage_keys(py::dict &out, std::vector<xp_key> &keys, const std::vector<int64_t> &lead) {
+    const auto dev = c10::Device(c10::kCUDA, index_);
+    std::vector<int64_t> shape;
+    for (size_t i = 0; i < keys_.size(); ++i) {
+      shape.assign(lead.begin(), lead.end());
+      shape.insert(shape.end(), meta_[i].tail.begin(), meta_[i].tail.end());
+      at::Tensor o = at::empty(shape, at::TensorOptions().dtype(meta_[i].dtype).device(dev));
+      xp_key k = keys_[i];
+      k.dst = o.data_ptr();
+      keys.push_back(k);
+      out[py::str(meta_[i].name)] = o;
+    }
+  }
+  int *err_ptr() { return err_.data_ptr<int>(); }
 
  private:
   std::vector<at::Tensor> leaves_;
@@ -209,10 +240,88 @@ class FastPer {
     ok(g.per_sample(&tree_, u, B, 1, size, beta, idx.data_ptr<int64_t>(), w.data_ptr<float>(), st.stream()),
        "xp_per_sample");
     py::dict out;
-    table_->gather_into(out, idx.data_ptr<int64_t>(), B, {B}, st);
+    if (sibling_) {
+      // linked n-step table (same capacity, index-aligned rows, train_off_policy.py:341-343): the rows of BOTH
+      // tables leave in ONE xp_gather launch; the sibling's batch is handed back under "__sibling__" and the
+      // Python host serves MultiStepReplayBuffer.sample_from_indices(batch["idxs"]) from it
+      std::vector<xp_key> keys;
+      keys.reserve(table_->n_keys() + sibling_->n_keys());
+      py::dict sib;
+      table_->stage_keys(out, keys, {B});
+      sibling_->stage_keys(sib, keys, {B, 1});  // storage[idxs] with (B,1) indices -> [B,1,...] (replay_buffer.py:204)
+      if (B > 0)
+        ok(g.gather(keys.data(), (int)keys.size(), idx.data_ptr<int64_t>(), B, max_size_, table_->err_ptr(),
+                    st.stream()), "xp_gather");
+      out["__sibling__"] = sib;
+    } else {
+      table_->gather_into(out, idx.data_ptr<int64_t>(), B, {B}, st);
+    }
     out["weights"] = w;
     out["idxs"] = idx;
     return out;
+  }
+
+  // link / unlink the n-step table whose rows are gathered together with this buffer's
+  void set_sibling(std::shared_ptr<FastGather> sib) {
+    if (sib) {
+      TORCH_CHECK(sib->max_size() == table_->max_size() && sib->index() == table_->index(),
+                  "linked buffers need the same capacity and device");
+      TORCH_CHECK(sib->n_keys() + table_->n_keys() <= XP_MAX_KEYS, "too many keys for one gather launch");
+    }
+    sibling_ = std::move(sib);
+  }
+
+  // Replicated shared memory (one process per GPU): this rank's (idx, priority) pairs go into its peer-mapped
+  // block, ONE kernel exchanges every rank's block over NVLink (device-resident epoch), and the update applies
+  // all ranks' pairs in rank-major order — population.ReplicatedReplay.update_priorities in one native call.
+  // block0/1: this rank's two blocks (device addresses); layout of a block: int64 idx[n] | float prio[n].
+  void set_exchange(std::vector<uint64_t> bases0, std::vector<uint64_t> bases1, std::vector<uint64_t> flags,
+                    int rank, at::Tensor epoch_dev, at::Tensor all_idx, at::Tensor all_prio, at::Tensor px_err,
+                    int64_t n) {
+    world_ = (int)bases0.size();
+    TORCH_CHECK(world_ >= 1 && world_ <= XP_MAX_PEERS && bases1.size() == bases0.size() && flags.size() == bases0.size());
+    for (int r = 0; r < world_; ++r) {
+      xb0_[r] = reinterpret_cast<const void *>(bases0[r]);
+      xb1_[r] = reinterpret_cast<const void *>(bases1[r]);
+      xfl_[r] = reinterpret_cast<void *>(flags[r]);
+    }
+    rank_ = rank;
+    x_epoch_ = std::move(epoch_dev);
+    x_idx_ = std::move(all_idx);
+    x_prio_ = std::move(all_prio);
+    x_err_ = std::move(px_err);
+    x_n_ = n;
+    segs_[0] = {0, x_idx_.data_ptr(), 8 * n};
+    segs_[1] = {8 * n, x_prio_.data_ptr(), 4 * n};
+  }
+
+  // `k`: the block the next exchange publishes (PeerExchange.current); idx int64 CUDA contiguous [n]; prio fp32
+  // on the host (pinned or not) or the device.
+  void update_replicated(int k, const at::Tensor &idx, const at::Tensor &prio) {
+    TORCH_CHECK(world_ > 0 && g.peer_allgather_graph, "exchange not set");
+    TORCH_CHECK(idx.numel() == x_n_ && prio.numel() == x_n_, "replicated update: every rank passes ", x_n_, " pairs");
+    const auto index = table_->index();
+    auto st = c10::cuda::getCurrentCUDAStream(index);
+    char *blk = const_cast<char *>(static_cast<const char *>((k ? xb1_ : xb0_)[rank_]));
+    C10_CUDA_CHECK(cudaMemcpyAsync(blk, idx.data_ptr<int64_t>(), (size_t)x_n_ * 8, cudaMemcpyDeviceToDevice, st.stream()));
+    if (prio.is_cuda()) {
+      C10_CUDA_CHECK(cudaMemcpyAsync(blk + 8 * x_n_, prio.data_ptr<float>(), (size_t)x_n_ * 4, cudaMemcpyDeviceToDevice,
+                                     st.stream()));
+    } else {
+      Slot &s = ring_.acquire(x_n_ * 4);
+      std::memcpy(s.hp, prio.data_ptr<float>(), (size_t)x_n_ * 4);
+      // straight from pinned memory into the peer-mapped block
+      if (have_ring_stream_ && st.stream() != ring_stream_) c10::cuda::device_synchronize();
+      ring_stream_ = st.stream();
+      have_ring_stream_ = true;
+      C10_CUDA_CHECK(cudaMemcpyAsync(blk + 8 * x_n_, s.hp, (size_t)x_n_ * 4, cudaMemcpyHostToDevice, st.stream()));
+      ring_.advance(st);
+    }
+    ok(g.peer_allgather_graph(xb0_, xb1_, xfl_, rank_, world_, reinterpret_cast<uint32_t *>(x_epoch_.data_ptr()), segs_,
+                              2, x_err_.data_ptr<int>(), st.stream()), "xp_peer_allgather_graph");
+    ok(g.per_update(&tree_, reinterpret_cast<xp_per_state *>(state_.data_ptr()), x_idx_.data_ptr<int64_t>(),
+                    x_prio_.data_ptr<float>(), x_n_ * world_, max_size_, alpha_, tree_err_.data_ptr<int>(), st.stream()),
+       "xp_per_update");
   }
 
   // update_priorities(indices, priorities): idx int64 CUDA contiguous; prio fp32 contiguous on the
@@ -242,6 +351,16 @@ class FastPer {
   int64_t max_size_;
   double alpha_;
   Ring ring_;
+  std::shared_ptr<FastGather> sibling_;
+  // replicated-update exchange (set_exchange)
+  const void *xb0_[XP_MAX_PEERS] = {nullptr}, *xb1_[XP_MAX_PEERS] = {nullptr};
+  void *xfl_[XP_MAX_PEERS] = {nullptr};
+  xp_peer_seg segs_[2];
+  at::Tensor x_epoch_, x_idx_, x_prio_, x_err_;
+  int world_ = 0, rank_ = 0;
+  int64_t x_n_ = 0;
+  cudaStream_t ring_stream_ = nullptr;
+  bool have_ring_stream_ = false;
 };
 
 }  // namespace
@@ -249,6 +368,7 @@ class FastPer {
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.doc() = "native fast path of the agilerl_b200 Python host (calls libb200xp.so)";
   m.def("bind", &bind);
+  m.def("bind_peer", &bind_peer);
   py::class_<FastGather, std::shared_ptr<FastGather>>(m, "FastGather")
       .def(py::init<std::vector<at::Tensor>, std::vector<std::string>, int64_t, at::Tensor>())
       .def("gather", &FastGather::gather);
@@ -256,5 +376,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def(py::init<std::shared_ptr<FastGather>, uint64_t, at::Tensor, at::Tensor, at::Tensor, at::Tensor,
                     int64_t, double>())
       .def("sample", &FastPer::sample)
-      .def("update", &FastPer::update);
+      .def("update", &FastPer::update)
+      .def("set_sibling", &FastPer::set_sibling)
+      .def("set_exchange", &FastPer::set_exchange)
+      .def("update_replicated", &FastPer::update_replicated);
 }

@@ -93,6 +93,13 @@ class PeerExchange:
         self._err_ev = None
         self._side = None
 
+    def base_addrs(self, k: int) -> list[int]:
+        """Peer-mapped address of block ``k`` on every rank (for native callers)."""
+        return [int(p) + k * self.block_bytes for p in self._hdl.buffer_ptrs]
+
+    def flag_addrs(self) -> list[int]:
+        return [int(p) + 2 * self.block_bytes for p in self._hdl.buffer_ptrs]
+
     def block(self, k: int) -> torch.Tensor:
         """This rank's block ``k`` (0/1) as a uint8 tensor: producers write their segments here."""
         return self._mem[k * self.block_bytes:(k + 1) * self.block_bytes]

@@ -150,10 +150,12 @@ class ReplicatedReplay:
     def update_priorities(self, local_idx: torch.Tensor, local_prio: torch.Tensor) -> None:
         """(idx, priority) pairs of this rank's agents -> applied everywhere in rank-major order
         (one batched last-writer-wins update per replica)."""
+        world = _group_size(self.group)
+        if world > 1 and self._peer_ok is not False and self._native_update(local_idx, local_prio):
+            return
         dev = self.memory.storage_device if _is_cuda_backend(self.group) else local_idx.device
         idx = torch.as_tensor(local_idx).to(device=dev, dtype=torch.int64).reshape(-1)
         pr = torch.as_tensor(local_prio).to(device=dev, dtype=torch.float32).reshape(-1)
-        world = _group_size(self.group)
         if world > 1 and _is_cuda_backend(self.group) and self._peer_ok is not False:
             # NVLink peer-memory exchange: one kernel signals, waits and pulls every rank's block
             n = idx.shape[0]
@@ -188,6 +190,57 @@ class ReplicatedReplay:
             self.memory.update_priorities(all_idx, all_pr)
             return
         self.memory.update_priorities(all_gather_rows(idx, self.group), all_gather_rows(pr, self.group))
+
+    def _native_update(self, local_idx, local_prio) -> bool:
+        """The whole replicated update in ONE native call (csrc/hostaccel.cpp ``FastPer.update_replicated``):
+        indices / priorities into this rank's peer-mapped block, the NVLink exchange kernel, the rank-major
+        update.  Taken when the indices are the canonical device tensor ``sample`` returned and the priorities
+        an fp32 array (host or device); anything else goes through the generic path below.  Returns False when
+        it did not run."""
+        mem = self.memory
+        if not (isinstance(local_idx, torch.Tensor) and local_idx.is_cuda and local_idx.dtype == torch.int64
+                and local_idx.is_contiguous() and _is_cuda_backend(self.group)):
+            return False
+        fp = getattr(mem, "_fast_per", None)
+        fp = fp() if fp is not None else None
+        if fp is None or local_idx.device != mem.storage_device or torch._C._cuda_getDevice() != local_idx.device.index:
+            return False
+        pr = local_prio if isinstance(local_prio, torch.Tensor) else torch.from_numpy(local_prio)
+        n = local_idx.numel()
+        if pr.dtype != torch.float32 or not pr.is_contiguous() or pr.numel() != n or (pr.is_cuda and pr.device != local_idx.device):
+            return False
+        try:
+            if self._px is None or self._px_n != n:
+                from . import peer
+
+                if not peer.available(self.group):
+                    raise RuntimeError("symmetric memory unavailable")
+                self._px = peer.PeerExchange(12 * n, [(0, 8 * n, torch.int64), (8 * n, 4 * n, torch.float32)],
+                                             torch.device(mem.storage_device), self.group)
+                self._px_n = n
+                self._peer_ok = True
+        except Exception:
+            if self._peer_ok:
+                raise
+            self._peer_ok = False
+            return False
+        px = self._px
+        if getattr(mem, "_xchg", None) is not px:  # bind the exchange to the buffer's native object once
+            fp.set_exchange(px.base_addrs(0), px.base_addrs(1), px.flag_addrs(), px.rank, px._epoch_dev,
+                            px._out[0], px._out[1], px.err, n)
+            mem._xchg = px
+        if mem._pending_err is not None:
+            mem._raise_deferred()
+        px._raise_if_failed()
+        fp.update_replicated(px.current, local_idx, pr)
+        px.epoch += 1
+        self._since_poll = getattr(self, "_since_poll", 0) + 1
+        if self._since_poll >= 32:  # a peer that never arrived / an index out of range: raised by a later call
+            self._since_poll = 0
+            px._poll_err_async()
+            if mem._pending_err is None:
+                mem._poll_err_async()
+        return True
 
     def sample(self, *args, **kwargs):
         """Sampling and gathering are local to a replica."""

@@ -445,6 +445,11 @@ class C2Workload:
         self.res_w_host = torch.empty(self.P * n, 1, dtype=torch.float32).pin_memory()
         self.res_ev = torch.cuda.Event()
         self.rep = None
+        # set-up, outside the timed loop: the two buffers are filled in lock-step, so
+        # memory.sample may gather both tables in one launch; the loop below keeps the reference's calls
+        import agilerl_b200
+
+        agilerl_b200.link_n_step(self.per, self.nstep)
         if self.world > 1:
             # the SAME algorithm as `value`: every agent's update is exchanged and applied on every replica
             from agilerl_b200.population import ReplicatedReplay
@@ -1076,7 +1081,9 @@ def b200_arm(args):
                "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo, "steps": Ke,
                "ms_per_step": ems / Ke,
                "api": "per agent: PrioritizedReplayBuffer.sample + MultiStepReplayBuffer."
-                      "sample_from_indices + update_priorities (host uniforms / host priorities)"}
+                      "sample_from_indices + update_priorities (host uniforms / host priorities); buffers linked once "
+                      "at set-up with agilerl_b200.link_n_step" + ("; updates through population.ReplicatedReplay "
+                      "(NVLink exchange + replicated update per agent)" if world > 1 else "")}
     clocks.stop()
 
     also = None

@@ -115,3 +115,69 @@ def test_deferred_index_error_through_fast_path(C, accel):
     b.update_priorities(bad, np.array([1.0, 2.0], dtype=np.float32))
     with pytest.raises(AssertionError):
         b.check_errors()
+
+
+def test_link_n_step_serves_sample_from_indices_from_one_gather(C, cuda_device, accel):
+    """agilerl_b200.link_n_step(memory, n_step_memory): PER.sample gathers both tables in one launch and the
+    reference's next call, n_step_memory.sample_from_indices(batch["idxs"]), is served from it — the same
+    rows as without the link; any other index tensor, a modified one, or an add in between fall back."""
+    import agilerl_b200
+    from agilerl_b200 import _native as nv
+
+    lib = nv.load()
+
+    def pair():
+        per = C.PrioritizedReplayBuffer(512, alpha=0.6, device=cuda_device)
+        nst = C.MultiStepReplayBuffer(512, n_step=3, gamma=0.9, device=cuda_device)
+        g = torch.Generator().manual_seed(3)
+        for _ in range(40):
+            n = 8
+            tr = C.TensorBatch({"obs": torch.randint(0, 255, (n, 2, 5), dtype=torch.uint8, generator=g),
+                                "action": torch.randn(n, generator=g), "reward": torch.randn(n, generator=g),
+                                "next_obs": torch.randint(0, 255, (n, 2, 5), dtype=torch.uint8, generator=g),
+                                "done": (torch.rand(n, generator=g) < 0.1).float()}, batch_size=[n])
+            one = nst.add(tr)
+            if one is not None:
+                per.add(one)
+        return per, nst, tr
+
+    per_a, nst_a, _ = pair()
+    per_b, nst_b, tr = pair()
+    agilerl_b200.link_n_step(per_b, nst_b)
+    for rnd in range(3):
+        torch.manual_seed(50 + rnd)
+        ea = per_a.sample(32, 0.4)
+        na = nst_a.sample_from_indices(ea["idxs"])
+        torch.manual_seed(50 + rnd)
+        c0 = lib.xp_launch_count()
+        eb = per_b.sample(32, 0.4)
+        c1 = lib.xp_launch_count()
+        nb = nst_b.sample_from_indices(eb["idxs"])
+        c2 = lib.xp_launch_count()
+        assert c1 - c0 == 2 and c2 == c1          # descent + ONE gather for both tables; nothing for the n-step call
+        assert torch.equal(ea["idxs"], eb["idxs"]) and torch.equal(ea["weights"], eb["weights"])
+        assert nb.batch_size == na.batch_size == torch.Size([32, 1])
+        for k in ("obs", "action", "reward", "next_obs", "done"):
+            assert torch.equal(ea[k], eb[k]) and torch.equal(na[k], nb[k]), k
+            assert nb[k].shape == na[k].shape
+        nb["reward"].zero_()                       # fresh copies: mutating them leaves the storage alone
+        assert float(nst_b.storage["reward"].abs().sum()) > 0
+    # fall-backs: another index tensor / a modified one / an add since the prefetch
+    eb = per_b.sample(16, 0.4)
+    other = eb["idxs"].clone()
+    c0 = lib.xp_launch_count()
+    r1 = nst_b.sample_from_indices(other)
+    assert lib.xp_launch_count() == c0 + 1 and torch.equal(r1["obs"], nst_b.storage["obs"][other.view(-1)].unsqueeze(1))
+    eb = per_b.sample(16, 0.4)
+    eb["idxs"].clamp_(max=3)
+    r2 = nst_b.sample_from_indices(eb["idxs"])
+    assert torch.equal(r2["reward"], nst_b.storage["reward"][eb["idxs"].view(-1)].unsqueeze(1))
+    eb = per_b.sample(16, 0.4)
+    one = nst_b.add(tr)
+    per_b.add(one)
+    r3 = nst_b.sample_from_indices(eb["idxs"])
+    assert torch.equal(r3["reward"], nst_b.storage["reward"][eb["idxs"].view(-1)].unsqueeze(1))
+    per_b.link_n_step(None)
+    c0 = lib.xp_launch_count()
+    per_b.sample(8, 0.4)
+    assert lib.xp_launch_count() == c0 + 2

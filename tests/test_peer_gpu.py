@@ -90,8 +90,21 @@ def _worker_rr(rank, world, port, out_dir):
     for step in range(5):
         idx = torch.randint(0, 24 * world, (16,), generator=g)
         rep.update_priorities(idx, torch.rand(16, generator=g) + 0.05)
+    # the learn-step pattern: device indices straight from sample(), priorities as an fp32 host array
+    # (dqn_rainbow.py:487) -> the one-call native path (FastPer.update_replicated)
+    native = []
+    for step in range(6):
+        batch = rep.sample(16, 0.4)
+        pr = (torch.rand(16, generator=g) + 0.05).numpy()
+        native.append(rep._native_update(batch["idxs"], pr) if step % 2 else None)
+        if not step % 2:
+            rep.update_priorities(batch["idxs"], pr)
     mem.check_errors()
-    torch.save({"peer": rep._peer_ok, "tree": mem._trees[2].nodes.cpu(), "obs": mem._leaves[("obs",)][:24 * world].cpu()},
+    rep._px.check()
+    from agilerl_b200 import _hostaccel
+
+    torch.save({"peer": rep._peer_ok, "tree": mem._trees[2].nodes.cpu(), "obs": mem._leaves[("obs",)][:24 * world].cpu(),
+                "native": [x for x in native if x is not None], "accel": _hostaccel.load() is not None},
                os.path.join(out_dir, f"q{rank}.pt"))
     dist.destroy_process_group()
 
@@ -101,6 +114,7 @@ def test_replicated_replay_uses_peer_exchange(tmp_path, world):
     _spawn(_worker_rr, world, tmp_path)
     q = [torch.load(tmp_path / f"q{r}.pt", weights_only=False) for r in range(world)]
     assert all(x["peer"] is True for x in q)
+    assert all(all(x["native"]) for x in q if x["accel"]), "the one-call native replicated update was not taken"
     for x in q[1:]:
         assert torch.equal(q[0]["tree"], x["tree"]) and torch.equal(q[0]["obs"], x["obs"])
 
