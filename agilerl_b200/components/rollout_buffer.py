@@ -606,19 +606,72 @@ class RolloutArena:
         self.gamma = kwargs.get("gamma", 0.99)
         self.gae_lambda = kwargs.get("gae_lambda", 0.95)
         self.use_gae = kwargs.get("use_gae", True)
+        self._foreign: set[int] = set()  # slots whose buffer does not live in the slab (adopt)
+
+    # -- keeping the one-launch path alive through evolution -------------------------------------------------
+    @classmethod
+    def from_buffers(cls, buffers: "list[RolloutBuffer]") -> "RolloutArena":
+        """Re-slab a population after a generation: an arena shaped like ``buffers[0]`` that ADOPTS every
+        buffer of the list (``[agent.rollout_buffer for agent in pop]``).  Buffers whose capacity or layout
+        differs (a mutated ``learn_step``, algorithms/ppo.py:336-339) stay standalone and get their own
+        launch."""
+        b0 = buffers[0]
+        arena = cls(len(buffers), b0.capacity, b0.observation_space, b0.action_space, num_envs=b0.num_envs,
+                    device=b0.device, gae_lambda=b0.gae_lambda, gamma=b0.gamma, recurrent=b0.recurrent,
+                    hidden_state_architecture=b0.hidden_state_architecture, use_gae=b0.use_gae,
+                    wrap_at_capacity=b0.wrap_at_capacity, max_seq_len=b0.max_seq_len,
+                    bptt_sequence_type=b0.bptt_sequence_type)
+        for i, b in enumerate(buffers):
+            arena.adopt(i, b)
+        return arena
+
+    def _fits(self, buffer: "RolloutBuffer") -> bool:
+        if buffer.capacity != self.capacity or buffer.num_envs != self.num_envs or buffer._sdev != self._sdev:
+            return False
+        return all(p in buffer._leaves and buffer._leaves[p].shape == t.shape[1:] and buffer._leaves[p].dtype == t.dtype
+                   for p, t in self.slab.items())
+
+    def adopt(self, index: int, buffer: "RolloutBuffer") -> "RolloutBuffer":
+        """Population slot ``index`` is served by ``buffer`` from now on — the SAME object the agent holds:
+        a deep copy made by ``agent.clone()`` (algorithms/core/base.py:444-503,871-937) or a fresh buffer from
+        ``create_rollout_buffer`` after a mutation (algorithms/ppo.py:336-339,360-378).  Its stored steps are
+        copied into the slab slot and its tables are re-bound to slab views, so one launch keeps covering the
+        whole population.  A buffer of another capacity / layout is kept as it is and computed by a launch of
+        its own.  Returns ``buffer``."""
+        if not 0 <= index < self.population:
+            raise IndexError(index)
+        self.buffers[index] = buffer
+        self._foreign.discard(index)
+        if not self._fits(buffer):
+            self._foreign.add(index)
+            return buffer
+        with nv.on_device(self._sdev):
+            for path, t in self.slab.items():
+                src = buffer._leaves[path]
+                if src.data_ptr() != t[index].data_ptr():
+                    t[index].copy_(src)
+                buffer._leaves[path] = t[index]
+        buffer.buffer = _nest(buffer._leaves, [buffer.capacity, buffer.num_envs])
+        return buffer
 
     def compute_returns_and_advantages(self, last_values, last_dones) -> None:
         """last_values / last_dones: ``[P, num_envs]`` (tensor or array). All agents must hold the
         same number of steps (they do: one collection phase per generation)."""
-        sizes = {b.capacity if b.full else b.pos for b in self.buffers}
-        if len(sizes) != 1:
-            raise ValueError(f"agents hold different numbers of steps: {sorted(sizes)}")
-        T = sizes.pop()
         P, N = self.population, self.num_envs
+        members = [i for i in range(P) if i not in self._foreign]
         lv = _as_f64(last_values, P * N, self._sdev)
         ld = _as_f64(last_dones, P * N, self._sdev)
-        S = self.slab
-        with nv.on_device(self._sdev):
-            xp.gae(S[("rewards",)], S[("values",)], S[("dones",)], lv, ld, S[("advantages",)],
-                   S[("returns",)], T, N, P, self.capacity * N, float(self.gamma),
-                   float(self.gae_lambda), bool(self.use_gae))
+        if members:
+            sizes = {self.buffers[i].capacity if self.buffers[i].full else self.buffers[i].pos for i in members}
+            if len(sizes) != 1:
+                raise ValueError(f"agents hold different numbers of steps: {sorted(sizes)}")
+            T = sizes.pop()
+            S = self.slab
+            # ONE launch over every slot of the slab (a slot whose buffer is standalone is computed too and
+            # ignored: cheaper than a second launch)
+            with nv.on_device(self._sdev):
+                xp.gae(S[("rewards",)], S[("values",)], S[("dones",)], lv, ld, S[("advantages",)],
+                       S[("returns",)], T, N, P, self.capacity * N, float(self.gamma),
+                       float(self.gae_lambda), bool(self.use_gae))
+        for i in sorted(self._foreign):
+            self.buffers[i].compute_returns_and_advantages(lv.view(P, N)[i], ld.view(P, N)[i])

@@ -146,3 +146,63 @@ def test_replay_dict_observations_size_setter_storage(cuda_device):  # :302-340,
             assert s["weights"].shape == (5, 1) and s["idxs"].shape == (5, 1)
         buf.size = 5
         assert buf._size == 5 and len(buf) == 5
+
+
+def test_arena_keeps_one_launch_through_clone_and_mutation(cuda_device):
+    """The evolutionary loop deep-copies a winner's buffer (agent.clone(), algorithms/core/base.py:444-503) and
+    re-creates buffers after a mutation (algorithms/ppo.py:336-339,360-378).  RolloutArena.adopt re-attaches such a
+    buffer — the same object the agent holds — to the slab, so ONE launch still covers the population; a buffer of
+    another capacity gets a launch of its own.  Results bit-equal to per-agent compute_returns_and_advantages."""
+    import copy
+
+    import agilerl_b200.components as C
+    from agilerl_b200 import _native as nv
+    from agilerl_b200.components import spaces
+
+    lib = nv.load()
+    P, T, N = 4, 12, 32
+    osp, asp = spaces.Box(-1, 1, (5,)), spaces.Discrete(3)
+    arena = C.RolloutArena(P, T, osp, asp, num_envs=N, device=cuda_device, gamma=0.97, gae_lambda=0.9)
+    rng = np.random.default_rng(0)
+
+    def fill(buf, steps):
+        buf.reset()
+        for _ in range(steps):
+            buf.add(obs=rng.standard_normal((N, 5)).astype(np.float32), action=rng.integers(0, 3, N),
+                    reward=rng.standard_normal(N).astype(np.float32), done=rng.random(N) < 0.1,
+                    value=rng.standard_normal(N).astype(np.float32), log_prob=rng.standard_normal(N).astype(np.float32))
+
+    for b in arena.buffers:
+        fill(b, T)
+    # tournament: agent 1 wins, its clone replaces agent 3; agent 2 is mutated to a shorter learn_step
+    clone = copy.deepcopy(arena.buffers[1])
+    assert clone._leaves[("rewards",)].data_ptr() != arena.slab[("rewards",)][1].data_ptr()  # standalone copy
+    got = arena.adopt(3, clone)
+    assert got is clone and arena.buffers[3] is clone
+    assert clone._leaves[("rewards",)].data_ptr() == arena.slab[("rewards",)][3].data_ptr()  # re-bound to the slab
+    assert torch.equal(clone.buffer["rewards"], arena.buffers[1].buffer["rewards"])           # contents came along
+    mutated = C.RolloutBuffer(T // 2, osp, asp, num_envs=N, device=cuda_device, gamma=0.97, gae_lambda=0.9)
+    arena.adopt(2, mutated)
+    assert 2 in arena._foreign
+    # next generation: everybody collects again through the objects the agents hold
+    for b in arena.buffers:
+        fill(b, b.capacity)
+    lv = rng.standard_normal((P, N)).astype(np.float32)
+    ld = rng.random((P, N)) < 0.2
+    c0 = lib.xp_launch_count()
+    arena.compute_returns_and_advantages(lv, ld)
+    assert lib.xp_launch_count() - c0 == 2  # the slab in one launch + the buffer of another capacity
+    for i, b in enumerate(arena.buffers):
+        ref = C.RolloutBuffer(b.capacity, osp, asp, num_envs=N, device=cuda_device, gamma=0.97, gae_lambda=0.9)
+        for k in ("rewards", "values", "dones"):
+            ref.buffer[k][:] = b.buffer[k]
+        ref.pos, ref.full = b.pos, b.full
+        ref.compute_returns_and_advantages(lv[i], ld[i])
+        assert torch.equal(ref.buffer["advantages"], b.buffer["advantages"]), i
+        assert torch.equal(ref.buffer["returns"], b.buffer["returns"]), i
+    # re-slab the whole population after the generation: the odd one out stays standalone
+    arena2 = C.RolloutArena.from_buffers(arena.buffers)
+    assert arena2._foreign == {2} and all(x is y for x, y in zip(arena2.buffers, arena.buffers))
+    before = [b.buffer["advantages"].clone() for b in arena2.buffers]
+    arena2.compute_returns_and_advantages(lv, ld)
+    assert all(torch.equal(x, b.buffer["advantages"]) for x, b in zip(before, arena2.buffers))
