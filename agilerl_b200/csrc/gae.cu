@@ -30,6 +30,7 @@ namespace {
 
 constexpr int kModeGae = 0;
 constexpr int kModeMc = 1;
+constexpr int kDefaultGaePdl = 0;      // see launch_scan
 constexpr bool kDefaultLanes = false;  // which kernel xp_gae launches by default
 
 struct ScanParams {
@@ -176,8 +177,13 @@ __global__ void __launch_bounds__(kThreads, 4) gae_tile_kernel(const ScanParams 
 // ---- TMA-fed kernel (aligned shapes): see gae_tma.cuh -------------------------------------------
 template <int MODE>
 __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams p,
-                                                     const __grid_constant__ gaetma::Maps maps) {
+                                                     const __grid_constant__ gaetma::Maps maps, const int pdl) {
   using namespace gaetma;
+  // programmatic launch: nothing above this line touches global memory, so stream order is kept exactly
+  if (pdl) {
+    if (pdl == 1) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+  }
   extern __shared__ __align__(128) unsigned char smem_tma[];
   Stage *stage = reinterpret_cast<Stage *>(smem_tma);
   __shared__ __align__(8) unsigned long long bars[kStages];
@@ -207,6 +213,9 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
   if (lane == 0) {
     for (int b = 0; b < kStages && b < nbox; ++b) issue(b);
   }
+  // every load of a short strip is in flight: let the next grid of the stream become resident now (it blocks at
+  // its own griddepcontrol.wait until this grid has completed and flushed)
+  if (pdl == 2 && nbox <= kStages) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   const bool env_ok = env0 + lane < p.N;
   double lv = 0.0, ld = 0.0;
@@ -617,7 +626,16 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
       }
       // (programmatic dependent launch was measured and dropped: early-resident CTAs of the next
       // launch slowed the running one, 11.5 vs 11.0 us at C3)
-      gae_tma_kernel<MODE><<<(unsigned)grid_tma, gaetma::kBoxE, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps);
+      static const int pdl = [] {
+        const char *e = getenv("XP_GAE_PDL");  // developer knob: 0 plain | 1 release at entry | 2 release after the loads
+        return (e && e[0]) ? atoi(e) : kDefaultGaePdl;
+      }();
+      if (pdl && xp::pdl_enabled()) {
+        xp::launch(gae_tma_kernel<MODE>, dim3((unsigned)grid_tma), dim3(gaetma::kBoxE),
+                   sizeof(gaetma::Stage) * gaetma::kStages, s, p, maps, pdl);
+      } else {
+        gae_tma_kernel<MODE><<<(unsigned)grid_tma, gaetma::kBoxE, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps, 0);
+      }
       return xp::check_launch("xp_gae (tma)");
     }
   }
