@@ -260,6 +260,23 @@ class ReplayBuffer:
         shape of the result (the shape of ``indices`` in the reference's ``storage[idxs]``)."""
         dev = self.storage_device
         idx = indices
+        if not idx.is_cuda and idx.numel():
+            # host indices: checked here like `storage[idx]` does (IndexError; Python negative indexing)
+            lo, hi = int(idx.min()), int(idx.max())
+            if lo < -self.max_size or hi >= self.max_size:
+                raise IndexError(f"index {lo if lo < -self.max_size else hi} is out of bounds for dimension 0 "
+                                 f"with size {self.max_size}")
+            if lo < 0:
+                idx = torch.where(idx < 0, idx + self.max_size, idx)
+        elif idx.is_cuda:
+            # device indices: the kernel zero-fills a row whose index is out of range and raises a sticky flag,
+            # read back without blocking every 32 gathers and reported by a later call (check_errors() forces it)
+            self._gathers_since_poll = getattr(self, "_gathers_since_poll", 0) + 1
+            if getattr(self, "_gerr_pending", None) is not None:
+                self._raise_gather_error()
+            elif self._gathers_since_poll >= 32 and self._err is not None:
+                self._gathers_since_poll = 0
+                self._poll_gather_error()
         if idx.device != dev or idx.dtype != torch.int64:
             idx = idx.to(device=dev, dtype=torch.int64)
         if idx.dim() != 1 or not idx.is_contiguous():
@@ -299,6 +316,32 @@ class ReplayBuffer:
             tb.batch_size = torch.Size(lead)
             return tb
         return _unflatten({p: out[p] for p in self._leaves}, list(lead))
+
+    def _poll_gather_error(self) -> None:
+        if getattr(self, "_gerr_pin", None) is None:
+            self._gerr_pin = torch.zeros(1, dtype=torch.int32).pin_memory()
+            self._gerr_ev = torch.cuda.Event()
+        with nv.on_device(self.storage_device):
+            self._gerr_pin.copy_(self._err, non_blocking=True)
+            self._gerr_ev.record()
+        self._gerr_pending = True
+
+    def _raise_gather_error(self, wait: bool = False) -> None:
+        if wait:
+            self._gerr_ev.synchronize()
+        if self._gerr_ev.query():
+            self._gerr_pending = None
+            if int(self._gerr_pin[0]) != 0:
+                self._err.zero_()
+                raise IndexError(f"a sampled index was out of bounds for dimension 0 with size {self.max_size} "
+                                 "(device indices are checked by the gather kernel; the rows came back as zeros)")
+
+    def check_gather_errors(self) -> None:
+        """Block until every queued gather ran and raise its IndexError, if any (device-side indices)."""
+        if self._err is None:
+            return
+        self._poll_gather_error()
+        self._raise_gather_error(wait=True)
 
     def sample(self, batch_size: int, return_idx: bool = False) -> TensorBatch:
         indices = self._uniform_indices(batch_size)

@@ -19,9 +19,17 @@
 
 namespace gaetma {
 
-constexpr int kBoxT = 32;    // time steps per box
-constexpr int kBoxE = 32;    // envs per box = threads per CTA
-constexpr int kStages = 4;   // boxes in flight per CTA
+#ifndef XP_GAE_BOXT
+#define XP_GAE_BOXT 64
+#endif
+#ifndef XP_GAE_STAGES
+#define XP_GAE_STAGES 2
+#endif
+// box sweep at C3 / 16x (us per launch): 8x16 13.5 / 109.8, 16x8 11.8 / 94.5, 32x4 11.1 / 94.1, 64x2 10.95 / 93.3,
+// 128x1 12.6 / 95.4 (nothing overlaps the strip's arrival), 128x2 17.2 / 132.7 (72 KB per CTA: 3 CTAs per SM)
+constexpr int kBoxT = XP_GAE_BOXT;      // time steps per box (a multiple of 8)
+constexpr int kBoxE = 32;               // envs per box = threads per CTA
+constexpr int kStages = XP_GAE_STAGES;  // boxes in flight per CTA
 constexpr int kStageBytes = kBoxT * kBoxE * (4 + 4 + 1);  // 9216
 
 struct __align__(128) Stage {

@@ -368,3 +368,23 @@ def test_walk_every_public_method(C, cuda_device):
     assert ro.get_tensor_batch()["advantages"].shape[0] == 8 and ro.get_tensor_batch(3)["advantages"].shape[0] == 3
     ro.reset()
     assert ro.size() == 0 and not ro.full
+
+
+def test_sample_from_indices_index_errors_and_negative_indices(C, cuda_device):
+    """``storage[idxs]`` semantics (replay_buffer.py:196-204): host indices raise IndexError at once and negative
+    ones wrap like Python's; device indices are checked by the kernel and reported by a later call."""
+    b = C.MultiStepReplayBuffer(max_size=16, n_step=1, device=cuda_device)
+    for i in range(16):
+        b.add(C.TensorBatch({"obs": torch.full((1, 2), float(i)), "action": torch.zeros(1), "reward": torch.ones(1),
+                             "next_obs": torch.zeros(1, 2), "done": torch.zeros(1)}, batch_size=[1]))
+    got = b.sample_from_indices(torch.tensor([-1, 0, -16]))
+    assert got["obs"][:, 0].tolist() == [15.0, 0.0, 0.0]
+    with pytest.raises(IndexError):
+        b.sample_from_indices(torch.tensor([3, 16]))
+    with pytest.raises(IndexError):
+        b.sample_from_indices(torch.tensor([-17]))
+    out = b.sample_from_indices(torch.tensor([2, 99], device=cuda_device))  # device indices: no host sync here
+    assert out["obs"][0, 0].item() == 2.0 and out["obs"][1].abs().sum().item() == 0.0
+    with pytest.raises(IndexError):
+        b.check_gather_errors()
+    b.check_gather_errors()  # flag cleared
