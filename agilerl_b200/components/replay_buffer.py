@@ -147,6 +147,19 @@ class ReplayBuffer:
     def _prepare(self, data) -> tuple[TensorBatch, int]:
         """``.to(device)`` and the 1-D -> (n,1) reshape of :79-94 (which mutates ``data``)."""
         data = as_batch(data)
+        # fast path (the per-env-step case): flat keys, every tensor already on the storage device — `.to` is
+        # the identity then and only the reference's in-place 1-D -> (n,1) reshape is left
+        d = data._d
+        dev = self.storage_device
+        for item in d.values():
+            if not isinstance(item, torch.Tensor) or item.device != dev:
+                break
+        else:
+            n = data.batch_size[0]
+            for key, item in d.items():
+                if item.ndim == 1:
+                    d[key] = item.reshape(n, 1)
+            return data, n
         data = data.to(self.storage_device)
         n = data.shape[0]
         for key, item in list(data.items()):
@@ -170,12 +183,53 @@ class ReplayBuffer:
             pairs.append((t.contiguous(), d))
         return pairs
 
+    def _insert(self, data: TensorBatch, dst: dict[tuple, torch.Tensor], n: int, cursor: int, rows: int,
+                slot: str) -> None:
+        """Ring-write the ``n`` rows of ``data`` into the table ``dst`` at ``cursor`` (one launch for every key).
+        The launch descriptor of a table — destination pointers, row sizes, dtypes — is built once and kept
+        under ``slot``; per call only the source pointers change."""
+        tab = self.__dict__.get(slot)
+        if tab is None or tab[0] is not dst:
+            paths = list(dst.keys())
+            keys = (nv.XpKey * len(paths))()
+            meta = []
+            for i, p in enumerate(paths):
+                t = dst[p]
+                keys[i].dst = t.data_ptr()
+                keys[i].row_bytes = xp.row_bytes(t)
+                meta.append((p, p[0] if len(p) == 1 else None, t.dtype, tuple(t.shape[1:])))
+            tab = (dst, keys, meta, nv.load().xp_ring_insert, len(paths))
+            self.__dict__[slot] = tab
+        _, keys, meta, fn, nk = tab
+        d = data._d
+        if len(d) != nk or n == 0:
+            # nested / missing / extra keys, empty batch: the general path (same checks and errors as before)
+            with nv.on_device(self.storage_device):
+                xp.ring_insert(self._pairs(data, dst), n, cursor, rows)
+            return
+        keep = []
+        for i, (path, flat_key, dtype, tail) in enumerate(meta):
+            t = d.get(flat_key) if flat_key is not None else None
+            if not isinstance(t, torch.Tensor) or tuple(t.shape[1:]) != tail:
+                with nv.on_device(self.storage_device):
+                    xp.ring_insert(self._pairs(data, dst), n, cursor, rows)
+                return
+            if t.dtype != dtype:
+                t = t.to(dtype)
+                keep.append(t)
+            if not t.is_contiguous():
+                t = t.contiguous()
+                keep.append(t)
+            keys[i].src = t.data_ptr()
+        dev = self.storage_device
+        with nv.on_device(dev):
+            nv.check(fn(keys, nk, n, cursor, rows, nv.raw_stream(dev.index)), "xp_ring_insert")
+
     def add(self, data: DataType) -> None:
         data, n = self._prepare(data)
         if self._storage is None:
             self._init(data)
-        with nv.on_device(self.storage_device):
-            xp.ring_insert(self._pairs(data, self._leaves), n, self._cursor, self.max_size)
+        self._insert(data, self._leaves, n, self._cursor, self.max_size, "_ins_storage")
         self._advance(n)
 
     def _add_rows_with(self, n: int, insert) -> None:
@@ -383,6 +437,9 @@ class MultiStepReplayBuffer(ReplayBuffer):
                                       device=self.storage_device)
                        for p, t in _flatten(data)}
         self._nstage_n = n
+        # the views of the stage ring handed out as n_step_buffer entries never change: one per slot
+        self._slot_views = [_unflatten({p: t[k * n:(k + 1) * n] for p, t in self._nstage.items()}, [n])
+                            for k in range(self.n_step)]
 
     def _detect_keys(self) -> None:
         first = self.n_step_buffer[0]
@@ -403,6 +460,16 @@ class MultiStepReplayBuffer(ReplayBuffer):
     def _fold_into(self, dst: dict[tuple, torch.Tensor], cursor: int, dst_rows: int) -> None:
         if not self.initialized or self.done_key is None:
             self._detect_keys()
+        fd = self.__dict__.get("_fold_desc")
+        if fd is not None and fd[0] is self._nstage and fd[1] is dst and fd[2] == (self.n_step, self.gamma, self.reward_key,
+                                                                                   self.done_key, self.ns_key):
+            # the launch descriptor of this (stage ring, destination table) pair, built by the general path below
+            _, _, _, keys, roles, nk, done_idx, done_bytes, gpow, fn = fd
+            dev = self.storage_device
+            with nv.on_device(dev):
+                nv.check(fn(keys, roles, nk, done_idx, done_bytes, self.n_step, self._nstage_count % self.n_step, gpow,
+                            self._nstage_n, cursor, dst_rows, nv.raw_stream(dev.index)), "xp_nstep_fold_insert")
+            return
         paths = list(self._nstage.keys())
         roles = []
         for p in paths:
@@ -428,6 +495,12 @@ class MultiStepReplayBuffer(ReplayBuffer):
             xp.nstep_fold_insert([(self._nstage[p], dst[p]) for p in paths], roles,
                                  paths.index(done_path), done_bytes, self.n_step, slot0, gpow,
                                  self._nstage_n, cursor, dst_rows)
+        import ctypes as _C
+
+        self._fold_desc = (self._nstage, dst, (self.n_step, self.gamma, self.reward_key, self.done_key, self.ns_key),
+                           xp.make_keys([(self._nstage[p], dst[p]) for p in paths]), (_C.c_int * len(paths))(*roles),
+                           len(paths), paths.index(done_path), done_bytes, (_C.c_float * len(gpow))(*gpow),
+                           nv.load().xp_nstep_fold_insert)
 
     def add(self, data: DataType) -> TensorBatch | None:
         data, n = self._prepare(data)
@@ -436,10 +509,9 @@ class MultiStepReplayBuffer(ReplayBuffer):
         if n != self._nstage_n:
             raise ValueError(f"n-step buffer was initialised with {self._nstage_n} envs, got {n}")
         slot = self._nstage_count % self.n_step
-        with nv.on_device(self.storage_device):
-            xp.ring_insert(self._pairs(data, self._nstage), n, slot * n, self.n_step * n)
+        self._insert(data, self._nstage, n, slot * n, self.n_step * n, "_ins_stage")
         self._nstage_count += 1
-        view = _unflatten({p: t[slot * n:(slot + 1) * n] for p, t in self._nstage.items()}, [n])
+        view = self._slot_views[slot]
         self.n_step_buffer.append(view)
 
         if len(self.n_step_buffer) < self.n_step:
@@ -560,11 +632,13 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         data, n = self._prepare(data)
         if self._storage is None:
             self._init(data)
-        _, _, st, h = self._ensure_trees()
-        with nv.on_device(self.storage_device):
-            xp.ring_insert(self._pairs(data, self._leaves), n, self._cursor, self.max_size)
+        self._ensure_trees()
+        self._insert(data, self._leaves, n, self._cursor, self.max_size, "_ins_storage")
+        dev = self.storage_device
+        with nv.on_device(dev):
             # leaves tree_ptr.. := max_priority ** alpha (:306-309), no host round trip
-            xp.per_add(h, self._state, self.tree_ptr, n, self.max_size, self.alpha)
+            nv.check(self._lib.xp_per_add(self._href, self._state.data_ptr(), self.tree_ptr, n, self.max_size,
+                                          self.alpha, nv.raw_stream(dev.index)), "xp_per_add")
         self._advance(n)
         self.tree_ptr = (self.tree_ptr + n) % self.max_size
 

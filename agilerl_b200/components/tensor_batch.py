@@ -44,12 +44,10 @@ class TensorBatch:
     # -- conversion --------------------------------------------------------------------------
     @staticmethod
     def _wrap(v, batch_size):
-        if isinstance(v, TensorBatch):
+        if isinstance(v, torch.Tensor) or isinstance(v, TensorBatch):  # the common cases first
             return v
         if isinstance(v, Mapping):
             return TensorBatch(v, batch_size=batch_size)
-        if isinstance(v, torch.Tensor):
-            return v
         return torch.as_tensor(v)
 
     # -- mapping -----------------------------------------------------------------------------
