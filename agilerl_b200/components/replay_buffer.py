@@ -733,27 +733,29 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         return self._out(samples)
 
     def _fast_per(self):
-        """Native host fast path of sample / update_priorities, or None."""
+        """Native host fast path of sample / update_priorities, or None.  Valid while the storage table, the
+        tree pair and the linked sibling's table are the objects it was built for (three identity tests)."""
+        fp = self.__dict__.get("_fper")
+        sib = self._sibling
+        sl = sib._leaves if sib is not None else None
+        if fp is not None and fp[0] is self._leaves and fp[1] is self._trees and fp[3] is sl:
+            return fp[2]
         tab = self._fast_table()
         if tab is None:
             return None
-        fp = getattr(self, "_fper", None)
-        sib = self._sibling
         stab = None
         if sib is not None and sib._leaves and sib.max_size == self.max_size and sib.storage_device == self.storage_device \
                 and len(sib._leaves) + len(self._leaves) <= 24:
             stab = sib._fast_table()
-        if fp is None or fp[0] is not tab or fp[1] is not self._trees or fp[3] is not stab:
-            import ctypes as _C
+        import ctypes as _C
 
-            _, _, st, h = self._ensure_trees()
-            obj = _hostaccel.load().FastPer(tab, _C.addressof(h), st.nodes, st.aux, self._state, st.err,
-                                            self.max_size, float(self.alpha))
-            obj.set_sibling(stab)
-            fp = (tab, self._trees, obj, stab)
-            self._fper = fp
-            self._xchg = None  # a replicated-update exchange bound to the previous object is gone with it
-        return fp[2]
+        _, _, st, h = self._ensure_trees()
+        obj = _hostaccel.load().FastPer(tab, _C.addressof(h), st.nodes, st.aux, self._state, st.err,
+                                        self.max_size, float(self.alpha))
+        obj.set_sibling(stab)
+        self._fper = (self._leaves, self._trees, obj, sl)
+        self._xchg = None  # a replicated-update exchange bound to the previous object is gone with it
+        return obj
 
     def link_n_step(self, n_step_memory: "MultiStepReplayBuffer | None") -> None:
         """Optional: tell this buffer which ``MultiStepReplayBuffer`` is filled in lock-step with it

@@ -4,6 +4,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
+
 #include "b200xp.h"
 
 #ifndef __CUDA_ARCH__
@@ -38,6 +40,22 @@ inline xp_status_t check_launch(const char *what, int n_kernels = 1) {
       return (code);                \
     }                               \
   } while (0)
+
+// "this set-up has been done on the current device" latch (cudaFuncSetAttribute is per device).  Different
+// buffers may be driven from different host threads (one thread per buffer): a plain static bool would be a
+// data race; here the worst case is two threads doing the same idempotent set-up once each.
+struct DeviceOnce {
+  std::atomic<bool> v[64];
+  DeviceOnce() {
+    for (auto &x : v) x.store(false, std::memory_order_relaxed);
+  }
+  static int dev() {
+    int d = 0;
+    return (cudaGetDevice(&d) == cudaSuccess && d >= 0 && d < 64) ? d : 0;
+  }
+  bool done() const { return v[dev()].load(std::memory_order_acquire); }
+  void set() { v[dev()].store(true, std::memory_order_release); }
+};
 
 // ---- programmatic dependent launch ------------------------------------------------------
 // The path is a chain of short kernels on one stream (sample -> gather -> gather -> update; hist ->

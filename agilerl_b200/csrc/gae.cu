@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
       }
     }
     fence_proxy_async();  // generic-proxy writes above -> visible to the TMA store
-    __syncthreads();      // both warps are done with the box
+    __syncthreads();      // the warp is done with the box
     if (lane == 0) {
       tma_store_3d(&maps.adv, env0, t0, agent, &st.r[0][0]);
       tma_store_3d(&maps.ret, env0, t0, agent, &st.v[0][0]);
@@ -481,16 +481,15 @@ typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, voi
                              CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
                              CUtensorMapFloatOOBfill);
 EncodeFn get_encode() {
-  static EncodeFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
+  // a function-local static is initialised exactly once, thread-safely (C++11)
+  static const EncodeFn fn = [] {
     void *f = nullptr;
     cudaDriverEntryPointQueryResult q;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
         q == cudaDriverEntryPointSuccess)
-      fn = (EncodeFn)f;
-  }
+      return (EncodeFn)f;
+    return (EncodeFn) nullptr;
+  }();
   return fn;
 }
 
@@ -613,8 +612,8 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
     if (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
         encode_map(&maps.d, p.dones, 1, p) && encode_map(&maps.adv, p.adv, 4, p) &&
         encode_map(&maps.ret, p.ret, 4, p)) {
-      static bool tma_attr[2] = {false, false};
-      if (!tma_attr[MODE]) {
+      static xp::DeviceOnce tma_attr[2];
+      if (!tma_attr[MODE].done()) {
         cudaError_t e = cudaFuncSetAttribute((const void *)gae_tma_kernel<MODE>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)(sizeof(gaetma::Stage) * gaetma::kStages));
@@ -622,7 +621,7 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
           xp::set_error("xp_gae: %s", cudaGetErrorString(e));
           return XP_ERR_CUDA;
         }
-        tma_attr[MODE] = true;
+        tma_attr[MODE].set();
       }
       // (programmatic dependent launch was measured and dropped: early-resident CTAs of the next
       // launch slowed the running one, 11.5 vs 11.0 us at C3)
@@ -639,15 +638,15 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
       return xp::check_launch("xp_gae (tma)");
     }
   }
-  static bool attr[2] = {false, false};
-  if (!attr[MODE]) {
+  static xp::DeviceOnce attr[2];
+  if (!attr[MODE].done()) {
     cudaError_t e = cudaFuncSetAttribute((const void *)gae_tile_kernel<MODE>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Tile));
     if (e != cudaSuccess) {
       xp::set_error("xp_gae: %s", cudaGetErrorString(e));
       return XP_ERR_CUDA;
     }
-    attr[MODE] = true;
+    attr[MODE].set();
   }
   gae_tile_kernel<MODE><<<(unsigned)grid, kThreads, sizeof(Tile), s>>>(p);
   return xp::check_launch("xp_gae");

@@ -381,15 +381,15 @@ xp_status_t xp_gae_tokens(const float *rewards, const float *values, const float
   if (B == 0 || S == 0) return XP_OK;
   XP_REQUIRE(rewards && values && mask && adv && ret, XP_ERR_INVALID, "xp_gae_tokens: null pointer");
   volatile double gl = gamma * gae_lambda;  // one Python-float product, rounded to fp32 by the tensor op
-  static bool attr = false;
-  if (!attr) {
+  static xp::DeviceOnce attr;
+  if (!attr.done()) {
     cudaError_t e = cudaFuncSetAttribute((const void *)gae_token_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)(2 * sizeof(TokStage)));
     if (e != cudaSuccess) {
       xp::set_error("xp_gae_tokens: %s", cudaGetErrorString(e));
       return XP_ERR_CUDA;
     }
-    attr = true;
+    attr.set();
   }
   const uintptr_t a = reinterpret_cast<uintptr_t>(rewards) | reinterpret_cast<uintptr_t>(values) |
                       reinterpret_cast<uintptr_t>(mask) | reinterpret_cast<uintptr_t>(adv) |

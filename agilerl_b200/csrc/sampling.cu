@@ -159,15 +159,15 @@ xp_status_t xp_randperm_prefix(const uint32_t *raw_dev, int64_t B, int64_t P, in
     int log_slots = 2;
     while ((1 << log_slots) < 4 * npow2) ++log_slots;
     const size_t hsmem = (size_t)8 << log_slots;
-    static bool hattr = false;
-    if (hsmem > 48 * 1024 && !hattr) {
+    static xp::DeviceOnce hattr;
+    if (hsmem > 48 * 1024 && !hattr.done()) {
       cudaError_t e = cudaFuncSetAttribute(randperm_prefix_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            128 * 1024);
       if (e != cudaSuccess) {
         xp::set_error("xp_randperm_prefix: %s", cudaGetErrorString(e));
         return XP_ERR_CUDA;
       }
-      hattr = true;
+      hattr.set();
     }
     const int hthreads = npow2 < kSortThreads ? (npow2 < 32 ? 32 : npow2) : kSortThreads;
     xp::launch(randperm_prefix_hash_kernel, dim3((unsigned)P), dim3(hthreads), hsmem, (cudaStream_t)stream,
@@ -175,14 +175,14 @@ xp_status_t xp_randperm_prefix(const uint32_t *raw_dev, int64_t B, int64_t P, in
     return xp::check_launch("xp_randperm_prefix");
   }
   const size_t smem = (size_t)npow2 * sizeof(unsigned long long);
-  static bool attr_set = false;
-  if (smem > 48 * 1024 && !attr_set) {
+  static xp::DeviceOnce attr_set;
+  if (smem > 48 * 1024 && !attr_set.done()) {
     cudaError_t e = cudaFuncSetAttribute(randperm_prefix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (1 << kIdxBits) * 8);
     if (e != cudaSuccess) {
       xp::set_error("xp_randperm_prefix: %s", cudaGetErrorString(e));
       return XP_ERR_CUDA;
     }
-    attr_set = true;
+    attr_set.set();
   }
   const int threads = npow2 < kSortThreads ? (npow2 < 32 ? 32 : npow2) : kSortThreads;
   xp::launch(randperm_prefix_kernel, dim3((unsigned)P), dim3(threads), smem, (cudaStream_t)stream,

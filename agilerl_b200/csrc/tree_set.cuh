@@ -800,14 +800,14 @@ inline int ilog2(long long v) {
   return l;
 }
 
-inline xp_status_t set_attr_once(const void *fn, size_t bytes, bool &done) {
-  if (done) return XP_OK;
+inline xp_status_t set_attr_once(const void *fn, size_t bytes, xp::DeviceOnce &done) {
+  if (done.done()) return XP_OK;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   if (e != cudaSuccess) {
     xp::set_error("tree set: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return XP_ERR_CUDA;
   }
-  done = true;
+  done.set();
   return XP_OK;
 }
 
@@ -876,7 +876,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     const unsigned grid = (unsigned)(nb / warps);
     size_t smem = (size_t)B * 4;
     if (B > kMidCompactFrom && smem < (size_t)kMidListCap * 8) smem = (size_t)kMidListCap * 8;
-    static bool mid_attr[2] = {false, false};
+    static xp::DeviceOnce mid_attr[2];
     xp_status_t rc = set_attr_once(paired ? (const void *)set_mid_kernel<true> : (const void *)set_mid_kernel<false>,
                                    (size_t)65536, mid_attr[paired ? 1 : 0]);
     if (rc != XP_OK) return rc;
@@ -920,7 +920,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
     Buckets bk = make_buckets(t, (int)nb, shift, B, want_vals);
     bk.top = top;
     xp::launch(set_hist_kernel, dim3(grid), dim3(256), 0, st, t, s, B, bk);
-    static bool scan_attr = false;
+    static xp::DeviceOnce scan_attr;
     {
       xp_status_t rc = set_attr_once((const void *)set_scan_kernel, (size_t)(32768 + 1024) * 4, scan_attr);
       if (rc != XP_OK) return rc;

@@ -888,7 +888,7 @@ def also_single_gpu(dev, with_cpu=True):
     c5["roofline"] = roofline(c5["algorithmic_bytes"], c5["us_sample"], kernel="move_kernel", capture="ncu_gather_c5.txt")
     cpu(c5, "time_c5", 6.0)
     torch.cuda.empty_cache()
-    ins = bench_insert(dev)
+    ins = cpu(bench_insert(dev), "time_insert", 3.0)
     torch.cuda.empty_cache()
     c1 = cpu(bench_c1(dev), "time_c1", 3.0)
     return [g, ga, g16, p, c5, ins, c1]

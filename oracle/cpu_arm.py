@@ -394,3 +394,37 @@ def time_c5(seconds: float, cap=10_000_000, B=1024) -> dict:
 
 def time_c1(seconds: float, cap=100_000, B=64) -> dict:
     return time_uniform(seconds, cap, B, cartpole_row, "C1 DQN CartPole uniform replay", fill_seconds=5.0)
+
+
+# ---- insert side: per env step, MultiStepReplayBuffer.add -> PrioritizedReplayBuffer.add ---------------------
+def time_insert(seconds: float, cap=65536, num_envs=16, n_step=3, gamma=0.99, alpha=0.6) -> dict:
+    """inserted rows / s of the per-step insert as training/train_off_policy.py:339-345 makes it: for each agent
+    ``one_step = n_step_memory.add(transition)`` then ``memory.add(one_step)`` with ``num_envs`` Atari rows
+    (the unmodified reference classes; every add walks both list trees once per new row)."""
+    if not ref_loader.available():
+        return {"value": None, "kind": "unavailable", "sample": "no copy of the reference on this machine"}
+    ref = ref_loader.load_reference()
+    per = ref.PrioritizedReplayBuffer(max_size=cap, alpha=alpha)
+    nst = ref.MultiStepReplayBuffer(max_size=cap, n_step=n_step, gamma=gamma)
+    g = torch.Generator().manual_seed(8)
+    trs = [atari_transition(ref.TensorDict, num_envs, g) for _ in range(8)]
+
+    def step(i):
+        src = trs[i % 8]
+        one = nst.add(ref.TensorDict({k: src[k] for k in src.keys()}, batch_size=[num_envs]))
+        if one is not None:
+            per.add(one)
+
+    for i in range(n_step + 2):
+        step(i)
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        step(n)
+        n += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    wall = time.perf_counter() - t0
+    return {"value": n * num_envs / wall, "unit": "rows/s", "cores": 1, "kind": "reference",
+            "sample": f"{n} agent-steps of {num_envs} rows (n_step_memory.add -> memory.add) in {wall:.1f} s "
+                      f"({1e6 * wall / n:.0f} us per agent-step); max_size {cap}; 1 process"}
