@@ -23,6 +23,16 @@ for i in range(50):
         t = time.perf_counter(); wl.per.update_priorities(b["idxs"], wl.prio_host[a]); acc["update"] += time.perf_counter() - t
     t = time.perf_counter(); torch.cuda.synchronize(); acc["sync"] += time.perf_counter() - t
 for k, v in acc.items(): print(f"{k:8s} {v / 50 / (wl.P if k != 'sync' else 1) * 1e6:8.1f} us per call")
+# the native calls alone (no Python wrappers)
+fp = wl.per._fast_per()
+idx = b["idxs"]
+import numpy as np
+prt = torch.from_numpy(wl.prio_host[0])
+for name, fn in (("FastPer.sample", lambda: fp.sample(wl.B, 0.4, wl.per._size, None)), ("FastPer.update", lambda: fp.update(idx, prt))):
+    torch.cuda.synchronize(); t = time.perf_counter()
+    for _ in range(400): fn()
+    dt = time.perf_counter() - t; torch.cuda.synchronize()
+    print(f"{name:16s} {dt / 400 * 1e6:8.1f} us per call (native only)")
 pr = cProfile.Profile(); pr.enable()
 for i in range(50): wl.e2e_step(i)
 torch.cuda.synchronize(); pr.disable()
