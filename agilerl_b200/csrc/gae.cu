@@ -3,11 +3,13 @@
 //
 // The recurrence carry_t = A_t + K_t * carry_{t+1} must be evaluated in the reference's order
 // with an fp64 carry (a re-associated parallel-in-time scan is not bit-compatible), so the chain
-// itself is one lane per (env, agent).  Two kernels:
+// itself is one lane per (env, agent).  Three kernels:
 //
 //   gae_tma_kernel  (gae_tma.cuh; shapes whose strides are 16-byte multiples): one warp per CTA,
-//           all HBM traffic issued by the TMA unit into / out of a 4-stage shared-memory ring;
+//           all HBM traffic issued by the TMA unit into / out of a shared-memory ring of time boxes;
 //           the lanes run the chain from shared memory and write results in place;
+//   gae_spec_kernel (same shapes, small launches — at most one strip on every other SM): the same data
+//           path with three producer warps preparing A_t and one warp running only the carry chain;
 //   gae_tile_kernel (any shape): 256 threads stage a [TC x 32 env] tile (A_t in fp64, v_t and a
 //           terminal flag) with coalesced loads, warp 0 runs the chain and stores 128-byte rows.
 // T longer than a tile / box is walked in chunks, newest first.
@@ -31,7 +33,6 @@ namespace {
 constexpr int kModeGae = 0;
 constexpr int kModeMc = 1;
 constexpr int kDefaultGaePdl = 0;      // see launch_scan
-constexpr bool kDefaultLanes = false;  // which kernel xp_gae launches by default
 
 struct ScanParams {
   const float *rewards;
@@ -306,173 +307,308 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
   if (lane == 0) tma_wait_read<0>();
 }
 
-// ---- "lanes" kernel: every warp loads and prepares one 32-step box, warp 0 only runs the chain -----
-// CTA = 4 warps on a strip of 32 envs; the strip is walked in chunks of 128 steps, newest first; warp w
-// owns rows [32w, 32w+32) of a chunk (row j <-> t = t_hi - j).  Lane = env.
-//   1. every thread requests its 32 (r, v, done) triples with plain coalesced loads — one 128-byte row per
-//      warp instruction, ~100 requests per thread in flight, all 14 warps of an SM at once (the TMA kernel
-//      has one thread per CTA issuing; what bounds C3 is bytes in flight, not bandwidth);
-//   2. it computes the carry-independent part A_t of its rows in fp64 (three of the four fp32<->fp64
-//      conversions of a step — the scarce unit, 16 lanes/clk/SM — now run on four warps instead of one)
-//      and parks A_t (fp64) + the carry-factor flag in shared memory; v_t stays in its registers;
-//   3. warp 0 walks the boxes in order: per step one 8-byte + one 1-byte shared load, DMUL -> DADD, one
-//      conversion, one 4-byte shared store (the value goes over A_t's slot);
-//   4. the box's own warp picks the chain's fp32 values up, finishes (ret = adv + v / adv = ret - v in
-//      fp32) and stores both outputs coalesced.
-// Hand-offs are named barriers between warp 0 and one box warp (64 threads), no CTA-wide barrier inside a
-// chunk.  Same operations in the same order as the TMA kernel => bit-identical results.
-namespace gaelanes {
-constexpr int kWarps = 4;
-constexpr int kRows = 32;             // rows per warp
-constexpr int kHalf = 16;             // rows requested together
-constexpr int kChunk = kWarps * kRows;
-// named barriers 1..3: "box w is parked" (warp w arrives, warp 0 waits); 4..6: "box w is chained" (the reverse)
-template <int ID>
-__device__ __forceinline__ void bar_sync() { asm volatile("bar.sync %0, 64;" ::"n"(ID) : "memory"); }
-template <int ID>
-__device__ __forceinline__ void bar_arrive() { asm volatile("bar.arrive %0, 64;" ::"n"(ID) : "memory"); }
-__device__ __forceinline__ void bar_sync_id(int id) {
-  if (id == 1) bar_sync<1>(); else if (id == 2) bar_sync<2>(); else if (id == 3) bar_sync<3>();
-  else if (id == 4) bar_sync<4>(); else if (id == 5) bar_sync<5>(); else bar_sync<6>();
-}
-__device__ __forceinline__ void bar_arrive_id(int id) {
-  if (id == 1) bar_arrive<1>(); else if (id == 2) bar_arrive<2>(); else if (id == 3) bar_arrive<3>();
-  else if (id == 4) bar_arrive<4>(); else if (id == 5) bar_arrive<5>(); else bar_arrive<6>();
-}
-}  // namespace gaelanes
+// ---- warp-specialised TMA kernel: three producer warps prepare A_t, warp 0 runs only the carry chain ------
+// Same data path as gae_tma_kernel (TMA boxes into a shared-memory ring, results written in place, TMA stores),
+// but the strip's work is cut by ROLE instead of being one warp's: the four fp32<->fp64 conversions of a step run
+// at 16 lanes/clk/SM, i.e. 8 issue cycles per warp instruction on ONE sub-partition, and make a step cost ~44
+// cycles where the DMUL -> DADD carry chain needs 16.  Here the strip is walked in blocks of kBlk steps
+// (processing order q = 0 .. T-1 <-> t = T-1-q):
+//   iteration k, producers (warps 1-3, one per remaining sub-partition): A_t (fp64) and the carry-factor flag of
+//                block k into buffer k & 1 — rows pw, pw+3, ... of the block — plus the block's OLDEST (v, done),
+//                which block k+1's first row needs after the chain has overwritten that row with its results;
+//   iteration k, chain (warp 0): block k-1 from buffer (k-1) & 1: LDS.64 + LDS.U8, DMUL -> DADD, one conversion
+//                (f64 -> f32, off the chain), adv / ret written in place over the reward / value boxes; a finished
+//                box leaves with two TMA stores;
+//   one __syncthreads() per iteration hands block k over and frees buffer (k+1) & 1.
+// Same operations in the same order per element as gae_tma_kernel => bit-identical results.
+namespace gaespec {
+constexpr int kBlk = 16;
+constexpr int kProducers = 3;
+}  // namespace gaespec
 
 template <int MODE>
-__global__ void __launch_bounds__(gaelanes::kWarps * 32, 4) gae_lanes_kernel(const ScanParams p) {
-  using namespace gaelanes;
-  __shared__ __align__(16) double s_a[kChunk][32];   // A_t, later (low word) the chain's fp32 value
-  __shared__ uint8_t s_f[kChunk][32];                // GAE: done[t+1]; MC: done[t]
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const long long tiles_per_agent = (p.N + 31) / 32;
-  const long long agent = blockIdx.x / tiles_per_agent;
-  const long long env0 = (blockIdx.x - agent * tiles_per_agent) * 32;
+__global__ void __launch_bounds__(128) gae_spec_kernel(const ScanParams p, const __grid_constant__ gaetma::Maps maps) {
+  using namespace gaetma;
+  using namespace gaespec;
+  extern __shared__ __align__(128) unsigned char smem_tma[];
+  Stage *stage = reinterpret_cast<Stage *>(smem_tma);
+  __shared__ __align__(8) unsigned long long bars[kStages];
+  __shared__ __align__(16) double s_a[2][kBlk][32];
+  __shared__ uint8_t s_f[2][kBlk][32];   // GAE: 0 -> k1, 1 -> k0 (done[t+1]), 2 -> bootstrap step; MC: done[t]
+  __shared__ float s_vb[2][32];          // v of the block's oldest row (v_{t+1} of the next block's first row)
+  __shared__ uint8_t s_db[2][32];        // its done flag
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tiles_per_agent = (int)((p.N + kBoxE - 1) / kBoxE);
+  const int agent = blockIdx.x / tiles_per_agent;
+  const int env0 = (blockIdx.x - agent * tiles_per_agent) * kBoxE;
+  const int T = (int)p.T;
+  const int nbox = (T + kBoxT - 1) / kBoxT;  // box b (0 = newest) covers t in [kBoxT (nbox-1-b), +kBoxT)
+  const int nblk = (T + kBlk - 1) / kBlk;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) mbar_init(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue = [&](int b) {  // thread 0 only
+    Stage &st = stage[b % kStages];
+    unsigned long long *bar = &bars[b % kStages];
+    const int t0 = kBoxT * (nbox - 1 - b);
+    mbar_expect_tx(bar, kStageBytes);
+    tma_load_3d(&st.r[0][0], &maps.r, env0, t0, agent, bar);
+    tma_load_3d(&st.v[0][0], &maps.v, env0, t0, agent, bar);
+    tma_load_3d(&st.d[0][0], &maps.d, env0, t0, agent, bar);
+  };
+  if (threadIdx.x == 0)
+    for (int b = 0; b < kStages && b < nbox; ++b) issue(b);
+
   const bool env_ok = env0 + lane < p.N;
-  const long long base = agent * p.agent_stride + env0 + lane;
-  const float *rw = p.rewards + base;
-  const float *vl = p.values + base;
-  const uint8_t *dn = p.dones + base;
-  float *adv = p.adv + base;
-  float *ret = p.ret + base;
   double lv = 0.0, ld = 0.0;
   if (env_ok) {
-    lv = p.last_value[agent * p.N + env0 + lane];
-    ld = p.last_done[agent * p.N + env0 + lane];
+    lv = p.last_value[(long long)agent * p.N + env0 + lane];
+    ld = p.last_done[(long long)agent * p.N + env0 + lane];
   }
-  double carry = (MODE == kModeMc) ? __dmul_rn(lv, __dsub_rn(1.0, ld)) : 0.0;  // warp 0 only
+  // chain state (warp 0)
+  double carry = (MODE == kModeMc) ? __dmul_rn(lv, __dsub_rn(1.0, ld)) : 0.0;
   const double k1 = __dmul_rn(p.gl, 1.0), k0 = __dmul_rn(p.gl, 0.0);
-  const double k_last = __dmul_rn(p.gl, __dsub_rn(1.0, ld));                   // t = T-1 (:463-466)
+  const double k_last = __dmul_rn(p.gl, __dsub_rn(1.0, ld));
+  int stored = 0;  // boxes handed to the TMA store so far (warp 0)
 
-  for (long long t_hi = p.T - 1; t_hi >= 0; t_hi -= kChunk) {
-    const int rows = (int)((t_hi + 1) < kChunk ? (t_hi + 1) : kChunk);
-    const int j0 = w * kRows;                                  // first (newest) row of this warp
-    const int mine = rows - j0 < 0 ? 0 : (rows - j0 < kRows ? rows - j0 : kRows);
-    // ---- 1 + 2. loads, A_t and the flag: two halves of 16 rows (48 requests per thread in flight) ------
-    float v[kRows];                                            // stays in registers for step 4
-    const long long t_first = t_hi - j0;
-    const bool boot = (t_first == p.T - 1);                    // bootstraps from last_value / last_done
-    float v_up = 0.f;                                          // the step after the half's newest row
-    uint8_t d_up = 0;
-    if (MODE == kModeGae && env_ok && mine > 0 && !boot) {     // the previous box's / chunk's oldest row
-      v_up = __ldg(vl + (t_first + 1) * p.N);
-      d_up = __ldg(dn + (t_first + 1) * p.N);
-    }
+  // T a multiple of kBlk (and kBoxT a multiple of kBlk): a block never straddles a box, so a block needs ONE
+  // barrier check, fixed row offsets and one end-of-box test; everything below is unrolled.  Other T take the
+  // general per-row path further down (same arithmetic).
+  const bool aligned = (T % kBlk) == 0 && (kBoxT % kBlk) == 0;
+  for (int k = 0; aligned && k <= nblk; ++k) {
+    if (warp > 0 && k < nblk) {
+      const int buf = k & 1;
+      const int t_hi = T - 1 - k * kBlk;                 // newest step of the block
+      const int b = nbox - 1 - t_hi / kBoxT;
+      const int r0 = t_hi - kBoxT * (nbox - 1 - b);      // its row in the box; the block is rows r0 .. r0-15
+      const Stage &st = stage[b % kStages];
+      mbar_wait(&bars[b % kStages], (unsigned)((b / kStages) & 1));
+      const int pw = warp - 1;
+      float r6[6], v6[6], vn6[6];
+      unsigned d6[6], dn6[6];
 #pragma unroll
-    for (int h = 0; h < kRows; h += kHalf) {
-      float r[kHalf];
-      uint8_t d[kHalf];
-#pragma unroll
-      for (int u = 0; u < kHalf; ++u) {
-        const long long t = t_first - h - u;
-        const bool ok = env_ok && h + u < mine;
-        r[u] = ok ? __ldcs(rw + t * p.N) : 0.f;
-        v[h + u] = ok ? __ldcs(vl + t * p.N) : 0.f;
-        d[u] = ok ? __ldcs(dn + t * p.N) : (uint8_t)0;
+      for (int i = 0; i < 6; ++i) {
+        const int j = pw + kProducers * i;
+        if (j < kBlk) {
+          const int row = r0 - j;
+          r6[i] = st.r[row][lane];
+          v6[i] = st.v[row][lane];
+          d6[i] = st.d[row][lane];
+          if (MODE == kModeGae) {
+            if (j == 0) {      // the previous block's oldest row (kept aside: the chain has overwritten it)
+              vn6[i] = k ? s_vb[buf ^ 1][lane] : 0.f;
+              dn6[i] = k ? s_db[buf ^ 1][lane] : 0u;
+            } else {           // row + 1: same block, not yet touched by the chain
+              vn6[i] = st.v[row + 1][lane];
+              dn6[i] = st.d[row + 1][lane];
+            }
+          }
+        }
       }
 #pragma unroll
-      for (int u = 0; u < kHalf; ++u) {
-        if (h + u < mine) {
+      for (int i = 0; i < 6; ++i) {
+        const int j = pw + kProducers * i;
+        if (j < kBlk) {
           double a;
-          uint8_t f;
+          unsigned f;
           if (MODE == kModeGae) {
-            const float vn = u == 0 ? v_up : v[h + u - 1];
-            f = u == 0 ? d_up : d[u - 1];
-            if (h + u == 0 && boot) {
+            if (k == 0 && j == 0) {  // t = T-1 bootstraps from last_value / last_done (:451-453)
               const double nnt = __dsub_rn(1.0, ld);
-              a = __dsub_rn(__dadd_rn((double)r[0], __dmul_rn(__dmul_rn(p.gamma, lv), nnt)), (double)v[0]);
+              a = __dsub_rn(__dadd_rn((double)r6[i], __dmul_rn(__dmul_rn(p.gamma, lv), nnt)), (double)v6[i]);
+              f = 2;
             } else {
-              const double g_nv = (double)__fmul_rn(p.gamma32, vn);
-              a = __dsub_rn(__dadd_rn((double)r[u], __dmul_rn(g_nv, f ? 0.0 : 1.0)), (double)v[h + u]);
+              const double g_nv = (double)__fmul_rn(p.gamma32, vn6[i]);
+              a = __dsub_rn(__dadd_rn((double)r6[i], __dmul_rn(g_nv, dn6[i] ? 0.0 : 1.0)), (double)v6[i]);
+              f = dn6[i] ? 1u : 0u;
             }
           } else {
-            a = (double)r[u];
-            f = d[u];
+            a = (double)r6[i];
+            f = d6[i] ? 1u : 0u;
           }
-          s_a[j0 + h + u][lane] = a;
-          s_f[j0 + h + u][lane] = f;
+          s_a[buf][j][lane] = a;
+          s_f[buf][j][lane] = (uint8_t)f;
+          if (j == kBlk - 1) {
+            s_vb[buf][lane] = v6[i];
+            s_db[buf][lane] = (uint8_t)d6[i];
+          }
         }
       }
-      v_up = v[h + kHalf - 1];
-      d_up = d[kHalf - 1];
-    }
-    // ---- 3. the chain (warp 0), box by box ---------------------------------------------------------
-    if (w == 0) {
-      for (int b = 0; b * kRows < rows; ++b) {
-        if (b > 0) bar_sync_id(b);         // box b's warp has parked its A_t
-        else __syncwarp();
-        const int jb = b * kRows;
-        const int nb = rows - jb < kRows ? rows - jb : kRows;
-        for (int g0 = 0; g0 < nb; g0 += 8) {
-          double a8[8];
-          uint8_t f8[8];
+    } else if (warp == 0 && k >= 1) {
+      const int buf = (k - 1) & 1;
+      const int t_hi = T - 1 - (k - 1) * kBlk;
+      const int b = nbox - 1 - t_hi / kBoxT;
+      const int t0 = kBoxT * (nbox - 1 - b);
+      const int r0 = t_hi - t0;
+      Stage &st = stage[b % kStages];
+      mbar_wait(&bars[b % kStages], (unsigned)((b / kStages) & 1));  // (complete already: the producers waited)
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int j = jb + (g0 + u < nb ? g0 + u : nb - 1);
-            a8[u] = s_a[j][lane];
-            f8[u] = s_f[j][lane];
+      for (int h = 0; h < kBlk; h += 8) {
+        double a8[8];
+        unsigned f8[8];
+        float v8[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          a8[u] = s_a[buf][h + u][lane];
+          f8[u] = s_f[buf][h + u][lane];
+          v8[u] = st.v[r0 - h - u][lane];
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          float av, rv;
+          if (MODE == kModeGae) {
+            const double kk = f8[u] == 0 ? k1 : (f8[u] == 1 ? k0 : k_last);
+            carry = __dadd_rn(a8[u], __dmul_rn(kk, carry));
+            av = __double2float_rn(carry);
+            rv = __fadd_rn(av, v8[u]);
+          } else {
+            carry = __dadd_rn(a8[u], __dmul_rn(__dmul_rn(p.gamma, carry), f8[u] ? 0.0 : 1.0));
+            rv = __double2float_rn(carry);
+            av = __fsub_rn(rv, v8[u]);
           }
+          st.r[r0 - h - u][lane] = av;
+          st.v[r0 - h - u][lane] = rv;
+        }
+      }
+      if (r0 - (kBlk - 1) == 0) {  // the block ended the box: out it goes
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(&maps.adv, env0, t0, agent, &st.r[0][0]);
+          tma_store_3d(&maps.ret, env0, t0, agent, &st.v[0][0]);
+          tma_commit();
+          if (b + kStages < nbox) {  // reload this stage as soon as its own stores have read it (see below)
+            tma_wait_read<0>();
+            issue(b + kStages);
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  for (int k = 0; !aligned && k <= nblk; ++k) {
+    if (warp > 0 && k < nblk) {
+      // ---- producers: block k -> buffer k & 1 -------------------------------------------------------------
+      const int buf = k & 1;
+      for (int j = warp - 1; j < kBlk; j += kProducers) {
+        const int q = k * kBlk + j;
+        if (q >= T) break;
+        const int t = T - 1 - q;
+        const int b = nbox - 1 - t / kBoxT;
+        const int row = t - kBoxT * (nbox - 1 - b);
+        mbar_wait(&bars[b % kStages], (unsigned)((b / kStages) & 1));
+        const Stage &st = stage[b % kStages];
+        const float r = st.r[row][lane], v = st.v[row][lane];
+        const unsigned d = st.d[row][lane];
+        double a;
+        unsigned f;
+        if (MODE == kModeGae) {
+          if (q == 0) {  // t = T-1 bootstraps from last_value / last_done (:451-453)
+            const double nnt = __dsub_rn(1.0, ld);
+            a = __dsub_rn(__dadd_rn((double)r, __dmul_rn(__dmul_rn(p.gamma, lv), nnt)), (double)v);
+            f = 2;
+          } else {
+            float vn;
+            unsigned dn;
+            if (j == 0) {  // the previous block's oldest row: already overwritten by the chain, kept aside
+              vn = s_vb[buf ^ 1][lane];
+              dn = s_db[buf ^ 1][lane];
+            } else {       // row t+1: same block, not yet touched by the chain
+              const int t1 = t + 1;
+              const int b1 = nbox - 1 - t1 / kBoxT;
+              const Stage &s1 = stage[b1 % kStages];
+              const int row1 = t1 - kBoxT * (nbox - 1 - b1);
+              vn = s1.v[row1][lane];
+              dn = s1.d[row1][lane];
+            }
+            const double g_nv = (double)__fmul_rn(p.gamma32, vn);
+            a = __dsub_rn(__dadd_rn((double)r, __dmul_rn(g_nv, dn ? 0.0 : 1.0)), (double)v);
+            f = dn ? 1u : 0u;
+          }
+        } else {
+          a = (double)r;
+          f = d ? 1u : 0u;
+        }
+        s_a[buf][j][lane] = a;
+        s_f[buf][j][lane] = (uint8_t)f;
+        if (j == kBlk - 1 || q == T - 1) {
+          s_vb[buf][lane] = v;
+          s_db[buf][lane] = (uint8_t)d;
+        }
+      }
+    } else if (warp == 0 && k >= 1) {
+      // ---- chain: block k-1 from buffer (k-1) & 1 -----------------------------------------------------------
+      const int buf = (k - 1) & 1;
+      const int q0 = (k - 1) * kBlk;
+      const int n = (T - q0) < kBlk ? (T - q0) : kBlk;
+      // groups of 8 steps staged through registers: the 24 shared-memory reads pipeline, then 8 x (DMUL -> DADD)
+      for (int j0 = 0; j0 < n; j0 += 8) {
+        double a8[8];
+        unsigned f8[8];
+        float v8[8];
+        float *pr[8], *pv[8];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            if (g0 + u < nb) {
-              const int j = jb + g0 + u;
-              if (MODE == kModeGae) {
-                double k = f8[u] ? k0 : k1;
-                if (t_hi - j == p.T - 1) k = k_last;
-                carry = __dadd_rn(a8[u], __dmul_rn(k, carry));
-              } else {
-                carry = __dadd_rn(a8[u], __dmul_rn(__dmul_rn(p.gamma, carry), f8[u] ? 0.0 : 1.0));
+        for (int u = 0; u < 8; ++u) {
+          const int j = (j0 + u < n) ? j0 + u : n - 1;
+          const int t = T - 1 - q0 - j;
+          const int b = nbox - 1 - t / kBoxT;
+          const int t0 = kBoxT * (nbox - 1 - b);
+          Stage &st = stage[b % kStages];
+          if (u == 0 || t == t0 + kBoxT - 1) mbar_wait(&bars[b % kStages], (unsigned)((b / kStages) & 1));  // (complete already)
+          a8[u] = s_a[buf][j][lane];
+          f8[u] = s_f[buf][j][lane];
+          pr[u] = &st.r[t - t0][lane];
+          pv[u] = &st.v[t - t0][lane];
+          v8[u] = *pv[u];
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (j0 + u < n) {
+            const int t = T - 1 - q0 - (j0 + u);
+            const int b = nbox - 1 - t / kBoxT;
+            const int t0 = kBoxT * (nbox - 1 - b);
+            float av, rv;
+            if (MODE == kModeGae) {
+              const double kk = f8[u] == 0 ? k1 : (f8[u] == 1 ? k0 : k_last);
+              carry = __dadd_rn(a8[u], __dmul_rn(kk, carry));
+              av = __double2float_rn(carry);
+              rv = __fadd_rn(av, v8[u]);
+            } else {
+              carry = __dadd_rn(a8[u], __dmul_rn(__dmul_rn(p.gamma, carry), f8[u] ? 0.0 : 1.0));
+              rv = __double2float_rn(carry);
+              av = __fsub_rn(rv, v8[u]);
+            }
+            *pr[u] = av;
+            *pv[u] = rv;
+            if (t == t0) {  // the box is finished (warp-uniform): out it goes
+              Stage &st = stage[b % kStages];
+              fence_proxy_async();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_3d(&maps.adv, env0, t0, agent, &st.r[0][0]);
+                tma_store_3d(&maps.ret, env0, t0, agent, &st.v[0][0]);
+                tma_commit();
+                // The producers run one block ahead of this warp and will wait for box b + kStages as soon as
+                // they leave the resident boxes: reload THIS box's stage as soon as its own stores have read it
+                // (deferring the reload to the end of the next box, as gae_tma_kernel does, would dead-lock).
+                if (b + kStages < nbox) {
+                  tma_wait_read<0>();
+                  issue(b + kStages);
+                }
               }
-              *reinterpret_cast<float *>(&s_a[j][lane]) = __double2float_rn(carry);
+              ++stored;
             }
           }
         }
-        if (b > 0) bar_arrive_id(kWarps - 1 + b);  // box b's values are ready for its warp
-        else __syncwarp();
-      }
-    } else if (mine > 0) {
-      bar_arrive_id(w);
-      bar_sync_id(kWarps - 1 + w);
-    }
-    // ---- 4. finish and store this warp's rows ------------------------------------------------------
-#pragma unroll
-    for (int u = 0; u < kRows; ++u) {
-      if (env_ok && u < mine) {
-        const long long t = t_hi - j0 - u;
-        const float x = *reinterpret_cast<const float *>(&s_a[j0 + u][lane]);
-        if (MODE == kModeGae) {
-          __stcs(adv + t * p.N, x);
-          __stcs(ret + t * p.N, __fadd_rn(x, v[u]));
-        } else {
-          __stcs(ret + t * p.N, x);
-          __stcs(adv + t * p.N, __fsub_rn(x, v[u]));
-        }
       }
     }
-    if (t_hi - kChunk >= 0) __syncthreads();  // shared memory is reused by the next chunk
+    __syncthreads();
   }
+  if (threadIdx.x == 0) tma_wait_read<0>();
+  (void)stored;
 }
 
 // cuTensorMapEncodeTiled through the runtime (no -lcuda): rank-3 maps {env, t, agent}.
@@ -597,15 +733,35 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   const bool tma_ok = (p.N % 16 == 0) && (astride % 16 == 0) && al16(p.rewards) && al16(p.values) &&
                       al16(p.dones) && al16(p.adv) && al16(p.ret) && p.T < (1ll << 30) &&
                       p.N < (1ll << 31) && p.P < (1ll << 31);
-  static const int which = [] {
-    const char *e = getenv("XP_GAE_KERNEL");  // developer knob: "tma" | "lanes" | "tile"
+  // developer / test knob, read per call (a getenv is ~50 ns): "tma" | "spec" | "tile"; default: by size
+  const int which = [] {
+    const char *e = getenv("XP_GAE_KERNEL");
     if (!e || !e[0]) return 0;
-    return e[0] == 'l' ? 1 : e[0] == 't' && e[1] == 'i' ? 2 : e[0] == 't' ? 3 : 0;
+    return e[0] == 't' && e[1] == 'i' ? 2 : e[0] == 't' ? 3 : e[0] == 's' ? 4 : 0;
   }();
-  const bool lanes_ok = p.T < (1ll << 30);
-  if (lanes_ok && (which == 1 || (which == 0 && kDefaultLanes))) {
-    gae_lanes_kernel<MODE><<<(unsigned)grid, gaelanes::kWarps * 32, 0, s>>>(p);
-    return xp::check_launch("xp_gae (lanes)");
+  // the warp-specialised kernel pays when the launch is latency-bound — at most one strip on every other SM, e.g. the
+  // per-agent call of the drop-in (1 024 envs = 32 strips): 6.37 vs 6.78 us per launch; with the GPU full it loses
+  // (C3 11.8 vs 10.9 us, 16x 108 vs 93 us: four times the warps for the same conversion work)
+  const bool want_spec = which == 4 || (which == 0 && 2 * grid_tma <= (long long)xp::sm_count());
+  if (tma_ok && want_spec) {
+    gaetma::Maps maps;
+    if (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
+        encode_map(&maps.d, p.dones, 1, p) && encode_map(&maps.adv, p.adv, 4, p) &&
+        encode_map(&maps.ret, p.ret, 4, p)) {
+      static xp::DeviceOnce spec_attr[2];
+      if (!spec_attr[MODE].done()) {
+        cudaError_t e = cudaFuncSetAttribute((const void *)gae_spec_kernel<MODE>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)(sizeof(gaetma::Stage) * gaetma::kStages));
+        if (e != cudaSuccess) {
+          xp::set_error("xp_gae: %s", cudaGetErrorString(e));
+          return XP_ERR_CUDA;
+        }
+        spec_attr[MODE].set();
+      }
+      gae_spec_kernel<MODE><<<(unsigned)grid_tma, 128, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps);
+      return xp::check_launch("xp_gae (spec)");
+    }
   }
   if (tma_ok && which != 2) {
     gaetma::Maps maps;

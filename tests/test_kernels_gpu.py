@@ -52,9 +52,15 @@ def test_gae_golden_bitwise(xp, cuda_device, seed):
     assert np.array_equal(adv[0], g["adv_mc"]) and np.array_equal(ret[0], g["ret_mc"])
 
 
-@pytest.mark.parametrize("shape", [(3, 50, 96), (2, 1, 32), (1, 7, 1), (4, 130, 64), (2, 33, 40), (1, 300, 33), (2, 257, 132)])
+@pytest.mark.parametrize("kernel", ["", "tma", "spec", "tile"])
+@pytest.mark.parametrize("shape", [(3, 50, 96), (2, 1, 32), (1, 7, 1), (4, 130, 64), (2, 33, 40), (1, 300, 33), (2, 257, 132),
+                                   (2, 128, 64), (1, 144, 32), (1, 272, 48)])
 @pytest.mark.parametrize("use_gae", [True, False])
-def test_gae_population_vs_oracle(xp, cuda_device, shape, use_gae):
+def test_gae_population_vs_oracle(xp, cuda_device, shape, use_gae, kernel, monkeypatch):
+    """Every kernel behind xp_gae on every shape (the knob is read per call; "" = the size-based default):
+    gae_tma_kernel (one warp per strip), gae_spec_kernel (warp-specialised; aligned blocks for T % 16 == 0, the
+    per-row path otherwise; stage recycling for T > 128), gae_tile_kernel (any alignment)."""
+    monkeypatch.setenv("XP_GAE_KERNEL", kernel)
     P, T, N = shape
     rng = np.random.default_rng(P * 1000 + T)
     r = rng.standard_normal((P, T, N)).astype(np.float32)
