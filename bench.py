@@ -69,7 +69,7 @@ def parse_args():
 class ClockSampler:
     BAD = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")
 
-    def __init__(self, index: int, period_s: float = 0.01):
+    def __init__(self, index: int, period_s: float = 0.002):
         self.index, self.period = index, period_s
         self.samples, self.reasons = [], set()
         self.max_mhz = None
