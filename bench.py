@@ -827,6 +827,55 @@ def bench_per_tree_replicated(dev, rank, world, reps=10):
             "note": "per replica: 1/N of the descents, ALL of the updates (replicated tree) + the NVLink exchange"}
 
 
+def bench_replicated_insert(dev, rank, world, steps=60):
+    """Insert side at N > 1 (north_star: "each step's newly inserted transitions broadcast over NVLink"): every rank
+    contributes the rows of its 8 agents x 16 envs per env step through population.ReplicatedReplay.add — ONE kernel
+    per rank (xp_peer_ring_insert) signals, waits and pulls every rank's rows straight into the local ring, then the
+    new leaves are set; all replicas insert world x 128 rows at the same cursor.  Host-inclusive wall time (it is a
+    host-driven call per env step), max over ranks; replicas compared afterwards."""
+    import torch
+    import torch.distributed as dist
+
+    from agilerl_b200.components import PrioritizedReplayBuffer, TensorBatch
+    from agilerl_b200.population import ReplicatedReplay
+
+    c = C2
+    n = c["P"] * c["num_envs"]
+    mem = PrioritizedReplayBuffer(32768, alpha=c["alpha"], device=dev)
+    rep = ReplicatedReplay(mem)
+    gd = torch.Generator(device=dev).manual_seed(90 + rank)
+    rows = [{"obs": torch.randint(0, 256, (n, *ATARI), dtype=torch.uint8, device=dev, generator=gd),
+             "action": torch.randint(0, 18, (n,), device=dev, generator=gd).float(),
+             "reward": torch.randn(n, device=dev, generator=gd),
+             "next_obs": torch.randint(0, 256, (n, *ATARI), dtype=torch.uint8, device=dev, generator=gd),
+             "done": (torch.rand(n, device=dev, generator=gd) < 0.01).float()} for _ in range(4)]
+    for i in range(5):
+        rep.add(TensorBatch(dict(rows[i % 4]), batch_size=[n]))
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        rep.add(TensorBatch(dict(rows[i % 4]), batch_size=[n]))
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    tt = torch.tensor([ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms = float(tt.item())
+    if rep._ix is not None:
+        rep._ix.check()
+    ck = torch.stack([mem._leaves[("obs",)].view(-1)[::4099].long().sum(), mem._leaves[("reward",)].view(torch.int32).long().sum(),
+                      mem._trees[2].nodes.view(-1).view(torch.int64)[2:].sum(),
+                      torch.tensor(mem._cursor * 65537 + mem.tree_ptr, device=dev)])
+    allck = [torch.empty_like(ck) for _ in range(world)]
+    dist.all_gather(allck, ck)
+    nbytes = world * n * R_C2
+    return {"workload": f"c2_replicated_insert_{n}rows_per_rank_x{world}", "metric": "inserted_rows_per_s",
+            "value": world * n / (ms * 1e-3), "unit": "rows/s (into EVERY replica)", "ms_per_env_step": ms,
+            "bytes_pulled_per_replica_per_step": nbytes, "peer_kernel": bool(rep._ix_ok),
+            "replicas_identical": all(bool(torch.equal(allck[0], x)) for x in allck[1:]),
+            "api": "population.ReplicatedReplay.add (xp_peer_ring_insert + xp_per_add), host-inclusive"}
+
+
 def also_multi_gpu(dev, rank, world):
     """The configs BASELINE.json names for 1/2/4/8 GPUs, per N: C3 and C5 shard by population with no
     exchange (each rank's agents own their rollout buffers / sample their replica); C4 is strong scaling with a
@@ -850,6 +899,8 @@ def also_multi_gpu(dev, rank, world):
                 "roofline_per_gpu": roofline(pl * C3["T"] * C3["N"] * 17, us), "exchange": "none"})
     torch.cuda.empty_cache()
     out.append(bench_per_tree_replicated(dev, rank, world))
+    torch.cuda.empty_cache()
+    out.append(bench_replicated_insert(dev, rank, world))
     torch.cuda.empty_cache()
     pl = max(1, C5["P"] // world)
     dist.barrier()
