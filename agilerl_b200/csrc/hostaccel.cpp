@@ -7,11 +7,13 @@
 // stream.  The Python classes use it when it is built and the inputs are in canonical form, and
 // fall back to their own (identical, slower) code otherwise; results are the same either way —
 // every byte is still produced by libb200xp.so kernels.
+#include <ATen/CPUGeneratorImpl.h>
 #include <ATen/cuda/CUDAEvent.h>
 #include <c10/cuda/CUDAStream.h>
 #include <torch/extension.h>
 
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -230,8 +232,14 @@ class FastPer {
       // batch_size x torch.rand(1).item() == torch.rand(batch_size) == uniform_(0,1) on the
       // default CPU generator (replay_buffer.py:377), drawn straight into pinned memory
       Slot &s = ring_.acquire(B * 4);
-      at::Tensor hv = at::from_blob(s.hp, {B}, at::TensorOptions().dtype(at::kFloat));
-      hv.uniform_(0.0, 1.0);
+      {
+        // what at::uniform_real_distribution<float> does per element (ATen/core/DistributionsHelper.h): one 32-bit
+        // word of the generator, low 24 bits scaled by 2^-24 — without a temporary tensor and a dispatcher trip
+        auto *gen = at::get_generator_or_default<at::CPUGeneratorImpl>(c10::nullopt, at::detail::getDefaultCPUGenerator());
+        std::lock_guard<std::mutex> lock(gen->mutex_);
+        float *h = reinterpret_cast<float *>(s.hp);
+        for (int64_t i = 0; i < B; ++i) h[i] = (float)(gen->random() & ((1u << 24) - 1u)) * (1.0f / 16777216.0f);
+      }
       ring_.push(s, B * 4, st);
       u = reinterpret_cast<const float *>(s.dp);
     }

@@ -1232,8 +1232,11 @@ def reference_arm(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64 tree / u8 rows", "data": "synthetic",
             "config": {"workload": c["name"], "rows": c["cap"], "batch": c["B"],
-                       "population_per_gpu": c["P"], "population": c["P"], "row_bytes": R_C2,
-                       "tree_levels": c["L"], "parallelism": "1 host process, agents sequential (the reference's model)"},
+                       "population_per_gpu": c["P"], "population": c["P"] * max(args.gpus, 1), "row_bytes": R_C2,
+                       "tree_levels": c["L"],
+                       "parallelism": "1 host process, agents sequential on one shared memory (the reference's model): its "
+                                      "rate per sampled transition does not depend on the population size, so the same "
+                                      "measurement stands beside every --gpus N"},
             "cpu_baseline": cpu,
             "population_parallel_upper_bound": upper,
             "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0,

@@ -33,6 +33,20 @@ for name, fn in (("FastPer.sample", lambda: fp.sample(wl.B, 0.4, wl.per._size, N
     for _ in range(400): fn()
     dt = time.perf_counter() - t; torch.cuda.synchronize()
     print(f"{name:16s} {dt / 400 * 1e6:8.1f} us per call (native only)")
+# pure host enqueue time: the GPU queue is drained before every call, only the call is timed
+for name, fn in (("per.sample", lambda: wl.per.sample(wl.B, 0.4)), ("FastPer.sample", lambda: fp.sample(wl.B, 0.4, wl.per._size, None)),
+                 ("FastPer.update", lambda: fp.update(idx, prt)), ("per.update_priorities", lambda: wl.per.update_priorities(idx, wl.prio_host[0]))):
+    tot = 0.0
+    for _ in range(200):
+        torch.cuda.synchronize(); t = time.perf_counter(); r = fn(); tot += time.perf_counter() - t
+    print(f"{name:22s} {tot / 200 * 1e6:8.1f} us host enqueue (queue drained)")
+# GPU time of one agent's triple
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+torch.cuda.synchronize(); ev[0].record()
+for _ in range(100):
+    b = wl.per.sample(wl.B, 0.4); nb = wl.nstep.sample_from_indices(b["idxs"]); wl.per.update_priorities(b["idxs"], wl.prio_host[0])
+ev[1].record(); torch.cuda.synchronize()
+print(f"device span per agent triple (100 back to back): {ev[0].elapsed_time(ev[1]) * 10:.1f} us")
 pr = cProfile.Profile(); pr.enable()
 for i in range(50): wl.e2e_step(i)
 torch.cuda.synchronize(); pr.disable()
