@@ -1111,8 +1111,8 @@ def b200_arm(args):
     e2e = None
     if not args.no_e2e:
         wl.e2e_setup()
-        Ke = max(3, min(K, 200))
-        for i in range(3):
+        Ke = max(100, min(K, 200))  # its own step count (reported as e2e.steps): a 20-step K would time 7 ms of a host-bound loop
+        for i in range(10):
             wl.e2e_step(i)
         sync()
         t0 = time.perf_counter()
