@@ -865,7 +865,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   // schedule M (one launch) up to 8 192 items; beyond that every CTA of M would re-read a batch that no longer
   // pays for saving two launches (cap 2^20, 16 384 items: M 21.7 us, S below; 32 768 items: S 16 us)
   static const int m_max = env_int("XP_SET_M_MAX", 8192);  // developer knob
-  const bool fits_s = slotted_scratch_ints(t.cap, [&] { long long nb = 1; while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1; return nb; }(), B, s.kind == kSrcPrio) <= t.cap && s.kind != kSrcRange;
+  const bool fits_s = slotted_scratch_ints(t.cap, [&] { long long nb = 1; while (nb * env_int("XP_BUCKET_ITEMS", 16) < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1; return nb; }(), B, s.kind == kSrcPrio) <= t.cap && s.kind != kSrcRange;
   if (B <= m_max || (B <= 16384 && !fits_s)) {  // schedule M: one launch
     long long nb = 1;
     while (nb * 8 < B && nb < 2048 && nb * 2 <= t.cap) nb <<= 1;
@@ -889,7 +889,8 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   const unsigned grid = (unsigned)((B + 255) / 256);
   long long nb = 1;
   const int use_half = 1;
-  while (nb * 16 < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;  // ~16 items per bucket
+  static const int per_bucket = env_int("XP_BUCKET_ITEMS", 16);  // developer knob
+  while (nb * per_bucket < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1;  // ~16 items per bucket
   const bool want_vals = s.kind == kSrcPrio;
   const int shift = L - ilog2(nb);
   // The sparse climb costs ~2 scattered sector requests per item per level; a dense coalesced
