@@ -123,7 +123,7 @@ def test_clear(C):
     assert list(b.storage.keys()) == ["y"] and len(b) == 3
 
 
-# ---- MultiStepReplayBuffer (reference :397-666) ------------------------------------------------------
+# ---- MultiStepReplayBuffer (reference :432-730) ------------------------------------------------------
 def test_nstep_reward_kats(C):
     # :532-569  R = 1 + 0.9*2 + 0.81*3 ; :571-628 early termination
     b = C.MultiStepReplayBuffer(max_size=100, n_step=3, gamma=0.9)
@@ -180,7 +180,7 @@ def test_ring_and_nstep_golden_through_api(C, seed):
     assert np.array_equal(got["reward"].cpu().numpy()[:, 0], g["nstep_reward"][[0, 2, 1]])
 
 
-# ---- PrioritizedReplayBuffer (reference :669-1056) ---------------------------------------------------
+# ---- PrioritizedReplayBuffer (reference :734-1056) ---------------------------------------------------
 def one(C, i):
     return TB(C, {"state": torch.tensor([[i, i + 1, i + 2]]), "action": torch.tensor([[i % 3]]),
                   "reward": torch.tensor([[float(i)]])}, 1)

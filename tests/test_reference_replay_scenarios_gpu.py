@@ -1,5 +1,5 @@
 """The reference's own MultiStepReplayBuffer / PrioritizedReplayBuffer test scenarios
-(/root/reference/tests/test_components/test_replay_buffer.py:397-1056), restated against
+(/root/reference/tests/test_components/test_replay_buffer.py:432-1056), restated against
 agilerl_b200.components with the same calls, in the same order, with the same assertions — the
 buffers are constructed exactly as the reference tests construct them (default ``device="cpu"``:
 batches come back on the CPU while the storage lives on the GPU).  ``TensorDict`` below is the
@@ -36,12 +36,12 @@ def nstep_buffer(C, **kw):
     return b
 
 
-def test_nstep_buffer_initialization(C):  # :399-411
+def test_nstep_buffer_initialization(C):  # :433-444
     b = C.MultiStepReplayBuffer(1000, 3, 0.99)
     assert b.max_size == 1000 and b.n_step == 3 and b.gamma == 0.99 and len(b.n_step_buffer) == 0
 
 
-def test_nstep_buffer_add(C):  # :415-459
+def test_nstep_buffer_add(C):  # :448-492
     b = nstep_buffer(C, max_size=1000, n_step=3, gamma=0.99)
     b.add(td1(C, {"state": torch.tensor([1, 2, 3]), "action": torch.tensor([0]), "reward": torch.tensor([1.0]),
                   "next_state": torch.tensor([4, 5, 6]), "done": torch.tensor([False])}))
@@ -53,7 +53,7 @@ def test_nstep_buffer_add(C):  # :415-459
     assert len(b) == 1 and len(b.n_step_buffer) == 3
 
 
-def test_nstep_buffer_add_with_images_and_sample(C):  # :461-496 — calls the INHERITED sample()
+def test_nstep_buffer_add_with_images_and_sample(C):  # :494-528 — calls the INHERITED sample()
     b = nstep_buffer(C, max_size=1000, n_step=3, gamma=0.99)
     for i in range(4):
         b.add(td1(C, {"state": torch.ones((3, 84, 84)) * i, "action": torch.tensor([i % 3]),
@@ -65,7 +65,7 @@ def test_nstep_buffer_add_with_images_and_sample(C):  # :461-496 — calls the I
     assert samples["state"].device.type == "cpu"  # device="cpu" buffers hand out CPU batches
 
 
-def test_nstep_reward_calculation_from_the_deque(C):  # :500-541 — fills n_step_buffer directly
+def test_nstep_reward_calculation_from_the_deque(C):  # :532-569 — fills n_step_buffer directly
     b = nstep_buffer(C, max_size=1000, n_step=3, gamma=0.9)
     b._storage = C.TensorBatch({}, batch_size=[0, 0])
     for i in range(3):
@@ -84,7 +84,7 @@ def test_nstep_reward_calculation_from_the_deque(C):  # :500-541 — fills n_ste
     assert torch.all(n_step_data["state"] == b.n_step_buffer[0]["state"])
 
 
-def test_nstep_early_termination_from_the_deque(C):  # :543-604
+def test_nstep_early_termination_from_the_deque(C):  # :571-628
     b = nstep_buffer(C, max_size=1000, n_step=3, gamma=0.9)
     data = [td1(C, {"state": torch.tensor(s), "action": torch.tensor([a]), "reward": torch.tensor([r]),
                     "next_state": torch.tensor(ns), "done": torch.tensor([d])})
@@ -99,7 +99,7 @@ def test_nstep_early_termination_from_the_deque(C):  # :543-604
 
 
 @pytest.mark.parametrize("key", ["termination", "terminated"])
-def test_multistep_done_key_detection(C, key):  # :606-646
+def test_multistep_done_key_detection(C, key):  # :630-666
     b = C.MultiStepReplayBuffer(max_size=100, n_step=3, gamma=0.99)
     b.reward_key = "reward"
     b.ns_key = "next_obs"
@@ -110,7 +110,7 @@ def test_multistep_done_key_detection(C, key):  # :606-646
     assert b.done_key == key
 
 
-def test_nstep_sampling_with_indices(C):  # :650-687 — MultiStepReplayBuffer.sample(n, return_idx=True)
+def test_nstep_sampling_with_indices(C):  # :670-704 — MultiStepReplayBuffer.sample(n, return_idx=True)
     b = nstep_buffer(C, max_size=1000, n_step=3, gamma=0.99)
     for i in range(10):
         b.add(td1(C, {"state": torch.tensor([i, i + 1, i + 2]), "action": torch.tensor([i % 3]),
@@ -130,7 +130,7 @@ def test_nstep_sampling_with_indices(C):  # :650-687 — MultiStepReplayBuffer.s
     assert torch.equal(s["state"].cpu(), b.storage["state"].cpu()[want])
 
 
-def test_multistep_buffer_sample_from_indices(C):  # :690-731
+def test_multistep_buffer_sample_from_indices(C):  # :708-730
     b = nstep_buffer(C, max_size=100, n_step=3, gamma=0.99)
     for i in range(6):
         b.add(td1(C, {"state": torch.tensor([i]), "action": torch.tensor([i % 2]),
@@ -147,13 +147,13 @@ def per_row(C, i):
                    "reward": torch.tensor([float(i)])})
 
 
-def test_prioritized_buffer_initialization(C):  # :735-748
+def test_prioritized_buffer_initialization(C):  # :735-747
     b = C.PrioritizedReplayBuffer(1000, 0.6)
     assert b.max_size == 1000 and b.alpha == 0.6 and b.max_priority == 1.0 and b.tree_ptr == 0
     assert isinstance(b.sum_tree, C.SumSegmentTree) and isinstance(b.min_tree, C.MinSegmentTree)
 
 
-def test_prioritized_buffer_add_and_add_batch(C):  # :752-793
+def test_prioritized_buffer_add_and_add_batch(C):  # :751-790
     b = C.PrioritizedReplayBuffer(max_size=100, alpha=0.6)
     b.add(td1(C, {"state": torch.tensor([1, 2, 3]), "action": torch.tensor([0]), "reward": torch.tensor([1.0])}))
     assert len(b) == 1 and b.tree_ptr == 1
@@ -167,7 +167,7 @@ def test_prioritized_buffer_add_and_add_batch(C):  # :752-793
     assert b.sum_tree[0] == b.max_priority**b.alpha and b.sum_tree[1] == b.max_priority**b.alpha
 
 
-def test_prioritized_buffer_with_image_observations(C):  # :797-829
+def test_prioritized_buffer_with_image_observations(C):  # :794-824
     b = C.PrioritizedReplayBuffer(max_size=100, alpha=0.6)
     for i in range(5):
         b.add(td1(C, {"state": torch.ones((3, 84, 84)) * i, "action": torch.tensor([i % 3]),
@@ -177,7 +177,7 @@ def test_prioritized_buffer_with_image_observations(C):  # :797-829
     assert samples["state"].shape == (3, 3, 84, 84) and "weights" in samples and "idxs" in samples
 
 
-def test_prioritized_buffer_with_dict_observations(C):  # :831-872
+def test_prioritized_buffer_with_dict_observations(C):  # :826-864
     b = C.PrioritizedReplayBuffer(max_size=100, alpha=0.6)
     for i in range(5):
         obs = C.TensorBatch({"image": torch.ones((3, 84, 84)) * i, "vector": torch.tensor([i, i + 1, i + 2])})
@@ -188,7 +188,7 @@ def test_prioritized_buffer_with_dict_observations(C):  # :831-872
     assert "weights" in samples and "idxs" in samples
 
 
-def test_prioritized_sampling(C):  # :874-908
+def test_prioritized_sampling(C):  # :866-897
     b = C.PrioritizedReplayBuffer(max_size=100, alpha=0.6)
     for i in range(10):
         b.add(per_row(C, i))
@@ -200,7 +200,7 @@ def test_prioritized_sampling(C):  # :874-908
     assert samples["weights"].shape == (5, 1) and samples["idxs"].shape == (5, 1)
 
 
-def test_prioritized_buffer_update_priorities(C):  # :912-952
+def test_prioritized_buffer_update_priorities(C):  # :901-936
     b = C.PrioritizedReplayBuffer(max_size=100, alpha=0.6)
     for i in range(5):
         b.add(per_row(C, i))
@@ -213,7 +213,7 @@ def test_prioritized_buffer_update_priorities(C):  # :912-952
     assert b.max_priority == 4.0
 
 
-def test_prioritized_buffer_update_priorities_small_priority_clamped(C):  # :954-970
+def test_prioritized_buffer_update_priorities_small_priority_clamped(C):  # :938-952
     b = C.PrioritizedReplayBuffer(max_size=10, alpha=0.6)
     for i in range(3):
         b.add(td1(C, {"state": torch.tensor([i]), "action": torch.tensor([0]), "reward": torch.tensor([1.0])}))
@@ -222,7 +222,7 @@ def test_prioritized_buffer_update_priorities_small_priority_clamped(C):  # :954
     assert b.sum_tree[0] == 1e-5**b.alpha  # max(p, 1e-5) ** alpha exactly (:425,322)
 
 
-def test_proportional_sampling_with_mocked_torch_rand(C):  # :974-1019 — replaces torch.rand itself
+def test_proportional_sampling_with_mocked_torch_rand(C):  # :956-1000 — replaces torch.rand itself
     b = C.PrioritizedReplayBuffer(max_size=100, alpha=0.6)
     for i in range(5):
         b.add(per_row(C, i))
@@ -270,7 +270,7 @@ def test_proportional_sampling_with_mocked_torch_rand(C):  # :974-1019 — repla
     assert indices.tolist() == want
 
 
-def test_weight_calculation(C):  # :1023-1058
+def test_weight_calculation(C):  # :1004-1039
     b = C.PrioritizedReplayBuffer(max_size=100, alpha=0.6)
     for i in range(5):
         b.add(per_row(C, i))
@@ -287,7 +287,7 @@ def test_weight_calculation(C):  # :1023-1058
         assert weight.item() == np.float32(expected_weight)                     # and bit-exact
 
 
-def test_prioritized_replay_buffer_update_priority_assert(C):  # :1062-1076
+def test_prioritized_replay_buffer_update_priority_assert(C):  # :1043-1056
     b = C.PrioritizedReplayBuffer(max_size=10, alpha=0.6)
     b.add(td1(C, {"state": torch.tensor([1]), "action": torch.tensor([0]), "reward": torch.tensor([1.0])}))
     with pytest.raises(AssertionError):
