@@ -388,3 +388,20 @@ def test_sample_from_indices_index_errors_and_negative_indices(C, cuda_device):
     with pytest.raises(IndexError):
         b.check_gather_errors()
     b.check_gather_errors()  # flag cleared
+
+
+def test_uniform_sample_larger_than_the_prefix_kernel_table(C):
+    """replay_buffer.py:125 with batch_size > 16 384 (beyond xp_randperm_prefix's shared-memory table): still the
+    exact torch.randperm(size)[:batch_size], and batch_size > size returns size rows like the reference's slice."""
+    b = C.ReplayBuffer(max_size=40_000)
+    b.add(C.TensorBatch({"x": torch.arange(40_000, dtype=torch.float32).view(-1, 1)}, batch_size=[40_000]))
+    torch.manual_seed(3)
+    want = torch.randperm(40_000)[:20_000]
+    torch.manual_seed(3)
+    s = b.sample(20_000, return_idx=True)
+    assert torch.equal(s["idxs"].cpu(), want) and torch.equal(s["x"].cpu().view(-1), want.float())
+    torch.manual_seed(4)
+    want = torch.randperm(40_000)[:50_000]
+    torch.manual_seed(4)
+    s = b.sample(50_000, return_idx=True)
+    assert s["idxs"].shape == (40_000,) and torch.equal(s["idxs"].cpu(), want)
