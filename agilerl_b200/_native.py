@@ -65,6 +65,8 @@ _SIGNATURES = {
     "xp_per_sample": (C.c_int, [C.POINTER(XpTree), c_vp, c_i64, c_i64, c_i64, C.c_double, c_vp, c_vp, c_vp]),
     "xp_per_weights": (C.c_int, [C.POINTER(XpTree), c_vp, c_i64, c_i64, C.c_double, c_vp, c_vp]),
     "xp_per_update": (C.c_int, [C.POINTER(XpTree), c_vp, c_vp, c_vp, c_i64, c_i64, C.c_double, c_vp, c_vp]),
+    "xp_per_sample_hostu": (C.c_int, [C.POINTER(XpTree), c_vp, c_i64, c_i64, C.c_double, c_vp, c_vp, c_vp]),
+    "xp_per_update_hostp": (C.c_int, [C.POINTER(XpTree), c_vp, c_vp, c_vp, c_i64, c_i64, C.c_double, c_vp, c_vp]),
     "xp_pow_batch": (C.c_int, [c_vp, C.c_double, c_vp, c_i64, c_vp]),
     "xp_nstep_fold_insert": (C.c_int, [C.POINTER(XpKey), C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int,
                                        C.c_int, C.c_int, C.POINTER(C.c_float), c_i64, c_i64, c_i64, c_vp]),

@@ -28,6 +28,8 @@ using sample_fn = xp_status_t (*)(const xp_tree *, const float *, int64_t, int64
                                   int64_t *, float *, void *);
 using update_fn = xp_status_t (*)(const xp_tree *, xp_per_state *, const int64_t *, const float *,
                                   int64_t, int64_t, double, int *, void *);
+using sample_hostu_fn = xp_status_t (*)(const xp_tree *, const float *, int64_t, int64_t, double, int64_t *, float *,
+                                        void *);
 using copy_fn = xp_status_t (*)(void *, const void *, int64_t, void *);
 using peer_fn = xp_status_t (*)(const void *const *, const void *const *, void *const *, int, int, uint32_t *,
                                 const xp_peer_seg *, int, int *, void *);
@@ -38,6 +40,8 @@ struct Fns {
   update_fn per_update = nullptr;
   copy_fn copy_to_device = nullptr;
   peer_fn peer_allgather_graph = nullptr;
+  sample_hostu_fn per_sample_hostu = nullptr;  // host-vector variants (B <= XP_HOST_VEC_MAX): no staging copy
+  update_fn per_update_hostp = nullptr;
   // agilerl_b200._native.check(status, what): raises the mapped exception.  A borrowed handle whose
   // reference is deliberately never released: this struct is destroyed by the C runtime's exit
   // handlers, after the interpreter has been finalised, where a Py_DECREF would touch freed memory.
@@ -46,6 +50,11 @@ struct Fns {
 
 void bind_peer(uint64_t peer_allgather_graph) {
   g.peer_allgather_graph = reinterpret_cast<peer_fn>(peer_allgather_graph);
+}
+
+void bind_host_vec(uint64_t per_sample_hostu, uint64_t per_update_hostp) {
+  g.per_sample_hostu = reinterpret_cast<sample_hostu_fn>(per_sample_hostu);
+  g.per_update_hostp = reinterpret_cast<update_fn>(per_update_hostp);
 }
 
 void bind(uint64_t gather, uint64_t per_sample, uint64_t per_update, uint64_t copy_to_device,
@@ -226,8 +235,15 @@ class FastPer {
     const auto dev = c10::Device(c10::kCUDA, index);
     auto st = c10::cuda::getCurrentCUDAStream(index);
     const float *u = nullptr;
+    float u_host[XP_HOST_VEC_MAX];
+    const bool in_launch = !u_dev.has_value() && B <= XP_HOST_VEC_MAX && g.per_sample_hostu;
     if (u_dev.has_value()) {
       u = u_dev->data_ptr<float>();
+    } else if (in_launch) {
+      // one agent's batch: the draws travel inside the launch as a kernel parameter (xp_per_sample_hostu)
+      auto *gen = at::get_generator_or_default<at::CPUGeneratorImpl>(c10::nullopt, at::detail::getDefaultCPUGenerator());
+      std::lock_guard<std::mutex> lock(gen->mutex_);
+      for (int64_t i = 0; i < B; ++i) u_host[i] = (float)(gen->random() & ((1u << 24) - 1u)) * (1.0f / 16777216.0f);
     } else {
       // batch_size x torch.rand(1).item() == torch.rand(batch_size) == uniform_(0,1) on the
       // default CPU generator (replay_buffer.py:377), drawn straight into pinned memory
@@ -245,8 +261,12 @@ class FastPer {
     }
     at::Tensor idx = at::empty({B, 1}, at::TensorOptions().dtype(at::kLong).device(dev));
     at::Tensor w = at::empty({B, 1}, at::TensorOptions().dtype(at::kFloat).device(dev));
-    ok(g.per_sample(&tree_, u, B, 1, size, beta, idx.data_ptr<int64_t>(), w.data_ptr<float>(), st.stream()),
-       "xp_per_sample");
+    if (in_launch)
+      ok(g.per_sample_hostu(&tree_, u_host, B, size, beta, idx.data_ptr<int64_t>(), w.data_ptr<float>(), st.stream()),
+         "xp_per_sample_hostu");
+    else
+      ok(g.per_sample(&tree_, u, B, 1, size, beta, idx.data_ptr<int64_t>(), w.data_ptr<float>(), st.stream()),
+         "xp_per_sample");
     py::dict out;
     if (sibling_) {
       // linked n-step table (same capacity, index-aligned rows, train_off_policy.py:341-343): the rows of BOTH
@@ -341,6 +361,12 @@ class FastPer {
     const float *p = nullptr;
     if (prio.is_cuda()) {
       p = prio.data_ptr<float>();
+    } else if (n <= XP_HOST_VEC_MAX && g.per_update_hostp) {
+      // one agent's batch: the priorities travel inside the launch (xp_per_update_hostp)
+      ok(g.per_update_hostp(&tree_, reinterpret_cast<xp_per_state *>(state_.data_ptr()), idx.data_ptr<int64_t>(),
+                            prio.data_ptr<float>(), n, max_size_, alpha_, tree_err_.data_ptr<int>(), st.stream()),
+         "xp_per_update_hostp");
+      return;
     } else {
       Slot &s = ring_.acquire(n * 4);
       std::memcpy(s.hp, prio.data_ptr<float>(), (size_t)n * 4);
@@ -377,6 +403,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.doc() = "native fast path of the agilerl_b200 Python host (calls libb200xp.so)";
   m.def("bind", &bind);
   m.def("bind_peer", &bind_peer);
+  m.def("bind_host_vec", &bind_host_vec);
   py::class_<FastGather, std::shared_ptr<FastGather>>(m, "FastGather")
       .def(py::init<std::vector<at::Tensor>, std::vector<std::string>, int64_t, at::Tensor>())
       .def("gather", &FastGather::gather);

@@ -7,6 +7,8 @@
 //
 // The batched set (B sequential `tree[idx] = val` of the reference, segment_tree.py:81-95) lives
 // in tree_set.cuh: sorted level-synchronous climbs, no global atomics on the tree.
+#include <string.h>
+
 #include "common.cuh"
 #include "pow.cuh"
 #include "tree_set.cuh"
@@ -405,6 +407,35 @@ __global__ void __launch_bounds__(256) per_sample_kernel(Tree t, const float *u,
   }
 }
 
+// The small draw with its uniforms INSIDE the launch: B <= XP_HOST_VEC_MAX fp32 values travel as a kernel parameter
+// (one agent's torch.rand draws, replay_buffer.py:377), so the caller needs no host-to-device copy in front of the
+// kernel — one driver call and one copy-engine -> kernel dependency less per sample() call.  Same arithmetic as
+// per_sample_kernel<1, true> with P = 1.
+struct HostVec {
+  float v[XP_HOST_VEC_MAX];
+};
+
+__global__ void __launch_bounds__(256) per_sample_hostu_kernel(Tree t, const __grid_constant__ HostVec uv, long long B,
+                                                               double size, double neg_beta, long long *idx_out,
+                                                               float *w_out) {
+  xp::pdl_enter();
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // stratum == sample slot (one agent)
+  if (i >= B) return;
+  const double total = __ldg(&t.sum[t.stride]);
+  const double seg = __ddiv_rn(total, (double)B);
+  const double a = __dmul_rn(seg, (double)i);
+  const double b = __dmul_rn(seg, (double)(i + 1));
+  const double ub = __dadd_rn(__dmul_rn((double)uv.v[i], __dsub_rn(b, a)), a);
+  const double mn = w_out ? __ldg(&t.mn[t.stride]) : 0.0;
+  double leaf_val = 0.0;
+  const long long leaf = descend_wide<4>(t.sum, t.stride, t.cap, ub, &leaf_val);
+  idx_out[i] = leaf;
+  if (w_out) {
+    const double max_w = xp::xp_pow(__dmul_rn(__ddiv_rn(mn, total), size), neg_beta);
+    w_out[i] = is_weight_of(leaf_val, total, size, neg_beta, max_w);
+  }
+}
+
 __global__ void __launch_bounds__(256) per_weights_kernel(Tree t, const long long *idx,
                                                           long long B, double size,
                                                           double neg_beta, float *w_out) {
@@ -545,6 +576,26 @@ xp_status_t xp_per_sample(const xp_tree *tree, const float *u_dev, int64_t B, in
   return xp::check_launch("xp_per_sample");
 }
 
+xp_status_t xp_per_sample_hostu(const xp_tree *tree, const float *u_host, int64_t B, int64_t size, double beta,
+                                int64_t *idx_out_dev, float *w_out_dev, void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_per_sample_hostu", false);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(t.sum, XP_ERR_INVALID, "xp_per_sample_hostu: needs a sum tree");
+  XP_REQUIRE(!w_out_dev || t.mn, XP_ERR_INVALID, "xp_per_sample_hostu: weights need a min tree");
+  XP_REQUIRE(B >= 0 && B <= XP_HOST_VEC_MAX, XP_ERR_INVALID,
+             "xp_per_sample_hostu: B = %lld not in [0, %d] (larger draws: xp_per_sample with device uniforms)",
+             (long long)B, XP_HOST_VEC_MAX);
+  if (B == 0) return XP_OK;
+  XP_REQUIRE(u_host && idx_out_dev, XP_ERR_INVALID, "xp_per_sample_hostu: null pointer");
+  HostVec uv;
+  memcpy(uv.v, u_host, (size_t)B * sizeof(float));
+  const unsigned grid = (unsigned)((B + 63) / 64);
+  xp::launch(per_sample_hostu_kernel, dim3(grid), dim3(64), 0, (cudaStream_t)stream, t, uv, (long long)B, (double)size,
+             -beta, (long long *)idx_out_dev, w_out_dev);
+  return xp::check_launch("xp_per_sample_hostu");
+}
+
 xp_status_t xp_per_weights(const xp_tree *tree, const int64_t *idx_dev, int64_t B, int64_t size,
                            double beta, float *w_out_dev, void *stream) {
   Tree t;
@@ -577,6 +628,30 @@ xp_status_t xp_per_update(const xp_tree *tree, xp_per_state *state_dev, const in
   s.limit = max_size;
   s.err = err_flag_dev;
   return xpset::run_set(t, s, B, (cudaStream_t)stream);
+}
+
+xp_status_t xp_per_update_hostp(const xp_tree *tree, xp_per_state *state_dev, const int64_t *idx_dev,
+                                const float *prio_host, int64_t B, int64_t max_size, double alpha,
+                                int *err_flag_dev, void *stream) {
+  Tree t;
+  xp_status_t st = to_tree(tree, t, "xp_per_update_hostp", true);
+  if (st != XP_OK) return st;
+  XP_REQUIRE(state_dev, XP_ERR_INVALID, "xp_per_update_hostp: null state");
+  XP_REQUIRE(max_size > 0 && max_size <= t.cap, XP_ERR_INVALID, "xp_per_update_hostp: bad max_size");
+  XP_REQUIRE(B >= 0 && B <= XP_HOST_VEC_MAX, XP_ERR_INVALID, "xp_per_update_hostp: B outside [0, XP_HOST_VEC_MAX]");
+  if (B == 0) return XP_OK;
+  XP_REQUIRE(idx_dev && prio_host, XP_ERR_INVALID, "xp_per_update_hostp: null input");
+  SetSrc s{};
+  s.kind = kSrcPrio;
+  s.idx = (const long long *)idx_dev;
+  s.prio = nullptr;  // (the kernel points it at its shared copy of the parameter vector)
+  s.alpha = alpha;
+  s.max_priority_bits = (unsigned long long *)&state_dev->max_priority;
+  s.limit = max_size;
+  s.err = err_flag_dev;
+  xpset::PrioVec pv;
+  memcpy(pv.v, prio_host, (size_t)B * sizeof(float));
+  return xpset::launch_mid(t, s, B, &pv, (cudaStream_t)stream);
 }
 
 xp_status_t xp_pow_batch(const double *x_dev, double y, double *out_dev, int64_t n, void *stream) {

@@ -343,8 +343,7 @@ constexpr int kMidWarps = 16;  // at most; small batches launch 4 warps per CTA
 constexpr int kMidListCap = 1024;   // compact list capacity per CTA (keys)
 constexpr int kMidCompactFrom = 1024;
 template <bool PAIRED>
-__global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc s, int B, int nb, int shift) {
-  xp::pdl_enter();
+__device__ __forceinline__ void set_mid_body(const Tree &t, const SetSrc &s, int B, int nb, int shift) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ u64 s_list[kMidWarps][32];
   __shared__ double2 s_top[32];
@@ -370,7 +369,7 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
       for (int u = 0; u < U; ++u) {
         const int i = min(i0 + u * (int)blockDim.x + (int)threadIdx.x, B - 1);
         raw[u] = (s.kind == kSrcRange) ? src_idx(s, i) : __ldg(s.idx + i);
-        pr[u] = fold ? __ldg(s.prio + i) : 0.0f;
+        pr[u] = fold ? s.prio[i] : 0.0f;  // (generic load: the host-vector variant keeps them in shared memory)
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
@@ -437,6 +436,29 @@ __global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc 
   __threadfence();
   // dense rebuild of the nb-leaf top by this CTA (nb <= 2048 <= 8 nodes per thread)
   cta_reduce<PAIRED, 8>(t, (int)(t.cap >> shift), nb, s_top);
+}
+
+template <bool PAIRED>
+__global__ void __launch_bounds__(kMidWarps * 32) set_mid_kernel(Tree t, SetSrc s, int B, int nb, int shift) {
+  xp::pdl_enter();
+  set_mid_body<PAIRED>(t, s, B, nb, shift);
+}
+
+// The same update with the B <= XP_HOST_VEC_MAX new priorities INSIDE the launch (a kernel parameter): what
+// update_priorities receives is a host ndarray of one agent's batch (replay_buffer.py:411-428, dqn_rainbow.py:487-488),
+// so no host-to-device copy has to precede the kernel.  Every CTA parks the vector in shared memory first.
+struct PrioVec {
+  float v[XP_HOST_VEC_MAX];
+};
+template <bool PAIRED>
+__global__ void __launch_bounds__(kMidWarps * 32) set_mid_hostp_kernel(Tree t, SetSrc s, const __grid_constant__ PrioVec pv,
+                                                                       int B, int nb, int shift) {
+  xp::pdl_enter();
+  __shared__ float s_prio[XP_HOST_VEC_MAX];
+  for (int i = threadIdx.x; i < B; i += blockDim.x) s_prio[i] = pv.v[i];
+  __syncthreads();
+  s.prio = s_prio;
+  set_mid_body<PAIRED>(t, s, B, nb, shift);
 }
 
 // ---- schedule L (large B): histogram+scan -> scatter -> one warp per bucket -> dense top --------
@@ -855,6 +877,37 @@ inline xp_status_t launch_dense(const Tree &t, int h0, long long width, bool pai
   return XP_OK;
 }
 
+// schedule M: ONE launch.  `pv` != NULL: the priorities travel inside the launch (set_mid_hostp_kernel).
+inline xp_status_t launch_mid(const Tree &t, const SetSrc &s, long long B, const PrioVec *pv, cudaStream_t st) {
+  const int L = ilog2(t.cap);
+  const bool paired = is_paired(t);
+  long long nb = 1;
+  while (nb * 8 < B && nb < 2048 && nb * 2 <= t.cap) nb <<= 1;
+  const int shift = L - ilog2(nb);
+  // every CTA reads the whole batch once: wider CTAs for larger batches keep that O(B * nb / warps)
+  int warps = B > 4096 ? 16 : B > 2048 ? 8 : 4;
+  if (warps > nb) warps = (int)nb;
+  const unsigned grid = (unsigned)(nb / warps);
+  size_t smem = (size_t)B * 4;
+  if (B > kMidCompactFrom && smem < (size_t)kMidListCap * 8) smem = (size_t)kMidListCap * 8;
+  if (pv) {  // B <= XP_HOST_VEC_MAX: well under the default shared-memory limit, no attribute needed
+    if (paired)
+      xp::launch(set_mid_hostp_kernel<true>, dim3(grid), dim3(warps * 32), smem, st, t, s, *pv, (int)B, (int)nb, shift);
+    else
+      xp::launch(set_mid_hostp_kernel<false>, dim3(grid), dim3(warps * 32), smem, st, t, s, *pv, (int)B, (int)nb, shift);
+    return xp::check_launch("tree set (M, host priorities)", 1);
+  }
+  static xp::DeviceOnce mid_attr[2];
+  xp_status_t rc = set_attr_once(paired ? (const void *)set_mid_kernel<true> : (const void *)set_mid_kernel<false>,
+                                 (size_t)65536, mid_attr[paired ? 1 : 0]);
+  if (rc != XP_OK) return rc;
+  if (paired)
+    xp::launch(set_mid_kernel<true>, dim3(grid), dim3(warps * 32), smem, st, t, s, (int)B, (int)nb, shift);
+  else
+    xp::launch(set_mid_kernel<false>, dim3(grid), dim3(warps * 32), smem, st, t, s, (int)B, (int)nb, shift);
+  return xp::check_launch("tree set (M)", 1);
+}
+
 inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStream_t st) {
   if (B == 0) return XP_OK;
   XP_REQUIRE(B < (1ll << 31) - 1, XP_ERR_INVALID, "tree set: batch too large");
@@ -866,26 +919,7 @@ inline xp_status_t run_set(const Tree &t, const SetSrc &s, long long B, cudaStre
   // pays for saving two launches (cap 2^20, 16 384 items: M 21.7 us, S below; 32 768 items: S 16 us)
   static const int m_max = env_int("XP_SET_M_MAX", 8192);  // developer knob
   const bool fits_s = slotted_scratch_ints(t.cap, [&] { long long nb = 1; while (nb * env_int("XP_BUCKET_ITEMS", 16) < B && nb < 32768 && nb * 4 <= t.cap) nb <<= 1; return nb; }(), B, s.kind == kSrcPrio) <= t.cap && s.kind != kSrcRange;
-  if (B <= m_max || (B <= 16384 && !fits_s)) {  // schedule M: one launch
-    long long nb = 1;
-    while (nb * 8 < B && nb < 2048 && nb * 2 <= t.cap) nb <<= 1;
-    const int shift = L - ilog2(nb);
-    // every CTA reads the whole batch once: wider CTAs for larger batches keep that O(B * nb / warps)
-    int warps = B > 4096 ? 16 : B > 2048 ? 8 : 4;
-    if (warps > nb) warps = (int)nb;
-    const unsigned grid = (unsigned)(nb / warps);
-    size_t smem = (size_t)B * 4;
-    if (B > kMidCompactFrom && smem < (size_t)kMidListCap * 8) smem = (size_t)kMidListCap * 8;
-    static xp::DeviceOnce mid_attr[2];
-    xp_status_t rc = set_attr_once(paired ? (const void *)set_mid_kernel<true> : (const void *)set_mid_kernel<false>,
-                                   (size_t)65536, mid_attr[paired ? 1 : 0]);
-    if (rc != XP_OK) return rc;
-    if (paired)
-      xp::launch(set_mid_kernel<true>, dim3(grid), dim3(warps * 32), smem, st, t, s, (int)B, (int)nb, shift);
-    else
-      xp::launch(set_mid_kernel<false>, dim3(grid), dim3(warps * 32), smem, st, t, s, (int)B, (int)nb, shift);
-    return xp::check_launch("tree set (M)", 1);
-  }
+  if (B <= m_max || (B <= 16384 && !fits_s)) return launch_mid(t, s, B, nullptr, st);  // schedule M: one launch
   const unsigned grid = (unsigned)((B + 255) / 256);
   long long nb = 1;
   const int use_half = 1;

@@ -169,6 +169,28 @@ def per_update(tree: XpTree, state: torch.Tensor, idx: torch.Tensor, prio: torch
           "xp_per_update")
 
 
+def per_sample_hostu(tree: XpTree, u_host, B: int, size: int, beta: float, idx_out: torch.Tensor,
+                     w_out: torch.Tensor | None) -> None:
+    """xp_per_sample for one agent with the fp32 uniforms still on the host (numpy array / CPU tensor)."""
+    u = torch.as_tensor(u_host)
+    if u.is_cuda or u.dtype != torch.float32 or not u.is_contiguous() or u.numel() < B:
+        raise ValueError("u_host: contiguous fp32 host vector of at least B elements")
+    check(nv.load().xp_per_sample_hostu(C.byref(tree), u.data_ptr(), B, size, beta, idx_out.data_ptr(),
+                                        ptr(w_out), _stream(idx_out)), "xp_per_sample_hostu")
+
+
+def per_update_hostp(tree: XpTree, state: torch.Tensor, idx: torch.Tensor, prio_host, max_size: int,
+                     alpha: float, err_flag=None) -> None:
+    """xp_per_update with the fp32 priorities still on the host (numpy array / CPU tensor), B <= 1024."""
+    _need(idx, torch.int64, "idx")
+    p = torch.as_tensor(prio_host)
+    if p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous() or p.numel() < idx.numel():
+        raise ValueError("prio_host: contiguous fp32 host vector of at least len(idx) elements")
+    check(nv.load().xp_per_update_hostp(C.byref(tree), state.data_ptr(), idx.data_ptr(), p.data_ptr(),
+                                        idx.numel(), max_size, alpha, ptr(err_flag), _stream(idx)),
+          "xp_per_update_hostp")
+
+
 def pow_batch(x: torch.Tensor, y: float) -> torch.Tensor:
     _need(x, torch.float64, "x")
     out = torch.empty_like(x)

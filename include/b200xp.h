@@ -146,6 +146,17 @@ xp_status_t xp_per_weights(const xp_tree *t, const int64_t *idx_dev, int64_t B, 
 xp_status_t xp_per_update(const xp_tree *t, xp_per_state *state_dev, const int64_t *idx_dev,
                           const float *prio_dev, int64_t B, int64_t max_size, double alpha,
                           int *err_flag_dev, void *stream);
+/* The two calls above for ONE agent's batch of B <= XP_HOST_VEC_MAX rows whose fp32 vector is still in HOST memory
+ * — the torch.rand draws of _sample_proportional (replay_buffer.py:377) and the ndarray update_priorities
+ * receives (replay_buffer.py:411-428, from dqn_rainbow.py:487-488): the vector is read during the call and travels
+ * inside the launch (a kernel parameter), so no host-to-device copy precedes the kernel and the caller may reuse
+ * the host array on return.  Same arithmetic, same results as xp_per_sample (P = 1) / xp_per_update.          */
+#define XP_HOST_VEC_MAX 1024
+xp_status_t xp_per_sample_hostu(const xp_tree *t, const float *u_host, int64_t B, int64_t size, double beta,
+                                int64_t *idx_out_dev, float *w_out_dev, void *stream);
+xp_status_t xp_per_update_hostp(const xp_tree *t, xp_per_state *state_dev, const int64_t *idx_dev,
+                                const float *prio_host, int64_t B, int64_t max_size, double alpha,
+                                int *err_flag_dev, void *stream);
 /* priority ** alpha as CPython computes it (glibc pow), batch, fp64 in/out
  * (replay_buffer.py:322,401,406).                                                       */
 xp_status_t xp_pow_batch(const double *x_dev, double y, double *out_dev, int64_t n,

@@ -523,6 +523,65 @@ def test_per_full_size_properties(xp, cuda_device):
     assert torch.equal(nodes, before) and int(per.tree.err.item()) == 0
 
 
+@pytest.mark.parametrize("max_size,B", [(1000, 32), (1 << 12, 1), (50_000, 257), (1 << 20, 1024), (1 << 22, 512)])
+def test_per_host_vector_variants_match_device_pointer_variants(xp, cuda_device, max_size, B):
+    """xp_per_sample_hostu / xp_per_update_hostp (the fp32 vector travels inside the launch) against
+    xp_per_sample (P = 1) / xp_per_update on twin trees: indices, weights, every tree node, max_priority
+    and the error flag — bit-exact — through three rounds, duplicates and an out-of-range index included;
+    and against the list oracle (replay_buffer.py:357-428) when the tree is small."""
+    alpha, beta = 0.6, 0.4
+    rng = np.random.default_rng(max_size + B)
+    a, b = DevPer(xp, cuda_device, max_size, alpha), DevPer(xp, cuda_device, max_size, alpha)
+    a.add(max_size), b.add(max_size)
+    ora = None
+    if max_size <= 50_000:                              # the list oracle finishes in seconds there
+        ora = xo.PerOracle(max_size, alpha)
+        ora.add(max_size)
+    for rnd in range(3):
+        idx = rng.integers(0, max_size, B)
+        if B > 4:
+            idx[B // 2:] = idx[: B - B // 2]          # duplicates: the last writer wins
+        pr = (np.abs(rng.standard_normal(B)) * (3.0 if rnd else 0.5) + 1e-7).astype(np.float32)
+        d_idx = dev(idx, cuda_device, torch.int64)
+        xp.per_update(a.tree.t, a.state, d_idx, dev(pr, cuda_device, torch.float32), max_size, alpha, a.tree.err)
+        keep = pr.copy()
+        xp.per_update_hostp(b.tree.t, b.state, d_idx, pr, max_size, alpha, b.tree.err)
+        pr[:] = -1.0                                    # the host array is the caller's again on return
+        u = rng.random(B, dtype=np.float32)
+        wi = torch.empty(B, dtype=torch.int64, device=cuda_device); ww = torch.empty(B, device=cuda_device)
+        gi = torch.empty_like(wi); gw = torch.empty_like(ww)
+        xp.per_sample(a.tree.t, dev(u, cuda_device, torch.float32), B, 1, max_size, beta, wi, ww)
+        keep_u = u.copy()
+        xp.per_sample_hostu(b.tree.t, u, B, max_size, beta, gi, gw)
+        u[:] = 2.0
+        torch.cuda.synchronize()
+        assert torch.equal(gi, wi) and torch.equal(gw, ww), rnd
+        assert torch.equal(a.tree.nodes, b.tree.nodes) and torch.equal(a.state, b.state), rnd
+        gi2 = torch.empty_like(gi)
+        xp.per_sample_hostu(b.tree.t, keep_u, B, max_size, beta, gi2, None)   # indices only
+        assert torch.equal(gi2, wi)
+        if ora is not None:
+            ora.update_priorities(idx, keep)
+            oi = ora.sample_proportional(B, keep_u)
+            assert np.array_equal(gi.cpu().numpy(), oi), rnd
+            assert np.array_equal(gw.cpu().numpy(), ora.calculate_weights(oi, beta)), rnd
+            assert float(b.state.item()) == ora.max_priority
+    # an index outside [0, max_size): flagged, row skipped — like xp_per_update
+    bad = dev(np.array([0, max_size, 1]), cuda_device, torch.int64)
+    three = np.array([0.5, 9.0, 0.25], dtype=np.float32)
+    xp.per_update(a.tree.t, a.state, bad, dev(three, cuda_device, torch.float32), max_size, alpha, a.tree.err)
+    xp.per_update_hostp(b.tree.t, b.state, bad, three, max_size, alpha, b.tree.err)
+    torch.cuda.synchronize()
+    assert int(a.tree.err.item()) == 1 and int(b.tree.err.item()) == 1
+    assert torch.equal(a.tree.nodes, b.tree.nodes) and torch.equal(a.state, b.state)
+    # limits
+    big = torch.zeros(1025, dtype=torch.int64, device=cuda_device)
+    with pytest.raises(ValueError):
+        xp.per_update_hostp(b.tree.t, b.state, big, np.ones(1025, dtype=np.float32), max_size, alpha, b.tree.err)
+    with pytest.raises(ValueError):
+        xp.per_sample_hostu(b.tree.t, np.ones(1025, dtype=np.float32), 1025, max_size, beta, big, None)
+
+
 def test_per_c4_size_indices_and_weights_vs_array_oracle(xp, cuda_device):
     """BASELINE.json config 4 (cap 2^24, 64 agents x 4 096 strata, L = 24) against an oracle OUTSIDE the
     library: oracle.xp_oracle.np_* (numpy restatement of segment_tree.py:136-156 / replay_buffer.py:357-409,
