@@ -8,7 +8,7 @@
 //   gae_tma_kernel  (gae_tma.cuh; shapes whose strides are 16-byte multiples): one warp per CTA,
 //           all HBM traffic issued by the TMA unit into / out of a shared-memory ring of time boxes;
 //           the lanes run the chain from shared memory and write results in place;
-//   gae_spec_kernel (same shapes, small launches — at most one strip on every other SM): the same data
+//   gae_spec_kernel (same shapes, small launches — at most one strip per SM): the same data
 //           path with three producer warps preparing A_t and one warp running only the carry chain;
 //   gae_tile_kernel (any shape): 256 threads stage a [TC x 32 env] tile (A_t in fp64, v_t and a
 //           terminal flag) with coalesced loads, warp 0 runs the chain and stores 128-byte rows.
@@ -176,9 +176,23 @@ __global__ void __launch_bounds__(kThreads, 4) gae_tile_kernel(const ScanParams 
 }
 
 // ---- TMA-fed kernel (aligned shapes): see gae_tma.cuh -------------------------------------------
+#ifdef XP_GAE_TRACE  // developer build only (tools/micro/gae_trace.py): per-CTA phase stamps of gae_tma_kernel
+__device__ unsigned long long g_gae_trace[4096 * 16];
+__device__ __forceinline__ unsigned long long trace_gt() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define XP_TR(k, v) do { const unsigned bid_ = blockIdx.x + blockIdx.y * gridDim.x; if ((threadIdx.x & 31) == 0 && bid_ < 4096) g_gae_trace[bid_ * 16 + (k)] = (v); } while (0)
+#define XP_TRC(k) XP_TR(k, (unsigned long long)clock64())
+#else
+#define XP_TR(k, v) do { } while (0)
+#define XP_TRC(k) do { } while (0)
+#endif
+
 template <int MODE>
 __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams p,
-                                                     const __grid_constant__ gaetma::Maps maps, const int pdl) {
+                                                                const __grid_constant__ gaetma::Maps maps, const int pdl) {
   using namespace gaetma;
   // programmatic launch: nothing above this line touches global memory, so stream order is kept exactly
   if (pdl) {
@@ -187,37 +201,57 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
   }
   extern __shared__ __align__(128) unsigned char smem_tma[];
   Stage *stage = reinterpret_cast<Stage *>(smem_tma);
-  __shared__ __align__(8) unsigned long long bars[kStages];
-  const int lane = threadIdx.x;  // env within the 64-wide box
-  const int tiles_per_agent = (int)((p.N + kBoxE - 1) / kBoxE);
-  const int agent = blockIdx.x / tiles_per_agent;
-  const int env0 = (blockIdx.x - agent * tiles_per_agent) * kBoxE;
+  __shared__ __align__(8) unsigned long long full[kStages];  // box landed (TMA transaction bytes)
+  const int lane = threadIdx.x;  // env within the box
+  if (elect_one()) {  // the TMA unit fetches a 128-byte descriptor before its first use of a map: start that now
+    tma_prefetch_map(&maps.r);
+    tma_prefetch_map(&maps.v);
+    tma_prefetch_map(&maps.d);
+  }
+#ifdef XP_GAE_TRACE
+  {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    XP_TR(0, (unsigned long long)smid);
+    XP_TR(1, trace_gt());
+    XP_TRC(2);
+  }
+#endif
+  const int agent = blockIdx.y;  // grid = (strips of an agent, agents): no division on the way to the first load
+  const int env0 = blockIdx.x * kBoxE;
   const int T = (int)p.T;
-  const int nbox = (T + kBoxT - 1) / kBoxT;  // box b (0 = newest) covers t in [32(nbox-1-b), +32)
+  const int nbox = (T + kBoxT - 1) / kBoxT;  // box b (0 = newest) covers t in [kBoxT (nbox-1-b), +kBoxT)
 
   if (lane == 0) {
 #pragma unroll
-    for (int s = 0; s < kStages; ++s) mbar_init(&bars[s], 1);
+    for (int s = 0; s < kStages; ++s) mbar_init(&full[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncthreads();
-  auto issue = [&](int b) {  // lane 0 only
-    Stage &st = stage[b % kStages];
-    unsigned long long *bar = &bars[b % kStages];
-    const int t0 = kBoxT * (nbox - 1 - b);  // coordinates stay non-negative; the newest box may
-                                            // run past T (zero-filled on load, clipped on store)
-    mbar_expect_tx(bar, kStageBytes);
-    tma_load_3d(&st.r[0][0], &maps.r, env0, t0, agent, bar);
-    tma_load_3d(&st.v[0][0], &maps.v, env0, t0, agent, bar);
-    tma_load_3d(&st.d[0][0], &maps.d, env0, t0, agent, bar);
+  __syncwarp();  // one warp per CTA
+  // the whole warp calls this; ONE elected lane talks to the TMA unit (elect.sync, so that the three UTMALDG are
+  // straight-line code: under `if (lane == 0)` each sits in a serialising loop over the active lanes)
+  auto issue = [&](int b) {
+    if (elect_one()) {
+      Stage &st = stage[b % kStages];
+      unsigned long long *bar = &full[b % kStages];
+      const int t0 = kBoxT * (nbox - 1 - b);  // coordinates stay non-negative; the newest box may
+                                              // run past T (zero-filled on load, clipped on store)
+      mbar_expect_tx(bar, kStageBytes);
+      tma_load_3d(&st.r[0][0], &maps.r, env0, t0, agent, bar);
+      tma_load_3d(&st.v[0][0], &maps.v, env0, t0, agent, bar);
+      tma_load_3d(&st.d[0][0], &maps.d, env0, t0, agent, bar);
+    }
   };
-  if (lane == 0) {
-    for (int b = 0; b < kStages && b < nbox; ++b) issue(b);
-  }
-  // every load of a short strip is in flight: let the next grid of the stream become resident now (it blocks at
+  for (int b = 0; b < kAhead && b < nbox; ++b) issue(b);
+  // every load the strip starts with is in flight: let the next grid of the stream become resident now (it blocks at
   // its own griddepcontrol.wait until this grid has completed and flushed)
-  if (pdl == 2 && nbox <= kStages) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (pdl == 2) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (elect_one()) {
+    tma_prefetch_map(&maps.adv);
+    tma_prefetch_map(&maps.ret);
+  }
 
+  XP_TRC(3);
   const bool env_ok = env0 + lane < p.N;
   double lv = 0.0, ld = 0.0;
   if (env_ok) {
@@ -231,7 +265,18 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
 
   for (int b = 0; b < nbox; ++b) {
     Stage &st = stage[b % kStages];
-    mbar_wait(&bars[b % kStages], (unsigned)((b / kStages) & 1));
+    mbar_wait(&full[b % kStages], (unsigned)((b / kStages) & 1));
+    if (b < 2) XP_TRC(4 + 3 * b);
+    if (b + kAhead < nbox) {
+      // box b is here: ask for box b + kAhead (kAhead boxes in flight, the oldest first in every queue).  Its stage
+      // last held box b + kAhead - kStages, whose stores — all but the newest kStages - kAhead - 1 bulk groups of
+      // lane 0 — must have read shared memory.
+      if (b + kAhead >= kStages) {
+        if (lane == 0) tma_wait_read<kStages - kAhead - 1>();
+        __syncwarp();
+      }
+      issue(b + kAhead);
+    }
     const int t0 = kBoxT * (nbox - 1 - b);
     int row = (T - 1 - t0) < (kBoxT - 1) ? (T - 1 - t0) : (kBoxT - 1);
     if (MODE == kModeGae && b == 0) {  // t = T-1 bootstraps from last_value / last_done (:451-453)
@@ -289,22 +334,23 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
         st.v[row - u][lane] = g8[u];
       }
     }
+    if (b < 2) XP_TRC(5 + 3 * b);
     fence_proxy_async();  // generic-proxy writes above -> visible to the TMA store
-    __syncthreads();      // the warp is done with the box
-    if (lane == 0) {
+    __syncwarp();         // the warp is done with the box
+    if (lane == 0) {      // (bulk groups are per thread: always the same lane)
       tma_store_3d(&maps.adv, env0, t0, agent, &st.r[0][0]);
       tma_store_3d(&maps.ret, env0, t0, agent, &st.v[0][0]);
       tma_commit();
-      // the stage box b-1 lived in is free once ITS stores have read shared memory
-      if (b >= 1 && b - 1 + kStages < nbox) {
-        tma_wait_read<1>();
-        issue(b - 1 + kStages);
-      }
     }
+    if (b < 2) XP_TRC(6 + 3 * b);
   }
-  // the CTA may retire once the stores have READ shared memory; their global writes complete on
-  // their own (kernel completion orders them)
+  // the CTA may retire once the stores have READ shared memory; their global writes complete on their own
+  // (kernel completion orders them)
   if (lane == 0) tma_wait_read<0>();
+  XP_TRC(10);
+#ifdef XP_GAE_TRACE
+  XP_TR(11, trace_gt());
+#endif
 }
 
 // ---- warp-specialised TMA kernel: three producer warps prepare A_t, warp 0 runs only the carry chain ------
@@ -739,10 +785,11 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
     if (!e || !e[0]) return 0;
     return e[0] == 't' && e[1] == 'i' ? 2 : e[0] == 't' ? 3 : e[0] == 's' ? 4 : 0;
   }();
-  // the warp-specialised kernel pays when the launch is latency-bound — at most one strip on every other SM, e.g. the
-  // per-agent call of the drop-in (1 024 envs = 32 strips): 6.37 vs 6.78 us per launch; with the GPU full it loses
-  // (C3 11.8 vs 10.9 us, 16x 108 vs 93 us: four times the warps for the same conversion work)
-  const bool want_spec = which == 4 || (which == 0 && 2 * grid_tma <= (long long)xp::sm_count());
+  // the warp-specialised kernel pays while there is at most one strip per SM, e.g. the per-agent call of the drop-in
+  // (1 024 envs = 32 strips) — us per launch at T = 128, N = 1 024 (spec / tma): 1 agent 5.57 / 6.50, 4 agents 5.98 /
+  // 6.81; with more strips than SMs it loses: 6 agents 7.87 / 7.67, C3 (16) 10.5 / 9.55, 16x 105 / 91.4 (four times
+  // the warps for the same conversion work)
+  const bool want_spec = which == 4 || (which == 0 && grid_tma <= (long long)xp::sm_count());
   if (tma_ok && want_spec) {
     gaetma::Maps maps;
     if (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
@@ -763,7 +810,7 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
       return xp::check_launch("xp_gae (spec)");
     }
   }
-  if (tma_ok && which != 2) {
+  if (tma_ok && which != 2 && p.P <= 65535) {
     gaetma::Maps maps;
     if (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
         encode_map(&maps.d, p.dones, 1, p) && encode_map(&maps.adv, p.adv, 4, p) &&
@@ -781,15 +828,16 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
       }
       // (programmatic dependent launch was measured and dropped: early-resident CTAs of the next
       // launch slowed the running one, 11.5 vs 11.0 us at C3)
+      const dim3 grid2((unsigned)((p.N + gaetma::kBoxE - 1) / gaetma::kBoxE), (unsigned)p.P);
       static const int pdl = [] {
         const char *e = getenv("XP_GAE_PDL");  // developer knob: 0 plain | 1 release at entry | 2 release after the loads
         return (e && e[0]) ? atoi(e) : kDefaultGaePdl;
       }();
       if (pdl && xp::pdl_enabled()) {
-        xp::launch(gae_tma_kernel<MODE>, dim3((unsigned)grid_tma), dim3(gaetma::kBoxE),
+        xp::launch(gae_tma_kernel<MODE>, grid2, dim3(gaetma::kBoxE),
                    sizeof(gaetma::Stage) * gaetma::kStages, s, p, maps, pdl);
       } else {
-        gae_tma_kernel<MODE><<<(unsigned)grid_tma, gaetma::kBoxE, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps, 0);
+        gae_tma_kernel<MODE><<<grid2, gaetma::kBoxE, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps, 0);
       }
       return xp::check_launch("xp_gae (tma)");
     }
@@ -882,3 +930,9 @@ xp_status_t xp_mc_returns(const float *rewards, const float *values, const uint8
 }
 
 }  // extern "C"
+
+#ifdef XP_GAE_TRACE
+extern "C" int xp_gae_trace_read(unsigned long long *host, int n_words) {
+  return (int)cudaMemcpyFromSymbol(host, g_gae_trace, (size_t)n_words * 8);
+}
+#endif

@@ -58,7 +58,7 @@ def test_gae_golden_bitwise(xp, cuda_device, seed):
 @pytest.mark.parametrize("use_gae", [True, False])
 def test_gae_population_vs_oracle(xp, cuda_device, shape, use_gae, kernel, monkeypatch):
     """Every kernel behind xp_gae on every shape (the knob is read per call; "" = the size-based default):
-    gae_tma_kernel (one warp per strip), gae_spec_kernel (warp-specialised; aligned blocks for T % 16 == 0, the
+    gae_tma_kernel (one warp per strip; look-ahead stage recycling for T > 128), gae_spec_kernel (warp-specialised; aligned blocks for T % 16 == 0, the
     per-row path otherwise; stage recycling for T > 128), gae_tile_kernel (any alignment)."""
     monkeypatch.setenv("XP_GAE_KERNEL", kernel)
     P, T, N = shape

@@ -8,8 +8,6 @@ timeout 900 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpur
 python -c "import json; d=json.loads(open('gpurun_out/bench_ref.json').read()); print('reference', round(d['value']), d['cpu_baseline']['kind'], 'wall', d['wall_s'], '| upper', round(d['population_parallel_upper_bound']['value']), d['population_parallel_upper_bound']['cores'])"
 timeout 1200 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -3 gpurun_out/bench.err
 python tools/show_bench.py gpurun_out/bench.json
-# small captures: n-step fold insert (move_kernel<2>) from the insert path, gae_spec_kernel at P = 1
-I="python tools/micro/insert_profile.py"
-timeout 300 $I > gpurun_out/insert_profile.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:move_kernel -s 30 -c 3 -f -o gpurun_out/prof_nstep $I > gpurun_out/ncu_nstep.log 2>&1; echo "ncu nstep rc=$?"
-G="python tools/micro/gae_once.py 1"
-timeout 120 $G > gpurun_out/gae_once.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:gae_spec -s 2 -c 2 -f -o gpurun_out/prof_gae_spec $G > gpurun_out/ncu_gae_spec.log 2>&1; echo "ncu gae_spec rc=$?"
+# capture of the dominant C3 kernel (gae_tma_kernel, 16 agents) with the final code
+G="python tools/micro/gae_once.py 16"
+timeout 120 $G > gpurun_out/gae_once.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:gae_tma -s 2 -c 2 -f -o gpurun_out/prof_gae $G > gpurun_out/ncu_gae.log 2>&1; echo "ncu gae rc=$?"
