@@ -44,7 +44,8 @@ def load():
                  addr(lib.xp_copy_to_device), nv.check)
         mod.bind_peer(addr(lib.xp_peer_allgather_graph))
         if os.environ.get("XP_NO_HOST_VEC", "0") != "1":  # developer knob: stage the 1 KB vectors through the pinned ring
-            mod.bind_host_vec(addr(lib.xp_per_sample_hostu), addr(lib.xp_per_update_hostp))
+            mod.bind_host_vec(addr(lib.xp_per_sample_hostu), addr(lib.xp_per_update_hostp),
+                              addr(lib.xp_peer_publish_allgather_graph))
         _MOD = mod
     except Exception as e:  # pragma: no cover - depends on the local toolchain
         warnings.warn(f"agilerl_b200: native host fast path unavailable ({e}); using the Python host")

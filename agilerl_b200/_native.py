@@ -50,6 +50,8 @@ _SIGNATURES = {
     "xp_bptt_indices": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "xp_peer_allgather": (C.c_int, [c_vp, c_vp, C.c_int, C.c_int, C.c_uint32, c_vp, C.c_int, c_vp, c_vp]),
     "xp_peer_allgather_graph": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, C.c_int, c_vp, c_vp, C.c_int, c_vp, c_vp]),
+    "xp_peer_publish_allgather_graph": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, C.c_int, c_vp, c_vp, C.c_int, c_vp, C.c_int,
+                                                  c_vp, c_vp, c_vp]),
     "xp_peer_set_timeout_cycles": (None, [c_i64]),
     "xp_peer_ring_insert": (C.c_int, [c_vp, c_vp, C.c_int, C.c_int, C.c_uint32, c_vp, C.c_int, c_i64, c_i64,
                                       c_i64, c_vp, c_vp]),

@@ -34,6 +34,9 @@ using copy_fn = xp_status_t (*)(void *, const void *, int64_t, void *);
 using peer_fn = xp_status_t (*)(const void *const *, const void *const *, void *const *, int, int, uint32_t *,
                                 const xp_peer_seg *, int, int *, void *);
 
+using peer_pub_fn = xp_status_t (*)(const void *const *, const void *const *, void *const *, int, int, uint32_t *,
+                                    const xp_peer_seg *, int, const void *const *, int, const float *, int *, void *);
+
 struct Fns {
   gather_fn gather = nullptr;
   sample_fn per_sample = nullptr;
@@ -42,6 +45,7 @@ struct Fns {
   peer_fn peer_allgather_graph = nullptr;
   sample_hostu_fn per_sample_hostu = nullptr;  // host-vector variants (B <= XP_HOST_VEC_MAX): no staging copy
   update_fn per_update_hostp = nullptr;
+  peer_pub_fn peer_publish_allgather_graph = nullptr;  // block written by the exchange kernel itself (<= 32 KB)
   // agilerl_b200._native.check(status, what): raises the mapped exception.  A borrowed handle whose
   // reference is deliberately never released: this struct is destroyed by the C runtime's exit
   // handlers, after the interpreter has been finalised, where a Py_DECREF would touch freed memory.
@@ -52,9 +56,10 @@ void bind_peer(uint64_t peer_allgather_graph) {
   g.peer_allgather_graph = reinterpret_cast<peer_fn>(peer_allgather_graph);
 }
 
-void bind_host_vec(uint64_t per_sample_hostu, uint64_t per_update_hostp) {
+void bind_host_vec(uint64_t per_sample_hostu, uint64_t per_update_hostp, uint64_t peer_publish_allgather_graph) {
   g.per_sample_hostu = reinterpret_cast<sample_hostu_fn>(per_sample_hostu);
   g.per_update_hostp = reinterpret_cast<update_fn>(per_update_hostp);
+  g.peer_publish_allgather_graph = reinterpret_cast<peer_pub_fn>(peer_publish_allgather_graph);
 }
 
 void bind(uint64_t gather, uint64_t per_sample, uint64_t per_update, uint64_t copy_to_device,
@@ -330,6 +335,18 @@ class FastPer {
     TORCH_CHECK(idx.numel() == x_n_ && prio.numel() == x_n_, "replicated update: every rank passes ", x_n_, " pairs");
     const auto index = table_->index();
     auto st = c10::cuda::getCurrentCUDAStream(index);
+    if (!prio.is_cuda() && x_n_ <= XP_HOST_VEC_MAX && g.peer_publish_allgather_graph) {
+      // one agent's batch: the exchange kernel writes this rank's block itself — the indices from the device tensor,
+      // the priorities from the host vector inside the launch — so two copy calls fall away
+      const void *src[2] = {idx.data_ptr<int64_t>(), nullptr};
+      ok(g.peer_publish_allgather_graph(xb0_, xb1_, xfl_, rank_, world_, reinterpret_cast<uint32_t *>(x_epoch_.data_ptr()),
+                                        segs_, 2, src, 1, prio.data_ptr<float>(), x_err_.data_ptr<int>(), st.stream()),
+         "xp_peer_publish_allgather_graph");
+      ok(g.per_update(&tree_, reinterpret_cast<xp_per_state *>(state_.data_ptr()), x_idx_.data_ptr<int64_t>(),
+                      x_prio_.data_ptr<float>(), x_n_ * world_, max_size_, alpha_, tree_err_.data_ptr<int>(), st.stream()),
+         "xp_per_update");
+      return;
+    }
     char *blk = const_cast<char *>(static_cast<const char *>((k ? xb1_ : xb0_)[rank_]));
     C10_CUDA_CHECK(cudaMemcpyAsync(blk, idx.data_ptr<int64_t>(), (size_t)x_n_ * 8, cudaMemcpyDeviceToDevice, st.stream()));
     if (prio.is_cuda()) {

@@ -16,6 +16,8 @@
 // the local replica's ring (the per-step insert broadcast of the shared memory).  No NCCL call,
 // no host synchronisation; a peer that never arrives is reported through the error flag after a
 // bounded wait instead of hanging the GPU.
+#include <string.h>
+
 #include "common.cuh"
 
 namespace {
@@ -149,6 +151,59 @@ __global__ void __launch_bounds__(256) peer_allgather_kernel(const __grid_consta
   }
 }
 
+// ---- publish + exchange in one kernel (small blocks) -----------------------------------------
+// The per-agent call of the replicated update (population.ReplicatedReplay.update_priorities) publishes 3 KB: the
+// 256 sampled indices (device) and the 256 new priorities, which the learner hands over as a HOST ndarray
+// (dqn_rainbow.py:487-488).  Here the block is written by the exchange kernel itself: segment q from pub_src[q]
+// (device memory) or — one segment — from an fp32 vector that travels inside the launch.  grid = (1, world): every
+// CTA writes the whole (small) block — the same bytes, so the copies of different CTAs do not conflict — then CTA r
+// signals peer r; no copy call precedes the kernel.
+struct PeerPubParams {
+  PeerParams p;
+  const char *pub_src[XP_MAX_PEER_SEGS];
+  int host_seg;  // the segment filled from hv, or -1
+  float hv[XP_HOST_VEC_MAX];
+};
+
+__global__ void __launch_bounds__(256) peer_publish_allgather_kernel(const __grid_constant__ PeerPubParams pp) {
+  xp::pdl_enter();  // pub_src may have been written by earlier kernels of this stream
+  const PeerParams &p = pp.p;
+  const int r = blockIdx.y;
+  __shared__ int s_ok;
+  __shared__ unsigned s_epoch;
+  if (threadIdx.x == 0) s_epoch = *reinterpret_cast<volatile unsigned *>(p.epoch_dev) + 1u;
+  __syncthreads();
+  const int k = (int)((s_epoch - 1u) & 1u);
+  // every peer has finished reading block k of exchange e - 2: it signalled e - 1 after that (stream order on its side)
+  char *mine = const_cast<char *>(p.base[k][p.rank]);
+  for (int q = 0; q < p.n_segs; ++q) {
+    const xp_peer_seg &sg = p.seg[q];
+    if (q == pp.host_seg) {
+      float *dst = reinterpret_cast<float *>(mine + sg.src_off);
+      for (int i = threadIdx.x; i < (int)(sg.bytes >> 2); i += blockDim.x) dst[i] = pp.hv[i];
+    } else if (pp.pub_src[q]) {
+      pull(pp.pub_src[q], mine + sg.src_off, sg.bytes, 0, 1);
+    }
+  }
+  __syncthreads();  // the CTA's copy of the block is complete before thread 0 fences and signals
+  if (threadIdx.x == 0) s_ok = peer_sync(p, r, true, s_epoch) ? 1 : 0;
+  __syncthreads();
+  if (s_ok) {
+    for (int q = 0; q < p.n_segs; ++q) {
+      const xp_peer_seg &sg = p.seg[q];
+      pull(p.base[k][r] + sg.src_off, static_cast<char *>(sg.dst) + (long long)r * sg.bytes, sg.bytes, 0, 1);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {  // the last CTA of the launch publishes the new epoch for the next launch to read
+    __threadfence();
+    if (atomicAdd(p.epoch_dev + 1, 1u) == gridDim.y - 1u) {
+      p.epoch_dev[1] = 0u;
+      *reinterpret_cast<volatile unsigned *>(p.epoch_dev) = s_epoch;
+    }
+  }
+}
+
 // ---- exchange + ring insert in one kernel --------------------------------------------------
 // Every rank's n_rows new rows per key sit in its peer-mapped block; rank-major row q = r*n_rows+i
 // lands in local ring slot (cursor + q) % ring_rows — ReplayBuffer.add of the concatenated batch
@@ -194,24 +249,23 @@ void xp_peer_set_timeout_cycles(int64_t cycles) {
   if (cycles > 0) g_peer_timeout_cycles = cycles;
 }
 
-static xp_status_t peer_allgather_common(const void *const *base0, const void *const *base1,
-                                         void *const *peer_flags, int rank, int world, uint32_t epoch,
-                                         uint32_t *epoch_state_dev, const xp_peer_seg *segs, int n_segs,
-                                         int *err_flag_dev, void *stream, const char *what) {
+static xp_status_t peer_fill_params(PeerParams &p, long long &bytes, const void *const *base0,
+                                    const void *const *base1, void *const *peer_flags, int rank, int world,
+                                    uint32_t epoch, uint32_t *epoch_state_dev, const xp_peer_seg *segs, int n_segs,
+                                    int *err_flag_dev, const char *what) {
   XP_REQUIRE(world >= 1 && world <= XP_MAX_PEERS, XP_ERR_INVALID, "%s: world %d not in [1,%d]", what, world,
              XP_MAX_PEERS);
   XP_REQUIRE(rank >= 0 && rank < world, XP_ERR_INVALID, "%s: bad rank", what);
   XP_REQUIRE(n_segs >= 1 && n_segs <= XP_MAX_PEER_SEGS, XP_ERR_INVALID, "%s: n_segs %d not in [1,%d]", what,
              n_segs, XP_MAX_PEER_SEGS);
   XP_REQUIRE(base0 && base1 && peer_flags && segs, XP_ERR_INVALID, "%s: null pointer", what);
-  PeerParams p{};
   for (int r = 0; r < world; ++r) {
     XP_REQUIRE(base0[r] && base1[r] && peer_flags[r], XP_ERR_INVALID, "%s: null peer pointer", what);
     p.base[0][r] = static_cast<const char *>(base0[r]);
     p.base[1][r] = static_cast<const char *>(base1[r]);
     p.flags[r] = static_cast<unsigned *>(peer_flags[r]);
   }
-  long long bytes = 0;
+  bytes = 0;
   for (int k = 0; k < n_segs; ++k) {
     XP_REQUIRE(segs[k].bytes >= 0 && segs[k].src_off >= 0 && (segs[k].bytes == 0 || segs[k].dst), XP_ERR_INVALID,
                "%s: bad segment %d", what, k);
@@ -225,6 +279,18 @@ static xp_status_t peer_allgather_common(const void *const *base0, const void *c
   p.epoch_dev = epoch_state_dev;
   p.err = err_flag_dev;
   p.timeout_cycles = g_peer_timeout_cycles;
+  return XP_OK;
+}
+
+static xp_status_t peer_allgather_common(const void *const *base0, const void *const *base1,
+                                         void *const *peer_flags, int rank, int world, uint32_t epoch,
+                                         uint32_t *epoch_state_dev, const xp_peer_seg *segs, int n_segs,
+                                         int *err_flag_dev, void *stream, const char *what) {
+  PeerParams p{};
+  long long bytes = 0;
+  xp_status_t rc = peer_fill_params(p, bytes, base0, base1, peer_flags, rank, world, epoch, epoch_state_dev, segs,
+                                    n_segs, err_flag_dev, what);
+  if (rc != XP_OK) return rc;
   // one CTA per 32 KB of a peer's block, never more CTAs than stay resident together (the signalling
   // CTAs must not queue behind waiting ones)
   long long parts = (bytes + 32767) / 32768;
@@ -248,6 +314,33 @@ xp_status_t xp_peer_allgather_graph(const void *const *peer_base0, const void *c
   XP_REQUIRE(epoch_state_dev, XP_ERR_INVALID, "xp_peer_allgather_graph: null epoch state");
   return peer_allgather_common(peer_base0, peer_base1, peer_flags, rank, world, 0, epoch_state_dev, segs, n_segs,
                                err_flag_dev, stream, "xp_peer_allgather_graph");
+}
+
+xp_status_t xp_peer_publish_allgather_graph(const void *const *peer_base0, const void *const *peer_base1,
+                                            void *const *peer_flags, int rank, int world, uint32_t *epoch_state_dev,
+                                            const xp_peer_seg *segs, int n_segs, const void *const *pub_src_dev,
+                                            int pub_host_seg, const float *pub_host, int *err_flag_dev, void *stream) {
+  const char *what = "xp_peer_publish_allgather_graph";
+  XP_REQUIRE(epoch_state_dev, XP_ERR_INVALID, "%s: null epoch state", what);
+  PeerPubParams pp{};
+  long long bytes = 0;
+  xp_status_t rc = peer_fill_params(pp.p, bytes, peer_base0, peer_base1, peer_flags, rank, world, 0, epoch_state_dev,
+                                    segs, n_segs, err_flag_dev, what);
+  if (rc != XP_OK) return rc;
+  XP_REQUIRE(bytes <= 32768, XP_ERR_INVALID, "%s: block of %lld bytes (the fused publish serves blocks up to 32 KB; "
+             "larger ones: write the block, then xp_peer_allgather_graph)", what, bytes);
+  XP_REQUIRE(pub_host_seg >= -1 && pub_host_seg < n_segs, XP_ERR_INVALID, "%s: bad host segment", what);
+  pp.host_seg = pub_host_seg;
+  for (int q = 0; q < n_segs; ++q) pp.pub_src[q] = pub_src_dev ? static_cast<const char *>(pub_src_dev[q]) : nullptr;
+  if (pub_host_seg >= 0) {
+    XP_REQUIRE(pub_host && segs[pub_host_seg].bytes % 4 == 0 && segs[pub_host_seg].bytes <= 4ll * XP_HOST_VEC_MAX &&
+                   segs[pub_host_seg].src_off % 4 == 0,
+               XP_ERR_INVALID, "%s: the host segment holds at most %d fp32 values", what, XP_HOST_VEC_MAX);
+    memcpy(pp.hv, pub_host, (size_t)segs[pub_host_seg].bytes);
+    pp.pub_src[pub_host_seg] = nullptr;
+  }
+  xp::launch(peer_publish_allgather_kernel, dim3(1, (unsigned)world), dim3(256), 0, (cudaStream_t)stream, pp);
+  return xp::check_launch(what);
 }
 
 xp_status_t xp_peer_ring_insert(const void *const *peer_base, void *const *peer_flags, int rank, int world,

@@ -321,6 +321,16 @@ xp_status_t xp_peer_allgather_graph(const void *const *peer_base0, const void *c
                                     void *const *peer_flags, int rank, int world,
                                     uint32_t *epoch_state_dev, const xp_peer_seg *segs, int n_segs,
                                     int *err_flag_dev, void *stream);
+/* xp_peer_allgather_graph for a SMALL block (all segments together <= 32 KB) that the exchange kernel fills itself:
+ * segment q of this rank's block is copied from pub_src_dev[q] (device memory; NULL: the caller has written it) and
+ * segment pub_host_seg (or -1) from the fp32 HOST vector pub_host (<= XP_HOST_VEC_MAX values, read during the call,
+ * carried inside the launch) — what ReplicatedReplay.update_priorities publishes per agent: the sampled indices on
+ * the device, the learner's priorities as a host ndarray (dqn_rainbow.py:487-488).  No copy call precedes the kernel. */
+xp_status_t xp_peer_publish_allgather_graph(const void *const *peer_base0, const void *const *peer_base1,
+                                            void *const *peer_flags, int rank, int world,
+                                            uint32_t *epoch_state_dev, const xp_peer_seg *segs, int n_segs,
+                                            const void *const *pub_src_dev, int pub_host_seg,
+                                            const float *pub_host, int *err_flag_dev, void *stream);
 /* Bounded wait of the handshake, in SM clock cycles (default 6e10, ~30 s).                       */
 void xp_peer_set_timeout_cycles(int64_t cycles);
 

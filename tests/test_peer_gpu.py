@@ -84,27 +84,50 @@ def _worker_rr(rank, world, port, out_dir):
 
     mem = PrioritizedReplayBuffer(1024, alpha=0.6, device=dev)
     rep = ReplicatedReplay(mem)
+    # shadow: ONE plain buffer that receives every rank's rows and (index, priority) pairs in rank-major order
+    # through the ordinary single-process calls — what the replicas must equal (its row contents do not matter)
+    exp = PrioritizedReplayBuffer(1024, alpha=0.6, device=dev)
+
+    def everyone(t):
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return torch.cat(out)
+
     g = torch.Generator().manual_seed(7 + rank)
     for _ in range(3):
         rep.add(TensorBatch({"obs": torch.randn(8, 3, generator=g), "reward": torch.randn(8, generator=g)}, batch_size=[8]))
+        exp.add(TensorBatch({"obs": torch.zeros(8 * world, 3), "reward": torch.zeros(8 * world)}, batch_size=[8 * world]))
     for step in range(5):
         idx = torch.randint(0, 24 * world, (16,), generator=g)
-        rep.update_priorities(idx, torch.rand(16, generator=g) + 0.05)
+        pr = torch.rand(16, generator=g) + 0.05
+        rep.update_priorities(idx, pr)
+        exp.update_priorities(everyone(idx.to(dev)), everyone(pr.to(dev)).cpu().numpy())
     # the learn-step pattern: device indices straight from sample(), priorities as an fp32 host array
-    # (dqn_rainbow.py:487) -> the one-call native path (FastPer.update_replicated)
+    # (dqn_rainbow.py:487) -> the one-call native path (FastPer.update_replicated; with B <= 1024 the exchange kernel
+    # writes this rank's block itself, xp_peer_publish_allgather_graph)
     native = []
     for step in range(6):
         batch = rep.sample(16, 0.4)
         pr = (torch.rand(16, generator=g) + 0.05).numpy()
+        keep = pr.copy()
         native.append(rep._native_update(batch["idxs"], pr) if step % 2 else None)
         if not step % 2:
             rep.update_priorities(batch["idxs"], pr)
+        pr[:] = -7.0  # the host array is the caller's again once the call has returned
+        exp.update_priorities(everyone(batch["idxs"].reshape(-1)), everyone(torch.from_numpy(keep).to(dev)).cpu().numpy())
+    # a batch above XP_HOST_VEC_MAX: the native path stages it through the pinned ring and copy calls
+    big_idx = torch.randint(0, 24 * world, (1500,), generator=g).to(dev)
+    big_pr = (torch.rand(1500, generator=g) + 0.05).numpy()
+    native.append(rep._native_update(big_idx, big_pr))
+    exp.update_priorities(everyone(big_idx), everyone(torch.from_numpy(big_pr).to(dev)).cpu().numpy())
     mem.check_errors()
     rep._px.check()
     from agilerl_b200 import _hostaccel
 
+    same = torch.equal(mem._trees[2].nodes, exp._trees[2].nodes) and mem.max_priority == exp.max_priority
     torch.save({"peer": rep._peer_ok, "tree": mem._trees[2].nodes.cpu(), "obs": mem._leaves[("obs",)][:24 * world].cpu(),
-                "native": [x for x in native if x is not None], "accel": _hostaccel.load() is not None},
+                "native": [x for x in native if x is not None], "accel": _hostaccel.load() is not None,
+                "equals_one_buffer": bool(same)},
                os.path.join(out_dir, f"q{rank}.pt"))
     dist.destroy_process_group()
 
@@ -115,6 +138,7 @@ def test_replicated_replay_uses_peer_exchange(tmp_path, world):
     q = [torch.load(tmp_path / f"q{r}.pt", weights_only=False) for r in range(world)]
     assert all(x["peer"] is True for x in q)
     assert all(all(x["native"]) for x in q if x["accel"]), "the one-call native replicated update was not taken"
+    assert all(x["equals_one_buffer"] for x in q), "replicas differ from ONE buffer fed in rank-major order"
     for x in q[1:]:
         assert torch.equal(q[0]["tree"], x["tree"]) and torch.equal(q[0]["obs"], x["obs"])
 

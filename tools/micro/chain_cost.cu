@@ -5,7 +5,7 @@
 #include <cuda_runtime.h>
 constexpr int R = 32;
 struct Box { float r[R][32]; float v[R][32]; uint8_t d[R][32]; double a[R][32]; };
-template <int V>
+template <int V, int LANES>
 __global__ void __launch_bounds__(256) walk(float *out, int iters, long long *cyc, double gl, float gamma32) {
   extern __shared__ __align__(16) unsigned char raw[];
   Box &s = reinterpret_cast<Box *>(raw)[threadIdx.x >> 5];
@@ -15,6 +15,7 @@ __global__ void __launch_bounds__(256) walk(float *out, int iters, long long *cy
   const double k1 = __dmul_rn(gl, 1.0), k0 = __dmul_rn(gl, 0.0);
   double carry = 0.0; float v_next = 0.f; unsigned d_next = 0;
   long long t0 = clock64();
+  if (lane < LANES)
   for (int it = 0; it < iters; ++it) {
     for (int row = R - 1; row >= 7; row -= 8) {
       float r8[8], v8[8], a8[8], g8[8]; unsigned d8[8]; double x8[8];
@@ -61,23 +62,21 @@ int main() {
   cudaMalloc(&out, 1 << 20); cudaMalloc(&cyc, 8);
   const int iters = 256;
   const char *names[] = {"full step (tma kernel)", "chain only (A ready)", "chain only, no f64->f32", "chain only, no stores", "prepare only", "full step, no f64->f32"};
+  int lanes = 32;
   auto run = [&](int v, int ctas, int warps) {
     size_t sm = sizeof(Box) * warps;
-#define GO(V) { cudaFuncSetAttribute((const void *)walk<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); walk<V><<<ctas, warps * 32, sm>>>(out, iters, cyc, 0.9405, 0.99f); }
+#define GO(V) { if (lanes == 32) { cudaFuncSetAttribute((const void *)walk<V, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); walk<V, 32><<<ctas, warps * 32, sm>>>(out, iters, cyc, 0.9405, 0.99f); } else if (lanes == 16) { cudaFuncSetAttribute((const void *)walk<V, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); walk<V, 16><<<ctas, warps * 32, sm>>>(out, iters, cyc, 0.9405, 0.99f); } else { cudaFuncSetAttribute((const void *)walk<V, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); walk<V, 8><<<ctas, warps * 32, sm>>>(out, iters, cyc, 0.9405, 0.99f); } }
     if (v == 0) GO(0) if (v == 1) GO(1) if (v == 2) GO(2) if (v == 3) GO(3) if (v == 4) GO(4) if (v == 5) GO(5)
   };
-  for (int warps : {1, 2, 3, 4, 8}) {
-    for (int v = 0; v < 6; ++v) {
-      for (int rep = 0; rep < 2; ++rep) { run(v, 1, warps); cudaDeviceSynchronize(); }
-      cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
-      printf("1 CTA of %d warps  %-28s %.1f cycles/row (warp 0)\n", warps, names[v], (double)h / iters / 32);
-    }
-  }
-  for (int ctas : {2, 3, 4}) {   // single-warp CTAs sharing one SM?  (148 * ctas CTAs, one wave)
-    for (int v : {0, 4, 1}) {
-      for (int rep = 0; rep < 2; ++rep) { run(v, 148 * ctas, 1); cudaDeviceSynchronize(); }
-      cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
-      printf("%d one-warp CTAs per SM  %-28s %.1f cycles/row (CTA 0)\n", ctas, names[v], (double)h / iters / 32);
+  for (int l : {32, 16, 8}) {
+    lanes = l;
+    for (int warps : {1, 4, 8, 12, 16}) {
+      for (int v : {0, 4, 1}) {
+        if (sizeof(Box) * warps > 220 * 1024) continue;
+        for (int rep = 0; rep < 2; ++rep) { run(v, 1, warps); cudaDeviceSynchronize(); }
+        cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
+        printf("active lanes %2d  1 CTA of %2d warps  %-28s %.1f cycles/row (warp 0)\n", l, warps, names[v], (double)h / iters / 32);
+      }
     }
   }
   return 0;
