@@ -32,7 +32,7 @@ namespace {
 
 constexpr int kModeGae = 0;
 constexpr int kModeMc = 1;
-constexpr int kDefaultGaePdl = 0;      // see launch_scan
+constexpr int kDefaultGaePdl = 4;      // see gae_pdl()
 
 struct ScanParams {
   const float *rewards;
@@ -192,8 +192,12 @@ __device__ __forceinline__ unsigned long long trace_gt() {
 
 template <int MODE>
 __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams p,
-                                                                const __grid_constant__ gaetma::Maps maps, const int pdl) {
+                                                                const __grid_constant__ gaetma::Maps maps, const int cfg) {
   using namespace gaetma;
+  const int pdl = cfg & 0xff;
+  // values sit a constant 16-byte-multiple behind rewards (returns behind advantages): maps.r / maps.adv are rank-4
+  // maps {env, t, agent, which} and ONE bulk tensor copy moves both boxes of a stage
+  const bool paired = (cfg >> 8) != 0;
   // programmatic launch: nothing above this line touches global memory, so stream order is kept exactly
   if (pdl) {
     if (pdl == 1) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -205,7 +209,7 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
   const int lane = threadIdx.x;  // env within the box
   if (elect_one()) {  // the TMA unit fetches a 128-byte descriptor before its first use of a map: start that now
     tma_prefetch_map(&maps.r);
-    tma_prefetch_map(&maps.v);
+    if (!paired) tma_prefetch_map(&maps.v);
     tma_prefetch_map(&maps.d);
   }
 #ifdef XP_GAE_TRACE
@@ -237,8 +241,12 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
       const int t0 = kBoxT * (nbox - 1 - b);  // coordinates stay non-negative; the newest box may
                                               // run past T (zero-filled on load, clipped on store)
       mbar_expect_tx(bar, kStageBytes);
-      tma_load_3d(&st.r[0][0], &maps.r, env0, t0, agent, bar);
-      tma_load_3d(&st.v[0][0], &maps.v, env0, t0, agent, bar);
+      if (paired) {
+        tma_load_4d(&st.r[0][0], &maps.r, env0, t0, agent, 0, bar);
+      } else {
+        tma_load_3d(&st.r[0][0], &maps.r, env0, t0, agent, bar);
+        tma_load_3d(&st.v[0][0], &maps.v, env0, t0, agent, bar);
+      }
       tma_load_3d(&st.d[0][0], &maps.d, env0, t0, agent, bar);
     }
   };
@@ -248,7 +256,7 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
   if (pdl == 2) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (elect_one()) {
     tma_prefetch_map(&maps.adv);
-    tma_prefetch_map(&maps.ret);
+    if (!paired) tma_prefetch_map(&maps.ret);
   }
 
   XP_TRC(3);
@@ -338,11 +346,18 @@ __global__ void __launch_bounds__(gaetma::kBoxE) gae_tma_kernel(const ScanParams
     fence_proxy_async();  // generic-proxy writes above -> visible to the TMA store
     __syncwarp();         // the warp is done with the box
     if (lane == 0) {      // (bulk groups are per thread: always the same lane)
-      tma_store_3d(&maps.adv, env0, t0, agent, &st.r[0][0]);
-      tma_store_3d(&maps.ret, env0, t0, agent, &st.v[0][0]);
+      if (paired) {
+        tma_store_4d(&maps.adv, env0, t0, agent, 0, &st.r[0][0]);
+      } else {
+        tma_store_3d(&maps.adv, env0, t0, agent, &st.r[0][0]);
+        tma_store_3d(&maps.ret, env0, t0, agent, &st.v[0][0]);
+      }
       tma_commit();
     }
     if (b < 2) XP_TRC(6 + 3 * b);
+    // the last box but one is out: from here on this CTA only walks what it already holds — let the next grid of the
+    // stream become resident and run its prologue (it blocks at griddepcontrol.wait until this grid has completed)
+    if ((pdl == 3 && b == nbox - 2) || (pdl == 4 && b == nbox - 1)) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   }
   // the CTA may retire once the stores have READ shared memory; their global writes complete on their own
   // (kernel completion orders them)
@@ -373,9 +388,11 @@ constexpr int kProducers = 3;
 }  // namespace gaespec
 
 template <int MODE>
-__global__ void __launch_bounds__(128) gae_spec_kernel(const ScanParams p, const __grid_constant__ gaetma::Maps maps) {
+__global__ void __launch_bounds__(128) gae_spec_kernel(const ScanParams p, const __grid_constant__ gaetma::Maps maps,
+                                                       const int pdl) {
   using namespace gaetma;
   using namespace gaespec;
+  if (pdl) asm volatile("griddepcontrol.wait;" ::: "memory");  // nothing above touches global memory
   extern __shared__ __align__(128) unsigned char smem_tma[];
   Stage *stage = reinterpret_cast<Stage *>(smem_tma);
   __shared__ __align__(8) unsigned long long bars[kStages];
@@ -653,6 +670,8 @@ __global__ void __launch_bounds__(128) gae_spec_kernel(const ScanParams p, const
     }
     __syncthreads();
   }
+  // every box is walked and on its way out: the next grid of the stream may become resident and run its prologue
+  if (pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (threadIdx.x == 0) tma_wait_read<0>();
   (void)stored;
 }
@@ -679,10 +698,11 @@ EncodeFn get_encode() {
 // time, so the last few descriptors are kept (keyed by address and shape).
 struct MapKey {
   const void *base;
-  long long n, t, p, astride;
+  long long n, t, p, astride, pair_bytes;
   int elem_bytes;
   bool operator==(const MapKey &o) const {
-    return base == o.base && n == o.n && t == o.t && p == o.p && astride == o.astride && elem_bytes == o.elem_bytes;
+    return base == o.base && n == o.n && t == o.t && p == o.p && astride == o.astride && elem_bytes == o.elem_bytes &&
+           pair_bytes == o.pair_bytes;
   }
 };
 constexpr int kMapCache = 64;
@@ -690,17 +710,19 @@ thread_local MapKey g_map_keys[kMapCache];
 thread_local CUtensorMap g_map_vals[kMapCache];
 thread_local int g_map_next = 0, g_map_count = 0;
 
-bool encode_map_uncached(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p);
+bool encode_map_uncached(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p, long long pair_bytes);
 
-bool encode_map(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p) {
+// pair_bytes != 0: a rank-4 map {env, t, agent, which} over TWO arrays of the same shape, the second `pair_bytes`
+// behind the first (a multiple of 16 below 2^40, the TMA stride rules)
+bool encode_map(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p, long long pair_bytes = 0) {
   const long long astride = p.P == 1 ? p.T * p.N : p.agent_stride;
-  const MapKey key{base, p.N, p.T, p.P, astride, elem_bytes};
+  const MapKey key{base, p.N, p.T, p.P, astride, pair_bytes, elem_bytes};
   for (int i = 0; i < g_map_count; ++i)
     if (g_map_keys[i] == key) {
       *m = g_map_vals[i];
       return true;
     }
-  if (!encode_map_uncached(m, base, elem_bytes, p)) return false;
+  if (!encode_map_uncached(m, base, elem_bytes, p, pair_bytes)) return false;
   g_map_keys[g_map_next] = key;
   g_map_vals[g_map_next] = *m;
   g_map_next = (g_map_next + 1) % kMapCache;
@@ -708,15 +730,17 @@ bool encode_map(CUtensorMap *m, const void *base, int elem_bytes, const ScanPara
   return true;
 }
 
-bool encode_map_uncached(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p) {
+bool encode_map_uncached(CUtensorMap *m, const void *base, int elem_bytes, const ScanParams &p, long long pair_bytes) {
   EncodeFn enc = get_encode();
   if (!enc) return false;
   const long long astride = p.P == 1 ? p.T * p.N : p.agent_stride;
-  const cuuint64_t dims[3] = {(cuuint64_t)p.N, (cuuint64_t)p.T, (cuuint64_t)p.P};
-  const cuuint64_t strides[2] = {(cuuint64_t)(p.N * elem_bytes), (cuuint64_t)(astride * elem_bytes)};
-  const cuuint32_t box[3] = {gaetma::kBoxE, gaetma::kBoxT, 1};
-  const cuuint32_t es[3] = {1, 1, 1};
-  const CUresult r = enc(m, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 3,
+  const cuuint64_t dims[4] = {(cuuint64_t)p.N, (cuuint64_t)p.T, (cuuint64_t)p.P, 2};
+  const cuuint64_t strides[3] = {(cuuint64_t)(p.N * elem_bytes), (cuuint64_t)(astride * elem_bytes),
+                                 (cuuint64_t)pair_bytes};
+  const cuuint32_t box[4] = {gaetma::kBoxE, gaetma::kBoxT, 1, 2};
+  const cuuint32_t es[4] = {1, 1, 1, 1};
+  const CUresult r = enc(m, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8,
+                         pair_bytes ? 4 : 3,
                          const_cast<void *>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -767,6 +791,19 @@ __global__ void __launch_bounds__(128) gae32_kernel(const float *rewards, const 
   }
 }
 
+// Programmatic dependent launch of the scan kernels.  Releasing the dependents EARLY (at entry: 1; after the first
+// loads: 2; after the last box but one: 3) puts the next grid's CTAs beside the running ones and costs more than
+// the boundary it hides (C3 10.4 / 10.4 / 9.65 us against 9.6 plain).  Releasing them after the LAST box has been
+// walked (4, the default) hides the next launch's latency and prologue under this grid's store drain and nothing
+// else: C3 9.61 -> 8.95 us, 12 agents 8.80 -> 8.17.  XP_GAE_PDL = 0..4 is the developer knob.
+static int gae_pdl() {
+  static const int pdl = [] {
+    const char *e = getenv("XP_GAE_PDL");
+    return (e && e[0]) ? atoi(e) : kDefaultGaePdl;
+  }();
+  return pdl;
+}
+
 template <int MODE>
 xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
   if (p.T == 0 || p.N == 0 || p.P == 0) return XP_OK;
@@ -806,15 +843,32 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
         }
         spec_attr[MODE].set();
       }
-      gae_spec_kernel<MODE><<<(unsigned)grid_tma, 128, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps);
+      if (gae_pdl() && xp::pdl_enabled())
+        xp::launch(gae_spec_kernel<MODE>, dim3((unsigned)grid_tma), dim3(128), sizeof(gaetma::Stage) * gaetma::kStages, s,
+                   p, maps, 1);
+      else
+        gae_spec_kernel<MODE><<<(unsigned)grid_tma, 128, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps, 0);
       return xp::check_launch("xp_gae (spec)");
     }
   }
   if (tma_ok && which != 2 && p.P <= 65535) {
-    gaetma::Maps maps;
-    if (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
-        encode_map(&maps.d, p.dones, 1, p) && encode_map(&maps.adv, p.adv, 4, p) &&
-        encode_map(&maps.ret, p.ret, 4, p)) {
+    gaetma::Maps maps{};
+    // values a constant distance behind rewards, returns behind advantages (any two device arrays qualify when the
+    // distance is a positive multiple of 16 below 2^40 — the TMA stride rules): rank-4 maps {env, t, agent, which}
+    // let ONE bulk tensor copy move both boxes of a stage — 2 UTMALDG + 1 UTMASTG per box instead of 3 + 2
+    const char *pair_knob = getenv("XP_GAE_PAIR");  // developer / test knob, read per call: 0 = always five rank-3 maps
+    const bool allow_pair = !(pair_knob && pair_knob[0] == '0');
+    const long long dv = reinterpret_cast<const char *>(p.values) - reinterpret_cast<const char *>(p.rewards);
+    const long long da = reinterpret_cast<const char *>(p.ret) - reinterpret_cast<const char *>(p.adv);
+    auto pairable = [](long long d) { return d > 0 && d % 16 == 0 && d < (1ll << 40); };
+    const bool paired = allow_pair && pairable(dv) && pairable(da);
+    const bool encoded =
+        paired ? (encode_map(&maps.r, p.rewards, 4, p, dv) && encode_map(&maps.d, p.dones, 1, p) &&
+                  encode_map(&maps.adv, p.adv, 4, p, da))
+               : (encode_map(&maps.r, p.rewards, 4, p) && encode_map(&maps.v, p.values, 4, p) &&
+                  encode_map(&maps.d, p.dones, 1, p) && encode_map(&maps.adv, p.adv, 4, p) &&
+                  encode_map(&maps.ret, p.ret, 4, p));
+    if (encoded) {
       static xp::DeviceOnce tma_attr[2];
       if (!tma_attr[MODE].done()) {
         cudaError_t e = cudaFuncSetAttribute((const void *)gae_tma_kernel<MODE>,
@@ -826,18 +880,14 @@ xp_status_t launch_scan(const ScanParams &p, cudaStream_t s) {
         }
         tma_attr[MODE].set();
       }
-      // (programmatic dependent launch was measured and dropped: early-resident CTAs of the next
-      // launch slowed the running one, 11.5 vs 11.0 us at C3)
       const dim3 grid2((unsigned)((p.N + gaetma::kBoxE - 1) / gaetma::kBoxE), (unsigned)p.P);
-      static const int pdl = [] {
-        const char *e = getenv("XP_GAE_PDL");  // developer knob: 0 plain | 1 release at entry | 2 release after the loads
-        return (e && e[0]) ? atoi(e) : kDefaultGaePdl;
-      }();
+      const int pdl = gae_pdl();
+      const int cfg = paired ? 0x100 : 0;
       if (pdl && xp::pdl_enabled()) {
         xp::launch(gae_tma_kernel<MODE>, grid2, dim3(gaetma::kBoxE),
-                   sizeof(gaetma::Stage) * gaetma::kStages, s, p, maps, pdl);
+                   sizeof(gaetma::Stage) * gaetma::kStages, s, p, maps, cfg | pdl);
       } else {
-        gae_tma_kernel<MODE><<<grid2, gaetma::kBoxE, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps, 0);
+        gae_tma_kernel<MODE><<<grid2, gaetma::kBoxE, sizeof(gaetma::Stage) * gaetma::kStages, s>>>(p, maps, cfg);
       }
       return xp::check_launch("xp_gae (tma)");
     }

@@ -48,7 +48,7 @@ constexpr int kStageBytes = kBoxT * kBoxE * (4 + 4 + 1);  // 9216
 
 struct __align__(128) Stage {
   float r[kBoxT][kBoxE];    // rewards   -> overwritten with advantages
-  float v[kBoxT][kBoxE];    // values    -> overwritten with returns
+  float v[kBoxT][kBoxE];    // values    -> overwritten with returns (directly behind r: one rank-4 box covers both)
   uint8_t d[kBoxT][kBoxE];  // dones
 };
 
@@ -97,6 +97,18 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, i
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
       ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
       : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *map, int c0, int c1, int c2, int c3,
+                                            unsigned long long *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap *map, int c0, int c1, int c2, int c3, const void *src) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%1, %2, %3, %4}], [%5];" ::"l"(map),
+               "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(smem_u32(src))
+               : "memory");
 }
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, int c0, int c1, int c2, const void *src) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(map),

@@ -77,6 +77,48 @@ def test_gae_population_vs_oracle(xp, cuda_device, shape, use_gae, kernel, monke
         assert np.array_equal(adv[p], a) and np.array_equal(ret[p], g)
 
 
+@pytest.mark.parametrize("shape", [(3, 128, 96), (2, 50, 64), (1, 300, 48), (16, 128, 1024)])
+@pytest.mark.parametrize("use_gae", [True, False])
+def test_gae_paired_tensor_maps(xp, cuda_device, shape, use_gae, monkeypatch):
+    """gae_tma_kernel moves rewards+values (and advantages+returns) of a stage with ONE rank-4 bulk tensor copy when
+    the second array lies a positive multiple of 16 bytes behind the first.  Inputs carved from one slab in both
+    orders (values behind rewards: paired; rewards behind values: five rank-3 maps), and the paired layout again
+    with XP_GAE_PAIR=0: all three bit-equal to the oracle (one agent) and to each other (all agents)."""
+    monkeypatch.setenv("XP_GAE_KERNEL", "tma")
+    P, T, N = shape
+    rng = np.random.default_rng(P * 7 + T)
+    r = rng.standard_normal((P, T, N)).astype(np.float32)
+    v = rng.standard_normal((P, T, N)).astype(np.float32)
+    d = rng.random((P, T, N)) < 0.05
+    lv = rng.standard_normal((P, N)).astype(np.float32)
+    ld = rng.random((P, N)) < 0.1
+    n = P * T * N
+    outs = []
+    for order, pair in (("rv", "1"), ("vr", "1"), ("rv", "0")):
+        monkeypatch.setenv("XP_GAE_PAIR", pair)
+        slab_in = torch.empty(2 * n + 8, dtype=torch.float32, device=cuda_device)
+        slab_out = torch.full((2 * n + 8,), float("nan"), dtype=torch.float32, device=cuda_device)
+        a, b = slab_in[:n].view(P, T, N), slab_in[n + 4: 2 * n + 4].view(P, T, N)   # 16 bytes of padding between
+        oa, ob = slab_out[:n].view(P, T, N), slab_out[n + 4: 2 * n + 4].view(P, T, N)
+        R, V = (a, b) if order == "rv" else (b, a)
+        A, G = (oa, ob) if order == "rv" else (ob, oa)
+        R.copy_(torch.from_numpy(r)), V.copy_(torch.from_numpy(v))
+        D = torch.from_numpy(d).to(cuda_device)
+        LV, LD = dev(lv, cuda_device, torch.float64), dev(ld, cuda_device, torch.float64)
+        xp.gae(R, V, D, LV, LD, A, G, T, N, P, T * N, 0.99, 0.95, use_gae)
+        torch.cuda.synchronize()
+        outs.append((A.cpu().numpy().copy(), G.cpu().numpy().copy()))
+        assert torch.isnan(slab_out[n: n + 4]).all() and torch.isnan(slab_out[2 * n + 4:]).all()  # nothing spilled
+    for a_, g_ in outs[1:]:
+        assert np.array_equal(a_, outs[0][0]) and np.array_equal(g_, outs[0][1])
+    p_ = P - 1
+    if use_gae:
+        ea, eg = xo.gae(r[p_], v[p_], d[p_], lv[p_], ld[p_], 0.99, 0.95)
+    else:
+        ea, eg = xo.mc_returns(r[p_], v[p_], d[p_], lv[p_], ld[p_], 0.99)
+    assert np.array_equal(outs[0][0][p_], ea) and np.array_equal(outs[0][1][p_], eg)
+
+
 def test_gae_empty_is_noop(xp, cuda_device):
     z = torch.empty(0, device=cuda_device)
     zd = torch.empty(0, device=cuda_device, dtype=torch.float64)

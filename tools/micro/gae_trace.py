@@ -14,11 +14,16 @@ dev = torch.device("cuda", 0)
 g = torch.Generator(device=dev).manual_seed(4)
 T, N, PP = 128, 1024, int(sys.argv[1]) if len(sys.argv) > 1 else 16
 sets = []
+SLAB = os.environ.get("XP_TRACE_SLAB", "0") == "1"   # values right behind rewards, returns behind advantages
 for _ in range(8):
-    r = torch.randn(PP, T, N, device=dev, generator=g); v = torch.randn(PP, T, N, device=dev, generator=g)
+    if SLAB:
+        rv = torch.randn(2, PP, T, N, device=dev, generator=g); r, v = rv[0], rv[1]
+    else:
+        r = torch.randn(PP, T, N, device=dev, generator=g); v = torch.randn(PP, T, N, device=dev, generator=g)
     d = torch.rand(PP, T, N, device=dev, generator=g) < 0.02
     lv = torch.randn(PP, N, device=dev, generator=g).double(); ld = torch.zeros(PP, N, device=dev, dtype=torch.float64)
-    sets.append((r, v, d, lv, ld, torch.empty_like(r), torch.empty_like(r)))
+    ag = torch.empty(2, PP, T, N, device=dev)
+    sets.append((r, v, d, lv, ld, ag[0], ag[1]) if SLAB else (r, v, d, lv, ld, torch.empty_like(r), torch.empty_like(r)))
 st = torch.cuda.current_stream().cuda_stream
 def run(s):
     r, v, d, lv, ld, a, gg = s
@@ -45,7 +50,7 @@ best = 1e9
 for rep in range(7):
     ev[0].record(); gr.replay(); ev[1].record(); torch.cuda.synchronize()
     best = min(best, ev[0].elapsed_time(ev[1]) * 25)
-print(f"{libname} XP_GAE_KERNEL={os.environ.get('XP_GAE_KERNEL', '')} P={PP}: us per launch (graph of 40, 8 rotating sets): best of 7 {best:.2f}")
+print(f"{libname} XP_GAE_KERNEL={os.environ.get('XP_GAE_KERNEL', '')} slab={int(SLAB)} pair={os.environ.get('XP_GAE_PAIR', '')} P={PP}: us per launch (graph of 40, 8 rotating sets): best of 7 {best:.2f}")
 if not TRACE: sys.exit(0)
 nct = PP * (N // 32)
 for trial in range(1):
