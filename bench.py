@@ -1111,6 +1111,7 @@ def b200_arm(args):
 
     # -- e2e through the public per-agent API ---------------------------------------------------
     e2e = None
+    clocks.period = 0.025  # the e2e loop is host-bound Python: the sampling thread competes for the GIL, so poll 12x less often
     if not args.no_e2e:
         wl.e2e_setup()
         Ke = max(100, min(K, 200))  # its own step count (reported as e2e.steps): a 20-step K would time 7 ms of a host-bound loop
