@@ -298,6 +298,8 @@ __device__ __forceinline__ void descend_team3(const double *sum, unsigned &idx, 
       asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
                    : "=d"(c0[s]), "=d"(m0), "=d"(c1[s]), "=d"(m1)
                    : "l"(sum + ((((unsigned long long)ids[s]) << 3) + 2 * q) * 2));
+      (void)m0;  // the interleaved min-tree halves of the 32-byte line: loaded with it, not used by the descent
+      (void)m1;
     }
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
